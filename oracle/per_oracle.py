@@ -1,0 +1,244 @@
+"""ctypes face of oracle/per_oracle.c -- TEST INFRASTRUCTURE ONLY.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl
+reference legs may import this module.  The product package (reth_b200/) must
+never import it.  Parity status: pinned against the reference's own njit code
+through tests/golden/ (see per_oracle.c header).
+
+Class names mirror the reference objects they restate:
+  OracleSumTree   <- reth_buffer/reth_buffer/utils/sumtree.py:82-113 (NumbaSumTree)
+  OraclePERSampler<- reth_buffer/reth_buffer/sampler/per_sampler.py:5-35
+  OracleRing      <- reth/reth/buffer/buffer.py:4-93 + cache_policy/fifo_policy.py:6-18
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "libper_oracle.so")
+
+
+def build(force=False):
+    """Compile per_oracle.c with gcc (also called by __graft_entry__.build())."""
+    src = os.path.join(_HERE, "per_oracle.c")
+    if force or not os.path.exists(_LIB_PATH) or os.path.getmtime(_LIB_PATH) < os.path.getmtime(src):
+        subprocess.check_call(
+            ["gcc", "-O2", "-fPIC", "-shared", "-ffp-contract=off", "-fno-fast-math",
+             "-fvisibility=hidden", "-o", _LIB_PATH, src, "-lm"])
+    return _LIB_PATH
+
+
+_lib = None
+_i64p = C.POINTER(C.c_int64)
+_f64p = C.POINTER(C.c_double)
+_f32p = C.POINTER(C.c_float)
+_u8p = C.POINTER(C.c_uint8)
+
+
+def lib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    build()
+    L = C.CDLL(_LIB_PATH)
+    vp = C.c_void_p
+    sig = {
+        "po_tree_create": (vp, [C.c_int64]),
+        "po_tree_destroy": (None, [vp]),
+        "po_tree_clear": (None, [vp]),
+        "po_tree_sum_ptr": (_f64p, [vp]),
+        "po_tree_min_ptr": (_f64p, [vp]),
+        "po_tree_val_ptr": (_f64p, [vp]),
+        "po_find_index": (C.c_int64, [vp, C.c_double]),
+        "po_tree_update": (None, [vp, vp, vp, C.c_int64]),
+        "po_tree_sample": (None, [vp, C.c_int64, vp, vp, vp]),
+        "po_tree_total": (C.c_double, [vp]),
+        "po_tree_minimum": (C.c_double, [vp, C.c_int]),
+        "po_normalize_f32": (None, [vp, C.c_int64, C.c_double, vp]),
+        "po_normalize_f64": (None, [vp, C.c_int64, C.c_double, vp]),
+        "po_is_weights": (None, [vp, C.c_int64, C.c_double, C.c_double, vp]),
+        "po_ring_create": (vp, [C.c_int64, C.c_int32, vp]),
+        "po_ring_destroy": (None, [vp]),
+        "po_ring_col_ptr": (_u8p, [vp, C.c_int]),
+        "po_ring_tail": (C.c_int64, [vp]),
+        "po_ring_size": (C.c_int64, [vp]),
+        "po_ring_reset": (None, [vp]),
+        "po_fifo_indices": (None, [C.c_int64, vp, C.c_int64, vp]),
+        "po_ring_append": (None, [vp, vp, C.c_int64, vp]),
+        "po_ring_select": (None, [vp, vp, C.c_int64, C.c_int64, vp]),
+        "po_step_loop": (C.c_double, [vp, vp, C.c_int64, C.c_int64, C.c_int64, vp, vp,
+                                      C.c_double, C.c_double, C.c_int, vp, vp, vp, vp, vp]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(L, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = L
+    return L
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class OracleSumTree:
+    """utils/sumtree.py:82-113; arrays are exposed as numpy views (_sum/_min/_val)."""
+
+    def __init__(self, capacity):
+        self.capacity = int(capacity)
+        self._h = lib().po_tree_create(self.capacity)
+        L = lib()
+        n = self.capacity
+        self._sum = np.ctypeslib.as_array(L.po_tree_sum_ptr(self._h), shape=(n,))
+        self._min = np.ctypeslib.as_array(L.po_tree_min_ptr(self._h), shape=(n,))
+        self._val = np.ctypeslib.as_array(L.po_tree_val_ptr(self._h), shape=(n,))
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().po_tree_destroy(self._h)
+            self._h = None
+
+    def clear(self):
+        lib().po_tree_clear(self._h)
+
+    def update(self, indices, weights):
+        idx = np.ascontiguousarray(np.atleast_1d(indices), dtype=np.int64)
+        w = np.ascontiguousarray(np.atleast_1d(weights), dtype=np.float64)
+        assert len(idx) == len(w)
+        lib().po_tree_update(self._h, _ptr(idx), _ptr(w), len(idx))
+
+    def sum(self):
+        return lib().po_tree_total(self._h)
+
+    def min(self, mode=0):
+        return lib().po_tree_minimum(self._h, mode)
+
+    def find_index(self, weight):
+        return lib().po_find_index(self._h, float(weight))
+
+    def sample(self, batch_size, u):
+        """_numba_sample (sumtree.py:70-79) with injected uniforms u[batch]."""
+        u = np.ascontiguousarray(u, dtype=np.float64)
+        assert len(u) == batch_size
+        idx = np.empty(batch_size, np.int64)
+        val = np.empty(batch_size, np.float64)
+        lib().po_tree_sample(self._h, batch_size, _ptr(u), _ptr(idx), _ptr(val))
+        return idx, val
+
+
+def normalize_weights(weights, alpha):
+    """per_sampler.py:16-17 in the dtype of the incoming array; returns float64."""
+    w = np.ascontiguousarray(np.atleast_1d(weights))
+    out = np.empty(len(w), np.float64)
+    if w.dtype == np.float32:
+        lib().po_normalize_f32(_ptr(w), len(w), float(alpha), _ptr(out))
+    else:
+        w = w.astype(np.float64)
+        lib().po_normalize_f64(_ptr(w), len(w), float(alpha), _ptr(out))
+    return out
+
+
+def is_weights(val, pmin, beta):
+    """per_sampler.py:26."""
+    val = np.ascontiguousarray(val, dtype=np.float64)
+    out = np.empty(len(val), np.float64)
+    lib().po_is_weights(_ptr(val), len(val), float(pmin), float(beta), _ptr(out))
+    return out
+
+
+class OraclePERSampler:
+    """per_sampler.py:5-35 with constant alpha/beta supplied per call (the
+    Schedule, utils/schedule.py, is host scalar logic shared with the product)."""
+
+    def __init__(self, capacity, min_mode=0):
+        self.sumtree = OracleSumTree(capacity)
+        self.min_mode = min_mode
+
+    def update(self, indices, weights, alpha, transform=True):
+        w = normalize_weights(weights, alpha) if transform else np.asarray(weights, np.float64)
+        self.sumtree.update(indices, w)
+
+    def sample(self, batch_size, u, beta):
+        idx, val = self.sumtree.sample(batch_size, u)
+        return idx, is_weights(val, self.sumtree.min(self.min_mode), beta), val
+
+
+class OracleRing:
+    """Columnar ring (buffer.py:57-93) with FIFO slots (fifo_policy.py:11-18)."""
+
+    def __init__(self, capacity, struct):
+        """struct: list of (dtype, per-row shape)."""
+        self.capacity = int(capacity)
+        self.struct = [(np.dtype(dt), tuple(sh)) for dt, sh in struct]
+        self.row_bytes = np.array(
+            [dt.itemsize * int(np.prod(sh, dtype=np.int64)) for dt, sh in self.struct], np.int64)
+        self._h = lib().po_ring_create(self.capacity, len(self.struct), _ptr(self.row_bytes))
+        if not self._h:
+            raise MemoryError("po_ring_create failed")
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().po_ring_destroy(self._h)
+            self._h = None
+
+    @property
+    def tail(self):
+        return lib().po_ring_tail(self._h)
+
+    @property
+    def size(self):
+        return lib().po_ring_size(self._h)
+
+    def column(self, c):
+        dt, sh = self.struct[c]
+        raw = np.ctypeslib.as_array(lib().po_ring_col_ptr(self._h, c),
+                                    shape=(self.capacity * int(self.row_bytes[c]),))
+        return raw.view(dt).reshape((self.capacity,) + sh)
+
+    def append_batch(self, cols):
+        n = len(cols[0])
+        assert n <= self.capacity
+        arrs = [np.ascontiguousarray(c, dtype=dt) for c, (dt, _) in zip(cols, self.struct)]
+        ptrs = (C.c_void_p * len(arrs))(*[a.ctypes.data for a in arrs])
+        idx = np.empty(n, np.int64)
+        lib().po_ring_append(self._h, ptrs, n, _ptr(idx))
+        return idx
+
+    def select(self, indices, slot_mask=-1):
+        idx = np.ascontiguousarray(indices, dtype=np.int64)
+        n = len(idx)
+        outs = [np.empty((n,) + sh, dt) for dt, sh in self.struct]
+        ptrs = (C.c_void_p * len(outs))(*[a.ctypes.data for a in outs])
+        lib().po_ring_select(self._h, _ptr(idx), n, slot_mask, ptrs)
+        return outs
+
+
+def fifo_indices(capacity, tail, n):
+    """fifo_policy.py:11-18 -> (indices, new_tail)."""
+    t = C.c_int64(tail)
+    out = np.empty(n, np.int64)
+    lib().po_fifo_indices(capacity, C.byref(t), n, _ptr(out))
+    return out, t.value
+
+
+def step_loop(tree, ring, slot_mask, steps, batch, u, new_prio, alpha, beta, min_mode=0):
+    """Timed CPU-baseline loop (po_step_loop). ring may be None (tree-only)."""
+    u = np.ascontiguousarray(u, np.float64)
+    new_prio = np.ascontiguousarray(new_prio, np.float32)
+    assert u.size >= steps * batch and new_prio.size >= steps * batch
+    idx = np.empty(batch, np.int64)
+    val = np.empty(batch, np.float64)
+    w = np.empty(batch, np.float64)
+    p = np.empty(batch, np.float64)
+    if ring is not None:
+        outs = [np.empty((batch,) + sh, dt) for dt, sh in ring.struct]
+        ptrs = (C.c_void_p * len(outs))(*[a.ctypes.data for a in outs])
+        rh = ring._h
+    else:
+        outs, ptrs, rh = [], None, None
+    acc = lib().po_step_loop(tree._h, rh, slot_mask, steps, batch, _ptr(u), _ptr(new_prio),
+                             float(alpha), float(beta), min_mode, _ptr(idx), _ptr(val), _ptr(w),
+                             _ptr(p), ptrs)
+    return acc, idx, w, outs
