@@ -1,0 +1,187 @@
+/*
+ * reth_replay.h -- C ABI of the B200-native prioritized-experience-replay shard.
+ *
+ * One handle = one replay shard on one GPU: an HBM-resident columnar ring of
+ * transitions, a warp-tiled float64 sum/min tree over the ring slots, and a
+ * ring of contiguous learner-batch buffers.  Every call is stream-ordered on
+ * the caller's cudaStream_t (passed as void*; NULL = the legacy default
+ * stream); a handle is NOT re-entrant (SURVEY.md 8b "Threading").
+ *
+ * Each entry point names the reference (sosp2021/Reth) interface it replaces;
+ * paths are relative to the reference checkout.  Semantics that callers of the
+ * reference rely on are kept: slot == tree node index == arrival order modulo
+ * capacity (cache_policy/fifo_policy.py:11-18), sequential last-writer-wins
+ * updates (utils/sumtree.py:61-67), stratified proportional sampling over the
+ * in-order traversal of the implicit heap (utils/sumtree.py:34-58,70-79),
+ * importance weights (val/min)^-beta (sampler/per_sampler.py:24-28).
+ *
+ * Return value: 0 on success, a negative reth_status on error; the message is
+ * available from reth_replay_last_error().  Nothing throws across this ABI.
+ */
+#ifndef RETH_REPLAY_H_
+#define RETH_REPLAY_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RETH_MAX_COLUMNS 16
+
+typedef struct reth_replay reth_replay_t;
+
+typedef enum reth_status {
+    RETH_OK = 0,
+    RETH_ERR_INVALID = -1,  /* bad argument (the reference asserts: client/client.py:22-25,38) */
+    RETH_ERR_CUDA = -2,     /* CUDA runtime error, see last_error */
+    RETH_ERR_OOM = -3,
+    RETH_ERR_RANGE = -4,    /* an index outside [0, capacity) reached a kernel */
+    RETH_ERR_STATE = -5     /* call not valid in this state (e.g. sample on empty tree) */
+} reth_status;
+
+/* where a pointer argument lives */
+typedef enum reth_loc { RETH_HOST = 0, RETH_DEVICE = 1 } reth_loc;
+/* element type of a priority / index array */
+typedef enum reth_dtype { RETH_F32 = 0, RETH_F64 = 1, RETH_I32 = 2, RETH_I64 = 3 } reth_dtype;
+
+/* tree min() flavour: utils/sumtree.py:109-110 (service) vs
+ * reth/reth/buffer/sumtree.py:112-113 (in-process twin) */
+typedef enum reth_min_mode { RETH_MIN_SERVICE = 0, RETH_MIN_INPROCESS = 1 } reth_min_mode;
+
+typedef struct reth_replay_config {
+    int64_t capacity;                       /* ring slots == tree nodes (start_per(capacity,..), __init__.py:30) */
+    int32_t n_columns;                      /* row struct discovered from the first row in the reference
+                                               (client/torch_cuda_loader.py:106-112); explicit here */
+    int64_t row_bytes[RETH_MAX_COLUMNS];    /* bytes of one row of each column */
+    int32_t max_batch;                      /* largest sample()/update() batch (batch_size of start_per) */
+    int32_t ring_depth;                     /* learner-batch slots (TorchCudaLoader buffer_size, :70) */
+    int32_t device;                         /* CUDA device ordinal */
+    int32_t min_mode;                       /* reth_min_mode */
+    int32_t update_cluster;                 /* CTAs per cluster of the tree-repair kernel (0 = default 8) */
+    int32_t gather_mode;                    /* 0 = auto, 1 = LDG/STG.128, 2 = TMA bulk (cp.async.bulk) */
+    int32_t store_rows;                     /* 0 = tree only (no frame ring; config 5 "tree-only") */
+    int32_t reserved[5];
+} reth_replay_config;
+
+/* counters for the throughput report (SURVEY.md 5 "Metrics") */
+typedef struct reth_replay_stats {
+    int64_t appended_rows, sampled_rows, updated_rows, gathered_rows;
+    int64_t kernel_launches;                /* launches of this library's own kernels */
+    int64_t tail;                           /* next FIFO slot */
+    int64_t size;                           /* min(appended, capacity) */
+    int64_t hbm_bytes;                      /* device memory held by the shard */
+} reth_replay_stats;
+
+/* ---- lifetime: replaces main_loop bring-up of storage + sampler state
+ *      (server/main_loop.py:110-216; LMDB init :48-53; PERSampler.__init__ per_sampler.py:6-14) */
+int reth_replay_create(const reth_replay_config *cfg, reth_replay_t **out);
+int reth_replay_destroy(reth_replay_t *h);
+const char *reth_replay_last_error(const reth_replay_t *h);   /* h may be NULL: create() errors */
+int reth_replay_abi_version(void);
+
+/* PERSampler.clear / NumbaSumTree.clear (per_sampler.py:19-22, utils/sumtree.py:98-101)
+ * + FIFO cursor reset (NumpyBuffer.clear, reth/reth/buffer/buffer.py:95-97) */
+int reth_replay_clear(reth_replay_t *h, void *stream);
+
+/* ---- append: replaces Client.append -> append_loop -> FIFOPolicy.get_indices ->
+ *      LMDB put -> PERSampler.update (client/client.py:21-35, server/main_loop.py:44-58,
+ *      cache_policy/fifo_policy.py:11-18, sampler/per_sampler.py:34-35) and the in-process
+ *      NumpyBuffer.append_batch + sumtree.update (reth/reth/buffer/prioritized_buffer.py:35-42).
+ *  cols[c]: n rows of row_bytes[c], C-contiguous, all on `cols_loc`.
+ *  prio: n priorities (|TD|) of prio_dtype (F32/F64) on prio_loc, or NULL = raw 1.0
+ *        (prioritized_buffer.py:36-37).
+ *  transform != 0: leaf = (w + 1e-6)^alpha in the dtype of prio (per_sampler.py:16-17);
+ *  transform == 0: leaf = w as given (prioritized_buffer.py:29-33).
+ *  Slots are tail, tail+1, ... mod capacity; first_slot_out (host, may be NULL) gets `tail`. */
+int reth_replay_append(reth_replay_t *h, const void *const *cols, int cols_loc,
+                       const void *prio, int prio_dtype, int prio_loc, int64_t n,
+                       double alpha, int transform, int64_t *first_slot_out, void *stream);
+
+/* Plugin cache policies (cache_policy/base_policy.py:4-7): rows go to caller-chosen slots.
+ * slots: int64[n] on slots_loc; duplicates resolve to the last row in batch order. */
+int reth_replay_append_at(reth_replay_t *h, const int64_t *slots, int slots_loc,
+                          const void *const *cols, int cols_loc,
+                          const void *prio, int prio_dtype, int prio_loc, int64_t n,
+                          double alpha, int transform, void *stream);
+
+/* ---- update_priorities: replaces Client.update_priorities -> PERSampler.update ->
+ *      _numba_update/_numba_maintain (client/client.py:37-39, per_sampler.py:34-35,
+ *      utils/sumtree.py:61-67,24-31,5-21).  idx_dtype I32 or I64.  Sequential semantics:
+ *      duplicate indices are last-writer-wins in batch order. */
+int reth_replay_update(reth_replay_t *h, const void *idx, int idx_dtype, int idx_loc,
+                       const void *prio, int prio_dtype, int prio_loc, int64_t n,
+                       double alpha, int transform, void *stream);
+
+/* Same, for the indices the shard itself drew into batch slot `slot` (no index copy). */
+int reth_replay_update_slot(reth_replay_t *h, int slot, const void *prio, int prio_dtype,
+                            int prio_loc, double alpha, int transform, void *stream);
+
+/* ---- sample: replaces PERSampler.sample -> NumbaSumTree.sample -> _numba_sample /
+ *      _numba_find_index + IS weights (per_sampler.py:24-28, utils/sumtree.py:70-79,34-58,109-110).
+ *  uniforms: double[batch] in [0,1) on uniforms_loc (parity mode: the reference draws these
+ *  from numba's private generator), or NULL = counter-based device generator keyed by
+ *  (seed, internal draw counter).  Results land in batch slot `slot`:
+ *  indices int64[batch], weights float64[batch], priorities float64[batch]. */
+int reth_replay_sample(reth_replay_t *h, int batch, const double *uniforms, int uniforms_loc,
+                       uint64_t seed, double beta, int slot, void *stream);
+
+/* ---- gather: replaces the loader row loop (client/numpy_loader.py:35-50,
+ *      client/torch_cuda_loader.py:49-61) and NumpyBuffer.select (reth/reth/buffer/buffer.py:92-93):
+ *      rows ring[c][indices[i]] -> contiguous batch column c of slot `slot`. */
+int reth_replay_gather(reth_replay_t *h, int slot, void *stream);
+
+/* Device pointers of a batch slot (lent, as TorchCudaLoader lends ring slots,
+ * torch_cuda_loader.py:152-163).  Any out pointer may be NULL. */
+int reth_replay_slot_ptrs(reth_replay_t *h, int slot, void **cols_out /*[n_columns]*/,
+                          int64_t **indices_out, double **weights_out, double **prios_out,
+                          int32_t *batch_out);
+
+/* Copy a slot's indices / weights (and optionally batch columns) to host memory and
+ * synchronise the stream: what NumpyLoader.sample returns (numpy_loader.py:27-51).
+ * Any of indices/weights/cols may be NULL. */
+int reth_replay_slot_read(reth_replay_t *h, int slot, int64_t *indices, double *weights,
+                          void *const *cols, void *stream);
+
+/* ---- parity / debug: the three arrays of NumbaSumTree in heap order (utils/sumtree.py:85-88).
+ *      host double[capacity] each; any may be NULL.  Synchronises. */
+int reth_replay_tree_read(reth_replay_t *h, double *sum, double *min, double *val, void *stream);
+/* root: sum() and min() as the reference defines them (utils/sumtree.py:106-110) */
+int reth_replay_tree_root(reth_replay_t *h, double *total, double *minimum, void *stream);
+/* Read rows straight from the ring (host out), for storage parity tests. */
+int reth_replay_ring_read(reth_replay_t *h, int column, int64_t first_slot, int64_t n,
+                          void *out_host, void *stream);
+
+int reth_replay_stats_get(reth_replay_t *h, reth_replay_stats *out);
+
+/* ---- multi-shard (SURVEY.md 8e "Mode G"): stratified targets over the GLOBAL CDF of
+ *      n_shards shards; this shard serves the targets inside its range.
+ *  root_dev(): device pointer to this shard's {total, min} pair (double[2]), the 16 bytes
+ *  each rank contributes to the all-gather.
+ *  sample_global(): all_roots = device double[2*n_shards] (the all-gather result, rank
+ *  order).  Draws `global_batch` stratified targets; the ones that fall in this shard are
+ *  a contiguous range [first, first+count) of the global batch; they are written to the
+ *  front of slot `slot` and {first,count} to the slot's meta (slot_meta()).  IS weights
+ *  use the global minimum.  The reference has no counterpart (it polls shards
+ *  round-robin, test/apex-dqn/trainer.py:33-36). */
+int reth_replay_root_dev(reth_replay_t *h, double **root_dev_out);
+int reth_replay_sample_global(reth_replay_t *h, int global_batch, const double *all_roots_dev,
+                              int n_shards, int shard, const double *uniforms, int uniforms_loc,
+                              uint64_t seed, double beta, int slot, void *stream);
+/* host int64[2] = {first, count} of the last sample_global into `slot`; synchronises. */
+int reth_replay_slot_meta(reth_replay_t *h, int slot, int64_t *first_count, void *stream);
+
+/* ---- measured loop (bench / learner-less soak): `steps` iterations of
+ *      sample(batch) -> gather || update_slot(new priorities), the tree chain and the
+ *      frame gather on two internal streams joined to `stream` at both ends, slots used
+ *      round-robin.  prio_dev: device float32[steps*batch] new |TD| priorities;
+ *      uniforms_dev: device double[steps*batch] or NULL (device generator).
+ *      flags bit0: skip gather (tree only); bit1: serialise everything on one stream. */
+int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, const float *prio_dev,
+                          const double *uniforms_dev, uint64_t seed, double alpha, double beta,
+                          int flags, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RETH_REPLAY_H_ */

@@ -1,0 +1,769 @@
+// replay.cu -- C ABI (include/reth_replay.h) of the B200-native PER shard.
+// Host-side state + launches; kernels live in tree.cuh / copy.cuh.
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -fmad=false ...
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/reth_replay.h"
+#include "copy.cuh"
+#include "tree.cuh"
+
+using namespace reth;
+
+#define RETH_EXPORT extern "C" __attribute__((visibility("default")))
+
+namespace {
+
+thread_local std::string g_create_error;
+
+struct BatchSlot {
+    uint8_t *cols[kMaxCols] = {};
+    int64_t *idx = nullptr;
+    double *w = nullptr;
+    double *prio = nullptr;
+    int64_t *meta = nullptr;   // {first, count}
+    int32_t batch = 0;
+};
+
+}  // namespace
+
+struct reth_replay {
+    reth_replay_config cfg{};
+    TreeGeom geom{};
+    int n_sms = 148;
+    // tree
+    double2 *desc = nullptr, *agg = nullptr;
+    uint32_t *stamp = nullptr, *mask = nullptr;
+    int32_t *worklist = nullptr, *counts = nullptr /*[2][kMaxTileLevels]*/, *err = nullptr;
+    int64_t max_n = 0;            // largest n of one update launch
+    uint32_t stamp_base = 0;
+    int counts_flip = 0;
+    uint64_t draw_counter = 0;
+    // staging for host-resident arguments
+    void *stage_idx = nullptr, *stage_prio = nullptr;
+    double *stage_u = nullptr;
+    int64_t *host_pin = nullptr;  // small pinned scratch (err/meta readback)
+    // ring + batch slots
+    uint8_t *ring[kMaxCols] = {};
+    std::vector<BatchSlot> slots;
+    int64_t tail = 0, size = 0;
+    reth_replay_stats st{};
+    // step loop
+    cudaStream_t s_tree = nullptr, s_gather = nullptr;
+    std::vector<cudaEvent_t> ev_sampled, ev_gathered;
+    cudaEvent_t ev_fork = nullptr, ev_join_t = nullptr, ev_join_g = nullptr;
+    int update_cluster = 8;
+    std::string error;
+};
+
+namespace {
+
+int fail(reth_replay *h, int code, const char *fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (h) h->error = buf; else g_create_error = buf;
+    return code;
+}
+
+#define CK(h, expr)                                                                       \
+    do {                                                                                  \
+        cudaError_t e__ = (expr);                                                         \
+        if (e__ != cudaSuccess)                                                           \
+            return fail(h, e__ == cudaErrorMemoryAllocation ? RETH_ERR_OOM : RETH_ERR_CUDA, \
+                        "%s: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, __LINE__); \
+    } while (0)
+
+template <class T>
+cudaError_t dalloc_zero(T **p, size_t count, int64_t *acct)
+{
+    cudaError_t e = cudaMalloc((void **)p, count * sizeof(T));
+    if (e != cudaSuccess) return e;
+    *acct += (int64_t)(count * sizeof(T));
+    return cudaMemset(*p, 0, count * sizeof(T));
+}
+
+inline cudaStream_t S(void *s) { return (cudaStream_t)s; }
+
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+size_t dtype_size(int dt) { return (dt == RETH_F32 || dt == RETH_I32) ? 4 : 8; }
+
+void free_all(reth_replay *h)
+{
+    cudaFree(h->desc); cudaFree(h->agg); cudaFree(h->stamp); cudaFree(h->mask);
+    cudaFree(h->worklist); cudaFree(h->counts); cudaFree(h->err);
+    cudaFree(h->stage_idx); cudaFree(h->stage_prio); cudaFree(h->stage_u);
+    if (h->host_pin) cudaFreeHost(h->host_pin);
+    for (int c = 0; c < kMaxCols; ++c) cudaFree(h->ring[c]);
+    for (auto &s : h->slots) {
+        for (int c = 0; c < kMaxCols; ++c) cudaFree(s.cols[c]);
+        cudaFree(s.idx); cudaFree(s.w); cudaFree(s.prio); cudaFree(s.meta);
+    }
+    for (auto e : h->ev_sampled) cudaEventDestroy(e);
+    for (auto e : h->ev_gathered) cudaEventDestroy(e);
+    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+    if (h->ev_join_t) cudaEventDestroy(h->ev_join_t);
+    if (h->ev_join_g) cudaEventDestroy(h->ev_join_g);
+    if (h->s_tree) cudaStreamDestroy(h->s_tree);
+    if (h->s_gather) cudaStreamDestroy(h->s_gather);
+}
+
+}  // namespace
+
+RETH_EXPORT int reth_replay_abi_version(void) { return 1; }
+
+RETH_EXPORT const char *reth_replay_last_error(const reth_replay_t *h)
+{
+    return h ? h->error.c_str() : g_create_error.c_str();
+}
+
+RETH_EXPORT int reth_replay_create(const reth_replay_config *cfg, reth_replay_t **out)
+{
+    if (!cfg || !out) return fail(nullptr, RETH_ERR_INVALID, "null argument");
+    *out = nullptr;
+    if (cfg->capacity < 1) return fail(nullptr, RETH_ERR_INVALID, "capacity must be >= 1");
+    if (cfg->capacity > (1ll << 31)) return fail(nullptr, RETH_ERR_INVALID, "capacity > 2^31 unsupported");
+    if (cfg->n_columns < 0 || cfg->n_columns > RETH_MAX_COLUMNS)
+        return fail(nullptr, RETH_ERR_INVALID, "n_columns out of range");
+    if (cfg->max_batch < 1) return fail(nullptr, RETH_ERR_INVALID, "max_batch must be >= 1");
+    for (int c = 0; c < cfg->n_columns; ++c)
+        if (cfg->row_bytes[c] < 1) return fail(nullptr, RETH_ERR_INVALID, "row_bytes[%d] < 1", c);
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return fail(nullptr, RETH_ERR_CUDA, "no CUDA device: the replay engine has no CPU fallback");
+    if (cfg->device < 0 || cfg->device >= ndev) return fail(nullptr, RETH_ERR_INVALID, "bad device ordinal");
+
+    reth_replay *h = new (std::nothrow) reth_replay();
+    if (!h) return fail(nullptr, RETH_ERR_OOM, "host allocation failed");
+    h->cfg = *cfg;
+    if (h->cfg.ring_depth < 1) h->cfg.ring_depth = 2;
+    h->geom = make_geom(cfg->capacity);
+    h->update_cluster = cfg->update_cluster > 0 ? cfg->update_cluster : 8;
+    DeviceGuard guard(cfg->device);
+    auto bail = [&](int code) { free_all(h); g_create_error = h->error; delete h; return code; };
+#define CKC(expr)                                                                          \
+    do {                                                                                   \
+        cudaError_t e__ = (expr);                                                          \
+        if (e__ != cudaSuccess) {                                                          \
+            fail(h, e__ == cudaErrorMemoryAllocation ? RETH_ERR_OOM : RETH_ERR_CUDA,       \
+                 "%s: %s", #expr, cudaGetErrorString(e__));                                \
+            cudaGetLastError();                                                            \
+            return bail(e__ == cudaErrorMemoryAllocation ? RETH_ERR_OOM : RETH_ERR_CUDA);  \
+        }                                                                                  \
+    } while (0)
+    cudaDeviceProp prop;
+    CKC(cudaGetDeviceProperties(&prop, cfg->device));
+    if (prop.major < 9)
+        return bail(fail(h, RETH_ERR_CUDA, "device sm_%d%d: built for sm_100a only", prop.major, prop.minor));
+    h->n_sms = prop.multiProcessorCount;
+    int64_t *acct = &h->st.hbm_bytes;
+    const size_t nt = (size_t)h->geom.n_tiles;
+    CKC(dalloc_zero(&h->desc, nt * 32, acct));
+    CKC(dalloc_zero(&h->agg, nt * 64, acct));
+    CKC(dalloc_zero(&h->stamp, (size_t)cfg->capacity, acct));
+    CKC(dalloc_zero(&h->mask, nt, acct));
+    h->max_n = cfg->max_batch > 16384 ? cfg->max_batch : 16384;
+    CKC(dalloc_zero(&h->worklist, (size_t)kMaxTileLevels * h->max_n, acct));
+    CKC(dalloc_zero(&h->counts, 2 * kMaxTileLevels, acct));
+    CKC(dalloc_zero(&h->err, 4, acct));
+    CKC(cudaMalloc(&h->stage_idx, h->max_n * 8));
+    CKC(cudaMalloc(&h->stage_prio, h->max_n * 8));
+    CKC(cudaMalloc((void **)&h->stage_u, (size_t)cfg->max_batch * 8));
+    CKC(cudaMallocHost((void **)&h->host_pin, 64 * sizeof(int64_t)));
+    if (cfg->store_rows)
+        for (int c = 0; c < cfg->n_columns; ++c) {
+            CKC(cudaMalloc((void **)&h->ring[c], (size_t)cfg->capacity * cfg->row_bytes[c]));
+            *acct += cfg->capacity * cfg->row_bytes[c];
+        }
+    h->slots.resize(h->cfg.ring_depth);
+    for (auto &s : h->slots) {
+        if (cfg->store_rows)
+            for (int c = 0; c < cfg->n_columns; ++c) {
+                CKC(cudaMalloc((void **)&s.cols[c], (size_t)cfg->max_batch * cfg->row_bytes[c]));
+                *acct += (int64_t)cfg->max_batch * cfg->row_bytes[c];
+            }
+        CKC(dalloc_zero(&s.idx, (size_t)cfg->max_batch, acct));
+        CKC(dalloc_zero(&s.w, (size_t)cfg->max_batch, acct));
+        CKC(dalloc_zero(&s.prio, (size_t)cfg->max_batch, acct));
+        CKC(dalloc_zero(&s.meta, 2, acct));
+    }
+    int lo = 0, hi = 0;
+    CKC(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    CKC(cudaStreamCreateWithPriority(&h->s_tree, cudaStreamNonBlocking, hi));
+    CKC(cudaStreamCreateWithPriority(&h->s_gather, cudaStreamNonBlocking, lo));
+    h->ev_sampled.resize(h->cfg.ring_depth);
+    h->ev_gathered.resize(h->cfg.ring_depth);
+    for (int i = 0; i < h->cfg.ring_depth; ++i) {
+        CKC(cudaEventCreateWithFlags(&h->ev_sampled[i], cudaEventDisableTiming));
+        CKC(cudaEventCreateWithFlags(&h->ev_gathered[i], cudaEventDisableTiming));
+    }
+    CKC(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
+    CKC(cudaEventCreateWithFlags(&h->ev_join_t, cudaEventDisableTiming));
+    CKC(cudaEventCreateWithFlags(&h->ev_join_g, cudaEventDisableTiming));
+    if (h->update_cluster > 8)
+        CKC(cudaFuncSetAttribute(per_update_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    CKC(cudaDeviceSynchronize());
+#undef CKC
+    *out = h;
+    return RETH_OK;
+}
+
+RETH_EXPORT int reth_replay_destroy(reth_replay_t *h)
+{
+    if (!h) return RETH_OK;
+    {
+        DeviceGuard guard(h->cfg.device);
+        cudaDeviceSynchronize();
+        free_all(h);
+    }
+    delete h;
+    return RETH_OK;
+}
+
+// ------------------------------------------------------------ launch helpers --
+namespace {
+
+// Bring a host-resident argument array to the device staging buffer.
+int to_device(reth_replay *h, const void *p, int loc, size_t bytes, void *staging,
+              cudaStream_t s, const void **out)
+{
+    if (loc == RETH_DEVICE) { *out = p; return RETH_OK; }
+    CK(h, cudaMemcpyAsync(staging, p, bytes, cudaMemcpyHostToDevice, s));
+    *out = staging;
+    return RETH_OK;
+}
+
+// One launch of the cluster tree-repair kernel for n <= max_n entries.
+int launch_update(reth_replay *h, UpdateArgs &a, cudaStream_t s)
+{
+    if (a.n <= 0) return RETH_OK;
+    a.g = h->geom; a.desc = h->desc; a.agg = h->agg; a.stamp = h->stamp; a.mask = h->mask;
+    a.worklist = h->worklist; a.err = h->err; a.max_n = h->max_n;
+    if (a.dedupe) {
+        if ((uint64_t)h->stamp_base + (uint64_t)a.n + 2ull >= 0xffffffffull) {
+            CK(h, cudaMemsetAsync(h->stamp, 0, (size_t)h->cfg.capacity * sizeof(uint32_t), s));
+            h->stamp_base = 0;
+        }
+        a.stamp_base = h->stamp_base;
+        h->stamp_base += (uint32_t)a.n;
+    }
+    a.counts = h->counts + h->counts_flip * kMaxTileLevels;
+    a.counts_next = h->counts + (h->counts_flip ^ 1) * kMaxTileLevels;
+    h->counts_flip ^= 1;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(h->update_cluster);
+    cfg.blockDim = dim3(kUpdateThreads);
+    cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = h->update_cluster;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    CK(h, cudaLaunchKernelEx(&cfg, per_update_kernel, (const UpdateArgs)a));
+    h->st.kernel_launches++;
+    return RETH_OK;
+}
+
+int set_prio(reth_replay *h, UpdateArgs &a, const void *prio, int prio_dtype, int prio_loc,
+             int64_t off, int64_t n, cudaStream_t s)
+{
+    if (!prio) { a.prio = nullptr; a.prio_kind = 2; return RETH_OK; }
+    if (prio_dtype != RETH_F32 && prio_dtype != RETH_F64)
+        return fail(h, RETH_ERR_INVALID, "priorities must be float32 or float64");
+    const size_t es = dtype_size(prio_dtype);
+    a.prio_kind = prio_dtype == RETH_F32 ? 0 : 1;
+    return to_device(h, (const uint8_t *)prio + off * es, prio_loc, n * es, h->stage_prio, s, &a.prio);
+}
+
+// Device-side error flag (index out of range seen by a kernel); checked at sync points.
+int check_device_err(reth_replay *h, cudaStream_t s)
+{
+    int32_t *flag = (int32_t *)h->host_pin;
+    CK(h, cudaMemcpyAsync(flag, h->err, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+    CK(h, cudaStreamSynchronize(s));
+    if (*flag) {
+        cudaMemsetAsync(h->err, 0, sizeof(int32_t), s);
+        return fail(h, RETH_ERR_RANGE, "an index outside [0, capacity) was passed to the shard");
+    }
+    return RETH_OK;
+}
+
+int slot_ok(reth_replay *h, int slot)
+{
+    if (slot < 0 || slot >= (int)h->slots.size()) return fail(h, RETH_ERR_INVALID, "bad batch slot %d", slot);
+    return RETH_OK;
+}
+
+}  // namespace
+
+RETH_EXPORT int reth_replay_clear(reth_replay_t *h, void *stream)
+{
+    if (!h) return RETH_ERR_INVALID;
+    DeviceGuard guard(h->cfg.device);
+    cudaStream_t s = S(stream);
+    const size_t nt = (size_t)h->geom.n_tiles;
+    CK(h, cudaMemsetAsync(h->desc, 0, nt * 32 * sizeof(double2), s));
+    CK(h, cudaMemsetAsync(h->agg, 0, nt * 64 * sizeof(double2), s));
+    CK(h, cudaMemsetAsync(h->mask, 0, nt * sizeof(uint32_t), s));
+    CK(h, cudaMemsetAsync(h->stamp, 0, (size_t)h->cfg.capacity * sizeof(uint32_t), s));
+    CK(h, cudaMemsetAsync(h->counts, 0, 2 * kMaxTileLevels * sizeof(int32_t), s));
+    h->stamp_base = 0;
+    h->tail = 0;
+    h->size = 0;
+    return RETH_OK;
+}
+
+RETH_EXPORT int reth_replay_append(reth_replay_t *h, const void *const *cols, int cols_loc,
+                                   const void *prio, int prio_dtype, int prio_loc, int64_t n,
+                                   double alpha, int transform, int64_t *first_slot_out, void *stream)
+{
+    if (!h) return RETH_ERR_INVALID;
+    if (n < 0 || n > h->cfg.capacity)   // fifo_policy.py:12
+        return fail(h, RETH_ERR_INVALID, "append of %lld rows exceeds capacity", (long long)n);
+    if (h->cfg.store_rows && h->cfg.n_columns > 0 && !cols) return fail(h, RETH_ERR_INVALID, "cols is null");
+    DeviceGuard guard(h->cfg.device);
+    cudaStream_t s = S(stream);
+    const int64_t cap = h->cfg.capacity;
+    if (first_slot_out) *first_slot_out = h->tail;
+    for (int64_t off = 0; off < n; off += h->max_n) {
+        const int64_t m = (n - off < h->max_n) ? n - off : h->max_n;
+        const int64_t start = h->tail;
+        if (h->cfg.store_rows && h->cfg.n_columns > 0) {
+            const int64_t len1 = (m < cap - start) ? m : cap - start, len2 = m - len1;
+            if (cols_loc == RETH_DEVICE) {
+                AppendArgs a = {};
+                a.ncols = h->cfg.n_columns; a.start = start; a.n = m; a.capacity = cap;
+                int64_t bytes = 0;
+                for (int c = 0; c < a.ncols; ++c) {
+                    a.rb[c] = h->cfg.row_bytes[c];
+                    a.src[c] = (const uint8_t *)cols[c] + off * a.rb[c];
+                    a.ring[c] = h->ring[c];
+                    bytes += m * a.rb[c];
+                }
+                int64_t blocks = (bytes / 16 + kCopyThreads * 4 - 1) / (kCopyThreads * 4);
+                const int64_t cap_blocks = (int64_t)h->n_sms * 8;
+                if (blocks > cap_blocks) blocks = cap_blocks;
+                if (blocks < 1) blocks = 1;
+                ring_append_kernel<<<(unsigned)blocks, kCopyThreads, 0, s>>>(a);
+                CK(h, cudaGetLastError());
+                h->st.kernel_launches++;
+            } else {
+                for (int c = 0; c < h->cfg.n_columns; ++c) {
+                    const int64_t rb = h->cfg.row_bytes[c];
+                    const uint8_t *src = (const uint8_t *)cols[c] + off * rb;
+                    CK(h, cudaMemcpyAsync(h->ring[c] + start * rb, src, len1 * rb, cudaMemcpyHostToDevice, s));
+                    if (len2 > 0)
+                        CK(h, cudaMemcpyAsync(h->ring[c], src + len1 * rb, len2 * rb, cudaMemcpyHostToDevice, s));
+                }
+            }
+        }
+        UpdateArgs a = {};
+        a.n = m; a.idx = nullptr; a.idx_kind = 2; a.iota_base = start;
+        a.alpha = alpha; a.transform = transform; a.dedupe = 0;
+        int rc = set_prio(h, a, prio, prio_dtype, prio_loc, off, m, s);
+        if (rc) return rc;
+        rc = launch_update(h, a, s);
+        if (rc) return rc;
+        h->tail = (start + m) % cap;
+        h->size = (h->size + m < cap) ? h->size + m : cap;
+        h->st.appended_rows += m;
+    }
+    h->st.tail = h->tail; h->st.size = h->size;
+    return RETH_OK;
+}
+
+RETH_EXPORT int reth_replay_update(reth_replay_t *h, const void *idx, int idx_dtype, int idx_loc,
+                                   const void *prio, int prio_dtype, int prio_loc, int64_t n,
+                                   double alpha, int transform, void *stream)
+{
+    if (!h) return RETH_ERR_INVALID;
+    if (n < 0 || (n > 0 && !idx)) return fail(h, RETH_ERR_INVALID, "bad indices");
+    if (idx_dtype != RETH_I32 && idx_dtype != RETH_I64)
+        return fail(h, RETH_ERR_INVALID, "indices must be int32 or int64");
+    DeviceGuard guard(h->cfg.device);
+    cudaStream_t s = S(stream);
+    const size_t es = dtype_size(idx_dtype);
+    // chunks keep batch order: later chunks run later on the stream, so
+    // last-writer-wins holds across chunk boundaries too
+    for (int64_t off = 0; off < n; off += h->max_n) {
+        const int64_t m = (n - off < h->max_n) ? n - off : h->max_n;
+        UpdateArgs a = {};
+        a.n = m; a.idx_kind = idx_dtype == RETH_I64 ? 0 : 1;
+        a.alpha = alpha; a.transform = transform; a.dedupe = 1;
+        int rc = to_device(h, (const uint8_t *)idx + off * es, idx_loc, m * es, h->stage_idx, s, &a.idx);
+        if (rc) return rc;
+        rc = set_prio(h, a, prio, prio_dtype, prio_loc, off, m, s);
+        if (rc) return rc;
+        rc = launch_update(h, a, s);
+        if (rc) return rc;
+        h->st.updated_rows += m;
+    }
+    return RETH_OK;
+}
+
+RETH_EXPORT int reth_replay_update_slot(reth_replay_t *h, int slot, const void *prio, int prio_dtype,
+                                        int prio_loc, double alpha, int transform, void *stream)
+{
+    if (!h) return RETH_ERR_INVALID;
+    if (slot_ok(h, slot)) return RETH_ERR_INVALID;
+    DeviceGuard guard(h->cfg.device);
+    BatchSlot &b = h->slots[slot];
+    if (b.batch <= 0) return fail(h, RETH_ERR_STATE, "slot %d holds no sampled batch", slot);
+    UpdateArgs a = {};
+    a.n = b.batch; a.idx = b.idx; a.idx_kind = 0;
+    a.alpha = alpha; a.transform = transform; a.dedupe = 1;
+    int rc = set_prio(h, a, prio, prio_dtype, prio_loc, 0, b.batch, S(stream));
+    if (rc) return rc;
+    rc = launch_update(h, a, S(stream));
+    if (rc) return rc;
+    h->st.updated_rows += b.batch;
+    return RETH_OK;
+}
+
+// ------------------------------------------------------------ sample / gather --
+namespace {
+
+int gather_units_target()
+{
+    static int v = [] {
+        const char *e = getenv("RETH_GATHER_UNITS");
+        int x = e ? atoi(e) : 1024;
+        return x < 64 ? 64 : x;
+    }();
+    return v;
+}
+
+// Work decomposition of a row move over `batch` rows (gather or scatter).
+void build_row_args(reth_replay *h, RowArgs &a, uint8_t *const *batch_cols, const int64_t *idx, int batch)
+{
+    a = RowArgs{};
+    a.ncols = h->cfg.n_columns;
+    a.idx = idx;
+    a.batch = batch;
+    a.capacity = h->cfg.capacity;
+    a.err = h->err;
+    int64_t items = 0;
+    bool narrow = false;
+    for (int c = 0; c < a.ncols; ++c) {
+        RowCol &col = a.col[c];
+        col.ring = h->ring[c];
+        col.batch = batch_cols[c];
+        col.rb = h->cfg.row_bytes[c];
+        const bool wide = (col.rb % 16 == 0) && col.rb >= 256 && ((uintptr_t)col.batch % 16 == 0);
+        if (wide) {
+            const int64_t upr = col.rb / 16;
+            col.chunks = (int32_t)((upr + gather_units_target() - 1) / gather_units_target());
+            col.units = (int32_t)((upr + col.chunks - 1) / col.chunks);
+            col.item_base = items;
+            items += (int64_t)batch * col.chunks;
+        } else {
+            col.chunks = 0;
+            narrow = true;
+        }
+    }
+    a.wide_items = items;
+    a.narrow_groups = narrow ? (batch + kCopyThreads - 1) / kCopyThreads : 0;
+}
+
+template <bool kScatter>
+int launch_row_move(reth_replay *h, const RowArgs &a, cudaStream_t s)
+{
+    int64_t total = a.wide_items + a.narrow_groups;
+    if (total <= 0) return RETH_OK;
+    const int64_t maxg = (int64_t)h->n_sms * 6 * 64;
+    const unsigned grid = (unsigned)(total < maxg ? total : maxg);
+    row_move_kernel<kScatter><<<grid, kCopyThreads, 0, s>>>(a);
+    CK(h, cudaGetLastError());
+    h->st.kernel_launches++;
+    return RETH_OK;
+}
+
+int do_sample(reth_replay *h, int batch, const double *uniforms, int uniforms_loc, uint64_t seed,
+              double beta, int slot, const double *all_roots, int n_shards, int shard, cudaStream_t s)
+{
+    if (slot_ok(h, slot)) return RETH_ERR_INVALID;
+    if (batch < 1 || batch > h->cfg.max_batch)
+        return fail(h, RETH_ERR_INVALID, "batch %d outside [1, max_batch=%d]", batch, h->cfg.max_batch);
+    BatchSlot &b = h->slots[slot];
+    SampleArgs a = {};
+    a.g = h->geom; a.desc = h->desc; a.agg = h->agg; a.batch = batch;
+    if (uniforms) {
+        const void *u = nullptr;
+        int rc = to_device(h, uniforms, uniforms_loc, (size_t)batch * 8, h->stage_u, s, &u);
+        if (rc) return rc;
+        a.uniforms = (const double *)u;
+    }
+    a.seed = seed; a.draw_base = h->draw_counter;
+    h->draw_counter += (uint64_t)batch;
+    a.beta = beta; a.min_mode = h->cfg.min_mode;
+    a.idx_out = b.idx; a.w_out = b.w; a.prio_out = b.prio; a.meta = b.meta;
+    a.all_roots = all_roots; a.n_shards = n_shards; a.shard = shard;
+    const int wpb = 4;
+    per_sample_kernel<<<(batch + wpb - 1) / wpb, wpb * 32, 0, s>>>(a);
+    CK(h, cudaGetLastError());
+    h->st.kernel_launches++;
+    h->st.sampled_rows += batch;
+    b.batch = batch;
+    return RETH_OK;
+}
+
+int do_gather(reth_replay *h, int slot, bool use_meta, cudaStream_t s)
+{
+    BatchSlot &b = h->slots[slot];
+    if (!h->cfg.store_rows || h->cfg.n_columns == 0) return RETH_OK;
+    RowArgs a;
+    build_row_args(h, a, b.cols, b.idx, b.batch);
+    a.meta = use_meta ? b.meta : nullptr;
+    int rc = launch_row_move<false>(h, a, s);
+    if (rc) return rc;
+    h->st.gathered_rows += b.batch;
+    return RETH_OK;
+}
+
+}  // namespace
+
+RETH_EXPORT int reth_replay_sample(reth_replay_t *h, int batch, const double *uniforms, int uniforms_loc,
+                                   uint64_t seed, double beta, int slot, void *stream)
+{
+    if (!h) return RETH_ERR_INVALID;
+    DeviceGuard guard(h->cfg.device);
+    return do_sample(h, batch, uniforms, uniforms_loc, seed, beta, slot, nullptr, 1, 0, S(stream));
+}
+
+RETH_EXPORT int reth_replay_sample_global(reth_replay_t *h, int global_batch, const double *all_roots_dev,
+                                          int n_shards, int shard, const double *uniforms, int uniforms_loc,
+                                          uint64_t seed, double beta, int slot, void *stream)
+{
+    if (!h) return RETH_ERR_INVALID;
+    if (!all_roots_dev || n_shards < 1 || shard < 0 || shard >= n_shards)
+        return fail(h, RETH_ERR_INVALID, "bad shard arguments");
+    DeviceGuard guard(h->cfg.device);
+    // n_shards == 1 still takes the global path when asked (keeps one code path testable)
+    return do_sample(h, global_batch, uniforms, uniforms_loc, seed, beta, slot, all_roots_dev,
+                     n_shards > 1 ? n_shards : 1, shard, S(stream));
+}
+
+RETH_EXPORT int reth_replay_gather(reth_replay_t *h, int slot, void *stream)
+{
+    if (!h) return RETH_ERR_INVALID;
+    if (slot_ok(h, slot)) return RETH_ERR_INVALID;
+    if (h->slots[slot].batch <= 0) return fail(h, RETH_ERR_STATE, "slot %d holds no sampled batch", slot);
+    DeviceGuard guard(h->cfg.device);
+    return do_gather(h, slot, true, S(stream));
+}
+
+RETH_EXPORT int reth_replay_append_at(reth_replay_t *h, const int64_t *slots, int slots_loc,
+                                      const void *const *cols, int cols_loc,
+                                      const void *prio, int prio_dtype, int prio_loc, int64_t n,
+                                      double alpha, int transform, void *stream)
+{
+    if (!h) return RETH_ERR_INVALID;
+    if (n < 0 || (n > 0 && !slots)) return fail(h, RETH_ERR_INVALID, "bad slots");
+    if (n > h->max_n) return fail(h, RETH_ERR_INVALID, "append_at: n > %lld", (long long)h->max_n);
+    if (n == 0) return RETH_OK;
+    DeviceGuard guard(h->cfg.device);
+    cudaStream_t s = S(stream);
+    UpdateArgs a = {};
+    a.n = n; a.idx_kind = 0; a.alpha = alpha; a.transform = transform; a.dedupe = 1;
+    int rc = to_device(h, slots, slots_loc, n * 8, h->stage_idx, s, &a.idx);
+    if (rc) return rc;
+    rc = set_prio(h, a, prio, prio_dtype, prio_loc, 0, n, s);
+    if (rc) return rc;
+    rc = launch_update(h, a, s);   // also arbitrates duplicates: stamp[slot] == base+1+i for the winner
+    if (rc) return rc;
+    if (h->cfg.store_rows && h->cfg.n_columns > 0) {
+        if (!cols) return fail(h, RETH_ERR_INVALID, "cols is null");
+        if (cols_loc != RETH_DEVICE)
+            return fail(h, RETH_ERR_INVALID, "append_at needs device-resident rows (stage them first)");
+        uint8_t *src[kMaxCols];
+        for (int c = 0; c < h->cfg.n_columns; ++c) src[c] = (uint8_t *)cols[c];
+        RowArgs r;
+        build_row_args(h, r, src, (const int64_t *)a.idx, (int)n);
+        r.stamp = h->stamp;
+        r.stamp_base = a.stamp_base;
+        rc = launch_row_move<true>(h, r, s);
+        if (rc) return rc;
+    }
+    h->st.appended_rows += n;
+    h->size = (h->size + n < h->cfg.capacity) ? h->size + n : h->cfg.capacity;
+    h->st.size = h->size;
+    return RETH_OK;
+}
+
+RETH_EXPORT int reth_replay_slot_ptrs(reth_replay_t *h, int slot, void **cols_out, int64_t **indices_out,
+                                      double **weights_out, double **prios_out, int32_t *batch_out)
+{
+    if (!h) return RETH_ERR_INVALID;
+    if (slot_ok(h, slot)) return RETH_ERR_INVALID;
+    BatchSlot &b = h->slots[slot];
+    if (cols_out) for (int c = 0; c < h->cfg.n_columns; ++c) cols_out[c] = b.cols[c];
+    if (indices_out) *indices_out = b.idx;
+    if (weights_out) *weights_out = b.w;
+    if (prios_out) *prios_out = b.prio;
+    if (batch_out) *batch_out = b.batch;
+    return RETH_OK;
+}
+
+RETH_EXPORT int reth_replay_slot_read(reth_replay_t *h, int slot, int64_t *indices, double *weights,
+                                      void *const *cols, void *stream)
+{
+    if (!h) return RETH_ERR_INVALID;
+    if (slot_ok(h, slot)) return RETH_ERR_INVALID;
+    DeviceGuard guard(h->cfg.device);
+    cudaStream_t s = S(stream);
+    BatchSlot &b = h->slots[slot];
+    const size_t n = (size_t)b.batch;
+    if (indices) CK(h, cudaMemcpyAsync(indices, b.idx, n * 8, cudaMemcpyDeviceToHost, s));
+    if (weights) CK(h, cudaMemcpyAsync(weights, b.w, n * 8, cudaMemcpyDeviceToHost, s));
+    if (cols && h->cfg.store_rows)
+        for (int c = 0; c < h->cfg.n_columns; ++c)
+            if (cols[c])
+                CK(h, cudaMemcpyAsync(cols[c], b.cols[c], n * h->cfg.row_bytes[c], cudaMemcpyDeviceToHost, s));
+    return check_device_err(h, s);
+}
+
+RETH_EXPORT int reth_replay_slot_meta(reth_replay_t *h, int slot, int64_t *first_count, void *stream)
+{
+    if (!h || !first_count) return RETH_ERR_INVALID;
+    if (slot_ok(h, slot)) return RETH_ERR_INVALID;
+    DeviceGuard guard(h->cfg.device);
+    CK(h, cudaMemcpyAsync(h->host_pin + 8, h->slots[slot].meta, 16, cudaMemcpyDeviceToHost, S(stream)));
+    CK(h, cudaStreamSynchronize(S(stream)));
+    first_count[0] = h->host_pin[8];
+    first_count[1] = h->host_pin[9];
+    return RETH_OK;
+}
+
+RETH_EXPORT int reth_replay_tree_read(reth_replay_t *h, double *sum, double *mn, double *val, void *stream)
+{
+    if (!h) return RETH_ERR_INVALID;
+    DeviceGuard guard(h->cfg.device);
+    cudaStream_t s = S(stream);
+    const int64_t cap = h->cfg.capacity;
+    double *d[3] = {nullptr, nullptr, nullptr};
+    double *host[3] = {sum, mn, val};
+    for (int k = 0; k < 3; ++k)
+        if (host[k]) CK(h, cudaMalloc((void **)&d[k], (size_t)cap * 8));
+    tree_read_kernel<<<(unsigned)((cap + 255) / 256), 256, 0, s>>>(h->geom, h->desc, h->agg, d[0], d[1], d[2]);
+    int rc = RETH_OK;
+    if (cudaGetLastError() != cudaSuccess) rc = fail(h, RETH_ERR_CUDA, "tree_read_kernel launch failed");
+    for (int k = 0; k < 3 && rc == RETH_OK; ++k)
+        if (host[k] && cudaMemcpyAsync(host[k], d[k], (size_t)cap * 8, cudaMemcpyDeviceToHost, s) != cudaSuccess)
+            rc = fail(h, RETH_ERR_CUDA, "tree_read copy failed");
+    cudaStreamSynchronize(s);
+    for (int k = 0; k < 3; ++k) cudaFree(d[k]);
+    if (rc) return rc;
+    return check_device_err(h, s);
+}
+
+RETH_EXPORT int reth_replay_tree_root(reth_replay_t *h, double *total, double *minimum, void *stream)
+{
+    if (!h) return RETH_ERR_INVALID;
+    DeviceGuard guard(h->cfg.device);
+    double *r = (double *)(h->host_pin + 16);
+    CK(h, cudaMemcpyAsync(r, &h->agg[1], 16, cudaMemcpyDeviceToHost, S(stream)));
+    CK(h, cudaStreamSynchronize(S(stream)));
+    if (total) *total = r[0];
+    if (minimum) {
+        if (h->cfg.min_mode == RETH_MIN_SERVICE) *minimum = (r[0] != 0.0) ? r[1] : 1.0;
+        else *minimum = (r[1] != 0.0) ? r[1] : 1.0;
+    }
+    return RETH_OK;
+}
+
+RETH_EXPORT int reth_replay_root_dev(reth_replay_t *h, double **root_dev_out)
+{
+    if (!h || !root_dev_out) return RETH_ERR_INVALID;
+    *root_dev_out = (double *)&h->agg[1];
+    return RETH_OK;
+}
+
+RETH_EXPORT int reth_replay_ring_read(reth_replay_t *h, int column, int64_t first_slot, int64_t n,
+                                      void *out_host, void *stream)
+{
+    if (!h || !out_host) return RETH_ERR_INVALID;
+    if (!h->cfg.store_rows || column < 0 || column >= h->cfg.n_columns)
+        return fail(h, RETH_ERR_INVALID, "bad column");
+    if (first_slot < 0 || n < 0 || first_slot + n > h->cfg.capacity)
+        return fail(h, RETH_ERR_INVALID, "slot range outside the ring");
+    DeviceGuard guard(h->cfg.device);
+    const int64_t rb = h->cfg.row_bytes[column];
+    CK(h, cudaMemcpyAsync(out_host, h->ring[column] + first_slot * rb, (size_t)(n * rb),
+                          cudaMemcpyDeviceToHost, S(stream)));
+    CK(h, cudaStreamSynchronize(S(stream)));
+    return RETH_OK;
+}
+
+RETH_EXPORT int reth_replay_stats_get(reth_replay_t *h, reth_replay_stats *out)
+{
+    if (!h || !out) return RETH_ERR_INVALID;
+    h->st.tail = h->tail;
+    h->st.size = h->size;
+    *out = h->st;
+    return RETH_OK;
+}
+
+// ------------------------------------------------------------------ step loop --
+RETH_EXPORT int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, const float *prio_dev,
+                                      const double *uniforms_dev, uint64_t seed, double alpha, double beta,
+                                      int flags, void *stream)
+{
+    if (!h) return RETH_ERR_INVALID;
+    if (steps < 0 || !prio_dev) return fail(h, RETH_ERR_INVALID, "bad step_loop arguments");
+    DeviceGuard guard(h->cfg.device);
+    cudaStream_t s = S(stream);
+    const bool no_gather = flags & 1, serial = flags & 2;
+    const int depth = (int)h->slots.size();
+    cudaStream_t st = serial ? s : h->s_tree, sg = serial ? s : h->s_gather;
+    if (!serial) {
+        CK(h, cudaEventRecord(h->ev_fork, s));
+        CK(h, cudaStreamWaitEvent(st, h->ev_fork, 0));
+        CK(h, cudaStreamWaitEvent(sg, h->ev_fork, 0));
+    }
+    for (int k = 0; k < steps; ++k) {
+        const int slot = k % depth;
+        // the slot's index buffer is re-drawn: its previous gather must have consumed it
+        if (!serial && !no_gather && k >= depth) CK(h, cudaStreamWaitEvent(st, h->ev_gathered[slot], 0));
+        int rc = do_sample(h, batch, uniforms_dev ? uniforms_dev + (size_t)k * batch : nullptr, RETH_DEVICE,
+                           seed, beta, slot, nullptr, 1, 0, st);
+        if (rc) return rc;
+        if (!no_gather) {
+            if (!serial) {
+                CK(h, cudaEventRecord(h->ev_sampled[slot], st));
+                CK(h, cudaStreamWaitEvent(sg, h->ev_sampled[slot], 0));
+            }
+            rc = do_gather(h, slot, false, sg);
+            if (rc) return rc;
+            if (!serial) CK(h, cudaEventRecord(h->ev_gathered[slot], sg));
+        }
+        UpdateArgs a = {};
+        a.n = batch; a.idx = h->slots[slot].idx; a.idx_kind = 0;
+        a.prio = prio_dev + (size_t)k * batch; a.prio_kind = 0;
+        a.alpha = alpha; a.transform = 1; a.dedupe = 1;
+        rc = launch_update(h, a, st);
+        if (rc) return rc;
+        h->st.updated_rows += batch;
+    }
+    if (!serial) {
+        CK(h, cudaEventRecord(h->ev_join_t, st));
+        CK(h, cudaEventRecord(h->ev_join_g, sg));
+        CK(h, cudaStreamWaitEvent(s, h->ev_join_t, 0));
+        CK(h, cudaStreamWaitEvent(s, h->ev_join_g, 0));
+    }
+    return RETH_OK;
+}

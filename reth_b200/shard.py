@@ -1,0 +1,333 @@
+"""ReplayShard: Python face of one C-ABI replay shard (include/reth_replay.h).
+
+Thin by design: argument marshalling (numpy = host pointers, torch CUDA tensors /
+__cuda_array_interface__ = device pointers), error translation, and the tensor
+hand-off to the learner.  All arithmetic runs in the CUDA library.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _cabi
+from ._cabi import DEVICE, F32, F64, HOST, I32, I64, MIN_INPROCESS, MIN_SERVICE, ReplayError  # noqa: F401
+
+_TYPESTR = {np.dtype(np.uint8): "|u1", np.dtype(np.int8): "|i1", np.dtype(np.bool_): "|b1"}
+
+
+def _typestr(dt):
+    dt = np.dtype(dt)
+    return _TYPESTR.get(dt, dt.str)
+
+
+class _DevArray:
+    """Borrowed device memory exposed through __cuda_array_interface__ (v3)."""
+
+    def __init__(self, ptr, shape, dtype, owner):
+        self._owner = owner
+        self.__cuda_array_interface__ = {
+            "shape": tuple(int(s) for s in shape), "typestr": _typestr(dtype),
+            "data": (int(ptr), False), "version": 3, "strides": None, "stream": None,
+        }
+
+
+def _is_torch(x):
+    return type(x).__module__.startswith("torch")
+
+
+def _ptr_loc(x):
+    """-> (address, loc, numpy dtype, nelems, keepalive)"""
+    if x is None:
+        return None, HOST, None, 0, None
+    if _is_torch(x):
+        if not x.is_contiguous():
+            x = x.contiguous()
+        dt = np.dtype(str(x.dtype).replace("torch.", ""))
+        return x.data_ptr(), (DEVICE if x.is_cuda else HOST), dt, x.numel(), x
+    if hasattr(x, "__cuda_array_interface__"):
+        cai = x.__cuda_array_interface__
+        if cai.get("strides"):
+            raise ValueError("device array must be C-contiguous")
+        n = int(np.prod(cai["shape"], dtype=np.int64))
+        return cai["data"][0], DEVICE, np.dtype(cai["typestr"]), n, x
+    a = np.ascontiguousarray(x)
+    return a.ctypes.data, HOST, a.dtype, a.size, a
+
+
+def _stream_handle(stream, device):
+    if stream is None:
+        import sys
+        torch = sys.modules.get("torch")
+        if torch is not None and torch.cuda.is_available() and torch.cuda.is_initialized():
+            return int(torch.cuda.current_stream(device).cuda_stream)
+        return 0
+    if hasattr(stream, "cuda_stream"):
+        return int(stream.cuda_stream)
+    return int(stream)
+
+
+class ReplayShard:
+    """One replay shard on one GPU.
+
+    struct: list of (dtype, per-row shape), the row layout the reference discovers
+    from its first row (client/torch_cuda_loader.py:106-112).
+    """
+
+    def __init__(self, capacity, struct, max_batch, ring_depth=2, device=0, min_mode=MIN_SERVICE,
+                 store_rows=True, update_cluster=0):
+        self._h = None
+        self._lib = _cabi.lib()
+        self.capacity = int(capacity)
+        self.struct = [(np.dtype(dt), tuple(int(s) for s in sh)) for dt, sh in (struct or [])]
+        self.row_bytes = [dt.itemsize * int(np.prod(sh, dtype=np.int64)) for dt, sh in self.struct]
+        self.max_batch = int(max_batch)
+        self.ring_depth = int(ring_depth)
+        self.device = int(device)
+        self.store_rows = bool(store_rows) and len(self.struct) > 0
+        cfg = _cabi.Config()
+        cfg.capacity = self.capacity
+        cfg.n_columns = len(self.struct)
+        for i, rb in enumerate(self.row_bytes):
+            cfg.row_bytes[i] = rb
+        cfg.max_batch = self.max_batch
+        cfg.ring_depth = self.ring_depth
+        cfg.device = self.device
+        cfg.min_mode = int(min_mode)
+        cfg.update_cluster = int(update_cluster)
+        cfg.store_rows = int(self.store_rows)
+        h = C.c_void_p()
+        rc = self._lib.reth_replay_create(C.byref(cfg), C.byref(h))
+        if rc != 0:
+            _cabi.check(None, rc)
+        self._h = h
+
+    # -- lifetime ---------------------------------------------------------
+    def close(self):
+        if self._h is not None:
+            self._lib.reth_replay_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc != 0:
+            _cabi.check(self._h, rc)
+
+    def _s(self, stream):
+        return C.c_void_p(_stream_handle(stream, self.device))
+
+    # -- marshalling ------------------------------------------------------
+    def _prio(self, prio, n):
+        if prio is None:
+            return None, F32, HOST, None
+        p, loc, dt, cnt, keep = _ptr_loc(prio)
+        if dt not in (np.dtype(np.float32), np.dtype(np.float64)):
+            if loc == DEVICE:
+                raise ValueError("device priorities must be float32 or float64")
+            keep = np.ascontiguousarray(keep, dtype=np.float64)   # ints etc. -> float64 like numpy would
+            p, dt = keep.ctypes.data, keep.dtype
+        if cnt != n:
+            raise AssertionError("len(weights) != number of rows")   # client/client.py:25,38
+        return p, (F32 if dt == np.dtype(np.float32) else F64), loc, keep
+
+    def _cols(self, cols, n):
+        if not self.store_rows:
+            return None, HOST, []
+        if not isinstance(cols, (list, tuple)) or len(cols) != len(self.struct):
+            raise AssertionError("data must be a list with one array per column")   # client.py:22
+        ptrs = (C.c_void_p * len(cols))()
+        keep, locs = [], set()
+        for i, (col, (dt, sh)) in enumerate(zip(cols, self.struct)):
+            if not _is_torch(col) and not hasattr(col, "__cuda_array_interface__"):
+                col = np.ascontiguousarray(col, dtype=dt)
+            p, loc, cdt, cnt, k = _ptr_loc(col)
+            if cdt.itemsize * cnt != n * self.row_bytes[i]:
+                raise AssertionError(f"column {i}: expected {n} rows of {self.row_bytes[i]} bytes")
+            ptrs[i] = p
+            keep.append(k)
+            locs.add(loc)
+        if len(locs) > 1:
+            raise ValueError("all columns of one append must live on the same side (host or device)")
+        return ptrs, locs.pop(), keep
+
+    # -- write side -------------------------------------------------------
+    def clear(self, stream=None):
+        self._ck(self._lib.reth_replay_clear(self._h, self._s(stream)))
+
+    def append(self, cols, prio=None, alpha=0.6, transform=True, stream=None):
+        """Client.append / PrioritizedBuffer.append_batch; returns the first FIFO slot."""
+        n = len(prio) if prio is not None else len(cols[0])
+        ptrs, cloc, keep = self._cols(cols, n)
+        p, pdt, ploc, pkeep = self._prio(prio, n)
+        first = C.c_int64(-1)
+        self._ck(self._lib.reth_replay_append(self._h, ptrs, cloc, p, pdt, ploc, n, float(alpha),
+                                              int(bool(transform)), C.byref(first), self._s(stream)))
+        self._keep = (keep, pkeep)
+        return first.value
+
+    def append_at(self, slots, cols, prio=None, alpha=0.6, transform=True, stream=None):
+        sp, sloc, sdt, n, skeep = _ptr_loc(slots)
+        if sdt != np.dtype(np.int64):
+            if sloc == DEVICE:
+                raise ValueError("device slots must be int64")
+            skeep = np.ascontiguousarray(skeep, dtype=np.int64)
+            sp = skeep.ctypes.data
+        ptrs, cloc, keep = self._cols(cols, n)
+        p, pdt, ploc, pkeep = self._prio(prio, n)
+        self._ck(self._lib.reth_replay_append_at(self._h, sp, sloc, ptrs, cloc, p, pdt, ploc, n,
+                                                 float(alpha), int(bool(transform)), self._s(stream)))
+        self._keep = (skeep, keep, pkeep)
+
+    def update(self, indices, prio, alpha=0.6, transform=True, stream=None):
+        """Client.update_priorities -> PERSampler.update."""
+        ip, iloc, idt, n, ikeep = _ptr_loc(indices)
+        if idt not in (np.dtype(np.int32), np.dtype(np.int64)):
+            if iloc == DEVICE:
+                raise ValueError("device indices must be int32 or int64")
+            ikeep = np.ascontiguousarray(ikeep, dtype=np.int64)
+            ip, idt = ikeep.ctypes.data, ikeep.dtype
+        p, pdt, ploc, pkeep = self._prio(prio, n)
+        if p is None:
+            raise AssertionError("update needs priorities")
+        self._ck(self._lib.reth_replay_update(self._h, ip, I32 if idt.itemsize == 4 else I64, iloc,
+                                              p, pdt, ploc, n, float(alpha), int(bool(transform)),
+                                              self._s(stream)))
+        self._keep = (ikeep, pkeep)
+
+    def update_slot(self, slot, prio, alpha=0.6, transform=True, stream=None):
+        p, pdt, ploc, pkeep = self._prio(prio, self.slot_batch(slot))
+        self._ck(self._lib.reth_replay_update_slot(self._h, slot, p, pdt, ploc, float(alpha),
+                                                   int(bool(transform)), self._s(stream)))
+        self._keep = pkeep
+
+    # -- read side --------------------------------------------------------
+    def sample(self, batch, beta=0.4, uniforms=None, seed=0, slot=0, stream=None):
+        up, uloc, udt, cnt, ukeep = _ptr_loc(uniforms)
+        if uniforms is not None:
+            if udt != np.dtype(np.float64):
+                if uloc == DEVICE:
+                    raise ValueError("device uniforms must be float64")
+                ukeep = np.ascontiguousarray(ukeep, dtype=np.float64)
+                up = ukeep.ctypes.data
+            assert cnt == batch
+        self._ck(self._lib.reth_replay_sample(self._h, int(batch), up, uloc, int(seed) & (2**64 - 1),
+                                              float(beta), int(slot), self._s(stream)))
+        self._keep = ukeep
+
+    def sample_global(self, global_batch, all_roots, n_shards, shard, beta=0.4, uniforms=None,
+                      seed=0, slot=0, stream=None):
+        rp, rloc, rdt, rcnt, rkeep = _ptr_loc(all_roots)
+        assert rloc == DEVICE and rdt == np.dtype(np.float64) and rcnt >= 2 * n_shards
+        up, uloc, udt, cnt, ukeep = _ptr_loc(uniforms)
+        if uniforms is not None and udt != np.dtype(np.float64):
+            ukeep = np.ascontiguousarray(ukeep, dtype=np.float64)
+            up = ukeep.ctypes.data
+        self._ck(self._lib.reth_replay_sample_global(self._h, int(global_batch), rp, int(n_shards),
+                                                     int(shard), up, uloc, int(seed) & (2**64 - 1),
+                                                     float(beta), int(slot), self._s(stream)))
+        self._keep = (rkeep, ukeep)
+
+    def gather(self, slot=0, stream=None):
+        self._ck(self._lib.reth_replay_gather(self._h, int(slot), self._s(stream)))
+
+    def slot_batch(self, slot):
+        b = C.c_int32()
+        self._ck(self._lib.reth_replay_slot_ptrs(self._h, slot, None, None, None, None, C.byref(b)))
+        return b.value
+
+    def slot_arrays(self, slot, rows=None):
+        """Device views of a batch slot (borrowed until the slot is re-used):
+        (columns, indices, weights, priorities) as __cuda_array_interface__ objects."""
+        cols = (C.c_void_p * max(1, len(self.struct)))()
+        ip, wp, pp, b = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_int32()
+        self._ck(self._lib.reth_replay_slot_ptrs(self._h, slot, cols, C.byref(ip), C.byref(wp),
+                                                 C.byref(pp), C.byref(b)))
+        n = b.value if rows is None else int(rows)
+        data = []
+        if self.store_rows:
+            data = [_DevArray(cols[i], (n,) + sh, dt, self) for i, (dt, sh) in enumerate(self.struct)]
+        return (data, _DevArray(ip.value, (n,), np.int64, self), _DevArray(wp.value, (n,), np.float64, self),
+                _DevArray(pp.value, (n,), np.float64, self))
+
+    def slot_tensors(self, slot, rows=None):
+        """Same as slot_arrays but as torch CUDA tensors (zero-copy hand-off to the learner)."""
+        import torch
+        dev = torch.device("cuda", self.device)
+        data, idx, w, p = self.slot_arrays(slot, rows)
+        t = lambda a: torch.as_tensor(a, device=dev)  # noqa: E731
+        return [t(a) for a in data], t(idx), t(w), t(p)
+
+    def slot_read(self, slot, with_rows=False, rows=None, stream=None):
+        """Host copies of a slot: (columns or None, indices int64, weights float64). Synchronises."""
+        n = self.slot_batch(slot)
+        idx = np.empty(n, np.int64)
+        w = np.empty(n, np.float64)
+        ptrs, outs = None, None
+        if with_rows and self.store_rows:
+            outs = [np.empty((n,) + sh, dt) for dt, sh in self.struct]
+            ptrs = (C.c_void_p * len(outs))(*[o.ctypes.data for o in outs])
+        self._ck(self._lib.reth_replay_slot_read(self._h, slot, idx.ctypes.data, w.ctypes.data, ptrs,
+                                                 self._s(stream)))
+        if rows is not None:
+            idx, w = idx[:rows], w[:rows]
+            outs = [o[:rows] for o in outs] if outs is not None else None
+        return outs, idx, w
+
+    def slot_meta(self, slot, stream=None):
+        fc = (C.c_int64 * 2)()
+        self._ck(self._lib.reth_replay_slot_meta(self._h, slot, fc, self._s(stream)))
+        return fc[0], fc[1]
+
+    # -- parity / debug ---------------------------------------------------
+    def tree_arrays(self, stream=None):
+        """(_sum, _min, _val) in the reference's heap order (utils/sumtree.py:85-88)."""
+        s, m, v = (np.empty(self.capacity, np.float64) for _ in range(3))
+        self._ck(self._lib.reth_replay_tree_read(self._h, s.ctypes.data, m.ctypes.data, v.ctypes.data,
+                                                 self._s(stream)))
+        return s, m, v
+
+    def root(self, stream=None):
+        t, m = C.c_double(), C.c_double()
+        self._ck(self._lib.reth_replay_tree_root(self._h, C.byref(t), C.byref(m), self._s(stream)))
+        return t.value, m.value
+
+    def root_dev(self):
+        p = C.c_void_p()
+        self._ck(self._lib.reth_replay_root_dev(self._h, C.byref(p)))
+        return _DevArray(p.value, (2,), np.float64, self)
+
+    def ring_read(self, column, first_slot, n, stream=None):
+        dt, sh = self.struct[column]
+        out = np.empty((n,) + sh, dt)
+        self._ck(self._lib.reth_replay_ring_read(self._h, column, first_slot, n, out.ctypes.data,
+                                                 self._s(stream)))
+        return out
+
+    def stats(self):
+        st = _cabi.Stats()
+        self._ck(self._lib.reth_replay_stats_get(self._h, C.byref(st)))
+        return {n: getattr(st, n) for n, _ in st._fields_}
+
+    @property
+    def size(self):
+        return self.stats()["size"]
+
+    @property
+    def tail(self):
+        return self.stats()["tail"]
+
+    def step_loop(self, steps, batch, prio_dev, uniforms_dev=None, seed=0, alpha=0.6, beta=0.4,
+                  gather=True, serial=False, stream=None):
+        pp, ploc, pdt, pcnt, pk = _ptr_loc(prio_dev)
+        assert ploc == DEVICE and pdt == np.dtype(np.float32) and pcnt >= steps * batch
+        up, uloc, udt, ucnt, uk = _ptr_loc(uniforms_dev)
+        if uniforms_dev is not None:
+            assert uloc == DEVICE and udt == np.dtype(np.float64) and ucnt >= steps * batch
+        flags = (0 if gather else 1) | (2 if serial else 0)
+        self._ck(self._lib.reth_replay_step_loop(self._h, int(steps), int(batch), pp, up,
+                                                 int(seed) & (2**64 - 1), float(alpha), float(beta),
+                                                 flags, self._s(stream)))
+        self._keep = (pk, uk)

@@ -1,0 +1,207 @@
+"""GPU parity: the CUDA shard (through the C ABI) against the oracle and the
+golden vectors of the reference.  Bit-exact for indices, leaf values, sums and
+mins (float64, same operation order); IS weights within 1e-5 relative
+(north_star tolerance; CUDA pow vs libm pow); transform within 1e-5 relative."""
+import hashlib
+
+import numpy as np
+import pytest
+
+from oracle import per_oracle as po
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-5
+
+
+def _sha(a):
+    return np.frombuffer(hashlib.sha256(np.ascontiguousarray(a).tobytes()).digest(), np.uint8)
+
+
+@pytest.fixture(scope="module")
+def Shard():
+    import __graft_entry__ as entry
+    entry.build()
+    from reth_b200 import ReplayShard
+    return ReplayShard
+
+
+def _replay_tape(Shard, g, prefix="", fill_p=None, cluster=0):
+    cap, batch = int(g[prefix + "cap"]), int(g[prefix + "batch"])
+    sh = Shard(cap, [], max_batch=max(batch, 64), store_rows=False, update_cluster=cluster)
+    fill_idx = g[prefix + "fill_idx"]
+    fill_p = g[prefix + "fill_p"] if fill_p is None else fill_p
+    for s in range(0, len(fill_idx), 64):
+        sh.update(fill_idx[s:s + 64], fill_p[s:s + 64], transform=False)
+    for t in range(len(g[prefix + "u"])):
+        sh.sample(batch, beta=0.4, uniforms=g[prefix + "u"][t], slot=t % 2)
+        _, idx, w = sh.slot_read(t % 2)
+        assert np.array_equal(idx, g[prefix + "idx"][t]), f"{prefix} step {t}"
+        total, mn = sh.root()
+        root = g[prefix + "root"][t]
+        assert total == root[0] and mn == root[1]
+        wref = (g[prefix + "val"][t] / root[1]) ** (-0.4)
+        assert np.allclose(w, wref, rtol=RTOL, atol=0)
+        sh.update(idx, g[prefix + "newp"][t], transform=False)
+    return sh
+
+
+@pytest.mark.parametrize("name", ["tree_cap1000_full", "tree_cap4096_sparse"])
+@pytest.mark.parametrize("cluster", [1, 8])
+def test_golden_tape_full_arrays(Shard, golden, name, cluster):
+    g = golden(name)
+    sh = _replay_tape(Shard, g, cluster=cluster)
+    s, m, v = sh.tree_arrays()
+    assert np.array_equal(v, g["valarr"])
+    assert np.array_equal(s, g["sum"])
+    assert np.array_equal(m, g["min"])     # includes the untouched-node / seed-1 quirk
+    sh.close()
+
+
+def test_golden_edge_capacities(Shard, golden):
+    g = golden("tree_edges")
+    for cap in g["caps"]:
+        pre = f"c{cap}_"
+        sh = _replay_tape(Shard, g, pre)
+        s, m, v = sh.tree_arrays()
+        assert np.array_equal(s, g[pre + "sum"]), cap
+        assert np.array_equal(m, g[pre + "min"]), cap
+        sh.close()
+
+
+def test_golden_heavy_tail_cap100000(Shard, golden):
+    g = golden("tree_cap100000_heavy")
+    rng = np.random.default_rng(int(g["seed"]))
+    n = 100000
+    fill_p = np.abs(rng.standard_normal(n)) * (1 + 9 * (rng.random(n) < 0.05)) + 1e-4
+    sh = _replay_tape(Shard, g, fill_p=fill_p)
+    s, m, v = sh.tree_arrays()
+    assert np.array_equal(_sha(s), g["sum_sha"])
+    assert np.array_equal(_sha(m), g["min_sha"])
+    assert np.array_equal(_sha(v), g["val_sha"])
+    sh.close()
+
+
+def test_golden_cfg1_per_sampler(Shard, golden):
+    """BASELINE config 1 shape through the PERSampler path (float32 |TD| in)."""
+    g = golden("per_cfg1_cap65536")
+    cap, B = int(g["cap"]), int(g["batch"])
+    struct = [(np.float32, (4,)), (np.int64, ()), (np.float32, ()), (np.float32, (4,)), (np.float32, ())]
+    sh = Shard(cap, struct, max_batch=B)
+    rng = np.random.default_rng(0)
+    cols = [rng.standard_normal((cap, 4)).astype(np.float32), rng.integers(0, 2, cap),
+            rng.standard_normal(cap).astype(np.float32), rng.standard_normal((cap, 4)).astype(np.float32),
+            np.zeros(cap, np.float32)]
+    for s in range(0, cap, 64):
+        first = sh.append([c[s:s + 64] for c in cols], g["fill_w"][s:s + 64], alpha=0.6)
+        assert first == s                     # slot == arrival order (test_rb.py:27-29)
+    _, _, v = sh.tree_arrays()
+    p32 = g["fill_p32"].astype(np.float64)
+    assert np.allclose(v, p32, rtol=RTOL, atol=0)          # transform gate
+    exact = np.mean(v == p32)
+    assert exact > 0.999, exact                            # correctly rounded float32 pow
+    # index parity is defined for identical leaves: inject the reference's
+    sh.update(np.arange(cap), p32, transform=False)
+    for t in range(len(g["u"])):
+        sh.sample(B, beta=0.4, uniforms=g["u"][t])
+        sh.gather(0)
+        data, idx, w = sh.slot_read(0, with_rows=True)
+        assert np.array_equal(idx, g["idx"][t])
+        assert np.allclose(w, g["w"][t], rtol=RTOL, atol=0)
+        for c in range(5):
+            assert np.array_equal(data[c], cols[c][idx].astype(data[c].dtype))
+        total, mn = sh.root()
+        assert total == g["root"][t][0] and mn == g["root"][t][1]
+        sh.update(idx, g["newp32"][t].astype(np.float64), transform=False)
+    s, m, v = sh.tree_arrays()
+    assert np.array_equal(_sha(s), g["sum_sha"])
+    assert np.array_equal(_sha(m), g["min_sha"])
+    assert np.array_equal(_sha(v), g["val_sha"])
+    sh.close()
+
+
+def test_schedule_golden_weights(Shard, golden):
+    """beta schedule 0.4 -> 1 (test/apex-dqn/config.yaml:27) feeding the fused IS weights."""
+    from reth_b200.sampler import Schedule
+    g = golden("schedule_per")
+    sh = Shard(2048, [], max_batch=32, store_rows=False)
+    sh.update(np.arange(2048), g["per_fill"], transform=False)
+    beta = Schedule.from_str("0.4,1,2000")
+    for t in range(len(g["per_u"])):
+        sh.sample(32, beta=beta.value(), uniforms=g["per_u"][t])
+        _, idx, w = sh.slot_read(0)
+        assert np.array_equal(idx, g["per_idx"][t])
+        assert np.allclose(w, g["per_w"][t], rtol=RTOL, atol=0)
+        for _ in range(60):
+            beta.step()
+    sh.close()
+
+
+@pytest.mark.parametrize("cap,B", [(1 << 16, 64), (1 << 20, 512), ((1 << 20) + 12345, 8192), (1 << 22, 2048)])
+def test_random_tape_vs_oracle(Shard, cap, B):
+    """Seeded tapes at BASELINE sizes: duplicates inside batches, sparse then full trees."""
+    rng = np.random.default_rng(cap % 1000 + B)
+    sh = Shard(cap, [], max_batch=B, store_rows=False)
+    ref = po.OracleSumTree(cap)
+    heavy = lambda n: np.abs(rng.standard_normal(n)) * (1 + 9 * (rng.random(n) < 0.05)) + 1e-3  # noqa: E731
+    # sparse arbitrary slots first (untouched-node min semantics), with explicit duplicates
+    idx = rng.integers(0, cap, 5000)
+    idx[100:200] = idx[0:100]
+    p = heavy(5000) + 1.0
+    sh.update(idx, p, transform=False)
+    ref.update(idx, p)
+    s, m, v = sh.tree_arrays()
+    assert np.array_equal(v, ref._val) and np.array_equal(s, ref._sum) and np.array_equal(m, ref._min)
+    # FIFO fill of everything (tree-only append: iota slots)
+    for st in range(0, cap, 1 << 18):
+        n = min(1 << 18, cap - st)
+        pw = heavy(n)
+        first = sh.append([], pw, transform=False)
+        assert first == st
+        ref.update(np.arange(st, st + n), pw)
+    for t in range(12):
+        u = rng.random(B)
+        sh.sample(B, beta=0.7, uniforms=u, slot=t % 2)
+        _, gi, gw = sh.slot_read(t % 2)
+        ri, rv = ref.sample(B, u)
+        assert np.array_equal(gi, ri), t
+        assert np.allclose(gw, po.is_weights(rv, ref.min(0), 0.7), rtol=RTOL, atol=0)
+        newp = heavy(B)
+        if t % 3 == 0:
+            sh.update_slot(t % 2, newp, transform=False)
+        else:
+            sh.update(gi if t % 3 == 1 else gi.astype(np.int32), newp, transform=False)
+        ref.update(ri, newp)
+        assert sh.root() == (ref.sum(), ref.min(0))
+    s, m, v = sh.tree_arrays()
+    assert np.array_equal(v, ref._val) and np.array_equal(s, ref._sum) and np.array_equal(m, ref._min)
+    sh.close()
+
+
+def test_transform_dtypes(Shard):
+    rng = np.random.default_rng(9)
+    sh = Shard(4096, [], max_batch=64, store_rows=False)
+    w32 = np.abs(rng.standard_normal(4096)).astype(np.float32)
+    sh.update(np.arange(4096), w32, alpha=0.5)
+    _, _, v = sh.tree_arrays()
+    assert np.allclose(v, po.normalize_weights(w32, 0.5), rtol=RTOL, atol=0)
+    w64 = np.abs(rng.standard_normal(4096))
+    sh.update(np.arange(4096), w64, alpha=0.6)
+    _, _, v = sh.tree_arrays()
+    assert np.allclose(v, po.normalize_weights(w64, 0.6), rtol=1e-12, atol=0)
+    sh.close()
+
+
+def test_errors(Shard):
+    from reth_b200 import ReplayError
+    sh = Shard(100, [(np.float32, (3,))], max_batch=16)
+    with pytest.raises(AssertionError):
+        sh.append([np.zeros((4, 3), np.float32)], np.ones(5, np.float32))
+    with pytest.raises(ReplayError):
+        sh.append([np.zeros((101, 3), np.float32)], np.ones(101, np.float32))   # > capacity
+    with pytest.raises(ReplayError):
+        sh.sample(17)
+    sh.update(np.array([5, 100]), np.ones(2), transform=False)                  # 100 is out of range
+    with pytest.raises(ReplayError, match="outside"):
+        sh.tree_arrays()
+    sh.close()
