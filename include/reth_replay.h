@@ -176,10 +176,19 @@ int reth_replay_slot_meta(reth_replay_t *h, int slot, int64_t *first_count, void
  *      frame gather on two internal streams joined to `stream` at both ends, slots used
  *      round-robin.  prio_dev: device float32[steps*batch] new |TD| priorities;
  *      uniforms_dev: device double[steps*batch] or NULL (device generator).
- *      flags bit0: skip gather (tree only); bit1: serialise everything on one stream. */
+ *      flags bit0: skip gather (tree only); bit1: serialise everything on one stream;
+ *      bit2: bracket every gather launch with CUDA events on its own stream (see gather_time);
+ *      bit3 / bit4: skip the sample / the update launch (kernel micro-timing only). */
 int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, const float *prio_dev,
                           const double *uniforms_dev, uint64_t seed, double alpha, double beta,
                           int flags, void *stream);
+/* Sum of the event-bracketed gather launch durations recorded since the last call
+ * (step_loop flag bit2), and how many launches that covers.  Synchronises the device. */
+int reth_replay_gather_time(reth_replay_t *h, double *total_ms, int64_t *launches);
+
+/* Diagnostic only: SM-clock stamps (int64[32]) of the stage boundaries of the last
+ * tree-repair launch; needs RETH_DEBUG_TIMING=1 in the environment at create time. */
+int reth_replay_debug_stamps(reth_replay_t *h, int64_t *out);
 
 #ifdef __cplusplus
 }

@@ -84,6 +84,8 @@ SIGNATURES = {
     "reth_replay_sample_global": [_vp, _i32, _vp, _i32, _i32, _vp, _i32, _u64, _f64, _i32, _vp],
     "reth_replay_slot_meta": [_vp, _i32, C.POINTER(_i64), _vp],
     "reth_replay_step_loop": [_vp, _i32, _i32, _vp, _vp, _u64, _f64, _f64, _i32, _vp],
+    "reth_replay_gather_time": [_vp, C.POINTER(_f64), C.POINTER(_i64)],
+    "reth_replay_debug_stamps": [_vp, C.POINTER(_i64)],
 }
 
 _lib = None

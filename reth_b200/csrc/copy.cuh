@@ -99,7 +99,6 @@ struct RowArgs {
     int32_t narrow_groups;     // ceil(batch / kCopyThreads) when narrow columns exist
     // scatter only: last-writer-wins arbitration (same stamps as the tree update)
     const uint32_t *stamp;
-    uint32_t stamp_base;
     int64_t capacity;
     int32_t *err;
 };
@@ -123,7 +122,7 @@ __global__ void __launch_bounds__(kCopyThreads, 6) row_move_kernel(const RowArgs
             if (row >= rows) continue;
             const int64_t slot = a.idx[row];
             if (slot < 0 || slot >= a.capacity) { if (threadIdx.x == 0) atomicOr(a.err, 1); continue; }
-            if (kScatter && a.stamp && a.stamp[slot] != a.stamp_base + 1u + (uint32_t)row) continue;
+            if (kScatter && a.stamp && a.stamp[slot] != 1u + (uint32_t)row) continue;
             const int64_t upr = col.rb >> 4;
             const int64_t u0 = (int64_t)chunk * col.units;
             const int64_t n = min((int64_t)col.units, upr - u0);
@@ -154,7 +153,7 @@ __global__ void __launch_bounds__(kCopyThreads, 6) row_move_kernel(const RowArgs
             if (row >= rows) continue;
             const int64_t slot = a.idx[row];
             if (slot < 0 || slot >= a.capacity) { atomicOr(a.err, 1); continue; }
-            if (kScatter && a.stamp && a.stamp[slot] != a.stamp_base + 1u + (uint32_t)row) continue;
+            if (kScatter && a.stamp && a.stamp[slot] != 1u + (uint32_t)row) continue;
             for (int c = 0; c < a.ncols; ++c) {
                 const RowCol &col = a.col[c];
                 if (col.chunks != 0) continue;

@@ -41,7 +41,6 @@ struct reth_replay {
     uint32_t *stamp = nullptr, *mask = nullptr;
     int32_t *worklist = nullptr, *counts = nullptr /*[2][kMaxTileLevels]*/, *err = nullptr;
     int64_t max_n = 0;            // largest n of one update launch
-    uint32_t stamp_base = 0;
     int counts_flip = 0;
     uint64_t draw_counter = 0;
     // staging for host-resident arguments
@@ -58,6 +57,9 @@ struct reth_replay {
     std::vector<cudaEvent_t> ev_sampled, ev_gathered;
     cudaEvent_t ev_fork = nullptr, ev_join_t = nullptr, ev_join_g = nullptr;
     int update_cluster = 8;
+    long long *dbg = nullptr;           // RETH_DEBUG_TIMING=1: stage clocks of the last update launch
+    std::vector<cudaEvent_t> ev_time;   // pairs (start, stop) around timed gather launches
+    size_t ev_time_used = 0;
     std::string error;
 };
 
@@ -105,6 +107,7 @@ void free_all(reth_replay *h)
 {
     cudaFree(h->desc); cudaFree(h->agg); cudaFree(h->stamp); cudaFree(h->mask);
     cudaFree(h->worklist); cudaFree(h->counts); cudaFree(h->err);
+    cudaFree(h->dbg);
     cudaFree(h->stage_idx); cudaFree(h->stage_prio); cudaFree(h->stage_u);
     if (h->host_pin) cudaFreeHost(h->host_pin);
     for (int c = 0; c < kMaxCols; ++c) cudaFree(h->ring[c]);
@@ -114,6 +117,7 @@ void free_all(reth_replay *h)
     }
     for (auto e : h->ev_sampled) cudaEventDestroy(e);
     for (auto e : h->ev_gathered) cudaEventDestroy(e);
+    for (auto e : h->ev_time) cudaEventDestroy(e);
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
     if (h->ev_join_t) cudaEventDestroy(h->ev_join_t);
     if (h->ev_join_g) cudaEventDestroy(h->ev_join_g);
@@ -183,6 +187,7 @@ RETH_EXPORT int reth_replay_create(const reth_replay_config *cfg, reth_replay_t 
     CKC(cudaMalloc(&h->stage_prio, h->max_n * 8));
     CKC(cudaMalloc((void **)&h->stage_u, (size_t)cfg->max_batch * 8));
     CKC(cudaMallocHost((void **)&h->host_pin, 64 * sizeof(int64_t)));
+    if (getenv("RETH_DEBUG_TIMING")) CKC(dalloc_zero(&h->dbg, 32, acct));
     if (cfg->store_rows)
         for (int c = 0; c < cfg->n_columns; ++c) {
             CKC(cudaMalloc((void **)&h->ring[c], (size_t)cfg->capacity * cfg->row_bytes[c]));
@@ -251,15 +256,7 @@ int launch_update(reth_replay *h, UpdateArgs &a, cudaStream_t s)
 {
     if (a.n <= 0) return RETH_OK;
     a.g = h->geom; a.desc = h->desc; a.agg = h->agg; a.stamp = h->stamp; a.mask = h->mask;
-    a.worklist = h->worklist; a.err = h->err; a.max_n = h->max_n;
-    if (a.dedupe) {
-        if ((uint64_t)h->stamp_base + (uint64_t)a.n + 2ull >= 0xffffffffull) {
-            CK(h, cudaMemsetAsync(h->stamp, 0, (size_t)h->cfg.capacity * sizeof(uint32_t), s));
-            h->stamp_base = 0;
-        }
-        a.stamp_base = h->stamp_base;
-        h->stamp_base += (uint32_t)a.n;
-    }
+    a.worklist = h->worklist; a.err = h->err; a.max_n = h->max_n; a.dbg = h->dbg;
     a.counts = h->counts + h->counts_flip * kMaxTileLevels;
     a.counts_next = h->counts + (h->counts_flip ^ 1) * kMaxTileLevels;
     h->counts_flip ^= 1;
@@ -322,7 +319,6 @@ RETH_EXPORT int reth_replay_clear(reth_replay_t *h, void *stream)
     CK(h, cudaMemsetAsync(h->mask, 0, nt * sizeof(uint32_t), s));
     CK(h, cudaMemsetAsync(h->stamp, 0, (size_t)h->cfg.capacity * sizeof(uint32_t), s));
     CK(h, cudaMemsetAsync(h->counts, 0, 2 * kMaxTileLevels * sizeof(int32_t), s));
-    h->stamp_base = 0;
     h->tail = 0;
     h->size = 0;
     return RETH_OK;
@@ -426,7 +422,7 @@ RETH_EXPORT int reth_replay_update_slot(reth_replay_t *h, int slot, const void *
     if (b.batch <= 0) return fail(h, RETH_ERR_STATE, "slot %d holds no sampled batch", slot);
     UpdateArgs a = {};
     a.n = b.batch; a.idx = b.idx; a.idx_kind = 0;
-    a.alpha = alpha; a.transform = transform; a.dedupe = 1;
+    a.alpha = alpha; a.transform = transform; a.dedupe = 2;   // own stratified draw: duplicates are adjacent
     int rc = set_prio(h, a, prio, prio_dtype, prio_loc, 0, b.batch, S(stream));
     if (rc) return rc;
     rc = launch_update(h, a, S(stream));
@@ -580,11 +576,12 @@ RETH_EXPORT int reth_replay_append_at(reth_replay_t *h, const int64_t *slots, in
     cudaStream_t s = S(stream);
     UpdateArgs a = {};
     a.n = n; a.idx_kind = 0; a.alpha = alpha; a.transform = transform; a.dedupe = 1;
+    a.keep_stamps = 1;
     int rc = to_device(h, slots, slots_loc, n * 8, h->stage_idx, s, &a.idx);
     if (rc) return rc;
     rc = set_prio(h, a, prio, prio_dtype, prio_loc, 0, n, s);
     if (rc) return rc;
-    rc = launch_update(h, a, s);   // also arbitrates duplicates: stamp[slot] == base+1+i for the winner
+    rc = launch_update(h, a, s);   // also arbitrates duplicates: stamp[slot] == 1+i for the winner
     if (rc) return rc;
     if (h->cfg.store_rows && h->cfg.n_columns > 0) {
         if (!cols) return fail(h, RETH_ERR_INVALID, "cols is null");
@@ -595,10 +592,13 @@ RETH_EXPORT int reth_replay_append_at(reth_replay_t *h, const int64_t *slots, in
         RowArgs r;
         build_row_args(h, r, src, (const int64_t *)a.idx, (int)n);
         r.stamp = h->stamp;
-        r.stamp_base = a.stamp_base;
         rc = launch_row_move<true>(h, r, s);
         if (rc) return rc;
     }
+    stamp_clear_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(h->stamp, (const int64_t *)a.idx, n,
+                                                                  h->cfg.capacity);
+    CK(h, cudaGetLastError());
+    h->st.kernel_launches++;
     h->st.appended_rows += n;
     h->size = (h->size + n < h->cfg.capacity) ? h->size + n : h->cfg.capacity;
     h->st.size = h->size;
@@ -727,7 +727,8 @@ RETH_EXPORT int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, co
     if (steps < 0 || !prio_dev) return fail(h, RETH_ERR_INVALID, "bad step_loop arguments");
     DeviceGuard guard(h->cfg.device);
     cudaStream_t s = S(stream);
-    const bool no_gather = flags & 1, serial = flags & 2;
+    const bool no_gather = flags & 1, serial = flags & 2, timed = flags & 4;
+    const bool no_sample = flags & 8, no_update = flags & 16;   // kernel micro-timing only
     const int depth = (int)h->slots.size();
     cudaStream_t st = serial ? s : h->s_tree, sg = serial ? s : h->s_gather;
     if (!serial) {
@@ -739,7 +740,9 @@ RETH_EXPORT int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, co
         const int slot = k % depth;
         // the slot's index buffer is re-drawn: its previous gather must have consumed it
         if (!serial && !no_gather && k >= depth) CK(h, cudaStreamWaitEvent(st, h->ev_gathered[slot], 0));
-        int rc = do_sample(h, batch, uniforms_dev ? uniforms_dev + (size_t)k * batch : nullptr, RETH_DEVICE,
+        int rc = RETH_OK;
+        if (!no_sample || h->slots[slot].batch != batch)
+            rc = do_sample(h, batch, uniforms_dev ? uniforms_dev + (size_t)k * batch : nullptr, RETH_DEVICE,
                            seed, beta, slot, nullptr, 1, 0, st);
         if (rc) return rc;
         if (!no_gather) {
@@ -747,14 +750,27 @@ RETH_EXPORT int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, co
                 CK(h, cudaEventRecord(h->ev_sampled[slot], st));
                 CK(h, cudaStreamWaitEvent(sg, h->ev_sampled[slot], 0));
             }
+            if (timed) {
+                while (h->ev_time.size() < h->ev_time_used + 2) {
+                    cudaEvent_t e;
+                    CK(h, cudaEventCreate(&e));
+                    h->ev_time.push_back(e);
+                }
+                CK(h, cudaEventRecord(h->ev_time[h->ev_time_used], sg));
+            }
             rc = do_gather(h, slot, false, sg);
             if (rc) return rc;
+            if (timed) {
+                CK(h, cudaEventRecord(h->ev_time[h->ev_time_used + 1], sg));
+                h->ev_time_used += 2;
+            }
             if (!serial) CK(h, cudaEventRecord(h->ev_gathered[slot], sg));
         }
+        if (no_update) continue;
         UpdateArgs a = {};
         a.n = batch; a.idx = h->slots[slot].idx; a.idx_kind = 0;
         a.prio = prio_dev + (size_t)k * batch; a.prio_kind = 0;
-        a.alpha = alpha; a.transform = 1; a.dedupe = 1;
+        a.alpha = alpha; a.transform = 1; a.dedupe = 2;
         rc = launch_update(h, a, st);
         if (rc) return rc;
         h->st.updated_rows += batch;
@@ -765,5 +781,34 @@ RETH_EXPORT int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, co
         CK(h, cudaStreamWaitEvent(s, h->ev_join_t, 0));
         CK(h, cudaStreamWaitEvent(s, h->ev_join_g, 0));
     }
+    return RETH_OK;
+}
+
+RETH_EXPORT int reth_replay_gather_time(reth_replay_t *h, double *total_ms, int64_t *launches)
+{
+    if (!h) return RETH_ERR_INVALID;
+    DeviceGuard guard(h->cfg.device);
+    CK(h, cudaDeviceSynchronize());
+    double tot = 0;
+    for (size_t i = 0; i + 1 < h->ev_time_used; i += 2) {
+        float ms = 0;
+        CK(h, cudaEventElapsedTime(&ms, h->ev_time[i], h->ev_time[i + 1]));
+        tot += ms;
+    }
+    if (total_ms) *total_ms = tot;
+    if (launches) *launches = (int64_t)(h->ev_time_used / 2);
+    h->ev_time_used = 0;
+    return RETH_OK;
+}
+
+// Diagnostic: SM-clock stamps of the stage boundaries of the last update launch
+// (only with RETH_DEBUG_TIMING=1 in the environment at create time). out: int64[32].
+RETH_EXPORT int reth_replay_debug_stamps(reth_replay_t *h, int64_t *out)
+{
+    if (!h || !out) return RETH_ERR_INVALID;
+    if (!h->dbg) return fail(h, RETH_ERR_STATE, "RETH_DEBUG_TIMING was not set at create time");
+    DeviceGuard guard(h->cfg.device);
+    CK(h, cudaDeviceSynchronize());
+    CK(h, cudaMemcpy(out, h->dbg, 32 * sizeof(int64_t), cudaMemcpyDeviceToHost));
     return RETH_OK;
 }

@@ -222,9 +222,12 @@ struct UpdateArgs {
     int32_t prio_kind;    // 0 float32[], 1 float64[], 2 constant 1.0 (raw)
     double alpha;
     int32_t transform;
-    uint32_t stamp_base;
-    int32_t dedupe;
+    int32_t keep_stamps;  // leave the winners' stamps in place (policy-slot scatter reads them)
+    int32_t dedupe;       // 0 none (distinct slots), 1 stamps (arbitrary order), 2 adjacent runs
+    long long *dbg;       // optional: SM-clock stamps of stage boundaries (CTA 0, thread 0)
 };
+
+#define RETH_STAMP(k) do { if (a.dbg && brank == 0 && threadIdx.x == 0) a.dbg[k] = clock64(); } while (0)
 
 __device__ __forceinline__ int64_t upd_index(const UpdateArgs &a, int64_t i)
 {
@@ -248,8 +251,20 @@ __device__ __forceinline__ double upd_leaf(const UpdateArgs &a, int64_t i)
     return a.transform ? pow(w + 1e-6, a.alpha) : w;
 }
 
-// Recompute the touched nodes of one tile bottom-up (5 levels in registers).
-__device__ __forceinline__ void repair_tile(const UpdateArgs &a, int64_t tile, int T, int lane)
+__device__ __forceinline__ double2 maintain_node(double v, const double2 &Lc, const double2 &Rc)
+{
+    // _numba_maintain_node, utils/sumtree.py:5-21 ((val + sum_l) + sum_r; min skips zeros)
+    double s = v + Lc.x;
+    s = s + Rc.x;
+    double mn = (v != 0.0) ? v : 1.0;
+    if (Lc.y != 0.0) mn = (Lc.y < mn) ? Lc.y : mn;
+    if (Rc.y != 0.0) mn = (Rc.y < mn) ? Rc.y : mn;
+    return make_double2(s, mn);
+}
+
+// Warp-cooperative repair of one tile with an arbitrary touched mask (several paths):
+// lane = node, 5 levels bottom-up through register shuffles.
+__device__ __forceinline__ void repair_tile_warp(const UpdateArgs &a, int64_t tile, int T, int lane)
 {
     double2 ag = ldcg2(&a.agg[tile * 64 + lane]);
     const double2 ex = ldcg2(&a.agg[tile * 64 + 32 + lane]);
@@ -260,20 +275,14 @@ __device__ __forceinline__ void repair_tile(const UpdateArgs &a, int64_t tile, i
     for (int l = 4; l >= 0; --l) {
         const int src = ((l == 4) ? 2 * (lane - 16) : 2 * lane) & 31;
         const double sx = (l == 4) ? ex.x : ag.x, sy = (l == 4) ? ex.y : ag.y;
-        const double Lx = __shfl_sync(0xffffffffu, sx, src);
-        const double Ly = __shfl_sync(0xffffffffu, sy, src);
-        const double Rx = __shfl_sync(0xffffffffu, sx, src | 1);
-        const double Ry = __shfl_sync(0xffffffffu, sy, src | 1);
+        double2 Lc, Rc;
+        Lc.x = __shfl_sync(0xffffffffu, sx, src);
+        Lc.y = __shfl_sync(0xffffffffu, sy, src);
+        Rc.x = __shfl_sync(0xffffffffu, sx, src | 1);
+        Rc.y = __shfl_sync(0xffffffffu, sy, src | 1);
         if (touched && (lane >> l) == 1) {
-            // _numba_maintain_node, utils/sumtree.py:5-21
-            double s = de.y + Lx;
-            s = s + Rx;
-            double mn = (de.y != 0.0) ? de.y : 1.0;
-            if (Ly != 0.0) mn = (Ly < mn) ? Ly : mn;
-            if (Ry != 0.0) mn = (Ry < mn) ? Ry : mn;
-            ag.x = s;
-            ag.y = mn;
-            de.x = Lx;
+            ag = maintain_node(de.y, Lc, Rc);
+            de.x = Lc.x;
         }
     }
     if (touched) {
@@ -282,73 +291,275 @@ __device__ __forceinline__ void repair_tile(const UpdateArgs &a, int64_t tile, i
     }
     if (lane == 1 && T > 0) {
         const int64_t rel = tile - tile_base(T);
-        const int64_t parent = tile_base(T - 1) + (rel >> 5);
-        __stcg(&a.agg[parent * 64 + 32 + (rel & 31)], ag);
+        __stcg(&a.agg[(tile_base(T - 1) + (rel >> 5)) * 64 + 32 + (rel & 31)], ag);
     }
     if (lane == 0) __stcg(&a.mask[tile], 0u);
 }
 
+// One THREAD repairs one tile whose touched set is a single root-ward chain (the
+// common case below the top levels): every load address follows from the deepest
+// touched node, so all (<= 11) loads are issued together and the <= 5 node
+// recomputations run in registers.  32 tiles per warp instead of one.
+__device__ __forceinline__ void repair_tile_chain(const UpdateArgs &a, int64_t tile, uint32_t m, int T)
+{
+    const int j = 31 - __clz(m);      // deepest touched node (1-based position in the tile)
+    const int r = 31 - __clz(j);      // its depth inside the tile, 0..4
+    const double2 *ag = a.agg + tile * 64;
+    double2 *dsc = a.desc + tile * 32;
+    double v[5];
+    double2 sib[5];
+#pragma unroll
+    for (int l = 0; l < 5; ++l) {
+        if (l > r) continue;
+        const int p = j >> (r - l);
+        v[l] = __ldcg(&dsc[p].y);
+        if (l > 0) sib[l] = ldcg2(&ag[p ^ 1]);
+    }
+    const int c = (r == 4) ? 32 + 2 * (j - 16) : 2 * j;   // children of the deepest node
+    const double2 c0 = ldcg2(&ag[c]), c1 = ldcg2(&ag[c + 1]);
+    double2 cur = make_double2(0.0, 0.0);
+#pragma unroll
+    for (int l = 4; l >= 0; --l) {
+        if (l > r) continue;
+        const int p = j >> (r - l);
+        double2 Lc, Rc;
+        if (l == r) { Lc = c0; Rc = c1; }
+        else {
+            const bool left = (((j >> (r - l - 1)) & 1) == 0);   // is the path child the left child?
+            Lc = left ? cur : sib[l + 1];
+            Rc = left ? sib[l + 1] : cur;
+        }
+        cur = maintain_node(v[l], Lc, Rc);
+        __stcg(&a.agg[tile * 64 + p], cur);
+        __stcg(&dsc[p].x, Lc.x);
+    }
+    if (T > 0) {
+        const int64_t rel = tile - tile_base(T);
+        __stcg(&a.agg[(tile_base(T - 1) + (rel >> 5)) * 64 + 32 + (rel & 31)], cur);
+    }
+    __stcg(&a.mask[tile], 0u);
+}
+
+// Tile levels 0 and 1 (heap depths 0..9, <= 1023 nodes) swept by one CTA in shared
+// memory, one __syncthreads per tree level.  A node is recomputed when its own mask
+// bit is set (it was written by this batch) or a child has ever been maintained
+// (child min != 0, which _numba_maintain_node guarantees for every node it visited):
+// its ancestors were maintained then too, so recomputing them is idempotent.  Deep
+// paths therefore need no marking atomics on the two top tile levels.
+__device__ __forceinline__ void repair_top(const UpdateArgs &a)
+{
+    __shared__ double sS[2048], sM[2048], sV[1024];
+    __shared__ uint8_t sK[1024];
+    const int NT = a.g.n_tile_levels;
+    const int D = (NT >= 2) ? 10 : 5;                    // tree levels in the sweep
+    const int nn = 1 << D;                                // nodes are heap k = 1 .. nn-1
+    const int64_t n1 = (NT >= 2) ? ((a.g.n_tiles - 1 < 32) ? a.g.n_tiles - 1 : 32) : 0;
+    // 2*nn <= 2048 entries over 512 threads: 4 per thread, all loads issued before any use
+    double2 g[4];
+    double v[4];
+    uint32_t mk[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const int k = threadIdx.x + q * kUpdateThreads;
+        g[q] = make_double2(0.0, 0.0);
+        v[q] = 0.0;
+        mk[q] = 0u;
+        if (k >= 2 * nn) continue;
+        if (k >= 1 && k < nn) {
+            const int d = 31 - __clz(k);
+            const int64_t tile = (d < 5) ? 0 : 1 + ((k >> (d - 5)) - 32);
+            const int local = (d < 5) ? k : ((1 << (d - 5)) | (k & ((1 << (d - 5)) - 1)));
+            if (tile <= n1) {
+                g[q] = ldcg2(&a.agg[tile * 64 + local]);
+                v[q] = __ldcg(&a.desc[tile * 32 + local].y);
+                mk[q] = (__ldcg(&a.mask[tile]) >> local) & 1u;
+            }
+        } else if (k >= nn) {                             // children of the last swept level
+            const int64_t tile = (NT >= 2) ? 1 + ((k >> 5) - 32) : 0;
+            if (tile <= n1) g[q] = ldcg2(&a.agg[tile * 64 + 32 + (k & 31)]);
+        }
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const int k = threadIdx.x + q * kUpdateThreads;
+        if (k >= 2 * nn) continue;
+        sS[k] = g[q].x;
+        sM[k] = g[q].y;
+        if (k < nn) { sV[k] = v[q]; sK[k] = (uint8_t)mk[q]; }
+    }
+    __syncthreads();
+    for (int l = D - 1; l >= 0; --l) {
+        for (int k = (1 << l) + threadIdx.x; k < (2 << l); k += kUpdateThreads) {
+            const double2 Lc = make_double2(sS[2 * k], sM[2 * k]), Rc = make_double2(sS[2 * k + 1], sM[2 * k + 1]);
+            if (sK[k] || Lc.y != 0.0 || Rc.y != 0.0) {
+                const double2 res = maintain_node(sV[k], Lc, Rc);
+                sS[k] = res.x;
+                sM[k] = res.y;
+                sK[k] = 2;
+            }
+        }
+        __syncthreads();
+    }
+    for (int k = 1 + threadIdx.x; k < nn; k += kUpdateThreads) {
+        if (sK[k] != 2) continue;
+        const int d = 31 - __clz(k);
+        const int64_t tile = (d < 5) ? 0 : 1 + ((k >> (d - 5)) - 32);
+        const int local = (d < 5) ? k : ((1 << (d - 5)) | (k & ((1 << (d - 5)) - 1)));
+        const double2 res = make_double2(sS[k], sM[k]);
+        __stcg(&a.agg[tile * 64 + local], res);
+        __stcg(&a.desc[tile * 32 + local].x, sS[2 * k]);
+        if (d == 5) __stcg(&a.agg[32 + (k - 32)], res);  // root of a level-1 tile: copy in tile 0
+    }
+    if (threadIdx.x <= n1) __stcg(&a.mask[threadIdx.x], 0u);
+}
+
 // Batched priority write-back with tree-path repair (utils/sumtree.py:61-67,
-// 24-31).  One thread-block cluster; phases are separated by cluster barriers:
-//   P0 stamp   : atomicMax(stamp[idx], base+1+i)  -> the last i of a duplicate wins
-//   P1 leaves  : winners write val, mark their path bits per tile; the first marker
-//                of a tile owns it and queues it on that tile level's worklist
-//   R  repair  : tile levels deepest -> root, one warp per owned tile
+// 24-31).  One thread-block cluster; stages separated by cluster barriers:
+//   P0 stamp  : atomicMax(stamp[idx], 1+i) -> the last i of a duplicate index wins
+//   P1 leaves : winners write val.  For tile levels >= 2 they OR their path bits into
+//               the per-tile masks (all atomics of a path issued together); the first
+//               marker of a tile owns it: worklist[T][i] = tile (else -1).  A leaf that
+//               itself lives in tile level 0/1 only sets its own mask bit.
+//   R  repair : tile levels deepest -> 2 (skipped when nobody owns a tile there); a
+//               lane takes one owned tile: single-chain tiles are repaired by that
+//               thread alone, multi-path tiles by the whole warp; cluster barrier
+//   TOP       : tile levels 1 and 0 by CTA 0 in shared memory (repair_top)
 // The result equals the reference's sequential loop because sum/min are pure
 // functions of the final leaves on the union of touched paths.
 __global__ void __launch_bounds__(kUpdateThreads) per_update_kernel(const UpdateArgs a)
 {
     cg::cluster_group cluster = cg::this_cluster();
-    const int64_t tid = cluster.thread_rank();
-    const int64_t nthr = cluster.num_threads();
+    const int nblk = (int)cluster.num_blocks(), brank = (int)cluster.block_rank();
+    const int64_t nthr = (int64_t)nblk * kUpdateThreads;
+    // consecutive work items are spread over the CTAs of the cluster
+    const int64_t L = (int64_t)threadIdx.x * nblk + brank;
     const int64_t cap = a.g.capacity;
+    const int lane = threadIdx.x & 31;
+    const int NT = a.g.n_tile_levels;
 
-    if (tid < kMaxTileLevels) a.counts_next[tid] = 0;
-    if (a.dedupe) {
-        for (int64_t i = tid; i < a.n; i += nthr) {
+    RETH_STAMP(0);
+    if (brank == 0 && threadIdx.x < kMaxTileLevels) a.counts_next[threadIdx.x] = 0;
+    if (a.dedupe == 1) {
+        for (int64_t i = L; i < a.n; i += nthr) {
             const int64_t idx = upd_index(a, i);
             if (idx < 0 || idx >= cap) { atomicOr(a.err, 1); continue; }
-            atomicMax(&a.stamp[idx], a.stamp_base + 1u + (uint32_t)i);
+            atomicMax(&a.stamp[idx], 1u + (uint32_t)i);
         }
+        RETH_STAMP(1);
         cluster.sync();
     }
-    for (int64_t i = tid; i < a.n; i += nthr) {
-        const int64_t idx = upd_index(a, i);
-        if (idx < 0 || idx >= cap) { atomicOr(a.err, 1); continue; }
-        if (a.dedupe && __ldcg(&a.stamp[idx]) != a.stamp_base + 1u + (uint32_t)i) continue;
-        const NodeLoc n = locate(idx);
-        __stcg(&a.desc[n.tile * 32 + n.local].y, upd_leaf(a, i));
-        // own tile, then every ancestor tile (entered at its bottom row)
-        int64_t tile = n.tile;
-        int local = n.local, r = n.r;
-        uint64_t kroot = ((uint64_t)idx + 1ull) >> n.r;   // heap k of the tile root
-        for (int T = n.T; T >= 0; --T) {
-            uint32_t bits = 0;
-            for (int j = 0; j <= r; ++j) bits |= 1u << (local >> (r - j));
-            const uint32_t old = atomicOr(&a.mask[tile], bits);
-            if (old == 0u) {
-                const int s = atomicAdd(&a.counts[T], 1);
-                a.worklist[(int64_t)T * a.max_n + s] = (int32_t)tile;
+    RETH_STAMP(2);
+    const int64_t iters = (a.n + nthr - 1) / nthr;      // warp-uniform trip count (ballots inside)
+    for (int64_t it = 0; it < iters; ++it) {
+        const int64_t i = it * nthr + L;
+        const bool inrange = i < a.n;
+        bool active = inrange;
+        int64_t idx = 0;
+        if (active) {
+            idx = upd_index(a, i);
+            if (idx < 0 || idx >= cap) { atomicOr(a.err, 1); active = false; }
+        }
+        uint32_t st = 0;
+        if (active && a.dedupe == 1) st = __ldcg(&a.stamp[idx]);
+        // dedupe 2: indices drawn by per_sample_kernel.  Stratified targets are monotone and
+        // _numba_find_index is a monotone step function of its target, so equal indices are
+        // always adjacent: the last element of a run is the sequential loop's last writer.
+        if (active && a.dedupe == 2 && i + 1 < a.n && upd_index(a, i + 1) == idx) active = false;
+        const double leaf = active ? upd_leaf(a, i) : 0.0;       // pow overlaps the stamp load
+        if (active && a.dedupe == 1) {
+            if (st != 1u + (uint32_t)i) active = false;
+            else if (!a.keep_stamps) __stcg(&a.stamp[idx], 0u);   // stamps are zero between launches
+        }
+        int64_t tiles[kMaxTileLevels];
+        uint32_t old[kMaxTileLevels];
+        int Tn = -1;
+        if (active) {
+            const NodeLoc n = locate(idx);
+            Tn = n.T;
+            __stcg(&a.desc[n.tile * 32 + n.local].y, leaf);
+            if (Tn <= 1) {
+                atomicOr(&a.mask[n.tile], 1u << n.local);         // own bit; ancestors are derived
+            } else {
+                uint32_t bits[kMaxTileLevels];
+                int64_t tile = n.tile;
+                int local = n.local, r = n.r;
+                uint64_t kroot = ((uint64_t)idx + 1ull) >> n.r;   // heap k of the tile root
+#pragma unroll
+                for (int T = kMaxTileLevels - 1; T >= 2; --T) {
+                    if (T > Tn) continue;
+                    uint32_t b = 0;
+                    for (int j = 0; j <= r; ++j) b |= 1u << (local >> (r - j));
+                    tiles[T] = tile;
+                    bits[T] = b;
+                    // parent of the tile root is a bottom-row node of the parent tile
+                    const uint64_t kp = kroot >> 1;
+                    local = 16 | (int)(kp & 15ull);
+                    r = 4;
+                    kroot = kp >> 4;
+                    tile = tile_base(T - 1) + (int64_t)(kroot - (1ull << (5 * (T - 1))));
+                }
+#pragma unroll
+                for (int T = kMaxTileLevels - 1; T >= 2; --T)
+                    if (T <= Tn) old[T] = atomicOr(&a.mask[tiles[T]], bits[T]);
             }
-            if (T == 0) break;
-            // parent of the tile root is a bottom-row node of the parent tile
-            const uint64_t kp = kroot >> 1;               // heap k, depth 5T-1
-            local = 16 | (int)(kp & 15ull);
-            r = 4;
-            kroot = kp >> 4;
-            tile = tile_base(T - 1) + (int64_t)(kroot - (1ull << (5 * (T - 1))));
+        }
+#pragma unroll
+        for (int T = kMaxTileLevels - 1; T >= 2; --T) {
+            if (T >= NT) continue;                                // uniform
+            const bool own = active && T <= Tn && old[T] == 0u;
+            if (inrange) a.worklist[(int64_t)T * a.max_n + i] = own ? (int32_t)tiles[T] : -1;
+            const unsigned bal = __ballot_sync(0xffffffffu, own);
+            if (bal != 0u && lane == __ffs(bal) - 1) atomicOr(&a.counts[T], 1);   // level has work
         }
     }
+    RETH_STAMP(3);
     cluster.sync();
+    RETH_STAMP(4);
 
-    const int lane = threadIdx.x & 31;
-    const int64_t warp = tid >> 5, nwarps = nthr >> 5;
-    for (int T = a.g.n_tile_levels - 1; T >= 0; --T) {
-        const int cnt = __ldcg(&a.counts[T]);
-        for (int64_t wi = warp; wi < cnt; wi += nwarps)
-            repair_tile(a, (int64_t)__ldcg(&a.worklist[(int64_t)T * a.max_n + wi]), T, lane);
-        if (T > 0) cluster.sync();
+    const int64_t warp = (int64_t)(threadIdx.x >> 5) * nblk + brank, nwarps = nthr >> 5;
+    // entry e of a level's worklist goes to lane (e / nwarps) of warp (e % nwarps): the owned
+    // tiles are spread thinly so that multi-path tiles rarely queue up inside one warp
+    const int64_t e0 = (int64_t)lane * nwarps + warp;
+    int flag[kMaxTileLevels], first_tile[kMaxTileLevels];
+#pragma unroll
+    for (int T = 2; T < kMaxTileLevels; ++T) {                    // one round trip, issued together
+        flag[T] = (T < NT) ? __ldcg(&a.counts[T]) : 0;
+        first_tile[T] = (T < NT && e0 < a.n) ? __ldcg(&a.worklist[(int64_t)T * a.max_n + e0]) : -1;
     }
+#pragma unroll
+    for (int T = kMaxTileLevels - 1; T >= 2; --T) {
+        if (flag[T] == 0) continue;                               // uniform over the cluster
+        for (int64_t base = 0; base < a.n; base += 32 * nwarps) {
+            const int64_t e = base + e0;
+            int32_t t = -1;
+            if (base == 0) t = first_tile[T];
+            else if (e < a.n) t = __ldcg(&a.worklist[(int64_t)T * a.max_n + e]);
+            uint32_t m = 0;
+            if (t >= 0) m = __ldcg(&a.mask[t]);
+            const bool chain = t >= 0 && __popc(m) == (31 - __clz(31 - __clz(m | 1u))) + 1 && m != 0u;
+            if (chain) repair_tile_chain(a, (int64_t)t, m, T);
+            unsigned rest = __ballot_sync(0xffffffffu, t >= 0 && !chain);
+            while (rest) {
+                const int src = __ffs(rest) - 1;
+                rest &= rest - 1;
+                repair_tile_warp(a, (int64_t)__shfl_sync(0xffffffffu, t, src), T, lane);
+            }
+        }
+        RETH_STAMP(5 + 2 * (T - 2));
+        cluster.sync();
+        RETH_STAMP(6 + 2 * (T - 2));
+    }
+    if (brank != 0) return;
+    RETH_STAMP(20);
+    repair_top(a);
+    RETH_STAMP(22);
+}
+
+// Zero the arbitration stamps of `n` slots (after a policy-slot scatter that needed them).
+__global__ void stamp_clear_kernel(uint32_t *stamp, const int64_t *slots, int64_t n, int64_t cap)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n && slots[i] >= 0 && slots[i] < cap) stamp[slots[i]] = 0u;
 }
 
 // ---------------------------------------------------------------- readback --
