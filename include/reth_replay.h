@@ -131,6 +131,20 @@ int reth_replay_sample(reth_replay_t *h, int batch, const double *uniforms, int 
  *      rows ring[c][indices[i]] -> contiguous batch column c of slot `slot`. */
 int reth_replay_gather(reth_replay_t *h, int slot, void *stream);
 
+/* ---- prefetch groups: the reference pre-samples (sampler HWM 1, sampler_loop.py:14) and its
+ *      loader keeps a ring of batches in flight (TorchCudaLoader buffer_size, torch_cuda_loader.py:70),
+ *      so batch k+1..k+G are drawn before update k lands.  These calls do that for n_slots
+ *      consecutive slots in ONE launch each (batch must equal max_batch when n_slots > 1):
+ *      n_slots independent stratified draws from the same tree state; one gather over
+ *      n_slots*batch rows; one write-back of n_slots*batch priorities (sequential semantics
+ *      over the concatenation, i.e. a later slot wins a duplicate). uniforms_dev: device
+ *      double[n_slots*batch] or NULL; prio: n_slots*batch values. */
+int reth_replay_sample_multi(reth_replay_t *h, int batch, int first_slot, int n_slots,
+                             const double *uniforms_dev, uint64_t seed, double beta, void *stream);
+int reth_replay_gather_multi(reth_replay_t *h, int first_slot, int n_slots, void *stream);
+int reth_replay_update_slots(reth_replay_t *h, int first_slot, int n_slots, const void *prio,
+                             int prio_dtype, int prio_loc, double alpha, int transform, void *stream);
+
 /* Device pointers of a batch slot (lent, as TorchCudaLoader lends ring slots,
  * torch_cuda_loader.py:152-163).  Any out pointer may be NULL. */
 int reth_replay_slot_ptrs(reth_replay_t *h, int slot, void **cols_out /*[n_columns]*/,
@@ -178,7 +192,9 @@ int reth_replay_slot_meta(reth_replay_t *h, int slot, int64_t *first_count, void
  *      uniforms_dev: device double[steps*batch] or NULL (device generator).
  *      flags bit0: skip gather (tree only); bit1: serialise everything on one stream;
  *      bit2: bracket every gather launch with CUDA events on its own stream (see gather_time);
- *      bit3 / bit4: skip the sample / the update launch (kernel micro-timing only). */
+ *      bit3 / bit4: skip the sample / the update launch (kernel micro-timing only);
+ *      bits 8..15: prefetch group G (0/1 = strict alternation): sample_multi / gather_multi /
+ *      update_slots over G slots per iteration (steps must be a multiple of G). */
 int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, const float *prio_dev,
                           const double *uniforms_dev, uint64_t seed, double alpha, double beta,
                           int flags, void *stream);

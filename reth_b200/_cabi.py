@@ -73,6 +73,9 @@ SIGNATURES = {
     "reth_replay_update_slot": [_vp, _i32, _vp, _i32, _i32, _f64, _i32, _vp],
     "reth_replay_sample": [_vp, _i32, _vp, _i32, _u64, _f64, _i32, _vp],
     "reth_replay_gather": [_vp, _i32, _vp],
+    "reth_replay_sample_multi": [_vp, _i32, _i32, _i32, _vp, _u64, _f64, _vp],
+    "reth_replay_gather_multi": [_vp, _i32, _i32, _vp],
+    "reth_replay_update_slots": [_vp, _i32, _i32, _vp, _i32, _i32, _f64, _i32, _vp],
     "reth_replay_slot_ptrs": [_vp, _i32, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp),
                               C.POINTER(_vp), C.POINTER(C.c_int32)],
     "reth_replay_slot_read": [_vp, _i32, _vp, _vp, _vp, _vp],

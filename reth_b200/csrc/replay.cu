@@ -49,6 +49,11 @@ struct reth_replay {
     int64_t *host_pin = nullptr;  // small pinned scratch (err/meta readback)
     // ring + batch slots
     uint8_t *ring[kMaxCols] = {};
+    // batch slots are carved from contiguous arrays so that G consecutive slots form one
+    // G*max_batch batch (group mode)
+    uint8_t *slot_cols[kMaxCols] = {};
+    int64_t *slot_idx = nullptr, *slot_meta = nullptr;
+    double *slot_w = nullptr, *slot_prio = nullptr;
     std::vector<BatchSlot> slots;
     int64_t tail = 0, size = 0;
     reth_replay_stats st{};
@@ -111,10 +116,8 @@ void free_all(reth_replay *h)
     cudaFree(h->stage_idx); cudaFree(h->stage_prio); cudaFree(h->stage_u);
     if (h->host_pin) cudaFreeHost(h->host_pin);
     for (int c = 0; c < kMaxCols; ++c) cudaFree(h->ring[c]);
-    for (auto &s : h->slots) {
-        for (int c = 0; c < kMaxCols; ++c) cudaFree(s.cols[c]);
-        cudaFree(s.idx); cudaFree(s.w); cudaFree(s.prio); cudaFree(s.meta);
-    }
+    for (int c = 0; c < kMaxCols; ++c) cudaFree(h->slot_cols[c]);
+    cudaFree(h->slot_idx); cudaFree(h->slot_w); cudaFree(h->slot_prio); cudaFree(h->slot_meta);
     for (auto e : h->ev_sampled) cudaEventDestroy(e);
     for (auto e : h->ev_gathered) cudaEventDestroy(e);
     for (auto e : h->ev_time) cudaEventDestroy(e);
@@ -194,16 +197,24 @@ RETH_EXPORT int reth_replay_create(const reth_replay_config *cfg, reth_replay_t 
             *acct += cfg->capacity * cfg->row_bytes[c];
         }
     h->slots.resize(h->cfg.ring_depth);
-    for (auto &s : h->slots) {
-        if (cfg->store_rows)
-            for (int c = 0; c < cfg->n_columns; ++c) {
-                CKC(cudaMalloc((void **)&s.cols[c], (size_t)cfg->max_batch * cfg->row_bytes[c]));
-                *acct += (int64_t)cfg->max_batch * cfg->row_bytes[c];
-            }
-        CKC(dalloc_zero(&s.idx, (size_t)cfg->max_batch, acct));
-        CKC(dalloc_zero(&s.w, (size_t)cfg->max_batch, acct));
-        CKC(dalloc_zero(&s.prio, (size_t)cfg->max_batch, acct));
-        CKC(dalloc_zero(&s.meta, 2, acct));
+    const size_t depth = (size_t)h->cfg.ring_depth, mb = (size_t)cfg->max_batch;
+    if (cfg->store_rows)
+        for (int c = 0; c < cfg->n_columns; ++c) {
+            CKC(cudaMalloc((void **)&h->slot_cols[c], depth * mb * cfg->row_bytes[c]));
+            *acct += (int64_t)(depth * mb * cfg->row_bytes[c]);
+        }
+    CKC(dalloc_zero(&h->slot_idx, depth * mb, acct));
+    CKC(dalloc_zero(&h->slot_w, depth * mb, acct));
+    CKC(dalloc_zero(&h->slot_prio, depth * mb, acct));
+    CKC(dalloc_zero(&h->slot_meta, depth * 2, acct));
+    for (size_t i = 0; i < depth; ++i) {
+        BatchSlot &s = h->slots[i];
+        for (int c = 0; c < cfg->n_columns; ++c)
+            s.cols[c] = h->slot_cols[c] ? h->slot_cols[c] + i * mb * cfg->row_bytes[c] : nullptr;
+        s.idx = h->slot_idx + i * mb;
+        s.w = h->slot_w + i * mb;
+        s.prio = h->slot_prio + i * mb;
+        s.meta = h->slot_meta + i * 2;
     }
     int lo = 0, hi = 0;
     CKC(cudaDeviceGetStreamPriorityRange(&lo, &hi));
@@ -490,11 +501,16 @@ int launch_row_move(reth_replay *h, const RowArgs &a, cudaStream_t s)
 }
 
 int do_sample(reth_replay *h, int batch, const double *uniforms, int uniforms_loc, uint64_t seed,
-              double beta, int slot, const double *all_roots, int n_shards, int shard, cudaStream_t s)
+              double beta, int slot, const double *all_roots, int n_shards, int shard, cudaStream_t s,
+              int groups = 1)
 {
     if (slot_ok(h, slot)) return RETH_ERR_INVALID;
     if (batch < 1 || batch > h->cfg.max_batch)
         return fail(h, RETH_ERR_INVALID, "batch %d outside [1, max_batch=%d]", batch, h->cfg.max_batch);
+    if (groups < 1 || slot + groups > (int)h->slots.size())
+        return fail(h, RETH_ERR_INVALID, "slots %d..%d outside the batch ring", slot, slot + groups - 1);
+    if (groups > 1 && (n_shards > 1 || batch != h->cfg.max_batch || (uniforms && uniforms_loc != RETH_DEVICE)))
+        return fail(h, RETH_ERR_INVALID, "multi-slot sampling: single shard, batch == max_batch, device uniforms");
     BatchSlot &b = h->slots[slot];
     SampleArgs a = {};
     a.g = h->geom; a.desc = h->desc; a.agg = h->agg; a.batch = batch;
@@ -505,29 +521,45 @@ int do_sample(reth_replay *h, int batch, const double *uniforms, int uniforms_lo
         a.uniforms = (const double *)u;
     }
     a.seed = seed; a.draw_base = h->draw_counter;
-    h->draw_counter += (uint64_t)batch;
+    h->draw_counter += (uint64_t)batch * groups;
+    a.groups = groups; a.out_stride = h->cfg.max_batch;
     a.beta = beta; a.min_mode = h->cfg.min_mode;
     a.idx_out = b.idx; a.w_out = b.w; a.prio_out = b.prio; a.meta = b.meta;
     a.all_roots = all_roots; a.n_shards = n_shards; a.shard = shard;
     const int wpb = 4;
-    per_sample_kernel<<<(batch + wpb - 1) / wpb, wpb * 32, 0, s>>>(a);
+    per_sample_kernel<<<(batch * groups + wpb - 1) / wpb, wpb * 32, 0, s>>>(a);
     CK(h, cudaGetLastError());
     h->st.kernel_launches++;
-    h->st.sampled_rows += batch;
-    b.batch = batch;
+    h->st.sampled_rows += (int64_t)batch * groups;
+    for (int g = 0; g < groups; ++g) h->slots[slot + g].batch = batch;
     return RETH_OK;
 }
 
-int do_gather(reth_replay *h, int slot, bool use_meta, cudaStream_t s)
+// groups > 1: slots slot..slot+groups-1 hold full batches (batch == max_batch), i.e. one
+// contiguous groups*batch index array and one contiguous output per column
+int do_gather(reth_replay *h, int slot, bool use_meta, cudaStream_t s, int groups = 1)
 {
     BatchSlot &b = h->slots[slot];
     if (!h->cfg.store_rows || h->cfg.n_columns == 0) return RETH_OK;
     RowArgs a;
-    build_row_args(h, a, b.cols, b.idx, b.batch);
-    a.meta = use_meta ? b.meta : nullptr;
+    build_row_args(h, a, b.cols, b.idx, b.batch * groups);
+    a.meta = (use_meta && groups == 1) ? b.meta : nullptr;
     int rc = launch_row_move<false>(h, a, s);
     if (rc) return rc;
-    h->st.gathered_rows += b.batch;
+    h->st.gathered_rows += (int64_t)b.batch * groups;
+    return RETH_OK;
+}
+
+int group_ok(reth_replay *h, int first_slot, int n_slots)
+{
+    if (n_slots < 1 || first_slot < 0 || first_slot + n_slots > (int)h->slots.size())
+        return fail(h, RETH_ERR_INVALID, "slots %d..%d outside the batch ring", first_slot, first_slot + n_slots - 1);
+    for (int g = 0; g < n_slots; ++g) {
+        const BatchSlot &b = h->slots[first_slot + g];
+        if (b.batch <= 0) return fail(h, RETH_ERR_STATE, "slot %d holds no sampled batch", first_slot + g);
+        if (n_slots > 1 && b.batch != h->cfg.max_batch)
+            return fail(h, RETH_ERR_STATE, "multi-slot calls need batch == max_batch");
+    }
     return RETH_OK;
 }
 
@@ -561,6 +593,43 @@ RETH_EXPORT int reth_replay_gather(reth_replay_t *h, int slot, void *stream)
     if (h->slots[slot].batch <= 0) return fail(h, RETH_ERR_STATE, "slot %d holds no sampled batch", slot);
     DeviceGuard guard(h->cfg.device);
     return do_gather(h, slot, true, S(stream));
+}
+
+RETH_EXPORT int reth_replay_sample_multi(reth_replay_t *h, int batch, int first_slot, int n_slots,
+                                         const double *uniforms_dev, uint64_t seed, double beta, void *stream)
+{
+    if (!h) return RETH_ERR_INVALID;
+    DeviceGuard guard(h->cfg.device);
+    return do_sample(h, batch, uniforms_dev, RETH_DEVICE, seed, beta, first_slot, nullptr, 1, 0, S(stream), n_slots);
+}
+
+RETH_EXPORT int reth_replay_gather_multi(reth_replay_t *h, int first_slot, int n_slots, void *stream)
+{
+    if (!h) return RETH_ERR_INVALID;
+    if (group_ok(h, first_slot, n_slots)) return h->error.find("holds no") != std::string::npos ? RETH_ERR_STATE : RETH_ERR_INVALID;
+    DeviceGuard guard(h->cfg.device);
+    return do_gather(h, first_slot, true, S(stream), n_slots);
+}
+
+RETH_EXPORT int reth_replay_update_slots(reth_replay_t *h, int first_slot, int n_slots, const void *prio,
+                                         int prio_dtype, int prio_loc, double alpha, int transform, void *stream)
+{
+    if (!h) return RETH_ERR_INVALID;
+    if (group_ok(h, first_slot, n_slots)) return h->error.find("holds no") != std::string::npos ? RETH_ERR_STATE : RETH_ERR_INVALID;
+    DeviceGuard guard(h->cfg.device);
+    const int64_t n = (int64_t)h->slots[first_slot].batch * n_slots;
+    if (n > h->max_n) return fail(h, RETH_ERR_INVALID, "group of %lld rows exceeds %lld", (long long)n, (long long)h->max_n);
+    UpdateArgs a = {};
+    a.n = n; a.idx = h->slots[first_slot].idx; a.idx_kind = 0;
+    a.alpha = alpha; a.transform = transform;
+    // one draw: duplicates adjacent; several draws: the same slot may recur anywhere -> stamps
+    a.dedupe = n_slots == 1 ? 2 : 1;
+    int rc = set_prio(h, a, prio, prio_dtype, prio_loc, 0, n, S(stream));
+    if (rc) return rc;
+    rc = launch_update(h, a, S(stream));
+    if (rc) return rc;
+    h->st.updated_rows += n;
+    return RETH_OK;
 }
 
 RETH_EXPORT int reth_replay_append_at(reth_replay_t *h, const int64_t *slots, int slots_loc,
@@ -730,20 +799,25 @@ RETH_EXPORT int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, co
     const bool no_gather = flags & 1, serial = flags & 2, timed = flags & 4;
     const bool no_sample = flags & 8, no_update = flags & 16;   // kernel micro-timing only
     const int depth = (int)h->slots.size();
+    int G = (flags >> 8) & 0xff;                      // batches per tree launch (prefetch group)
+    if (G < 1) G = 1;
+    if (G > 1 && (batch != h->cfg.max_batch || depth % G != 0 || depth < 2 * G || steps % G != 0 ||
+                  (int64_t)G * batch > h->max_n))
+        return fail(h, RETH_ERR_INVALID, "group %d needs batch == max_batch, ring_depth a multiple >= 2*group, steps %% group == 0", G);
     cudaStream_t st = serial ? s : h->s_tree, sg = serial ? s : h->s_gather;
     if (!serial) {
         CK(h, cudaEventRecord(h->ev_fork, s));
         CK(h, cudaStreamWaitEvent(st, h->ev_fork, 0));
         CK(h, cudaStreamWaitEvent(sg, h->ev_fork, 0));
     }
-    for (int k = 0; k < steps; ++k) {
+    for (int k = 0; k < steps; k += G) {
         const int slot = k % depth;
-        // the slot's index buffer is re-drawn: its previous gather must have consumed it
+        // the slots' index buffers are re-drawn: their previous gather must have consumed them
         if (!serial && !no_gather && k >= depth) CK(h, cudaStreamWaitEvent(st, h->ev_gathered[slot], 0));
         int rc = RETH_OK;
         if (!no_sample || h->slots[slot].batch != batch)
             rc = do_sample(h, batch, uniforms_dev ? uniforms_dev + (size_t)k * batch : nullptr, RETH_DEVICE,
-                           seed, beta, slot, nullptr, 1, 0, st);
+                           seed, beta, slot, nullptr, 1, 0, st, G);
         if (rc) return rc;
         if (!no_gather) {
             if (!serial) {
@@ -758,7 +832,7 @@ RETH_EXPORT int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, co
                 }
                 CK(h, cudaEventRecord(h->ev_time[h->ev_time_used], sg));
             }
-            rc = do_gather(h, slot, false, sg);
+            rc = do_gather(h, slot, false, sg, G);
             if (rc) return rc;
             if (timed) {
                 CK(h, cudaEventRecord(h->ev_time[h->ev_time_used + 1], sg));
@@ -768,12 +842,12 @@ RETH_EXPORT int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, co
         }
         if (no_update) continue;
         UpdateArgs a = {};
-        a.n = batch; a.idx = h->slots[slot].idx; a.idx_kind = 0;
+        a.n = (int64_t)batch * G; a.idx = h->slots[slot].idx; a.idx_kind = 0;
         a.prio = prio_dev + (size_t)k * batch; a.prio_kind = 0;
-        a.alpha = alpha; a.transform = 1; a.dedupe = 2;
+        a.alpha = alpha; a.transform = 1; a.dedupe = G == 1 ? 2 : 1;
         rc = launch_update(h, a, st);
         if (rc) return rc;
-        h->st.updated_rows += batch;
+        h->st.updated_rows += (int64_t)batch * G;
     }
     if (!serial) {
         CK(h, cudaEventRecord(h->ev_join_t, st));

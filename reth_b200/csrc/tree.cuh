@@ -27,7 +27,7 @@
 namespace reth {
 namespace cg = cooperative_groups;
 
-constexpr int kMaxTileLevels = 8;
+constexpr int kMaxTileLevels = 7;   // capacity <= 2^31 -> heap depth <= 31 -> tile levels 0..6
 constexpr int kUpdateThreads = 512;
 
 struct TreeGeom {
@@ -101,6 +101,8 @@ struct SampleArgs {
     int64_t *meta;             // {first, count}
     const double *all_roots;   // global mode: double[2*n_shards]
     int32_t n_shards, shard;
+    int32_t groups;            // independent stratified draws of `batch` in one launch (>= 1)
+    int32_t out_stride;        // elements between the outputs of consecutive draws
 };
 
 __device__ __forceinline__ double draw_u(const SampleArgs &a, int64_t i)
@@ -133,8 +135,9 @@ __device__ __forceinline__ int64_t lower_bound_target(const SampleArgs &a, doubl
 __global__ void __launch_bounds__(256) per_sample_kernel(const SampleArgs a)
 {
     const int lane = threadIdx.x & 31;
-    const int64_t i = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (i >= a.batch) return;
+    const int64_t W = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (W >= (int64_t)a.batch * a.groups) return;
+    const int64_t grp = W / a.batch, i = W - grp * a.batch;   // draw `grp`, stratum i
     const int64_t cap = a.g.capacity;
 
     double total, pmin, prefix = 0.0;
@@ -162,10 +165,10 @@ __global__ void __launch_bounds__(256) per_sample_kernel(const SampleArgs a)
         total = root.x;
         if (a.min_mode == 0) pmin = (root.x != 0.0) ? root.y : 1.0;   // utils/sumtree.py:109-110
         else pmin = (root.y != 0.0) ? root.y : 1.0;                   // reth/buffer/sumtree.py:112-113
-        if (i == 0 && lane == 0) { a.meta[0] = 0; a.meta[1] = a.batch; }
+        if (i == 0 && lane == 0) { a.meta[2 * grp] = 0; a.meta[2 * grp + 1] = a.batch; }
     }
     const double segment = total / (double)a.batch;                  // sumtree.py:73
-    double w = ((double)i + draw_u(a, i)) * segment;                 // sumtree.py:74
+    double w = ((double)i + draw_u(a, W)) * segment;                 // sumtree.py:74
     w -= prefix;                                                      // 0.0 for a single shard
 
     int64_t idx = 0, tile = 0, tile_rel = 0;
@@ -196,7 +199,7 @@ __global__ void __launch_bounds__(256) per_sample_kernel(const SampleArgs a)
         tile = tile_base(T) + tile_rel;
     }
     if (lane == 0) {
-        const int64_t o = i - first;
+        const int64_t o = grp * a.out_stride + i - first;
         a.idx_out[o] = idx;
         a.prio_out[o] = val;
         a.w_out[o] = pow(val / pmin, -a.beta);      // per_sampler.py:26
@@ -241,14 +244,20 @@ __device__ __forceinline__ int64_t upd_index(const UpdateArgs &a, int64_t i)
 __device__ __forceinline__ double upd_leaf(const UpdateArgs &a, int64_t i)
 {
     if (a.prio_kind == 2) return 1.0;                    // prioritized_buffer.py:36-37
-    if (a.prio_kind == 0) {
+    const bool f32 = a.prio_kind == 0;
+    double base, expo = a.alpha;
+    if (f32) {
         const float w = ((const float *)a.prio)[i];
         if (!a.transform) return (double)w;
-        const float x = w + 1e-6f;
-        return (double)(float)pow((double)x, (double)(float)a.alpha);
+        base = (double)(w + 1e-6f);
+        expo = (double)(float)a.alpha;
+    } else {
+        const double w = ((const double *)a.prio)[i];
+        if (!a.transform) return w;
+        base = w + 1e-6;
     }
-    const double w = ((const double *)a.prio)[i];
-    return a.transform ? pow(w + 1e-6, a.alpha) : w;
+    const double r = pow(base, expo);                    // one call site keeps the kernel small
+    return f32 ? (double)(float)r : r;
 }
 
 __device__ __forceinline__ double2 maintain_node(double v, const double2 &Lc, const double2 &Rc)
@@ -387,6 +396,7 @@ __device__ __forceinline__ void repair_top(const UpdateArgs &a)
         sM[k] = g[q].y;
         if (k < nn) { sV[k] = v[q]; sK[k] = (uint8_t)mk[q]; }
     }
+    if (a.dbg && threadIdx.x == 0) a.dbg[23] = clock64();
     __syncthreads();
     for (int l = D - 1; l >= 0; --l) {
         for (int k = (1 << l) + threadIdx.x; k < (2 << l); k += kUpdateThreads) {
@@ -400,6 +410,7 @@ __device__ __forceinline__ void repair_top(const UpdateArgs &a)
         }
         __syncthreads();
     }
+    if (a.dbg && threadIdx.x == 0) a.dbg[24] = clock64();
     for (int k = 1 + threadIdx.x; k < nn; k += kUpdateThreads) {
         if (sK[k] != 2) continue;
         const int d = 31 - __clz(k);
@@ -465,7 +476,9 @@ __global__ void __launch_bounds__(kUpdateThreads) per_update_kernel(const Update
         // _numba_find_index is a monotone step function of its target, so equal indices are
         // always adjacent: the last element of a run is the sequential loop's last writer.
         if (active && a.dedupe == 2 && i + 1 < a.n && upd_index(a, i + 1) == idx) active = false;
+        if (it == 0) RETH_STAMP(11);
         const double leaf = active ? upd_leaf(a, i) : 0.0;       // pow overlaps the stamp load
+        if (it == 0) RETH_STAMP(12);
         if (active && a.dedupe == 1) {
             if (st != 1u + (uint32_t)i) active = false;
             else if (!a.keep_stamps) __stcg(&a.stamp[idx], 0u);   // stamps are zero between launches
@@ -503,13 +516,14 @@ __global__ void __launch_bounds__(kUpdateThreads) per_update_kernel(const Update
                     if (T <= Tn) old[T] = atomicOr(&a.mask[tiles[T]], bits[T]);
             }
         }
+        if (it == 0) RETH_STAMP(13);
 #pragma unroll
         for (int T = kMaxTileLevels - 1; T >= 2; --T) {
             if (T >= NT) continue;                                // uniform
             const bool own = active && T <= Tn && old[T] == 0u;
             if (inrange) a.worklist[(int64_t)T * a.max_n + i] = own ? (int32_t)tiles[T] : -1;
             const unsigned bal = __ballot_sync(0xffffffffu, own);
-            if (bal != 0u && lane == __ffs(bal) - 1) atomicOr(&a.counts[T], 1);   // level has work
+            if (bal != 0u && lane == __ffs(bal) - 1) atomicOr(&a.counts[0], 1 << T);   // level has work
         }
     }
     RETH_STAMP(3);
@@ -520,24 +534,20 @@ __global__ void __launch_bounds__(kUpdateThreads) per_update_kernel(const Update
     // entry e of a level's worklist goes to lane (e / nwarps) of warp (e % nwarps): the owned
     // tiles are spread thinly so that multi-path tiles rarely queue up inside one warp
     const int64_t e0 = (int64_t)lane * nwarps + warp;
-    int flag[kMaxTileLevels], first_tile[kMaxTileLevels];
-#pragma unroll
-    for (int T = 2; T < kMaxTileLevels; ++T) {                    // one round trip, issued together
-        flag[T] = (T < NT) ? __ldcg(&a.counts[T]) : 0;
-        first_tile[T] = (T < NT && e0 < a.n) ? __ldcg(&a.worklist[(int64_t)T * a.max_n + e0]) : -1;
-    }
-#pragma unroll
-    for (int T = kMaxTileLevels - 1; T >= 2; --T) {
-        if (flag[T] == 0) continue;                               // uniform over the cluster
+    const int flags = __ldcg(&a.counts[0]);                       // bit T: somebody owns a tile at level T
+#pragma unroll 1
+    for (int T = NT - 1; T >= 2; --T) {
+        if (!((flags >> T) & 1)) continue;                        // uniform over the cluster
         for (int64_t base = 0; base < a.n; base += 32 * nwarps) {
             const int64_t e = base + e0;
             int32_t t = -1;
-            if (base == 0) t = first_tile[T];
-            else if (e < a.n) t = __ldcg(&a.worklist[(int64_t)T * a.max_n + e]);
+            if (e < a.n) t = __ldcg(&a.worklist[(int64_t)T * a.max_n + e]);
             uint32_t m = 0;
             if (t >= 0) m = __ldcg(&a.mask[t]);
+            if (m) RETH_STAMP(14 + (T & 1));
             const bool chain = t >= 0 && __popc(m) == (31 - __clz(31 - __clz(m | 1u))) + 1 && m != 0u;
             if (chain) repair_tile_chain(a, (int64_t)t, m, T);
+            RETH_STAMP(16 + (T & 1));
             unsigned rest = __ballot_sync(0xffffffffu, t >= 0 && !chain);
             while (rest) {
                 const int src = __ffs(rest) - 1;

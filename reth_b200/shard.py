@@ -230,6 +230,24 @@ class ReplayShard:
                                                      float(beta), int(slot), self._s(stream)))
         self._keep = (rkeep, ukeep)
 
+    def sample_multi(self, batch, first_slot, n_slots, beta=0.4, uniforms_dev=None, seed=0, stream=None):
+        """n_slots independent stratified draws in one launch (prefetch group)."""
+        up, uloc, udt, cnt, ukeep = _ptr_loc(uniforms_dev)
+        if uniforms_dev is not None:
+            assert uloc == DEVICE and udt == np.dtype(np.float64) and cnt >= batch * n_slots
+        self._ck(self._lib.reth_replay_sample_multi(self._h, int(batch), int(first_slot), int(n_slots), up,
+                                                    int(seed) & (2**64 - 1), float(beta), self._s(stream)))
+        self._keep = ukeep
+
+    def gather_multi(self, first_slot, n_slots, stream=None):
+        self._ck(self._lib.reth_replay_gather_multi(self._h, int(first_slot), int(n_slots), self._s(stream)))
+
+    def update_slots(self, first_slot, n_slots, prio, alpha=0.6, transform=True, stream=None):
+        p, pdt, ploc, pkeep = self._prio(prio, self.slot_batch(first_slot) * n_slots)
+        self._ck(self._lib.reth_replay_update_slots(self._h, int(first_slot), int(n_slots), p, pdt, ploc,
+                                                    float(alpha), int(bool(transform)), self._s(stream)))
+        self._keep = pkeep
+
     def gather(self, slot=0, stream=None):
         self._ck(self._lib.reth_replay_gather(self._h, int(slot), self._s(stream)))
 
@@ -320,13 +338,13 @@ class ReplayShard:
         return self.stats()["tail"]
 
     def step_loop(self, steps, batch, prio_dev, uniforms_dev=None, seed=0, alpha=0.6, beta=0.4,
-                  gather=True, serial=False, time_gather=False, sample=True, update=True, stream=None):
+                  gather=True, serial=False, time_gather=False, sample=True, update=True, group=1, stream=None):
         pp, ploc, pdt, pcnt, pk = _ptr_loc(prio_dev)
         assert ploc == DEVICE and pdt == np.dtype(np.float32) and pcnt >= steps * batch
         up, uloc, udt, ucnt, uk = _ptr_loc(uniforms_dev)
         if uniforms_dev is not None:
             assert uloc == DEVICE and udt == np.dtype(np.float64) and ucnt >= steps * batch
-        flags = (0 if gather else 1) | (2 if serial else 0) | (4 if time_gather else 0) | (0 if sample else 8) | (0 if update else 16)
+        flags = (0 if gather else 1) | (2 if serial else 0) | (4 if time_gather else 0) | (0 if sample else 8) | (0 if update else 16) | ((int(group) & 0xff) << 8)
         self._ck(self._lib.reth_replay_step_loop(self._h, int(steps), int(batch), pp, up,
                                                  int(seed) & (2**64 - 1), float(alpha), float(beta),
                                                  flags, self._s(stream)))

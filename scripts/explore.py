@@ -8,7 +8,7 @@ from reth_b200 import ReplayShard
 ATARI = [(np.uint8, (4, 84, 84)), (np.int64, ()), (np.float32, ()), (np.uint8, (4, 84, 84)), (np.float32, ())]
 R = 56464
 cap = int(os.environ.get("CAP", 1 << 20)); B = int(os.environ.get("B", 512))
-depth = int(os.environ.get("DEPTH", 4)); cluster = int(os.environ.get("CLUSTER", 8))
+depth = int(os.environ.get("DEPTH", 8)); cluster = int(os.environ.get("CLUSTER", 8))
 sh = ReplayShard(cap, ATARI, max_batch=B, ring_depth=depth, update_cluster=cluster)
 g = torch.Generator(device="cuda").manual_seed(0)
 chunk = 1 << 14
@@ -60,9 +60,10 @@ print(f"gather rotating slots: {g_us:.2f} us -> {2*B*R/g_us/1e3:.0f} GB/s")
 for label, kw in [("sample-only", {"gather": False, "update": False, "serial": True}),
                   ("update-only", {"gather": False, "sample": False, "serial": True}),
                   ("gather-only", {"sample": False, "update": False, "serial": True}),
-                  ("pipelined", {}), ("serial", {"serial": True}), ("tree-only", {"gather": False}), ("pipelined+timed", {"time_gather": True})]:
+                  ("pipelined", {}), ("pipelined g2", {"group": 2}), ("pipelined g4", {"group": 4}),
+                  ("tree-only g4", {"gather": False, "group": 4}), ("gather-only g4", {"sample": False, "update": False, "serial": True, "group": 4}), ("serial", {"serial": True}), ("tree-only", {"gather": False}), ("pipelined+timed", {"time_gather": True})]:
     steps = 1000
-    sh.step_loop(50, B, prio, **kw); torch.cuda.synchronize(); sh.gather_time()
+    sh.step_loop(48, B, prio, **kw); torch.cuda.synchronize(); sh.gather_time()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t = time.perf_counter(); e0.record()
     sh.step_loop(steps, B, prio, **kw)

@@ -207,3 +207,81 @@ def test_errors(Shard):
     with pytest.raises(ReplayError, match="outside"):
         sh.tree_arrays()
     sh.close()
+
+
+@pytest.mark.parametrize("G", [2, 4])
+def test_prefetch_group_vs_oracle(Shard, G):
+    """sample_multi / update_slots: G independent stratified draws from one tree state, then one
+    sequential-semantics write-back of the concatenation (duplicates across draws included)."""
+    import torch
+    cap, B = 200_000, 256
+    rng = np.random.default_rng(40 + G)
+    sh = Shard(cap, [], max_batch=B, ring_depth=2 * G, store_rows=False)
+    ref = po.OracleSumTree(cap)
+    p = np.abs(rng.standard_normal(cap)) + 1e-3
+    p[rng.choice(cap, 40, replace=False)] = 2500.0          # leaves wider than a stratum: duplicates
+    sh.append([], p, transform=False)
+    ref.update(np.arange(cap), p)
+    for t in range(6):
+        first = (t % 2) * G
+        u = rng.random(G * B)
+        sh.sample_multi(B, first, G, beta=0.5, uniforms_dev=torch.from_numpy(u).cuda())
+        ridx = []
+        for g in range(G):
+            _, gi, gw = sh.slot_read(first + g)
+            ri, rv = ref.sample(B, u[g * B:(g + 1) * B])
+            assert np.array_equal(gi, ri), (t, g)
+            assert np.allclose(gw, po.is_weights(rv, ref.min(0), 0.5), rtol=RTOL, atol=0)
+            ridx.append(ri)
+        ridx = np.concatenate(ridx)
+        if t == 0:
+            assert len(np.unique(ridx)) < len(ridx) - B // 4   # duplicates within and across draws
+        newp = np.abs(rng.standard_normal(G * B)) + 1e-3
+        newp[rng.random(G * B) < 0.05] = 2500.0            # keep some leaves wider than a stratum
+        sh.update_slots(first, G, newp, transform=False)
+        ref.update(ridx, newp)
+        assert sh.root() == (ref.sum(), ref.min(0))
+    s, m, v = sh.tree_arrays()
+    assert np.array_equal(v, ref._val) and np.array_equal(s, ref._sum) and np.array_equal(m, ref._min)
+    sh.close()
+
+
+def test_step_loop_matches_stepwise_calls(Shard):
+    """The measured loop (two streams, events) equals the same calls issued one by one."""
+    import torch
+    cap, B, steps = 1 << 16, 128, 24
+    struct = [(np.uint8, (512,)), (np.float32, ())]
+    rng = np.random.default_rng(77)
+    rows = [rng.integers(0, 256, (cap, 512), dtype=np.uint8), rng.standard_normal(cap).astype(np.float32)]
+    w0 = (np.abs(rng.standard_normal(cap)) + 0.01).astype(np.float32)
+    u = torch.from_numpy(rng.random(steps * B)).cuda()
+    prio = torch.from_numpy(np.abs(rng.standard_normal(steps * B)).astype(np.float32)).cuda()
+    out = []
+    for mode in ("loop", "loop_g4", "calls", "calls_g4"):
+        sh = Shard(cap, struct, max_batch=B, ring_depth=8)
+        sh.append(rows, w0, alpha=0.6)
+        G = 4 if mode.endswith("g4") else 1
+        if mode.startswith("loop"):
+            sh.step_loop(steps, B, prio, uniforms_dev=u, alpha=0.6, beta=0.4, group=G)
+        else:
+            for k in range(0, steps, G):
+                slot = k % 8
+                if G == 1:
+                    sh.sample(B, beta=0.4, uniforms=u[k * B:(k + 1) * B], slot=slot)
+                    sh.gather(slot)
+                    sh.update_slot(slot, prio[k * B:(k + 1) * B], alpha=0.6)
+                else:
+                    sh.sample_multi(B, slot, G, beta=0.4, uniforms_dev=u[k * B:(k + G) * B])
+                    sh.gather_multi(slot, G)
+                    sh.update_slots(slot, G, prio[k * B:(k + G) * B], alpha=0.6)
+        torch.cuda.synchronize()
+        last = [sh.slot_read(s, with_rows=True) for s in range(8)]
+        out.append((sh.tree_arrays(), last))
+        for data, idx, _ in last:                               # gathered rows are the ring rows
+            assert np.array_equal(data[0], rows[0][idx]) and np.array_equal(data[1], rows[1][idx])
+        sh.close()
+    for a, b in ((0, 2), (1, 3)):
+        for x, y in zip(out[a][0], out[b][0]):
+            assert np.array_equal(x, y)
+        for (da, ia, wa), (db, ib, wb) in zip(out[a][1], out[b][1]):
+            assert np.array_equal(ia, ib) and np.array_equal(wa, wb) and np.array_equal(da[0], db[0])
