@@ -1,0 +1,401 @@
+#!/usr/bin/env python
+"""Benchmark of the prioritized-experience-replay hot path (BASELINE.json metric):
+sampled transitions/s over  sample B -> gather B rows -> update B priorities.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+N=1 workload = BASELINE.json configs[1]: Atari 84x84x4 uint8 transitions (56 464 B rows),
+PER capacity 2^20 (59.2 GB of frames resident in HBM), batch 512, alpha 0.6, beta 0.4.
+One bench "step" = ITERS consecutive learner iterations (sample+gather+update of one batch
+of 512 each); `value` = sampled transitions / s over the K timed steps.
+
+Keys (see DESIGN.md "Measurement"): value = device-resident loop (reth_replay_step_loop, CUDA
+events on the launching stream, max over ranks); e2e = the public Python API with HOST index /
+priority buffers crossing PCIe every iteration; roofline = the gather kernel against the
+measured HBM copy peak; cpu_baseline = the oracle (a C port of the reference's njit tree + numpy
+ring) on the box's host cores.  --impl reference prints the CPU arm as its own line.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+ATARI = [(np.uint8, (4, 84, 84)), (np.int64, ()), (np.float32, ()), (np.uint8, (4, 84, 84)), (np.float32, ())]
+ROW_BYTES = 28224 + 8 + 4 + 28224 + 4          # 56 464
+ALPHA, BETA = 0.6, 0.4
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+# ------------------------------------------------------------------ clocks --
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled every 200 ms during the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                       "-lms", "200", "-i", str(self.gpu)], stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.p is None:
+            return out
+        time.sleep(0.25)
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        rows = [r.strip().split(",") for r in open(self.f.name) if r.strip()]
+        os.unlink(self.f.name)
+        sm, reasons = [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in rows:
+            r = [x.strip() for x in r]
+            if len(r) < 9:
+                continue
+            try:
+                sm.append(float(r[1]))
+                out["sm_max_mhz"] = float(r[2])
+            except ValueError:
+                continue
+            for n, v in zip(names, r[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        if sm:
+            out["sm_mhz"] = float(np.median(sm))
+        out["reasons"] = sorted(reasons)
+        out["samples"] = len(sm)
+        return out
+
+
+# ------------------------------------------------------------- CPU baseline --
+def cpu_reference_arm(steps, warmup, iters, batch, cap, threads, ring_rows=1 << 14):
+    """The reference's CPU path (oracle port: C restatement of the njit tree + memcpy row gather,
+    SURVEY.md 8d Tier A) as `threads` independent replicas, one per host core.  Bounded sample:
+    the tree has the full capacity, the frame ring holds `ring_rows` rows (slot & mask) so the
+    host allocation stays below 1 GB; rows are still gathered from random slots."""
+    from oracle import per_oracle as po
+    rng = np.random.default_rng(0)
+    ring = po.OracleRing(ring_rows, ATARI)
+    for c in (0, 3):
+        ring.column(c)[:] = rng.integers(0, 256, ring.column(c).shape, dtype=np.uint8)
+    prio0 = po.normalize_weights((np.abs(rng.standard_normal(cap)) * (1 + 9 * (rng.random(cap) < 0.05))
+                                  ).astype(np.float32), ALPHA)
+    trees = []
+    for _ in range(threads):
+        t = po.OracleSumTree(cap)
+        t.update(np.arange(cap), prio0)
+        trees.append(t)
+    total_steps = steps + warmup
+    u = np.random.default_rng(1).random(total_steps * iters * batch)
+    newp = np.abs(np.random.default_rng(2).standard_normal(total_steps * iters * batch)).astype(np.float32)
+
+    def run(nsteps, offset):
+        def work(t):
+            n = nsteps * iters
+            po.step_loop(t, ring, ring_rows - 1, n, batch, u[offset:], newp[offset:], ALPHA, BETA)
+        th = [threading.Thread(target=work, args=(t,)) for t in trees]
+        t0 = time.perf_counter()
+        [x.start() for x in th]
+        [x.join() for x in th]
+        return time.perf_counter() - t0
+
+    if warmup:
+        run(warmup, 0)
+    dt = run(steps, warmup * iters * batch)
+    return threads * steps * iters * batch / dt, dt
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return                                        # rank 0 alone runs the CPU arm
+    import __graft_entry__ as entry
+    from oracle import per_oracle as po
+    po.build()
+    del entry
+    cores = os.cpu_count() or 1
+    iters = args.cpu_iters
+    value, dt = cpu_reference_arm(args.steps, args.warmup, iters, args.batch, args.capacity, cores)
+    sample = (f"{cores} replicas x {args.steps} steps x {iters} iterations of batch {args.batch}; tree capacity "
+              f"{args.capacity}, frame ring bounded to 16384 rows (slot & mask)")
+    line = {
+        "impl": "reference", "metric": "sampled transitions/sec (sample+gather+priority update)",
+        "value": value, "unit": "transitions/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": dt * 1e3 / max(1, args.steps), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8 rows / f64 tree", "data": "synthetic",
+        "config": workload_config(args), "iterations_per_step": iters,
+        "cpu_baseline": {"value": value, "unit": "transitions/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "transitions/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args):
+    return {"workload": f"Atari 84x84x4 uint8 transitions ({ROW_BYTES} B rows), PER capacity {args.capacity} per GPU, "
+                        f"batch {args.batch}, alpha {ALPHA} beta {BETA} (BASELINE.json configs[1])",
+            "capacity_per_gpu": args.capacity, "batch": args.batch, "row_bytes": ROW_BYTES,
+            "prefetch_group": args.group,
+            "l2": "inputs larger than L2: rows are gathered from random slots of a 59 GB ring"}
+
+
+# ----------------------------------------------------------------- our arm --
+def fill_shard(torch, shard, cap, seed):
+    """Synthetic Atari-shaped rows generated on the device (a 59 GB host array is avoided)."""
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    chunk = 1 << 14
+    for st in range(0, cap, chunk):
+        n = min(chunk, cap - st)
+        s0 = torch.randint(0, 256, (n, 4, 84, 84), dtype=torch.uint8, device="cuda", generator=g)
+        s1 = torch.randint(0, 256, (n, 4, 84, 84), dtype=torch.uint8, device="cuda", generator=g)
+        a = torch.randint(0, 18, (n,), device="cuda", generator=g)
+        r = torch.randint(-1, 2, (n,), device="cuda", generator=g).float()
+        d = (torch.rand(n, device="cuda", generator=g) < 0.01).float()
+        w = torch.randn(n, device="cuda", generator=g).abs() * (1 + 9 * (torch.rand(n, device="cuda", generator=g) < 0.05))
+        shard.append([s0, a, r, s1, d], w.float(), alpha=ALPHA)
+    torch.cuda.synchronize()
+
+
+def timed_loop(torch, dist, shard, steps, warmup, iters, batch, prio, group, world, time_gather):
+    def one_step(k):
+        off = (k % prio_steps) * iters * batch
+        shard.step_loop(iters, batch, prio[off:], seed=1234, alpha=ALPHA, beta=BETA, group=group,
+                        time_gather=time_gather)
+    prio_steps = prio.numel() // (iters * batch)
+    for k in range(warmup):
+        one_step(k)
+    torch.cuda.synchronize()
+    shard.gather_time()
+    l0 = shard.stats()["kernel_launches"]
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for k in range(steps):
+        one_step(warmup + k)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+        dist.barrier()
+    launches = shard.stats()["kernel_launches"] - l0
+    return ms, launches, shard.gather_time()
+
+
+def e2e_loop(torch, dist, shard, iters_total, warm, batch, world):
+    """Public API, host buffers: sample -> gather (batch stays on the device for the learner, as
+    TorchCudaLoader delivers it) -> indices + IS weights D2H -> host |TD| priorities -> update H2D."""
+    rng = np.random.default_rng(3)
+    newp = torch.from_numpy(np.abs(rng.standard_normal((64, batch))).astype(np.float32)).pin_memory().numpy()
+    depth = shard.ring_depth
+
+    def it(i):
+        slot = i % depth
+        shard.sample(batch, beta=BETA, seed=99, slot=slot)
+        shard.gather(slot)
+        _, idx, w = shard.slot_read(slot)                 # D2H indices + weights, stream sync
+        shard.update(idx, newp[i % 64], alpha=ALPHA)      # H2D indices + priorities
+    for i in range(warm):
+        it(i)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(iters_total):
+        it(warm + i)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    return world * iters_total * batch / (ms / 1e3), batch * (8 + 4), batch * (8 + 8)
+
+
+def append_rate(torch, shard, n=16384, reps=10):
+    cols = [torch.randint(0, 256, (n, 4, 84, 84), dtype=torch.uint8, device="cuda"),
+            torch.zeros(n, dtype=torch.int64, device="cuda"), torch.zeros(n, device="cuda"),
+            torch.randint(0, 256, (n, 4, 84, 84), dtype=torch.uint8, device="cuda"), torch.zeros(n, device="cuda")]
+    w = torch.rand(n, device="cuda")
+    for _ in range(3):
+        shard.append(cols, w, alpha=ALPHA)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        shard.append(cols, w, alpha=ALPHA)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    return n / (ms / 1e3), 2 * n * ROW_BYTES / (ms / 1e3) / 1e9
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the replay engine has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    import __graft_entry__ as entry
+    if rank == 0:
+        entry.build()
+    if world > 1:
+        dist.barrier()
+    from reth_b200 import ReplayShard
+
+    B, cap, iters, G = args.batch, args.capacity, args.iters, args.group
+    if iters % G:
+        iters += G - iters % G
+    depth = max(2 * G, 2)
+    t0 = time.time()
+    shard = ReplayShard(cap, ATARI, max_batch=B, ring_depth=depth, device=local)
+    fill_shard(torch, shard, cap, seed=rank)
+    log(f"[rank {rank}] filled {cap} rows ({shard.stats()['hbm_bytes'] / 1e9:.1f} GB) in {time.time() - t0:.1f}s")
+    pool_steps = min(args.steps + args.warmup, 64)
+    g = torch.Generator(device="cuda").manual_seed(100 + rank)
+    prio = torch.randn(pool_steps * iters * B, device="cuda", generator=g).abs().float()
+
+    # multi-GPU: shards are independent (reference: one server per shard, trainer.py:52-61); the only
+    # exchange is the 16-byte shard root {total, min}, combined with an NCCL all-gather per bench step
+    roots = None
+    if world > 1:
+        roots = torch.zeros(2 * world, device="cuda", dtype=torch.float64)
+
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    ms, launches, (gt_ms, gt_n) = timed_loop(torch, dist, shard, args.steps, args.warmup, iters, B, prio, G, world, True)
+    if world > 1:
+        mine = torch.as_tensor(shard.root_dev(), device="cuda").clone()
+        dist.all_gather_into_tensor(roots, mine)
+    clk = clocks.stop() if rank == 0 else None
+    value = world * args.steps * iters * B / (ms / 1e3)
+
+    # strict alternation (no prefetch): sample k+1 sees update k
+    ms1, _, _ = timed_loop(torch, dist, shard, max(1, args.steps // 2), 1, iters, B, prio, 1, world, False)
+    strict = world * max(1, args.steps // 2) * iters * B / (ms1 / 1e3)
+    # end to end through the public API with host buffers
+    e2e_iters = min(2000, max(200, args.steps * iters))
+    e2e, h2d, d2h = e2e_loop(torch, dist, shard, e2e_iters, 50, B, world)
+    app_rows, app_gbs = append_rate(torch, shard) if rank == 0 or world == 1 else (None, None)
+
+    peak, peak_src = measured_peak()
+    rows_per_launch = G * B
+    gather_us = gt_ms * 1e3 / max(1, gt_n)
+    achieved = 2 * rows_per_launch * ROW_BYTES / (gather_us * 1e-6) / 1e9 if gt_n else None
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "gather_traffic.json")
+    if os.path.exists(tpath):
+        try:
+            tj = json.load(open(tpath))
+            if int(tj.get("rows_per_launch", -1)) == rows_per_launch:
+                traffic = tj["dram_bytes_per_launch"]
+        except Exception:
+            pass
+    line = {
+        "metric": "sampled transitions/sec (sample+gather+priority update)", "value": value, "unit": "transitions/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / max(1, args.steps),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8 rows / f64 tree",
+        "data": "synthetic", "config": workload_config(args), "iterations_per_step": iters,
+        "clocks": clk, "gpu_launches": int(launches),
+        "e2e": {"value": e2e, "unit": "transitions/s", "h2d_bytes_per_step": h2d * iters, "d2h_bytes_per_step": d2h * iters,
+                "note": "public API, strict alternation: sample+gather on device (batch handed to the learner as CUDA "
+                        "tensors, as TorchCudaLoader does), indices+weights D2H, host indices+|TD| H2D, per iteration"},
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": (achieved / peak) if achieved else None, "traffic": traffic, "peak_source": peak_src,
+                     "kernel": "row_move_kernel<false> (frame gather)", "rows_per_launch": rows_per_launch,
+                     "algorithmic_bytes_per_launch": 2 * rows_per_launch * ROW_BYTES, "avg_launch_us": gather_us,
+                     "launches_timed": int(gt_n)},
+        "hbm_gbs_whole_loop": 2 * ROW_BYTES * value / 1e9 / world,
+        "strict_alternation": {"value": strict, "unit": "transitions/s", "prefetch_group": 1},
+        "append": {"rows_per_s": app_rows, "gbs": app_gbs, "rows_per_call": 16384, "source": "device"},
+        "shard_mode": "independent shards; NCCL all-gather of shard {total,min} once per run" if world > 1 else "single shard",
+    }
+    if world > 1:
+        line["shard_totals"] = [float(x) for x in roots.cpu()[0::2]]
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cores = os.cpu_count() or 1
+        v, dt = cpu_reference_arm(args.cpu_steps, 1, args.cpu_iters, B, cap, cores)
+        v1, _ = cpu_reference_arm(max(1, args.cpu_steps // 2), 1, args.cpu_iters, B, cap, 1)
+        line["cpu_baseline"] = {
+            "value": v, "unit": "transitions/s", "cores": cores, "kind": "port", "one_core": v1,
+            "sample": f"{cores} replicas x {args.cpu_steps} steps x {args.cpu_iters} iterations of batch {B} "
+                      f"({dt:.1f} s); tree capacity {cap}, frame ring bounded to 16384 rows (slot & mask)"}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    shard.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--capacity", type=int, default=1 << 20)
+    ap.add_argument("--batch", type=int, default=512)
+    ap.add_argument("--iters", type=int, default=128, help="learner iterations per bench step")
+    ap.add_argument("--group", type=int, default=4, help="prefetch group (reference loader ring: trainer.py:23 buffer_size=4)")
+    ap.add_argument("--cpu-steps", type=int, default=4)
+    ap.add_argument("--cpu-iters", type=int, default=64, help="iterations per step of the CPU arm (bounded sample)")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "ours":
+        args.warmup = 3
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()
