@@ -1,0 +1,148 @@
+"""Drop-in surface on the GPU: the reference's own tests, restated against the shim.
+  reth_buffer/test/test_rb.py:12-35   (FIFO slot order + gather correctness through the service)
+  reth/test/test_buffer.py:113-167    (PrioritizedBuffer data/weights and sampling distribution)"""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def reth_buffer():
+    import __graft_entry__ as entry
+    entry.build()
+    sys.path.insert(0, os.path.join(ROOT, "reth_b200", "compat"))
+    import reth_buffer
+    yield reth_buffer
+    sys.path.remove(os.path.join(ROOT, "reth_b200", "compat"))
+
+
+def test_rb_basic(reth_buffer):
+    """test_rb.py:12-35 verbatim in structure."""
+    CAPACITY, BATCH_SIZE = 100000, 32
+    rb_proc, addr = reth_buffer.start_server(CAPACITY, BATCH_SIZE)
+    try:
+        client = reth_buffer.Client(addr)
+        loader = reth_buffer.NumpyLoader(addr)
+        data = [np.random.rand(1000, 4, 84), np.random.rand(1000), np.arange(1000)]
+        buf_weights = np.random.rand(1000) + 1
+        for start in range(0, 1000, 100):
+            batch = [x[start:start + 100] for x in data]
+            client.append(batch, buf_weights[start:start + 100])
+        for _ in range(10):
+            batch, indices, weights = loader.sample()
+            assert indices.dtype == np.int64 and weights.dtype == np.float64
+            for i, idx in enumerate(indices):
+                assert batch[2][i] == idx
+                assert batch[1][i] == data[1][idx]
+                assert np.array_equal(batch[0][i], data[0][idx])
+        buf_weights = np.random.rand(1000) + 10
+        client.update_priorities(np.arange(1000), buf_weights)
+    finally:
+        rb_proc.terminate()
+        rb_proc.join()
+
+
+def test_torch_cuda_loader_and_gating(reth_buffer):
+    import torch
+    B = 64
+    proc, addr = reth_buffer.start_per(5000, B, alpha=0.5, beta="0.4,1,2000", sample_start=200)
+    try:
+        client = reth_buffer.Client(addr)
+        loader = reth_buffer.TorchCudaLoader(addr, buffer_size=4, num_procs=2)     # trainer.py:23
+        rng = np.random.default_rng(0)
+        s0 = rng.integers(0, 256, (300, 4, 84, 84), dtype=np.uint8)
+        cols = [s0, rng.integers(0, 18, 300), rng.standard_normal(300).astype(np.float32), s0[::-1].copy(),
+                np.zeros(300, np.float32)]
+        client.append([c[:100] for c in cols], np.ones(100, np.float32))
+        with pytest.raises(TimeoutError):                    # cnt < max(sample_start, batch): no batch yet
+            loader._eng.wait_ready(timeout=0.05)
+        client.append([c[100:] for c in cols], np.ones(200, np.float32))
+        seen_beta = []
+        for it in range(12):
+            data, indices, weights = loader.sample()
+            assert isinstance(indices, np.ndarray) and indices.dtype == np.int64
+            assert weights.is_cuda and weights.dtype == torch.float64 and tuple(weights.shape) == (B,)
+            assert data[0].is_cuda and data[0].dtype == torch.uint8 and tuple(data[0].shape) == (B, 4, 84, 84)
+            assert np.array_equal(data[0].cpu().numpy(), s0[indices])
+            assert np.array_equal(data[1].cpu().numpy(), cols[1][indices])
+            loss = np.abs(rng.standard_normal(B)).astype(np.float32)
+            client.update_priorities(np.asarray(indices), np.asarray(loss))         # trainer.py:36
+            seen_beta.append(loader._eng.sampler["beta"].value())
+        assert seen_beta[0] == pytest.approx(0.4 + 0.6 / 2000) and seen_beta[-1] > seen_beta[0]
+        with pytest.raises(AssertionError):
+            client.append([c[:10] for c in cols], np.ones(9))
+        with pytest.raises(AssertionError):
+            client.append([list(range(10))], np.ones(10))
+    finally:
+        proc.terminate()
+        proc.join()
+    with pytest.raises(ConnectionError):
+        reth_buffer.Client(addr)
+
+
+def _generate_data(size):
+    obs_space = (4, 84, 84)
+    return [np.arange(size, dtype="i8"), np.random.rand(size, *obs_space).astype("f4"),
+            np.random.randint(0, 10, size, dtype="i8"), np.random.rand(size).astype("f4"),
+            np.random.rand(size, *obs_space).astype("f4"), np.random.randint(0, 2, size).astype("f4")]
+
+
+def test_prioritized_buffer_per():
+    """reth/test/test_buffer.py:113-132."""
+    from reth_b200.buffer import PrioritizedBuffer
+    capacity, sample_size = 1000, 64
+    buf = PrioritizedBuffer(capacity)
+    data = _generate_data(capacity)
+    weights = np.random.rand(capacity)
+    buf.append_batch(data, weights=weights)
+    assert buf.size == capacity and buf.capacity == capacity
+    for i, (dtype, shape) in enumerate(buf.struct):           # test_buffer.py:27-35
+        assert np.dtype(dtype) == data[i].dtype and (capacity, *shape) == data[i].shape
+    res, indices, res_weights = buf.sample(sample_size)
+    for i, col in enumerate(res):
+        for j, line in enumerate(col):
+            idx = res[0][j]
+            assert idx == indices[j]
+            assert np.array_equal(line, data[i][idx])
+    out_weights = (weights + 1e-6) ** buf.alpha.value()
+    out_weights = (out_weights / min(out_weights)) ** (-buf.beta.value())
+    for i, w in enumerate(res_weights):
+        assert abs(out_weights[indices[i]] - w) < 1e-3
+
+
+def test_prioritized_buffer_distribution():
+    """reth/test/test_buffer.py:135-167."""
+    from reth_b200.buffer import PrioritizedBuffer
+    # the reference's 100 draws put this statistic at 0.083 +- 0.01 against its 0.1 bound for a
+    # perfect sampler (scripts/dist_check.py); 300 draws keep the same bound without the flake
+    np.random.seed(7)
+    capacity, sample_size, sample_cnt = 100, 64, 300
+    buf = PrioritizedBuffer(capacity)
+    data = _generate_data(capacity)
+    weights = np.random.rand(capacity)
+    buf.append_batch(data, weights=weights)
+
+    def check(weights):
+        cnt = np.zeros(capacity)
+        for _ in range(sample_cnt):
+            _, indices, _ = buf.sample(sample_size)
+            np.add.at(cnt, indices, 1)
+        p = (weights + 1e-6) ** buf.alpha.value()
+        l1 = np.sum(np.abs(cnt / cnt.sum() - p / p.sum()) / (p / p.sum()))
+        assert l1 / capacity < 0.1
+
+    check(weights)
+    weights = np.random.rand(capacity)
+    buf.update_priorities(np.arange(capacity), weights)
+    check(weights)
+    # append(data, weight) stores the raw weight; clear() resets schedules and cursor
+    buf.append([col[0] for col in data], 3.0)
+    buf.clear()
+    assert buf.size == 0
+    buf.append([col[0] for col in data])
+    assert buf.size == 1 and buf._shard.root() == (1.0, 1.0)
