@@ -145,6 +145,11 @@ int reth_replay_gather_multi(reth_replay_t *h, int first_slot, int n_slots, void
 int reth_replay_update_slots(reth_replay_t *h, int first_slot, int n_slots, const void *prio,
                              int prio_dtype, int prio_loc, double alpha, int transform, void *stream);
 
+/* indices (and weights) of n_slots consecutive full slots in one device->host copy each:
+ * host int64[n_slots*batch] / double[n_slots*batch], either may be NULL.  Synchronises. */
+int reth_replay_group_read(reth_replay_t *h, int first_slot, int n_slots, int64_t *indices,
+                           double *weights, void *stream);
+
 /* Device pointers of a batch slot (lent, as TorchCudaLoader lends ring slots,
  * torch_cuda_loader.py:152-163).  Any out pointer may be NULL. */
 int reth_replay_slot_ptrs(reth_replay_t *h, int slot, void **cols_out /*[n_columns]*/,

@@ -706,6 +706,19 @@ RETH_EXPORT int reth_replay_slot_read(reth_replay_t *h, int slot, int64_t *indic
     return check_device_err(h, s);
 }
 
+RETH_EXPORT int reth_replay_group_read(reth_replay_t *h, int first_slot, int n_slots, int64_t *indices,
+                                       double *weights, void *stream)
+{
+    if (!h) return RETH_ERR_INVALID;
+    if (group_ok(h, first_slot, n_slots)) return RETH_ERR_INVALID;
+    DeviceGuard guard(h->cfg.device);
+    cudaStream_t s = S(stream);
+    const size_t n = (size_t)h->slots[first_slot].batch * n_slots;
+    if (indices) CK(h, cudaMemcpyAsync(indices, h->slots[first_slot].idx, n * 8, cudaMemcpyDeviceToHost, s));
+    if (weights) CK(h, cudaMemcpyAsync(weights, h->slots[first_slot].w, n * 8, cudaMemcpyDeviceToHost, s));
+    return check_device_err(h, s);
+}
+
 RETH_EXPORT int reth_replay_slot_meta(reth_replay_t *h, int slot, int64_t *first_count, void *stream)
 {
     if (!h || !first_count) return RETH_ERR_INVALID;

@@ -67,14 +67,15 @@ class _Engine:
         self.struct = None
         self.cnt = 0                                          # sampler_loop.py:20,36
         self.lock = threading.RLock()
+        self._pending = []
         self.closed = False
         self.max_ring = 16
 
     # -- server side of Client.append (server/main_loop.py:44-58) -----------
-    def _ensure_shard(self, data):
+    def _ensure_shard(self, data, struct=None):
         if self.shard is not None:
             return
-        self.struct = [(np.asarray(col).dtype, tuple(np.asarray(col).shape[1:])) for col in data]
+        self.struct = struct or [(np.asarray(col).dtype, tuple(np.asarray(col).shape[1:])) for col in data]
         self.shard = ReplayShard(self.capacity, self.struct, max_batch=self.batch_size,
                                  ring_depth=self.max_ring, device=self.device, min_mode=MIN_SERVICE)
 
@@ -92,15 +93,35 @@ class _Engine:
                 self.shard.append_at(slots, dev, weights, alpha=alpha, transform=True)
             self.cnt += len(weights)
 
-    def update(self, indices, weights, step):
+    def update(self, indices, weights, step, coalesce=1):
+        """sampler_loop.py:29-36.  coalesce > 1: updates are queued like the frames the reference
+        keeps in its PUSH/SUB pipes (fire-and-forget, client.py:37-39) and written back in one
+        launch once `coalesce` are pending or the sampler is about to draw (flush()); order and
+        last-writer-wins are those of the message sequence.  alpha is constant over a run here
+        when coalescing (the schedule still advances once per message)."""
         with self.lock:
             if self.shard is None:
                 return                                        # nothing stored yet: the reference drops into an empty tree
             if step:                                          # sampler_loop.py:33-34, per_sampler.py:30-32
                 self.sampler["alpha"].step()
                 self.sampler["beta"].step()
-            self.shard.update(indices, weights, alpha=self.sampler["alpha"].value(), transform=True)
             self.cnt += len(indices)
+            if coalesce <= 1 and not self._pending:
+                self.shard.update(indices, weights, alpha=self.sampler["alpha"].value(), transform=True)
+                return
+            self._pending.append((np.asarray(indices, dtype=np.int64), np.asarray(weights)))
+            if len(self._pending) >= coalesce:
+                self.flush()
+
+    def flush(self):
+        with self.lock:
+            if not self._pending or self.shard is None:
+                return
+            idx = np.concatenate([p[0] for p in self._pending])
+            dts = {p[1].dtype for p in self._pending}
+            w = np.concatenate([p[1] if len(dts) == 1 else p[1].astype(np.float64) for p in self._pending])
+            self._pending = []
+            self.shard.update(idx, w, alpha=self.sampler["alpha"].value(), transform=True)
 
     def ready(self):
         return self.shard is not None and self.cnt >= self.sampler["sample_start"]
@@ -169,8 +190,9 @@ def _engine(meta_addr):
 class Client:
     """client/client.py:8-39."""
 
-    def __init__(self, meta_addr):
+    def __init__(self, meta_addr, coalesce_updates=1):
         self._eng = _engine(meta_addr)
+        self.coalesce_updates = int(coalesce_updates)
         self.meta = {"capacity": self._eng.capacity, "batch_size": self._eng.batch_size, "meta_addr": meta_addr}
 
     def append(self, data, weights, compress=False):
@@ -182,7 +204,7 @@ class Client:
 
     def update_priorities(self, indices, weights, step=True):
         assert len(indices) == len(weights)                   # :38
-        self._eng.update(np.asarray(indices), np.asarray(weights), step)
+        self._eng.update(np.asarray(indices), np.asarray(weights), step, self.coalesce_updates)
 
 
 class _LoaderBase:
@@ -204,6 +226,7 @@ class _LoaderBase:
         eng = self._eng
         eng.wait_ready()
         with eng.lock:
+            eng.flush()                                       # pending priority messages land before the draw
             sh, B, G = eng.shard, eng.batch_size, self.prefetch
             depth = sh.ring_depth
             first = self._next_group
@@ -217,9 +240,13 @@ class _LoaderBase:
             else:
                 sh.sample_multi(B, first, G, beta=beta, seed=0x5EED)
                 sh.gather_multi(first, G)
-            for g in range(G):                                # one D2H of indices per batch, one sync per group
-                _, idx, _ = sh.slot_read(first + g)
-                self._queue.append((first + g, idx))
+            if G == 1:
+                idx, _ = sh.group_read(first, 1)
+                self._queue.append((first, idx))
+            else:                                             # one D2H of all indices, one sync per group
+                idx, _ = sh.group_read(first, G)
+                for g in range(G):
+                    self._queue.append((first + g, idx[g * B:(g + 1) * B]))
 
     def get_indices(self):
         """numpy_loader.py:53-56: (indices, weights) of the next batch."""
@@ -261,10 +288,14 @@ class TorchCudaLoader(_LoaderBase):
         super().__init__(meta_addr, topic, min(g, eng.max_ring // 2))
         self.buffer_size = buffer_size
         self.num_procs = num_procs                            # accepted, unused: no gather processes are needed
+        self._views = {}                                      # slot -> cached zero-copy torch views
 
     def sample(self):
         if not self._queue:
             self._refill()
         slot, indices = self._queue.pop(0)
-        data, _, weights, _ = self._eng.shard.slot_tensors(slot)
-        return data, indices, weights
+        v = self._views.get(slot)
+        if v is None:
+            data, _, weights, _ = self._eng.shard.slot_tensors(slot)
+            v = self._views[slot] = (data, weights)
+        return v[0], indices, v[1]

@@ -294,6 +294,15 @@ class ReplayShard:
             outs = [o[:rows] for o in outs] if outs is not None else None
         return outs, idx, w
 
+    def group_read(self, first_slot, n_slots, with_weights=False, stream=None):
+        """Host indices (and weights) of n_slots consecutive slots: one D2H copy, one sync."""
+        n = self.slot_batch(first_slot) * n_slots
+        idx = np.empty(n, np.int64)
+        w = np.empty(n, np.float64) if with_weights else None
+        self._ck(self._lib.reth_replay_group_read(self._h, int(first_slot), int(n_slots), idx.ctypes.data,
+                                                  w.ctypes.data if with_weights else None, self._s(stream)))
+        return idx, w
+
     def slot_meta(self, slot, stream=None):
         fc = (C.c_int64 * 2)()
         self._ck(self._lib.reth_replay_slot_meta(self._h, slot, fc, self._s(stream)))
