@@ -6,7 +6,8 @@ import torch
 from reth_b200 import ReplayShard
 ATARI = [(np.uint8, (4, 84, 84)), (np.int64, ()), (np.float32, ()), (np.uint8, (4, 84, 84)), (np.float32, ())]
 cap = int(os.environ.get("CAP", 1 << 20)); B = int(os.environ.get("B", 512)); steps = int(os.environ.get("STEPS", 20))
-sh = ReplayShard(cap, ATARI, max_batch=B, ring_depth=4, update_cluster=int(os.environ.get("CLUSTER", 8)))
+G = int(os.environ.get("GROUP", 1))
+sh = ReplayShard(cap, ATARI, max_batch=B, ring_depth=max(4, 2 * G), update_cluster=int(os.environ.get("CLUSTER", 8)))
 g = torch.Generator(device="cuda").manual_seed(0)
 chunk = 1 << 14
 for st in range(0, cap, chunk):
@@ -17,6 +18,6 @@ for st in range(0, cap, chunk):
     sh.append([s0, a, r, s0, r], w.float(), alpha=0.6)
 prio = torch.randn(steps * B, device="cuda").abs().float()
 torch.cuda.synchronize()
-sh.step_loop(steps, B, prio, serial=True)
+sh.step_loop(steps, B, prio, serial=True, group=G)
 torch.cuda.synchronize()
 print("done", sh.stats()["kernel_launches"])
