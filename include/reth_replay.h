@@ -59,7 +59,8 @@ typedef struct reth_replay_config {
     int32_t device;                         /* CUDA device ordinal */
     int32_t min_mode;                       /* reth_min_mode */
     int32_t update_cluster;                 /* CTAs per cluster of the tree-repair kernel (0 = default 8) */
-    int32_t gather_mode;                    /* 0 = auto, 1 = LDG/STG.128, 2 = TMA bulk (cp.async.bulk) */
+    int32_t gather_mode;                    /* 0 = auto (= 1, the faster one on B200), 1 = LDG/STG.128,
+                                               2 = TMA bulk copies (cp.async.bulk + mbarrier ring) */
     int32_t store_rows;                     /* 0 = tree only (no frame ring; config 5 "tree-only") */
     int32_t reserved[5];
 } reth_replay_config;

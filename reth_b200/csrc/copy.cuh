@@ -165,4 +165,212 @@ __global__ void __launch_bounds__(kCopyThreads, 6) row_move_kernel(const RowArgs
     }
 }
 
+
+// ------------------------------------------------ gather, TMA bulk-copy variant --
+// The sampled-row gather as pure DMA: a persistent grid (one CTA per SM), each CTA
+// owning a ring of row-sized shared-memory stages.  One thread per CTA issues
+//   cp.async.bulk  global -> shared   (completion on an mbarrier, complete_tx bytes)
+//   cp.async.bulk  shared -> global   (completion through bulk async-groups)
+// so up to kStages x chunk bytes are in flight per SM with ~no instruction issue and
+// no register staging; the other warps move the narrow scalar columns meanwhile.
+// Items are (row, wide column, chunk) triples, grid-strided; chunk = the whole column
+// row when it fits a stage (28 224 B for an Atari frame stack), else equal 16 B-multiple
+// pieces.  Replaces the per-row Python loop of client/numpy_loader.py:35-50 and
+// client/torch_cuda_loader.py:49-61.
+constexpr int kBulkThreads = 128;
+constexpr int kBulkSlotCache = 512;      // items whose ring slots are staged in shared memory per round
+
+struct BulkArgs {
+    RowArgs r;                  // same decomposition as row_move_kernel (chunks/units per column)
+    int32_t stage_bytes;        // bytes of one shared-memory stage (>= the largest chunk)
+    int32_t stages;             // ring depth
+    int32_t evict_first_loads;  // L2 policy for the ring reads (rows are touched once)
+    int32_t evict_first_stores;
+};
+
+__device__ __forceinline__ uint32_t smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}"
+        :: "r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_first()
+{
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_last()
+{
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst_smem, const void *src, uint32_t bytes, uint32_t bar,
+                                         uint64_t policy, bool hint)
+{
+    if (hint)
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint "
+                     "[%0], [%1], %2, [%3], %4;"
+                     :: "r"(dst_smem), "l"(src), "r"(bytes), "r"(bar), "l"(policy) : "memory");
+    else
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     :: "r"(dst_smem), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void *dst, uint32_t src_smem, uint32_t bytes, uint64_t policy, bool hint)
+{
+    if (hint)
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;"
+                     :: "l"(dst), "r"(src_smem), "r"(bytes), "l"(policy) : "memory");
+    else
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                     :: "l"(dst), "r"(src_smem), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+
+struct BulkItem {
+    const uint8_t *src;
+    uint8_t *dst;
+    uint32_t bytes;             // 0 = skip (row beyond meta count, bad slot)
+};
+
+// item -> (source in the ring, destination in the batch, bytes); slot comes from the shared cache
+__device__ __forceinline__ BulkItem bulk_item(const RowArgs &a, int64_t item, int64_t slot, int rows)
+{
+    int c = 0;
+#pragma unroll 1
+    for (int k = 0; k < a.ncols; ++k)
+        if (a.col[k].chunks > 0 && item >= a.col[k].item_base) c = k;
+    const RowCol &col = a.col[c];
+    const int64_t rel = item - col.item_base;
+    const int row = (int)(rel / col.chunks), chunk = (int)(rel - (int64_t)row * col.chunks);
+    BulkItem it;
+    it.bytes = 0;
+    if (row >= rows || slot < 0 || slot >= a.capacity) return it;
+    const int64_t off = (int64_t)chunk * col.units * 16;
+    const int64_t left = col.rb - off;
+    it.bytes = (uint32_t)(left < (int64_t)col.units * 16 ? left : (int64_t)col.units * 16);
+    it.src = col.ring + slot * col.rb + off;
+    it.dst = col.batch + (int64_t)row * col.rb + off;
+    return it;
+}
+
+__device__ __forceinline__ int bulk_item_row(const RowArgs &a, int64_t item)
+{
+    int c = 0;
+#pragma unroll 1
+    for (int k = 0; k < a.ncols; ++k)
+        if (a.col[k].chunks > 0 && item >= a.col[k].item_base) c = k;
+    return (int)((item - a.col[c].item_base) / a.col[c].chunks);
+}
+
+__global__ void __launch_bounds__(kBulkThreads, 1) row_gather_bulk_kernel(const BulkArgs b)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    const RowArgs &a = b.r;
+    const int S = b.stages;
+    uint8_t *stage0 = smem;
+    uint64_t *bars = (uint64_t *)(smem + (size_t)S * b.stage_bytes);
+    int64_t *slot_cache = (int64_t *)(bars + 16);
+    const int rows = a.meta ? (int)a.meta[1] : a.batch;
+    const int64_t total = a.wide_items;
+    // this CTA's items: blockIdx.x, blockIdx.x + gridDim.x, ...
+    const int64_t n_local = total > blockIdx.x ? (total - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < S; ++s) mbar_init(smem_addr(&bars[s]), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    uint64_t pol = 0;
+    if (b.evict_first_loads || b.evict_first_stores) pol = l2_policy_evict_first();
+
+    int64_t issued = 0, stored = 0;      // running item counters of the issuing thread (persist across rounds)
+    for (int64_t base = 0; base < n_local; base += kBulkSlotCache) {
+        const int64_t cnt = (n_local - base < kBulkSlotCache) ? n_local - base : kBulkSlotCache;
+        __syncthreads();                 // previous round's cache fully consumed
+        for (int64_t j = threadIdx.x; j < cnt; j += kBulkThreads) {
+            const int64_t item = blockIdx.x + (base + j) * gridDim.x;
+            const int row = bulk_item_row(a, item);
+            int64_t slot = -1;
+            if (row < rows) {
+                slot = a.idx[row];
+                if (slot < 0 || slot >= a.capacity) atomicOr(a.err, 1);
+            }
+            slot_cache[j] = slot;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            // software pipeline over this round: S-1 loads in flight while one stage drains; stage = item % S
+            const int64_t end = base + cnt;
+            for (;;) {
+                // refill: issue loads while a stage is free (a stage is free once the store that read it
+                // has finished READING shared memory: all but the newest bulk group)
+                while (issued < end && issued - stored < S - 1) {
+                    if (issued >= S) {
+                        // stage of item `issued` was last used by item issued-S, whose store was committed
+                        // at position issued-S; allow only groups newer than that to be pending
+                        const int64_t newer = stored - 1 - (issued - S);   // stores committed after it
+                        if (newer <= 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+                        else if (newer == 1) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+                        else if (newer == 2) asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory");
+                        else if (newer == 3) asm volatile("cp.async.bulk.wait_group.read 3;" ::: "memory");
+                        // newer >= 4: with S <= 8 the store is old enough only if we also wait; be safe
+                        else asm volatile("cp.async.bulk.wait_group.read 4;" ::: "memory");
+                    }
+                    const int s = (int)(issued % S);
+                    const BulkItem it = bulk_item(a, blockIdx.x + issued * gridDim.x, slot_cache[issued - base], rows);
+                    const uint32_t bar = smem_addr(&bars[s]);
+                    mbar_expect_tx(bar, it.bytes);           // bytes == 0: the phase completes at once
+                    if (it.bytes)
+                        bulk_g2s(smem_addr(stage0 + (size_t)s * b.stage_bytes), it.src, it.bytes, bar, pol,
+                                 b.evict_first_loads != 0);
+                    ++issued;
+                }
+                if (stored >= end) break;
+                // drain one: wait for the oldest load, push it out
+                const int s = (int)(stored % S);
+                mbar_wait(smem_addr(&bars[s]), (uint32_t)((stored / S) & 1));
+                const BulkItem it = bulk_item(a, blockIdx.x + stored * gridDim.x, slot_cache[stored - base], rows);
+                if (it.bytes)
+                    bulk_s2g(it.dst, smem_addr(stage0 + (size_t)s * b.stage_bytes), it.bytes, pol,
+                             b.evict_first_stores != 0);
+                else
+                    asm volatile("cp.async.bulk.commit_group;" ::: "memory");   // keep group count == item count
+                ++stored;
+            }
+        }
+    }
+    if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+
+    // narrow / unaligned columns by warps 1..3 (one thread per row), overlapping the DMA above
+    if (a.narrow_groups > 0 && threadIdx.x >= 32) {
+        const int per = kBulkThreads - 32;
+        for (int row = blockIdx.x * per + (threadIdx.x - 32); row < rows; row += gridDim.x * per) {
+            const int64_t slot = a.idx[row];
+            if (slot < 0 || slot >= a.capacity) { atomicOr(a.err, 1); continue; }
+            for (int c = 0; c < a.ncols; ++c) {
+                const RowCol &col = a.col[c];
+                if (col.chunks != 0) continue;
+                span_copy(col.batch + (int64_t)row * col.rb, col.ring + slot * col.rb, col.rb, 0, 1);
+            }
+        }
+    }
+}
+
 }  // namespace reth

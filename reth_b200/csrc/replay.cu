@@ -62,6 +62,9 @@ struct reth_replay {
     std::vector<cudaEvent_t> ev_sampled, ev_gathered;
     cudaEvent_t ev_fork = nullptr, ev_join_t = nullptr, ev_join_g = nullptr;
     int update_cluster = 8;
+    int max_dyn_smem = 0;               // opt-in shared memory per block
+    bool gather_bulk = false;           // gather through row_gather_bulk_kernel (TMA bulk copies)
+    int bulk_grid_cap = 0;              // RETH_BULK_GRID at create time: cap on the persistent grid (tests)
     long long *dbg = nullptr;           // RETH_DEBUG_TIMING=1: stage clocks of the last update launch
     std::vector<cudaEvent_t> ev_time;   // pairs (start, stop) around timed gather launches
     size_t ev_time_used = 0;
@@ -176,6 +179,19 @@ RETH_EXPORT int reth_replay_create(const reth_replay_config *cfg, reth_replay_t 
     if (prop.major < 9)
         return bail(fail(h, RETH_ERR_CUDA, "device sm_%d%d: built for sm_100a only", prop.major, prop.minor));
     h->n_sms = prop.multiProcessorCount;
+    h->max_dyn_smem = (int)prop.sharedMemPerBlockOptin;
+    {
+        int mode = cfg->gather_mode;
+        if (const char *e = getenv("RETH_GATHER_MODE")) mode = atoi(e);
+        bool any_wide = false;
+        for (int c = 0; c < cfg->n_columns; ++c)
+            if (cfg->row_bytes[c] % 16 == 0 && cfg->row_bytes[c] >= 256) any_wide = true;
+        h->gather_bulk = (mode == 2) && any_wide;   // auto = LDG/STG.128: measured faster (profiles/r01_gather_sweep.log)
+        if (const char *e = getenv("RETH_BULK_GRID")) h->bulk_grid_cap = atoi(e);
+        if (h->gather_bulk)
+            CKC(cudaFuncSetAttribute(row_gather_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     h->max_dyn_smem));
+    }
     int64_t *acct = &h->st.hbm_bytes;
     const size_t nt = (size_t)h->geom.n_tiles;
     CKC(dalloc_zero(&h->desc, nt * 32, acct));
@@ -456,8 +472,10 @@ int gather_units_target()
 }
 
 // Work decomposition of a row move over `batch` rows (gather or scatter).
-void build_row_args(reth_replay *h, RowArgs &a, uint8_t *const *batch_cols, const int64_t *idx, int batch)
+void build_row_args(reth_replay *h, RowArgs &a, uint8_t *const *batch_cols, const int64_t *idx, int batch,
+                    int units_target = 0)
 {
+    if (units_target <= 0) units_target = gather_units_target();
     a = RowArgs{};
     a.ncols = h->cfg.n_columns;
     a.idx = idx;
@@ -474,7 +492,7 @@ void build_row_args(reth_replay *h, RowArgs &a, uint8_t *const *batch_cols, cons
         const bool wide = (col.rb % 16 == 0) && col.rb >= 256 && ((uintptr_t)col.batch % 16 == 0);
         if (wide) {
             const int64_t upr = col.rb / 16;
-            col.chunks = (int32_t)((upr + gather_units_target() - 1) / gather_units_target());
+            col.chunks = (int32_t)((upr + units_target - 1) / units_target);
             col.units = (int32_t)((upr + col.chunks - 1) / col.chunks);
             col.item_base = items;
             items += (int64_t)batch * col.chunks;
@@ -495,6 +513,45 @@ int launch_row_move(reth_replay *h, const RowArgs &a, cudaStream_t s)
     const int64_t maxg = (int64_t)h->n_sms * 6 * 64;
     const unsigned grid = (unsigned)(total < maxg ? total : maxg);
     row_move_kernel<kScatter><<<grid, kCopyThreads, 0, s>>>(a);
+    CK(h, cudaGetLastError());
+    h->st.kernel_launches++;
+    return RETH_OK;
+}
+
+int env_int(const char *name, int dflt)
+{
+    const char *e = getenv(name);
+    return e ? atoi(e) : dflt;
+}
+
+// TMA bulk-copy gather (row_gather_bulk_kernel): persistent, one CTA per SM.
+int launch_gather_bulk(reth_replay *h, uint8_t *const *batch_cols, const int64_t *idx, int batch,
+                       const int64_t *meta, cudaStream_t s)
+{
+    static const int units_cap = env_int("RETH_BULK_UNITS", 3584);     // 57 344 B: >= 4 stages per SM
+    static const int ctas_per_sm = env_int("RETH_BULK_CTAS", 1);
+    static const int ef_loads = env_int("RETH_BULK_EF_LOADS", 1), ef_stores = env_int("RETH_BULK_EF_STORES", 0);
+    BulkArgs b = {};
+    build_row_args(h, b.r, batch_cols, idx, batch, units_cap);
+    b.r.meta = meta;
+    int max_units = 0;
+    for (int c = 0; c < b.r.ncols; ++c)
+        if (b.r.col[c].chunks > 0 && b.r.col[c].units > max_units) max_units = b.r.col[c].units;
+    b.stage_bytes = (max_units * 16 + 127) & ~127;
+    const int fixed = 128 + kBulkSlotCache * 8;
+    const int budget = h->max_dyn_smem / ctas_per_sm - (ctas_per_sm > 1 ? 1024 : 0) - fixed;
+    int stages = b.stage_bytes > 0 ? budget / b.stage_bytes : 2;
+    if (stages > 8) stages = 8;
+    if (stages < 2) return fail(h, RETH_ERR_INVALID, "bulk gather: a %d-byte stage does not fit shared memory", b.stage_bytes);
+    b.stages = stages;
+    b.evict_first_loads = ef_loads;
+    b.evict_first_stores = ef_stores;
+    const size_t smem = (size_t)stages * b.stage_bytes + fixed;
+    int64_t grid = (int64_t)h->n_sms * ctas_per_sm;
+    const int64_t work = b.r.wide_items > 0 ? b.r.wide_items : 1;
+    if (grid > work) grid = work;
+    if (h->bulk_grid_cap > 0 && grid > h->bulk_grid_cap) grid = h->bulk_grid_cap;
+    row_gather_bulk_kernel<<<(unsigned)grid, kBulkThreads, smem, s>>>(b);
     CK(h, cudaGetLastError());
     h->st.kernel_launches++;
     return RETH_OK;
@@ -541,10 +598,16 @@ int do_gather(reth_replay *h, int slot, bool use_meta, cudaStream_t s, int group
 {
     BatchSlot &b = h->slots[slot];
     if (!h->cfg.store_rows || h->cfg.n_columns == 0) return RETH_OK;
-    RowArgs a;
-    build_row_args(h, a, b.cols, b.idx, b.batch * groups);
-    a.meta = (use_meta && groups == 1) ? b.meta : nullptr;
-    int rc = launch_row_move<false>(h, a, s);
+    const int64_t *meta = (use_meta && groups == 1) ? b.meta : nullptr;
+    int rc;
+    if (h->gather_bulk) {
+        rc = launch_gather_bulk(h, b.cols, b.idx, b.batch * groups, meta, s);
+    } else {
+        RowArgs a;
+        build_row_args(h, a, b.cols, b.idx, b.batch * groups);
+        a.meta = meta;
+        rc = launch_row_move<false>(h, a, s);
+    }
     if (rc) return rc;
     h->st.gathered_rows += (int64_t)b.batch * groups;
     return RETH_OK;

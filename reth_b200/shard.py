@@ -73,7 +73,7 @@ class ReplayShard:
     """
 
     def __init__(self, capacity, struct, max_batch, ring_depth=2, device=0, min_mode=MIN_SERVICE,
-                 store_rows=True, update_cluster=0):
+                 store_rows=True, update_cluster=0, gather_mode=0):
         self._h = None
         self._lib = _cabi.lib()
         self.capacity = int(capacity)
@@ -94,6 +94,7 @@ class ReplayShard:
         cfg.min_mode = int(min_mode)
         cfg.update_cluster = int(update_cluster)
         cfg.store_rows = int(self.store_rows)
+        cfg.gather_mode = int(gather_mode)      # 0 auto (TMA bulk when a column is wide), 1 LDG/STG, 2 TMA bulk
         h = C.c_void_p()
         rc = self._lib.reth_replay_create(C.byref(cfg), C.byref(h))
         if rc != 0:

@@ -10,6 +10,8 @@ pytestmark = pytest.mark.gpu
 
 ATARI = [(np.uint8, (4, 84, 84)), (np.int64, ()), (np.float32, ()), (np.uint8, (4, 84, 84)), (np.float32, ())]
 ODD = [(np.uint8, (7,)), (np.float64, (3,)), (np.int16, (5,)), (np.float32, (64, 8)), (np.uint8, (1,))]
+# float32 frames as test/apex-dqn/worker.py:47-51 sends them: 112 896 B rows -> two bulk chunks per row
+ATARI_F32 = [(np.float32, (4, 84, 84)), (np.int64, ()), (np.float32, ()), (np.float32, (4, 84, 84)), (np.float32, ())]
 
 
 @pytest.fixture(scope="module")
@@ -34,11 +36,12 @@ def _rows(rng, struct, n):
 
 @pytest.mark.parametrize("struct", [ATARI, ODD], ids=["atari", "odd"])
 @pytest.mark.parametrize("src", ["host", "device"])
-def test_append_wrap_and_gather(Shard, struct, src):
+@pytest.mark.parametrize("gather_mode", [1, 2], ids=["ldg", "tma"])
+def test_append_wrap_and_gather(Shard, struct, src, gather_mode):
     import torch
     cap, B = 1000, 96
     rng = np.random.default_rng(7)
-    sh = Shard(cap, struct, max_batch=B)
+    sh = Shard(cap, struct, max_batch=B, gather_mode=gather_mode)
     ring = po.OracleRing(cap, struct)
     for n in (300, 1, 450, 400, 999, 64, 1000):       # wraps several times, full-capacity append
         cols = _rows(rng, struct, n)
@@ -63,6 +66,33 @@ def test_append_wrap_and_gather(Shard, struct, src):
     cols_t, idx_t, w_t, _ = sh.slot_tensors(1)
     assert np.array_equal(cols_t[0].cpu().numpy(), data[0])
     assert np.array_equal(idx_t.cpu().numpy(), idx)
+    sh.close()
+
+
+@pytest.mark.parametrize("gather_mode", [1, 2], ids=["ldg", "tma"])
+@pytest.mark.parametrize("struct,B", [(ATARI, 700), (ATARI_F32, 64), (ATARI, 1)], ids=["atari700", "f32x64", "one"])
+def test_group_gather_modes(Shard, struct, B, gather_mode, monkeypatch):
+    """Multi-slot gather (one launch over G*B rows) and single-row batches, both gather kernels;
+    B=700 on a grid capped to 2 CTAs gives each CTA of the persistent TMA kernel several
+    rounds of its shared-memory slot cache (512 items per round)."""
+    cap, G = 3000, 4
+    rng = np.random.default_rng(11)
+    if B == 700:
+        monkeypatch.setenv("RETH_BULK_GRID", "2")
+    sh = Shard(cap, struct, max_batch=B, ring_depth=2 * G, gather_mode=gather_mode)
+    ring = po.OracleRing(cap, struct)
+    for n in (1500, 1500, 500):
+        cols = _rows(rng, struct, n)
+        sh.append(cols, rng.random(n).astype(np.float32) + 0.1)
+        ring.append_batch(cols)
+    for first in (0, G):
+        sh.sample_multi(B, first, G, seed=first + 1)
+        sh.gather_multi(first, G)
+        for g in range(G):
+            data, idx, _ = sh.slot_read(first + g, with_rows=True)
+            assert len(idx) == B
+            for got, want in zip(data, ring.select(idx)):
+                assert np.array_equal(got, want)
     sh.close()
 
 
