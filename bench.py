@@ -220,17 +220,17 @@ def timed_loop(torch, dist, shard, steps, warmup, iters, batch, prio, group, wor
     return ms, launches, shard.gather_time()
 
 
-def e2e_loop(torch, dist, service, addr, iters_total, warm, batch, world, group):
+def e2e_loop(torch, dist, service, addr, iters_total, warm, batch, world, group, ahead):
     """Public reth_buffer-style API with HOST buffers, per learner iteration:
         data, indices, weights = loader.sample()       # TorchCudaLoader: batch lent as CUDA tensors,
-                                                       # indices D2H to a host int64 array
+                                                       # indices = host int64 array (D2H inside)
         client.update_priorities(indices, loss)        # host int64 indices + host float32 |TD| -> H2D
-    group = loader prefetch / update coalescing (the reference's loader ring and PUSH queue);
-    group 1 = strict alternation."""
+    group/ahead = the loader's prefetch (the reference's loader ring + sampler queue);
+    group 1 / ahead 0 = strict alternation."""
     rng = np.random.default_rng(3)
     newp = np.abs(rng.standard_normal((64, batch))).astype(np.float32)
-    client = service.Client(addr, coalesce_updates=group)
-    loader = service.TorchCudaLoader(addr, buffer_size=max(2, 2 * group), prefetch=group)
+    client = service.Client(addr)
+    loader = service.TorchCudaLoader(addr, buffer_size=(ahead + 1) * group, prefetch=group, ahead=ahead)
     eng = service._ENGINES[addr]
 
     def it(i):
@@ -238,7 +238,7 @@ def e2e_loop(torch, dist, service, addr, iters_total, warm, batch, world, group)
         client.update_priorities(indices, newp[i % 64])
     for i in range(warm):
         it(i)
-    eng.flush()
+    eng.drain()
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
@@ -247,17 +247,17 @@ def e2e_loop(torch, dist, service, addr, iters_total, warm, batch, world, group)
     e0.record()
     for i in range(iters_total):
         it(warm + i)
-    eng.flush()
+    eng.drain()
     e1.record()
     torch.cuda.synchronize()
     wall = (time.perf_counter() - t0) * 1e3
-    ms = max(e0.elapsed_time(e1), wall)                 # host-bound loop: the wall clock is the honest one
+    ms = max(e0.elapsed_time(e1), wall)                 # host-driven loop: the wall clock is the honest one
     if world > 1:
         t = torch.tensor([ms], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
     loader.close()
-    return world * iters_total * batch / (ms / 1e3), batch * (8 + 4), batch * 8
+    return world * iters_total * batch / (ms / 1e3), batch * (8 + 4), batch * (8 + 8)
 
 
 def append_rate(torch, shard, n=16384, reps=10):
@@ -303,7 +303,8 @@ def run_ours(args):
     t0 = time.time()
     # the shard is owned by a reth_buffer-style server (start_per) so that the device loop and the
     # end-to-end loader/client loop run on the very same buffer
-    proc, addr = service.start_per(cap, B, alpha=ALPHA, beta=BETA, sample_start=B, device=local)
+    proc, addr = service.start_per(cap, B, alpha=ALPHA, beta=BETA, sample_start=B, device=local,
+                                   max_ring=max(16, (args.ahead + 1) * G))
     eng = service._ENGINES[addr]
     eng._ensure_shard(None, struct=ATARI)
     shard = eng.shard
@@ -336,8 +337,8 @@ def run_ours(args):
     # end to end through the public API with host buffers
     e2e_iters = min(4000, max(400, args.steps * iters))
     e2e_iters -= e2e_iters % G
-    e2e, h2d, d2h = e2e_loop(torch, dist, service, addr, e2e_iters, 64, B, world, G)
-    e2e_strict, _, _ = e2e_loop(torch, dist, service, addr, min(1000, e2e_iters), 16, B, world, 1)
+    e2e, h2d, d2h = e2e_loop(torch, dist, service, addr, e2e_iters, 64, B, world, G, args.ahead)
+    e2e_strict, _, _ = e2e_loop(torch, dist, service, addr, min(1000, e2e_iters), 16, B, world, 1, 0)
     app_rows, app_gbs = append_rate(torch, shard) if rank == 0 or world == 1 else (None, None)
 
     peak, peak_src = measured_peak()
@@ -361,9 +362,11 @@ def run_ours(args):
         "clocks": clk, "gpu_launches": int(launches),
         "e2e": {"value": e2e, "unit": "transitions/s", "h2d_bytes_per_step": h2d * iters, "d2h_bytes_per_step": d2h * iters,
                 "strict_alternation": e2e_strict,
+                "loader": {"prefetch_group": G, "groups_ahead": args.ahead, "buffer_size": (args.ahead + 1) * G},
                 "note": "reth_buffer-style public API per iteration: TorchCudaLoader.sample() (batch lent as CUDA "
-                        "tensors, indices D2H) + Client.update_priorities(host int64 indices, host float32 |TD|); "
-                        "loader prefetch = update coalescing = prefetch_group"},
+                        "tensors; indices + weights D2H into pinned host rings, indices returned as a host int64 "
+                        "array) + Client.update_priorities(host int64 indices, host float32 |TD|) -> pinned "
+                        "staging -> H2D -> tree update; strict_alternation = prefetch 1 / 0 ahead"},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": (achieved / peak) if achieved else None, "traffic": traffic, "peak_source": peak_src,
                      "kernel": "row_move_kernel<false> (frame gather)", "rows_per_launch": rows_per_launch,
@@ -402,6 +405,7 @@ def main():
     ap.add_argument("--batch", type=int, default=512)
     ap.add_argument("--iters", type=int, default=128, help="learner iterations per bench step")
     ap.add_argument("--group", type=int, default=4, help="prefetch group (reference loader ring: trainer.py:23 buffer_size=4)")
+    ap.add_argument("--ahead", type=int, default=1, help="e2e loader: groups drawn ahead of the one being consumed")
     ap.add_argument("--cpu-steps", type=int, default=4)
     ap.add_argument("--cpu-iters", type=int, default=64, help="iterations per step of the CPU arm (bounded sample)")
     ap.add_argument("--no-cpu", action="store_true")

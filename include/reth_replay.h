@@ -191,6 +191,50 @@ int reth_replay_sample_global(reth_replay_t *h, int global_batch, const double *
 /* host int64[2] = {first, count} of the last sample_global into `slot`; synchronises. */
 int reth_replay_slot_meta(reth_replay_t *h, int slot, int64_t *first_count, void *stream);
 
+
+/* ---- asynchronous loader pipeline (the end-to-end path with HOST index / priority buffers).
+ *      Replaces, in one process, what the reference spreads over sampler_loop (pre-sampled batch
+ *      behind a HWM-1 PUSH socket, server/sampler_loop.py:14,25-28,37-39), the TorchCudaLoader
+ *      worker processes + device ring + interprocess events (client/torch_cuda_loader.py:20-66,
+ *      94-135,152-163) and the fire-and-forget update channel (client/client.py:37-39 ->
+ *      server/main_loop.py:79-88 -> sampler_loop.py:29-36).
+ *  A "group" is `group` consecutive batch slots drawn by one launch; the batch ring holds
+ *  n_groups = ring_depth / group group slots.  pipe_issue() enqueues, without blocking, on the
+ *  shard's own streams:  sample `group` batches -> {indices, weights} D2H into pinned host rings
+ *  || gather of group*batch rows.  pipe_wait() blocks until the OLDEST issued group is complete
+ *  and lends it: its device batch slots and host index rows stay valid until the next
+ *  pipe_wait() (the borrow rule of TorchCudaLoader.sample, torch_cuda_loader.py:152-163).
+ *  At most n_groups - 1 groups can be issued-but-not-released at a time.
+ *  Priority write-back: pipe_update_begin() reserves an entry of a pinned staging ring (entry e
+ *  is the 16*entry_elems bytes at upd_host + e*16*entry_elems: int64 indices first, priorities
+ *  (float32 or float64, packed) from byte 8*entry_elems), pipe_update_commit() enqueues ONE host->device copy and
+ *  the tree update on the same stream as the sampling, so updates and draws are totally ordered
+ *  by call order (the reference's single SUB socket).  pipe_stream() is that stream: pass it
+ *  as `stream` to reth_replay_append() while a pipe is open to keep appends in the same order. */
+typedef struct reth_pipe_info {
+    int32_t batch, group, n_groups, upd_entries;
+    int64_t entry_elems;        /* elements per group slot / staging entry = group * batch */
+    int64_t *idx_host;          /* pinned int64 [n_groups][entry_elems]: delivered indices */
+    double *w_host;             /* pinned double[n_groups][entry_elems]: delivered IS weights */
+    void *upd_host;             /* pinned bytes [upd_entries][16*entry_elems] (see above) */
+} reth_pipe_info;
+int reth_replay_pipe_open(reth_replay_t *h, int batch, int group, uint64_t seed, reth_pipe_info *out);
+int reth_replay_pipe_close(reth_replay_t *h);
+int reth_replay_pipe_stream(reth_replay_t *h, void **stream_out);
+int reth_replay_pipe_issue(reth_replay_t *h, double beta);
+/* group_out: group slot g -> batch slots g*group .. g*group+group-1, host rows idx_host[g], w_host[g] */
+int reth_replay_pipe_wait(reth_replay_t *h, int32_t *group_out);
+/* pipe_wait() of the oldest group followed by pipe_issue() of a new one, in one call */
+int reth_replay_pipe_next(reth_replay_t *h, double beta, int32_t *group_out);
+int reth_replay_pipe_update_begin(reth_replay_t *h, int32_t *entry_out);
+int reth_replay_pipe_update_commit(reth_replay_t *h, int entry, int64_t n, int prio_dtype, double alpha,
+                                   int transform);
+/* convenience for C callers: begin + memcpy + commit */
+int reth_replay_update_async(reth_replay_t *h, const int64_t *idx_host, const void *prio_host, int prio_dtype,
+                             int64_t n, double alpha, int transform);
+/* wait until everything enqueued on the pipe's streams has finished */
+int reth_replay_pipe_drain(reth_replay_t *h);
+
 /* ---- measured loop (bench / learner-less soak): `steps` iterations of
  *      sample(batch) -> gather || update_slot(new priorities), the tree chain and the
  *      frame gather on two internal streams joined to `stream` at both ends, slots used

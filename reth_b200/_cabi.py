@@ -42,6 +42,12 @@ class Stats(C.Structure):
                                          "gathered_rows", "kernel_launches", "tail", "size", "hbm_bytes")]
 
 
+class PipeInfo(C.Structure):
+    _fields_ = [("batch", C.c_int32), ("group", C.c_int32), ("n_groups", C.c_int32), ("upd_entries", C.c_int32),
+                ("entry_elems", C.c_int64), ("idx_host", C.c_void_p), ("w_host", C.c_void_p),
+                ("upd_host", C.c_void_p)]
+
+
 def _sources():
     d = os.path.join(_HERE, "csrc")
     return [os.path.join(d, f) for f in sorted(os.listdir(d))] + [HEADER]
@@ -87,6 +93,16 @@ SIGNATURES = {
     "reth_replay_root_dev": [_vp, C.POINTER(_vp)],
     "reth_replay_sample_global": [_vp, _i32, _vp, _i32, _i32, _vp, _i32, _u64, _f64, _i32, _vp],
     "reth_replay_slot_meta": [_vp, _i32, C.POINTER(_i64), _vp],
+    "reth_replay_pipe_open": [_vp, _i32, _i32, _u64, C.POINTER(PipeInfo)],
+    "reth_replay_pipe_close": [_vp],
+    "reth_replay_pipe_stream": [_vp, C.POINTER(_vp)],
+    "reth_replay_pipe_issue": [_vp, _f64],
+    "reth_replay_pipe_wait": [_vp, C.POINTER(C.c_int32)],
+    "reth_replay_pipe_next": [_vp, _f64, C.POINTER(C.c_int32)],
+    "reth_replay_pipe_update_begin": [_vp, C.POINTER(C.c_int32)],
+    "reth_replay_pipe_update_commit": [_vp, _i32, _i64, _i32, _f64, _i32],
+    "reth_replay_update_async": [_vp, _vp, _vp, _i32, _i64, _f64, _i32],
+    "reth_replay_pipe_drain": [_vp],
     "reth_replay_step_loop": [_vp, _i32, _i32, _vp, _vp, _u64, _f64, _f64, _i32, _vp],
     "reth_replay_gather_time": [_vp, C.POINTER(_f64), C.POINTER(_i64)],
     "reth_replay_debug_stamps": [_vp, C.POINTER(_i64)],

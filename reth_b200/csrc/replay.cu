@@ -68,6 +68,22 @@ struct reth_replay {
     long long *dbg = nullptr;           // RETH_DEBUG_TIMING=1: stage clocks of the last update launch
     std::vector<cudaEvent_t> ev_time;   // pairs (start, stop) around timed gather launches
     size_t ev_time_used = 0;
+    // asynchronous loader pipeline (reth_replay_pipe_*)
+    struct Pipe {
+        bool open = false;
+        int batch = 0, G = 0, n_groups = 0, upd_entries = 0;
+        int64_t E = 0;
+        uint64_t seed = 0;
+        int64_t *idx_host = nullptr;
+        double *w_host = nullptr;
+        int32_t *err_host = nullptr;
+        uint8_t *upd_host = nullptr;
+        uint8_t *upd_dev = nullptr;
+        cudaStream_t s_copy = nullptr;
+        std::vector<cudaEvent_t> ev_smp, ev_gat, ev_done, ev_upd;
+        std::vector<char> upd_used;
+        int64_t issued = 0, waited = 0, upd_next = 0;
+    } pipe;
     std::string error;
 };
 
@@ -253,12 +269,15 @@ RETH_EXPORT int reth_replay_create(const reth_replay_config *cfg, reth_replay_t 
     return RETH_OK;
 }
 
+namespace { void pipe_free(reth_replay *h); }
+
 RETH_EXPORT int reth_replay_destroy(reth_replay_t *h)
 {
     if (!h) return RETH_OK;
     {
         DeviceGuard guard(h->cfg.device);
         cudaDeviceSynchronize();
+        pipe_free(h);
         free_all(h);
     }
     delete h;
@@ -860,6 +879,236 @@ RETH_EXPORT int reth_replay_stats_get(reth_replay_t *h, reth_replay_stats *out)
     h->st.tail = h->tail;
     h->st.size = h->size;
     *out = h->st;
+    return RETH_OK;
+}
+
+
+// ------------------------------------------------------- asynchronous pipeline --
+namespace {
+
+void pipe_free(reth_replay *h)
+{
+    auto &p = h->pipe;
+    if (p.idx_host) cudaFreeHost(p.idx_host);
+    if (p.w_host) cudaFreeHost(p.w_host);
+    if (p.err_host) cudaFreeHost(p.err_host);
+    if (p.upd_host) cudaFreeHost(p.upd_host);
+    cudaFree(p.upd_dev);
+    for (auto *v : {&p.ev_smp, &p.ev_gat, &p.ev_done, &p.ev_upd}) {
+        for (auto e : *v) cudaEventDestroy(e);
+        v->clear();
+    }
+    if (p.s_copy) cudaStreamDestroy(p.s_copy);
+    p = reth_replay::Pipe();
+}
+
+int pipe_issue(reth_replay *h, double beta)
+{
+    auto &p = h->pipe;
+    if (!p.open) return fail(h, RETH_ERR_STATE, "no pipe is open");
+    if (p.issued - p.waited + (p.waited > 0 ? 1 : 0) >= p.n_groups)
+        return fail(h, RETH_ERR_STATE, "all %d group slots are issued or lent", p.n_groups);
+    const int g = (int)(p.issued % p.n_groups), slot = g * p.G;
+    int rc = do_sample(h, p.batch, nullptr, RETH_DEVICE, p.seed, beta, slot, nullptr, 1, 0, h->s_tree, p.G);
+    if (rc) return rc;
+    CK(h, cudaEventRecord(p.ev_smp[g], h->s_tree));
+    CK(h, cudaStreamWaitEvent(p.s_copy, p.ev_smp[g], 0));
+    const size_t E = (size_t)p.E;
+    CK(h, cudaMemcpyAsync(p.idx_host + g * E, h->slots[slot].idx, E * 8, cudaMemcpyDeviceToHost, p.s_copy));
+    CK(h, cudaMemcpyAsync(p.w_host + g * E, h->slots[slot].w, E * 8, cudaMemcpyDeviceToHost, p.s_copy));
+    CK(h, cudaMemcpyAsync(p.err_host + g, h->err, sizeof(int32_t), cudaMemcpyDeviceToHost, p.s_copy));
+    CK(h, cudaStreamWaitEvent(h->s_gather, p.ev_smp[g], 0));
+    rc = do_gather(h, slot, false, h->s_gather, p.G);
+    if (rc) return rc;
+    CK(h, cudaEventRecord(p.ev_gat[g], h->s_gather));
+    CK(h, cudaStreamWaitEvent(p.s_copy, p.ev_gat[g], 0));
+    CK(h, cudaEventRecord(p.ev_done[g], p.s_copy));
+    p.issued++;
+    return RETH_OK;
+}
+
+int pipe_wait(reth_replay *h, int32_t *group_out)
+{
+    auto &p = h->pipe;
+    if (!p.open) return fail(h, RETH_ERR_STATE, "no pipe is open");
+    if (p.issued <= p.waited) return fail(h, RETH_ERR_STATE, "pipe_wait: no group has been issued");
+    const int g = (int)(p.waited % p.n_groups);
+    CK(h, cudaEventSynchronize(p.ev_done[g]));
+    p.waited++;
+    if (group_out) *group_out = g;
+    if (p.err_host[g]) {
+        cudaMemsetAsync(h->err, 0, sizeof(int32_t), h->s_tree);
+        return fail(h, RETH_ERR_RANGE, "an index outside [0, capacity) was passed to the shard");
+    }
+    return RETH_OK;
+}
+
+}  // namespace
+
+RETH_EXPORT int reth_replay_pipe_open(reth_replay_t *h, int batch, int group, uint64_t seed, reth_pipe_info *out)
+{
+    if (!h) return RETH_ERR_INVALID;
+    auto &p = h->pipe;
+    if (p.open) return fail(h, RETH_ERR_STATE, "a pipe is already open");
+    const int depth = (int)h->slots.size();
+    if (group < 1 || batch < 1 || batch > h->cfg.max_batch || (group > 1 && batch != h->cfg.max_batch))
+        return fail(h, RETH_ERR_INVALID, "pipe: batch %d / group %d invalid (group > 1 needs batch == max_batch)", batch, group);
+    if (depth / group < 2) return fail(h, RETH_ERR_INVALID, "pipe: ring_depth %d holds fewer than 2 groups of %d", depth, group);
+    if ((int64_t)batch * group > h->max_n) return fail(h, RETH_ERR_INVALID, "pipe: group of %d rows exceeds %lld", batch * group, (long long)h->max_n);
+    DeviceGuard guard(h->cfg.device);
+    p.batch = batch; p.G = group; p.n_groups = depth / group; p.E = (int64_t)batch * group;
+    p.upd_entries = 2 * p.n_groups + 2;
+    p.seed = seed;
+    const size_t E = (size_t)p.E;
+    auto bail = [&](int code) { pipe_free(h); return code; };
+#define CKP(expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) return bail(fail(h, RETH_ERR_CUDA, "%s: %s", #expr, cudaGetErrorString(e__))); } while (0)
+    CKP(cudaMallocHost((void **)&p.idx_host, p.n_groups * E * 8));
+    CKP(cudaMallocHost((void **)&p.w_host, p.n_groups * E * 8));
+    CKP(cudaMallocHost((void **)&p.err_host, p.n_groups * sizeof(int32_t)));
+    memset(p.err_host, 0, p.n_groups * sizeof(int32_t));
+    CKP(cudaMallocHost((void **)&p.upd_host, p.upd_entries * E * 16));
+    CKP(cudaMalloc((void **)&p.upd_dev, E * 16));
+    CKP(cudaStreamCreateWithFlags(&p.s_copy, cudaStreamNonBlocking));
+    for (auto *v : {&p.ev_smp, &p.ev_gat, &p.ev_done})
+        for (int i = 0; i < p.n_groups; ++i) {
+            cudaEvent_t e;
+            CKP(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            v->push_back(e);
+        }
+    for (int i = 0; i < p.upd_entries; ++i) {
+        cudaEvent_t e;
+        CKP(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        p.ev_upd.push_back(e);
+    }
+#undef CKP
+    p.upd_used.assign(p.upd_entries, 0);
+    p.issued = p.waited = p.upd_next = 0;
+    p.open = true;
+    if (out) {
+        out->batch = batch; out->group = group; out->n_groups = p.n_groups; out->upd_entries = p.upd_entries;
+        out->entry_elems = p.E; out->idx_host = p.idx_host; out->w_host = p.w_host; out->upd_host = p.upd_host;
+    }
+    return RETH_OK;
+}
+
+RETH_EXPORT int reth_replay_pipe_close(reth_replay_t *h)
+{
+    if (!h) return RETH_ERR_INVALID;
+    if (!h->pipe.open) return RETH_OK;
+    DeviceGuard guard(h->cfg.device);
+    cudaStreamSynchronize(h->s_tree);
+    cudaStreamSynchronize(h->s_gather);
+    cudaStreamSynchronize(h->pipe.s_copy);
+    pipe_free(h);
+    return RETH_OK;
+}
+
+RETH_EXPORT int reth_replay_pipe_stream(reth_replay_t *h, void **stream_out)
+{
+    if (!h || !stream_out) return RETH_ERR_INVALID;
+    *stream_out = (void *)h->s_tree;
+    return RETH_OK;
+}
+
+RETH_EXPORT int reth_replay_pipe_issue(reth_replay_t *h, double beta)
+{
+    if (!h) return RETH_ERR_INVALID;
+    DeviceGuard guard(h->cfg.device);
+    return pipe_issue(h, beta);
+}
+
+RETH_EXPORT int reth_replay_pipe_wait(reth_replay_t *h, int32_t *group_out)
+{
+    if (!h) return RETH_ERR_INVALID;
+    DeviceGuard guard(h->cfg.device);
+    return pipe_wait(h, group_out);
+}
+
+RETH_EXPORT int reth_replay_pipe_next(reth_replay_t *h, double beta, int32_t *group_out)
+{
+    if (!h) return RETH_ERR_INVALID;
+    DeviceGuard guard(h->cfg.device);
+    int rc = pipe_wait(h, group_out);
+    if (rc) return rc;
+    return pipe_issue(h, beta);
+}
+
+RETH_EXPORT int reth_replay_pipe_update_begin(reth_replay_t *h, int32_t *entry_out)
+{
+    if (!h || !entry_out) return RETH_ERR_INVALID;
+    auto &p = h->pipe;
+    if (!p.open) return fail(h, RETH_ERR_STATE, "no pipe is open");
+    const int e = (int)(p.upd_next % p.upd_entries);
+    if (p.upd_used[e]) {
+        DeviceGuard guard(h->cfg.device);
+        CK(h, cudaEventSynchronize(p.ev_upd[e]));     // its previous host->device copy has drained
+        p.upd_used[e] = 0;
+    }
+    *entry_out = e;
+    return RETH_OK;
+}
+
+RETH_EXPORT int reth_replay_pipe_update_commit(reth_replay_t *h, int entry, int64_t n, int prio_dtype, double alpha,
+                                               int transform)
+{
+    if (!h) return RETH_ERR_INVALID;
+    auto &p = h->pipe;
+    if (!p.open) return fail(h, RETH_ERR_STATE, "no pipe is open");
+    if (entry != (int)(p.upd_next % p.upd_entries)) return fail(h, RETH_ERR_STATE, "commit of entry %d out of order", entry);
+    if (n < 0 || n > p.E) return fail(h, RETH_ERR_INVALID, "commit of %lld elements exceeds the entry (%lld)", (long long)n, (long long)p.E);
+    if (prio_dtype != RETH_F32 && prio_dtype != RETH_F64) return fail(h, RETH_ERR_INVALID, "priorities must be float32 or float64");
+    if (n == 0) return RETH_OK;
+    DeviceGuard guard(h->cfg.device);
+    const size_t E = (size_t)p.E, ps = dtype_size(prio_dtype);
+    const uint8_t *src = p.upd_host + (size_t)entry * E * 16;
+    if ((size_t)n == E) {
+        CK(h, cudaMemcpyAsync(p.upd_dev, src, E * 8 + E * ps, cudaMemcpyHostToDevice, h->s_tree));
+    } else {
+        CK(h, cudaMemcpyAsync(p.upd_dev, src, (size_t)n * 8, cudaMemcpyHostToDevice, h->s_tree));
+        CK(h, cudaMemcpyAsync(p.upd_dev + E * 8, src + E * 8, (size_t)n * ps, cudaMemcpyHostToDevice, h->s_tree));
+    }
+    CK(h, cudaEventRecord(p.ev_upd[entry], h->s_tree));
+    p.upd_used[entry] = 1;
+    p.upd_next++;
+    UpdateArgs a = {};
+    a.n = n; a.idx = p.upd_dev; a.idx_kind = 0;
+    a.prio = p.upd_dev + E * 8; a.prio_kind = prio_dtype == RETH_F32 ? 0 : 1;
+    a.alpha = alpha; a.transform = transform; a.dedupe = 1;
+    int rc = launch_update(h, a, h->s_tree);
+    if (rc) return rc;
+    h->st.updated_rows += n;
+    return RETH_OK;
+}
+
+RETH_EXPORT int reth_replay_update_async(reth_replay_t *h, const int64_t *idx_host, const void *prio_host,
+                                         int prio_dtype, int64_t n, double alpha, int transform)
+{
+    if (!h) return RETH_ERR_INVALID;
+    if (!h->pipe.open) return fail(h, RETH_ERR_STATE, "no pipe is open");
+    if (n < 0 || (n > 0 && (!idx_host || !prio_host))) return fail(h, RETH_ERR_INVALID, "bad arguments");
+    if (prio_dtype != RETH_F32 && prio_dtype != RETH_F64) return fail(h, RETH_ERR_INVALID, "priorities must be float32 or float64");
+    const size_t ps = dtype_size(prio_dtype);
+    for (int64_t off = 0; off < n; off += h->pipe.E) {
+        const int64_t m = n - off < h->pipe.E ? n - off : h->pipe.E;
+        int32_t e = 0;
+        int rc = reth_replay_pipe_update_begin(h, &e);
+        if (rc) return rc;
+        uint8_t *dst = h->pipe.upd_host + (size_t)e * h->pipe.E * 16;
+        memcpy(dst, idx_host + off, (size_t)m * 8);
+        memcpy(dst + h->pipe.E * 8, (const uint8_t *)prio_host + off * ps, (size_t)m * ps);
+        rc = reth_replay_pipe_update_commit(h, e, m, prio_dtype, alpha, transform);
+        if (rc) return rc;
+    }
+    return RETH_OK;
+}
+
+RETH_EXPORT int reth_replay_pipe_drain(reth_replay_t *h)
+{
+    if (!h) return RETH_ERR_INVALID;
+    DeviceGuard guard(h->cfg.device);
+    CK(h, cudaStreamSynchronize(h->s_tree));
+    CK(h, cudaStreamSynchronize(h->s_gather));
+    if (h->pipe.open) CK(h, cudaStreamSynchronize(h->pipe.s_copy));
     return RETH_OK;
 }
 

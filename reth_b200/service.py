@@ -14,10 +14,12 @@ process (the fast path: calls go straight to the C ABI under a lock, which repro
 total order the reference gets from its single SUB socket, sampler_loop.py:30-36).  Row
 storage, slot allocation, tree, sampling, IS weights and the batch gather all run on the GPU.
 
-Staleness semantics are kept: a loader pre-samples `prefetch` batches per launch group, the
-analogue of sampler HWM 1 + the loader ring (torch_cuda_loader.py:70, trainer.py:23), so a
-priority update lands after up to `prefetch` further batches were drawn.  prefetch=1 gives the
-strict alternation of the in-process twin.
+Staleness semantics are kept: batches are drawn ahead of their consumption, `prefetch` per
+launch group and `ahead` groups beyond the one being consumed -- the analogue of the sampler's
+HWM-1 PUSH socket + the loader worker processes + the loader ring (sampler_loop.py:14,
+torch_cuda_loader.py:70, trainer.py:23) -- so a priority update lands after up to
+(ahead + 1) * prefetch further batches were drawn.  prefetch=1, ahead=0 gives the strict
+alternation of the in-process twin.  Priority write-backs are fire-and-forget (client.py:37-39).
 """
 import itertools
 import threading
@@ -34,9 +36,14 @@ _SCHEME = "inproc://reth-b200/"
 
 
 class _Engine:
-    """Server-side state of one replay buffer: shard + PER schedules + gating counters."""
+    """Server-side state of one replay buffer: shard + PER schedules + gating counters.
 
-    def __init__(self, capacity, batch_size, samplers=None, cache_policy=None, device=0):
+    Every mutation (append, update, draw) is enqueued on the shard's own ordering stream, in
+    call order, under `lock`: the total order the reference gets from its single SUB socket
+    (sampler_loop.py:30-36).  Nothing here waits for the device except a loader taking delivery
+    of a pre-sampled group (ShardPipe.wait)."""
+
+    def __init__(self, capacity, batch_size, samplers=None, cache_policy=None, device=0, max_ring=16):
         self.capacity = int(capacity)
         self.batch_size = int(batch_size)
         self.device = device
@@ -65,11 +72,22 @@ class _Engine:
         self.cache_policy = cache_policy
         self.shard = None
         self.struct = None
+        self.stream = None                                    # the shard's ordering stream
         self.cnt = 0                                          # sampler_loop.py:20,36
         self.lock = threading.RLock()
-        self._pending = []
         self.closed = False
-        self.max_ring = 16
+        self.max_ring = int(max_ring)
+        # loader pipeline (opened by the first loader): groups of `group` batches, `ahead` groups
+        # issued beyond the one being consumed
+        self.pipe = None
+        self.group = 1
+        self.ahead = 0
+        self.loaders = 0
+        self._queue = []                                      # delivered, not yet consumed: (slot, indices)
+        # priority write-backs being coalesced into one staging entry
+        self._upd_e = -1
+        self._upd_k = 0
+        self._upd_f32 = True
 
     # -- server side of Client.append (server/main_loop.py:44-58) -----------
     def _ensure_shard(self, data, struct=None):
@@ -78,55 +96,148 @@ class _Engine:
         self.struct = struct or [(np.asarray(col).dtype, tuple(np.asarray(col).shape[1:])) for col in data]
         self.shard = ReplayShard(self.capacity, self.struct, max_batch=self.batch_size,
                                  ring_depth=self.max_ring, device=self.device, min_mode=MIN_SERVICE)
+        self.stream = self.shard.pipe_stream
 
     def append(self, data, weights):
         with self.lock:
             self._ensure_shard(data)
             alpha = self.sampler["alpha"].value()
             if self.cache_policy is None:
-                self.shard.append(list(data), weights, alpha=alpha, transform=True)
+                self.shard.append(list(data), weights, alpha=alpha, transform=True, stream=self.stream)
             else:
                 import torch
                 slots = np.asarray(self.cache_policy.get_indices(len(weights)), dtype=np.int64)
                 dev = [torch.from_numpy(np.ascontiguousarray(c, dtype=dt)).cuda(self.device)
                        for c, (dt, _) in zip(data, self.struct)]
-                self.shard.append_at(slots, dev, weights, alpha=alpha, transform=True)
+                torch.cuda.current_stream(self.device).synchronize()
+                self.shard.append_at(slots, dev, weights, alpha=alpha, transform=True, stream=self.stream)
             self.cnt += len(weights)
 
-    def update(self, indices, weights, step, coalesce=1):
-        """sampler_loop.py:29-36.  coalesce > 1: updates are queued like the frames the reference
-        keeps in its PUSH/SUB pipes (fire-and-forget, client.py:37-39) and written back in one
-        launch once `coalesce` are pending or the sampler is about to draw (flush()); order and
-        last-writer-wins are those of the message sequence.  alpha is constant over a run here
-        when coalescing (the schedule still advances once per message)."""
+    # -- loader pipeline --------------------------------------------------
+    def open_pipe(self, group, ahead):
+        """Called by a loader: `group` batches per launch group, `ahead` groups in flight beyond
+        the one being consumed (ahead 0 = strict alternation: a draw sees every earlier update)."""
+        with self.lock:
+            group = max(1, int(group))
+            ahead = max(0, int(ahead))
+            if self.pipe is not None:
+                if (group, ahead) != (self.group, self.ahead):
+                    if self.loaders > 0:
+                        raise ValueError(f"this buffer already serves loaders with prefetch group {self.group} / "
+                                         f"{self.ahead} ahead")
+                    self._close_pipe()
+            self.group, self.ahead = group, ahead
+            self.loaders += 1
+
+    def _close_pipe(self):
+        if self.pipe is not None:
+            self.flush()
+            self.pipe.close()
+            self.pipe = None
+            self._queue = []
+
+    def release_pipe(self):
+        with self.lock:
+            self.loaders = max(0, self.loaders - 1)
+            if self.loaders == 0:
+                self._close_pipe()
+
+    def _ensure_pipe(self):
+        if self.pipe is None:
+            need = (self.ahead + 1) * self.group
+            if need > self.shard.ring_depth:
+                raise ValueError(f"prefetch of {need} batches exceeds the batch ring ({self.shard.ring_depth})")
+            self.pipe = self.shard.open_pipe(self.batch_size, self.group, seed=0x5EED)
+        return self.pipe
+
+    def next_batch(self):
+        """-> (batch slot, host indices view) of the next pre-sampled batch."""
+        if self._queue:
+            return self._queue.pop()
+        self.wait_ready()
+        with self.lock:
+            if self._queue:
+                return self._queue.pop()
+            pipe = self._ensure_pipe()
+            self.flush()                                      # partially staged write-backs land before the draw
+            beta = self.sampler["beta"].value()
+            if pipe.in_flight == self.ahead and self.ahead > 0:
+                g = pipe.next(beta)                           # steady state: take delivery + draw one more group
+            else:
+                if pipe.in_flight == 0:                       # first delivery, or strict alternation
+                    pipe.issue(beta)
+                g = pipe.wait()
+                while pipe.in_flight < self.ahead and pipe.can_issue():
+                    pipe.issue(beta)
+            G = self.group
+            idx = pipe.idx_host[g]
+            self._queue = [(g * G + k, idx[k]) for k in range(G - 1, -1, -1)]
+            return self._queue.pop()
+
+    # -- server side of Client.update_priorities (sampler_loop.py:29-36) --
+    def update(self, indices, weights, step):
+        """Fire-and-forget like the reference (client.py:37-39): the write-back is staged in pinned
+        host memory and enqueued behind everything issued so far; `group` consecutive messages of
+        batch_size share one staging entry = one host->device copy + one tree-update launch (the
+        frames the reference keeps in its PUSH/SUB pipes).  Order and last-writer-wins are those of
+        the message sequence; alpha is read when the entry is committed."""
         with self.lock:
             if self.shard is None:
-                return                                        # nothing stored yet: the reference drops into an empty tree
+                return                                        # nothing stored yet: the reference updates an empty tree
             if step:                                          # sampler_loop.py:33-34, per_sampler.py:30-32
                 self.sampler["alpha"].step()
                 self.sampler["beta"].step()
-            self.cnt += len(indices)
-            if coalesce <= 1 and not self._pending:
-                self.shard.update(indices, weights, alpha=self.sampler["alpha"].value(), transform=True)
+            n = len(indices)
+            self.cnt += n
+            pipe = self.pipe
+            B = self.batch_size
+            w = weights if isinstance(weights, np.ndarray) else np.asarray(weights)
+            if pipe is None:
+                self.shard.update(np.asarray(indices), w, alpha=self.sampler["alpha"].value(), transform=True,
+                                  stream=self.stream)
                 return
-            self._pending.append((np.asarray(indices, dtype=np.int64), np.asarray(weights)))
-            if len(self._pending) >= coalesce:
+            f32 = w.dtype == np.float32
+            if n != B:                                        # not a learner batch: one launch per 16 384 indices
+                self.flush()
+                self.shard.update(np.asarray(indices), w, alpha=self.sampler["alpha"].value(), transform=True,
+                                  stream=self.stream)
+                return
+            k = self._upd_k
+            if k and f32 != self._upd_f32:
+                self.flush()
+                k = 0
+            if k == 0:
+                self._upd_e = pipe.update_begin()
+                self._upd_f32 = f32
+            e = self._upd_e
+            pipe.upd_idx[e, k * B:(k + 1) * B] = indices
+            (pipe.upd_p32 if f32 else pipe.upd_p64)[e, k * B:(k + 1) * B] = w
+            self._upd_k = k + 1
+            if k + 1 >= self.group:
                 self.flush()
 
     def flush(self):
         with self.lock:
-            if not self._pending or self.shard is None:
-                return
-            idx = np.concatenate([p[0] for p in self._pending])
-            dts = {p[1].dtype for p in self._pending}
-            w = np.concatenate([p[1] if len(dts) == 1 else p[1].astype(np.float64) for p in self._pending])
-            self._pending = []
-            self.shard.update(idx, w, alpha=self.sampler["alpha"].value(), transform=True)
+            if self._upd_k and self.pipe is not None:
+                k, self._upd_k = self._upd_k, 0
+                self.pipe.update_commit(self._upd_e, k * self.batch_size, self._upd_f32,
+                                        self.sampler["alpha"].value())
+
+    def drain(self):
+        """Block until every enqueued append / update / draw has executed (tests, benchmarks)."""
+        with self.lock:
+            self.flush()
+            if self.pipe is not None:
+                self.pipe.drain()
+            elif self.shard is not None:
+                self.shard._ck(self.shard._lib.reth_replay_pipe_drain(self.shard._h))
 
     def ready(self):
         return self.shard is not None and self.cnt >= self.sampler["sample_start"]
 
     def wait_ready(self, timeout=60.0):
+        if self.ready():
+            return
         t0 = time.time()
         while not self.ready():
             if self.closed:
@@ -138,6 +249,9 @@ class _Engine:
     def close(self):
         with self.lock:
             self.closed = True
+            if self.pipe is not None:
+                self.pipe.close()
+                self.pipe = None
             if self.shard is not None:
                 self.shard.close()
                 self.shard = None
@@ -164,20 +278,21 @@ class _ServerHandle:
     kill = terminate
 
 
-def start_server(capacity, batch_size, host=None, port=None, samplers=None, cache_policy=None, device=0):
+def start_server(capacity, batch_size, host=None, port=None, samplers=None, cache_policy=None, device=0,
+                 max_ring=16):
     """reth_buffer.start_server (__init__.py:11-27).  host/port are accepted for signature
     compatibility; the engine is reached through the returned in-process address."""
     addr = f"{_SCHEME}{next(_COUNTER)}"
-    _ENGINES[addr] = _Engine(capacity, batch_size, samplers, cache_policy, device)
+    _ENGINES[addr] = _Engine(capacity, batch_size, samplers, cache_policy, device, max_ring)
     return _ServerHandle(addr), addr
 
 
 def start_per(capacity, batch_size, alpha=0.6, beta=0.4, sample_start=1000, num_sampler_procs=1,
-              host=None, port=None, cache_policy=None, device=0):
+              host=None, port=None, cache_policy=None, device=0, max_ring=16):
     """reth_buffer.start_per (__init__.py:30-49)."""
     samplers = [{"sampler_cls": PERSampler, "num_procs": num_sampler_procs, "sample_start": sample_start,
                  "kwargs": {"alpha": alpha, "beta": beta}}]
-    return start_server(capacity, batch_size, host, port, samplers, cache_policy, device)
+    return start_server(capacity, batch_size, host, port, samplers, cache_policy, device, max_ring)
 
 
 def _engine(meta_addr):
@@ -190,9 +305,8 @@ def _engine(meta_addr):
 class Client:
     """client/client.py:8-39."""
 
-    def __init__(self, meta_addr, coalesce_updates=1):
+    def __init__(self, meta_addr):
         self._eng = _engine(meta_addr)
-        self.coalesce_updates = int(coalesce_updates)
         self.meta = {"capacity": self._eng.capacity, "batch_size": self._eng.batch_size, "meta_addr": meta_addr}
 
     def append(self, data, weights, compress=False):
@@ -204,17 +318,21 @@ class Client:
 
     def update_priorities(self, indices, weights, step=True):
         assert len(indices) == len(weights)                   # :38
-        self._eng.update(np.asarray(indices), np.asarray(weights), step, self.coalesce_updates)
+        self._eng.update(indices, weights, step)
 
 
 class _LoaderBase:
-    def __init__(self, meta_addr, topic="default", prefetch=1):
+    """prefetch = batches per launch group, ahead = groups in flight beyond the one being consumed;
+    (ahead + 1) * prefetch batches are resident in the lending ring (the reference's buffer_size)."""
+
+    def __init__(self, meta_addr, topic="default", prefetch=1, ahead=0):
         self._eng = _engine(meta_addr)
         assert topic == self._eng.topic
         self.meta = {"capacity": self._eng.capacity, "batch_size": self._eng.batch_size}
         self.prefetch = max(1, int(prefetch))
-        self._queue = []          # (slot, indices) of pre-sampled, not yet delivered batches
-        self._next_group = 0
+        self.ahead = max(0, int(ahead))
+        self._eng.open_pipe(self.prefetch, self.ahead)
+        self._open = True
 
     def __iter__(self):
         return self
@@ -222,80 +340,63 @@ class _LoaderBase:
     def __next__(self):
         return self.sample()
 
-    def _refill(self):
-        eng = self._eng
-        eng.wait_ready()
-        with eng.lock:
-            eng.flush()                                       # pending priority messages land before the draw
-            sh, B, G = eng.shard, eng.batch_size, self.prefetch
-            depth = sh.ring_depth
-            first = self._next_group
-            if first + G > depth:
-                first = 0
-            self._next_group = first + G if first + 2 * G <= depth else 0
-            beta = eng.sampler["beta"].value()
-            if G == 1:
-                sh.sample(B, beta=beta, seed=0x5EED, slot=first)
-                sh.gather(first)
-            else:
-                sh.sample_multi(B, first, G, beta=beta, seed=0x5EED)
-                sh.gather_multi(first, G)
-            if G == 1:
-                idx, _ = sh.group_read(first, 1)
-                self._queue.append((first, idx))
-            else:                                             # one D2H of all indices, one sync per group
-                idx, _ = sh.group_read(first, G)
-                for g in range(G):
-                    self._queue.append((first + g, idx[g * B:(g + 1) * B]))
-
     def get_indices(self):
         """numpy_loader.py:53-56: (indices, weights) of the next batch."""
-        if not self._queue:
-            self._refill()
-        slot, idx = self._queue.pop(0)
-        _, _, w = self._eng.shard.slot_read(slot)
-        return idx, w
+        slot, idx = self._eng.next_batch()
+        pipe = self._eng.pipe
+        return np.array(idx), np.array(pipe.w_host[slot // pipe.group, slot % pipe.group])
 
     def close(self):
-        self._queue = []
+        if self._open:
+            self._open = False
+            self._eng.release_pipe()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 class NumpyLoader(_LoaderBase):
     """client/numpy_loader.py:8-56: fresh host arrays (data, indices int64, weights float64)."""
 
-    def __init__(self, meta_addr, topic="default", prefetch=1):
-        super().__init__(meta_addr, topic, prefetch)
+    def __init__(self, meta_addr, topic="default", prefetch=1, ahead=0):
+        super().__init__(meta_addr, topic, prefetch, ahead)
 
     def sample(self):
-        if not self._queue:
-            self._refill()
-        slot, _ = self._queue.pop(0)
-        with self._eng.lock:
-            data, indices, weights = self._eng.shard.slot_read(slot, with_rows=True)
-        return data, indices, weights
+        eng = self._eng
+        slot, idx = eng.next_batch()
+        with eng.lock:
+            data, _, _ = eng.shard.slot_read(slot, with_rows=True, stream=eng.stream)
+            pipe = eng.pipe
+            return data, np.array(idx), np.array(pipe.w_host[slot // pipe.group, slot % pipe.group])
 
 
 class TorchCudaLoader(_LoaderBase):
     """client/torch_cuda_loader.py:69-163: data = list of CUDA tensors lent until the next
     sample() (:152-163), indices on the host (np.int64), weights a CUDA float64 tensor.
-    buffer_size = depth of the lending ring; prefetch defaults to buffer_size // 2 batches drawn
-    per launch group (the reference keeps buffer_size batches in flight)."""
+    buffer_size = batches resident in the lending ring, as in the reference; by default half of
+    them form the group being consumed and the other half is drawn + gathered ahead
+    (prefetch = buffer_size // 2, ahead = 1).  prefetch=1, ahead=0 is strict alternation."""
 
-    def __init__(self, meta_addr, topic="default", buffer_size=8, num_procs=6, prefetch=None):
+    def __init__(self, meta_addr, topic="default", buffer_size=8, num_procs=6, prefetch=None, ahead=None):
         eng = _engine(meta_addr)
-        buffer_size = max(2, min(int(buffer_size), eng.max_ring))
-        g = max(1, buffer_size // 2) if prefetch is None else int(prefetch)
-        super().__init__(meta_addr, topic, min(g, eng.max_ring // 2))
+        buffer_size = max(1, min(int(buffer_size), eng.max_ring))
+        if prefetch is None:
+            prefetch = max(1, buffer_size // 2)
+        if ahead is None:
+            ahead = max(0, buffer_size // int(prefetch) - 1)
+        ahead = min(int(ahead), max(0, eng.max_ring // int(prefetch) - 1))
+        super().__init__(meta_addr, topic, prefetch, ahead)
         self.buffer_size = buffer_size
         self.num_procs = num_procs                            # accepted, unused: no gather processes are needed
         self._views = {}                                      # slot -> cached zero-copy torch views
 
     def sample(self):
-        if not self._queue:
-            self._refill()
-        slot, indices = self._queue.pop(0)
+        slot, idx = self._eng.next_batch()
         v = self._views.get(slot)
         if v is None:
             data, _, weights, _ = self._eng.shard.slot_tensors(slot)
             v = self._views[slot] = (data, weights)
-        return v[0], indices, v[1]
+        return v[0], np.array(idx), v[1]

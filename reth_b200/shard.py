@@ -65,6 +65,85 @@ def _stream_handle(stream, device):
     return int(stream)
 
 
+class ShardPipe:
+    """Asynchronous loader pipeline of a shard (reth_replay_pipe_*, include/reth_replay.h):
+    groups of `group` batches are drawn + gathered ahead on the shard's own streams, indices and
+    weights land in pinned host rings, priority write-backs go through a pinned staging ring."""
+
+    def __init__(self, shard, batch, group, seed=0):
+        self.shard = shard
+        self._lib, self._h = shard._lib, shard._h
+        info = _cabi.PipeInfo()
+        shard._ck(self._lib.reth_replay_pipe_open(self._h, int(batch), int(group), int(seed) & (2**64 - 1),
+                                                  C.byref(info)))
+        self.batch, self.group, self.n_groups = info.batch, info.group, info.n_groups
+        self.upd_entries, E = info.upd_entries, info.entry_elems
+        self.entry_elems = E
+
+        def host(addr, nbytes):
+            return np.frombuffer((C.c_uint8 * nbytes).from_address(addr), np.uint8)
+        self.idx_host = host(info.idx_host, self.n_groups * E * 8).view(np.int64).reshape(self.n_groups, group, batch)
+        self.w_host = host(info.w_host, self.n_groups * E * 8).view(np.float64).reshape(self.n_groups, group, batch)
+        raw = host(info.upd_host, self.upd_entries * E * 16).reshape(self.upd_entries, E * 16)
+        self.upd_idx = raw[:, :E * 8].view(np.int64)              # [entry][E]
+        self.upd_p32 = raw[:, E * 8:E * 12].view(np.float32)      # [entry][E]
+        self.upd_p64 = raw[:, E * 8:].view(np.float64)            # [entry][E]
+        self.issued = self.waited = 0
+        self._g = C.c_int32()
+        self._e = C.c_int32()
+        p = C.c_void_p()
+        shard._ck(self._lib.reth_replay_pipe_stream(self._h, C.byref(p)))
+        self.stream = p.value
+
+    @property
+    def in_flight(self):
+        return self.issued - self.waited
+
+    def can_issue(self):
+        return self.in_flight + (1 if self.waited else 0) < self.n_groups
+
+    def issue(self, beta):
+        self.shard._ck(self._lib.reth_replay_pipe_issue(self._h, float(beta)))
+        self.issued += 1
+
+    def wait(self):
+        self.shard._ck(self._lib.reth_replay_pipe_wait(self._h, C.byref(self._g)))
+        self.waited += 1
+        return self._g.value
+
+    def next(self, beta):
+        """wait() for the oldest group, then issue() a new one: one C call."""
+        self.shard._ck(self._lib.reth_replay_pipe_next(self._h, float(beta), C.byref(self._g)))
+        self.waited += 1
+        self.issued += 1
+        return self._g.value
+
+    def update_begin(self):
+        self.shard._ck(self._lib.reth_replay_pipe_update_begin(self._h, C.byref(self._e)))
+        return self._e.value
+
+    def update_commit(self, entry, n, f32, alpha, transform=True):
+        self.shard._ck(self._lib.reth_replay_pipe_update_commit(self._h, entry, n, F32 if f32 else F64,
+                                                                float(alpha), int(bool(transform))))
+
+    def update_async(self, indices, prio, alpha, transform=True):
+        idx = np.ascontiguousarray(indices, dtype=np.int64)
+        w = np.ascontiguousarray(prio)
+        if w.dtype != np.float32:
+            w = w.astype(np.float64, copy=False)
+        self.shard._ck(self._lib.reth_replay_update_async(self._h, idx.ctypes.data, w.ctypes.data,
+                                                          F32 if w.dtype == np.float32 else F64, idx.size,
+                                                          float(alpha), int(bool(transform))))
+
+    def drain(self):
+        self.shard._ck(self._lib.reth_replay_pipe_drain(self._h))
+
+    def close(self):
+        if self._h is not None and self.shard._h is not None:
+            self._lib.reth_replay_pipe_close(self._h)
+        self._h = None
+
+
 class ReplayShard:
     """One replay shard on one GPU.
 
@@ -308,6 +387,16 @@ class ReplayShard:
         fc = (C.c_int64 * 2)()
         self._ck(self._lib.reth_replay_slot_meta(self._h, slot, fc, self._s(stream)))
         return fc[0], fc[1]
+
+    def open_pipe(self, batch, group, seed=0):
+        return ShardPipe(self, batch, group, seed)
+
+    @property
+    def pipe_stream(self):
+        """The shard's own ordering stream (tree updates + sampling) as a raw cudaStream_t."""
+        p = C.c_void_p()
+        self._ck(self._lib.reth_replay_pipe_stream(self._h, C.byref(p)))
+        return p.value
 
     # -- parity / debug ---------------------------------------------------
     def tree_arrays(self, stream=None):
