@@ -194,7 +194,7 @@ def timed_loop(torch, dist, shard, steps, warmup, iters, batch, prio, group, wor
     def one_step(k):
         off = (k % prio_steps) * iters * batch
         shard.step_loop(iters, batch, prio[off:], seed=1234, alpha=ALPHA, beta=BETA, group=group,
-                        time_gather=time_gather)
+                        time_gather=time_gather, one_gather_stream=time_gather)
     prio_steps = prio.numel() // (iters * batch)
     for k in range(warmup):
         one_step(k)
@@ -324,13 +324,17 @@ def run_ours(args):
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()
-    ms, launches, (gt_ms, gt_n) = timed_loop(torch, dist, shard, args.steps, args.warmup, iters, B, prio, G, world, True)
+    ms, launches, _ = timed_loop(torch, dist, shard, args.steps, args.warmup, iters, B, prio, G, world, False)
     if world > 1:
         mine = torch.as_tensor(shard.root_dev(), device="cuda").clone()
         dist.all_gather_into_tensor(roots, mine)
     clk = clocks.stop() if rank == 0 else None
     value = world * args.steps * iters * B / (ms / 1e3)
 
+    # roofline pass: the same loop with every gather launch bracketed by CUDA events on ONE gather stream
+    # (in the headline loop consecutive gathers alternate between two streams and overlap, so a per-launch
+    # bracket there would not be a kernel duration); the tree kernels still run concurrently
+    _, _, (gt_ms, gt_n) = timed_loop(torch, dist, shard, max(2, args.steps // 2), 1, iters, B, prio, G, world, True)
     # strict alternation (no prefetch): sample k+1 sees update k
     ms1, _, _ = timed_loop(torch, dist, shard, max(1, args.steps // 2), 1, iters, B, prio, 1, world, False)
     strict = world * max(1, args.steps // 2) * iters * B / (ms1 / 1e3)
@@ -371,7 +375,10 @@ def run_ours(args):
                      "frac": (achieved / peak) if achieved else None, "traffic": traffic, "peak_source": peak_src,
                      "kernel": "row_move_kernel<false> (frame gather)", "rows_per_launch": rows_per_launch,
                      "algorithmic_bytes_per_launch": 2 * rows_per_launch * ROW_BYTES, "avg_launch_us": gather_us,
-                     "launches_timed": int(gt_n)},
+                     "launches_timed": int(gt_n),
+                     "how": "CUDA events around every gather launch on its own stream, in a second pass of the same "
+                            "loop with all gathers on one stream (tree kernels concurrent); the headline loop "
+                            "alternates two gather streams, see hbm_gbs_whole_loop for its aggregate"},
         "hbm_gbs_whole_loop": 2 * ROW_BYTES * value / 1e9 / world,
         "strict_alternation": {"value": strict, "unit": "transitions/s", "prefetch_group": 1},
         "append": {"rows_per_s": app_rows, "gbs": app_gbs, "rows_per_call": 16384, "source": "device"},
@@ -382,7 +389,7 @@ def run_ours(args):
     if rank == 0 and world == 1 and not args.no_cpu:
         cores = os.cpu_count() or 1
         v, dt = cpu_reference_arm(args.cpu_steps, 1, args.cpu_iters, B, cap, cores)
-        v1, _ = cpu_reference_arm(max(1, args.cpu_steps // 2), 1, args.cpu_iters, B, cap, 1)
+        v1, _ = cpu_reference_arm(max(1, args.cpu_steps // 6), 1, args.cpu_iters, B, cap, 1)
         line["cpu_baseline"] = {
             "value": v, "unit": "transitions/s", "cores": cores, "kind": "port", "one_core": v1,
             "sample": f"{cores} replicas x {args.cpu_steps} steps x {args.cpu_iters} iterations of batch {B} "
@@ -404,9 +411,12 @@ def main():
     ap.add_argument("--capacity", type=int, default=1 << 20)
     ap.add_argument("--batch", type=int, default=512)
     ap.add_argument("--iters", type=int, default=128, help="learner iterations per bench step")
-    ap.add_argument("--group", type=int, default=4, help="prefetch group (reference loader ring: trainer.py:23 buffer_size=4)")
+    ap.add_argument("--group", type=int, default=8,
+                    help="prefetch group: batches drawn per launch; with --ahead 1 the lending ring holds 16 batches, the "
+                         "number the reference keeps in flight by default (TorchCudaLoader buffer_size=8 + num_procs=6 "
+                         "worker batches + 2 on the sampler side, torch_cuda_loader.py:70, sampler_loop.py:14)")
     ap.add_argument("--ahead", type=int, default=1, help="e2e loader: groups drawn ahead of the one being consumed")
-    ap.add_argument("--cpu-steps", type=int, default=4)
+    ap.add_argument("--cpu-steps", type=int, default=24)
     ap.add_argument("--cpu-iters", type=int, default=64, help="iterations per step of the CPU arm (bounded sample)")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()

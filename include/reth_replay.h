@@ -58,7 +58,7 @@ typedef struct reth_replay_config {
     int32_t ring_depth;                     /* learner-batch slots (TorchCudaLoader buffer_size, :70) */
     int32_t device;                         /* CUDA device ordinal */
     int32_t min_mode;                       /* reth_min_mode */
-    int32_t update_cluster;                 /* CTAs per cluster of the tree-repair kernel (0 = default 8) */
+    int32_t update_cluster;                 /* CTAs per cluster of the tree-repair kernel (0 = default: 16, or 8 if the device cannot host 16) */
     int32_t gather_mode;                    /* 0 = auto (= 1, the faster one on B200), 1 = LDG/STG.128,
                                                2 = TMA bulk copies (cp.async.bulk + mbarrier ring) */
     int32_t store_rows;                     /* 0 = tree only (no frame ring; config 5 "tree-only") */
@@ -243,6 +243,9 @@ int reth_replay_pipe_drain(reth_replay_t *h);
  *      flags bit0: skip gather (tree only); bit1: serialise everything on one stream;
  *      bit2: bracket every gather launch with CUDA events on its own stream (see gather_time);
  *      bit3 / bit4: skip the sample / the update launch (kernel micro-timing only);
+ *      bit5: all gathers on ONE internal stream (default: consecutive gathers alternate between two
+ *      streams so the tail of one overlaps the ramp-up of the next; bit2 timings are only per-kernel
+ *      durations with bit5 set);
  *      bits 8..15: prefetch group G (0/1 = strict alternation): sample_multi / gather_multi /
  *      update_slots over G slots per iteration (steps must be a multiple of G). */
 int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, const float *prio_dev,

@@ -39,7 +39,7 @@ struct reth_replay {
     // tree
     double2 *desc = nullptr, *agg = nullptr;
     uint32_t *stamp = nullptr, *mask = nullptr;
-    int32_t *worklist = nullptr, *counts = nullptr /*[2][kMaxTileLevels]*/, *err = nullptr;
+    int32_t *counts = nullptr /*[2][kMaxTileLevels]*/, *err = nullptr;
     int64_t max_n = 0;            // largest n of one update launch
     int counts_flip = 0;
     uint64_t draw_counter = 0;
@@ -58,7 +58,8 @@ struct reth_replay {
     int64_t tail = 0, size = 0;
     reth_replay_stats st{};
     // step loop
-    cudaStream_t s_tree = nullptr, s_gather = nullptr;
+    cudaStream_t s_tree = nullptr, s_gather = nullptr, s_gather2 = nullptr;   // gathers alternate between two streams
+    int two_gather_streams = 1;
     std::vector<cudaEvent_t> ev_sampled, ev_gathered;
     cudaEvent_t ev_fork = nullptr, ev_join_t = nullptr, ev_join_g = nullptr;
     int update_cluster = 8;
@@ -130,7 +131,7 @@ size_t dtype_size(int dt) { return (dt == RETH_F32 || dt == RETH_I32) ? 4 : 8; }
 void free_all(reth_replay *h)
 {
     cudaFree(h->desc); cudaFree(h->agg); cudaFree(h->stamp); cudaFree(h->mask);
-    cudaFree(h->worklist); cudaFree(h->counts); cudaFree(h->err);
+    cudaFree(h->counts); cudaFree(h->err);
     cudaFree(h->dbg);
     cudaFree(h->stage_idx); cudaFree(h->stage_prio); cudaFree(h->stage_u);
     if (h->host_pin) cudaFreeHost(h->host_pin);
@@ -145,6 +146,7 @@ void free_all(reth_replay *h)
     if (h->ev_join_g) cudaEventDestroy(h->ev_join_g);
     if (h->s_tree) cudaStreamDestroy(h->s_tree);
     if (h->s_gather) cudaStreamDestroy(h->s_gather);
+    if (h->s_gather2) cudaStreamDestroy(h->s_gather2);
 }
 
 }  // namespace
@@ -215,7 +217,6 @@ RETH_EXPORT int reth_replay_create(const reth_replay_config *cfg, reth_replay_t 
     CKC(dalloc_zero(&h->stamp, (size_t)cfg->capacity, acct));
     CKC(dalloc_zero(&h->mask, nt, acct));
     h->max_n = cfg->max_batch > 16384 ? cfg->max_batch : 16384;
-    CKC(dalloc_zero(&h->worklist, (size_t)kMaxTileLevels * h->max_n, acct));
     CKC(dalloc_zero(&h->counts, 2 * kMaxTileLevels, acct));
     CKC(dalloc_zero(&h->err, 4, acct));
     CKC(cudaMalloc(&h->stage_idx, h->max_n * 8));
@@ -252,6 +253,8 @@ RETH_EXPORT int reth_replay_create(const reth_replay_config *cfg, reth_replay_t 
     CKC(cudaDeviceGetStreamPriorityRange(&lo, &hi));
     CKC(cudaStreamCreateWithPriority(&h->s_tree, cudaStreamNonBlocking, hi));
     CKC(cudaStreamCreateWithPriority(&h->s_gather, cudaStreamNonBlocking, lo));
+    CKC(cudaStreamCreateWithPriority(&h->s_gather2, cudaStreamNonBlocking, lo));
+    if (const char *e = getenv("RETH_GATHER_STREAMS")) h->two_gather_streams = atoi(e) >= 2;
     h->ev_sampled.resize(h->cfg.ring_depth);
     h->ev_gathered.resize(h->cfg.ring_depth);
     for (int i = 0; i < h->cfg.ring_depth; ++i) {
@@ -261,8 +264,27 @@ RETH_EXPORT int reth_replay_create(const reth_replay_config *cfg, reth_replay_t 
     CKC(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
     CKC(cudaEventCreateWithFlags(&h->ev_join_t, cudaEventDisableTiming));
     CKC(cudaEventCreateWithFlags(&h->ev_join_g, cudaEventDisableTiming));
-    if (h->update_cluster > 8)
+    if (h->update_cluster > 16) h->update_cluster = 16;
+    if (cfg->update_cluster <= 0) {
+        // default: a 16-CTA cluster (non-portable size, measured fastest) when the device can host one
         CKC(cudaFuncSetAttribute(per_update_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+        cudaLaunchConfig_t lc = {};
+        lc.gridDim = dim3(16);
+        lc.blockDim = dim3(kUpdateThreads);
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = 16; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        lc.attrs = at;
+        lc.numAttrs = 1;
+        int nclusters = 0;
+        if (cudaOccupancyMaxActiveClusters(&nclusters, per_update_kernel, &lc) == cudaSuccess && nclusters > 0)
+            h->update_cluster = 16;
+        else
+            h->update_cluster = 8;
+        cudaGetLastError();
+    } else if (h->update_cluster > 8) {
+        CKC(cudaFuncSetAttribute(per_update_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    }
     CKC(cudaDeviceSynchronize());
 #undef CKC
     *out = h;
@@ -297,28 +319,42 @@ int to_device(reth_replay *h, const void *p, int loc, size_t bytes, void *stagin
     return RETH_OK;
 }
 
-// One launch of the cluster tree-repair kernel for n <= max_n entries.
+// Tree update of n <= max_n entries: one launch of the cluster kernel per (cluster size x 512)
+// entries, in batch order on one stream, so last-writer-wins holds across the launches too.
 int launch_update(reth_replay *h, UpdateArgs &a, cudaStream_t s)
 {
     if (a.n <= 0) return RETH_OK;
     a.g = h->geom; a.desc = h->desc; a.agg = h->agg; a.stamp = h->stamp; a.mask = h->mask;
-    a.worklist = h->worklist; a.err = h->err; a.max_n = h->max_n; a.dbg = h->dbg;
-    a.counts = h->counts + h->counts_flip * kMaxTileLevels;
-    a.counts_next = h->counts + (h->counts_flip ^ 1) * kMaxTileLevels;
-    h->counts_flip ^= 1;
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(h->update_cluster);
-    cfg.blockDim = dim3(kUpdateThreads);
-    cfg.stream = s;
-    cudaLaunchAttribute at[1];
-    at[0].id = cudaLaunchAttributeClusterDimension;
-    at[0].val.clusterDim.x = h->update_cluster;
-    at[0].val.clusterDim.y = 1;
-    at[0].val.clusterDim.z = 1;
-    cfg.attrs = at;
-    cfg.numAttrs = 1;
-    CK(h, cudaLaunchKernelEx(&cfg, per_update_kernel, (const UpdateArgs)a));
-    h->st.kernel_launches++;
+    a.err = h->err; a.dbg = h->dbg;
+    const int64_t per = (int64_t)h->update_cluster * kUpdateThreads;
+    const int64_t n = a.n;
+    const uint8_t *idx0 = (const uint8_t *)a.idx, *prio0 = (const uint8_t *)a.prio;
+    const int64_t iota0 = a.iota_base;
+    const size_t is = a.idx_kind == 0 ? 8 : 4, ps = a.prio_kind == 0 ? 4 : 8;
+    for (int64_t off = 0; off < n; off += per) {
+        a.n = n - off < per ? n - off : per;
+        a.stamp_base = (uint32_t)off;
+        if (a.idx_kind != 2) a.idx = idx0 + off * is;
+        if (a.prio_kind != 2) a.prio = prio0 + off * ps;
+        a.iota_base = iota0 + off;
+        a.counts = h->counts + h->counts_flip * kMaxTileLevels;
+        a.counts_next = h->counts + (h->counts_flip ^ 1) * kMaxTileLevels;
+        h->counts_flip ^= 1;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(h->update_cluster);
+        cfg.blockDim = dim3(kUpdateThreads);
+        cfg.stream = s;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = h->update_cluster;
+        at[0].val.clusterDim.y = 1;
+        at[0].val.clusterDim.z = 1;
+        cfg.attrs = at;
+        cfg.numAttrs = 1;
+        CK(h, cudaLaunchKernelEx(&cfg, per_update_kernel, (const UpdateArgs)a));
+        h->st.kernel_launches++;
+    }
+    a.n = n; a.idx = idx0; a.prio = prio0; a.iota_base = iota0;
     return RETH_OK;
 }
 
@@ -917,10 +953,11 @@ int pipe_issue(reth_replay *h, double beta)
     CK(h, cudaMemcpyAsync(p.idx_host + g * E, h->slots[slot].idx, E * 8, cudaMemcpyDeviceToHost, p.s_copy));
     CK(h, cudaMemcpyAsync(p.w_host + g * E, h->slots[slot].w, E * 8, cudaMemcpyDeviceToHost, p.s_copy));
     CK(h, cudaMemcpyAsync(p.err_host + g, h->err, sizeof(int32_t), cudaMemcpyDeviceToHost, p.s_copy));
-    CK(h, cudaStreamWaitEvent(h->s_gather, p.ev_smp[g], 0));
-    rc = do_gather(h, slot, false, h->s_gather, p.G);
+    cudaStream_t sg = (h->two_gather_streams && (p.issued & 1)) ? h->s_gather2 : h->s_gather;
+    CK(h, cudaStreamWaitEvent(sg, p.ev_smp[g], 0));
+    rc = do_gather(h, slot, false, sg, p.G);
     if (rc) return rc;
-    CK(h, cudaEventRecord(p.ev_gat[g], h->s_gather));
+    CK(h, cudaEventRecord(p.ev_gat[g], sg));
     CK(h, cudaStreamWaitEvent(p.s_copy, p.ev_gat[g], 0));
     CK(h, cudaEventRecord(p.ev_done[g], p.s_copy));
     p.issued++;
@@ -998,6 +1035,7 @@ RETH_EXPORT int reth_replay_pipe_close(reth_replay_t *h)
     DeviceGuard guard(h->cfg.device);
     cudaStreamSynchronize(h->s_tree);
     cudaStreamSynchronize(h->s_gather);
+    cudaStreamSynchronize(h->s_gather2);
     cudaStreamSynchronize(h->pipe.s_copy);
     pipe_free(h);
     return RETH_OK;
@@ -1108,6 +1146,7 @@ RETH_EXPORT int reth_replay_pipe_drain(reth_replay_t *h)
     DeviceGuard guard(h->cfg.device);
     CK(h, cudaStreamSynchronize(h->s_tree));
     CK(h, cudaStreamSynchronize(h->s_gather));
+    CK(h, cudaStreamSynchronize(h->s_gather2));
     if (h->pipe.open) CK(h, cudaStreamSynchronize(h->pipe.s_copy));
     return RETH_OK;
 }
@@ -1123,20 +1162,24 @@ RETH_EXPORT int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, co
     cudaStream_t s = S(stream);
     const bool no_gather = flags & 1, serial = flags & 2, timed = flags & 4;
     const bool no_sample = flags & 8, no_update = flags & 16;   // kernel micro-timing only
+    const bool one_gather_stream = flags & 32;
     const int depth = (int)h->slots.size();
     int G = (flags >> 8) & 0xff;                      // batches per tree launch (prefetch group)
     if (G < 1) G = 1;
     if (G > 1 && (batch != h->cfg.max_batch || depth % G != 0 || depth < 2 * G || steps % G != 0 ||
                   (int64_t)G * batch > h->max_n))
         return fail(h, RETH_ERR_INVALID, "group %d needs batch == max_batch, ring_depth a multiple >= 2*group, steps %% group == 0", G);
-    cudaStream_t st = serial ? s : h->s_tree, sg = serial ? s : h->s_gather;
+    cudaStream_t st = serial ? s : h->s_tree;
     if (!serial) {
         CK(h, cudaEventRecord(h->ev_fork, s));
         CK(h, cudaStreamWaitEvent(st, h->ev_fork, 0));
-        CK(h, cudaStreamWaitEvent(sg, h->ev_fork, 0));
+        CK(h, cudaStreamWaitEvent(h->s_gather, h->ev_fork, 0));
+        CK(h, cudaStreamWaitEvent(h->s_gather2, h->ev_fork, 0));
     }
     for (int k = 0; k < steps; k += G) {
         const int slot = k % depth;
+        // consecutive gathers alternate streams: the tail of one overlaps the ramp-up of the next
+        cudaStream_t sg = serial ? s : ((h->two_gather_streams && !one_gather_stream && ((k / G) & 1)) ? h->s_gather2 : h->s_gather);
         // the slots' index buffers are re-drawn: their previous gather must have consumed them
         if (!serial && !no_gather && k >= depth) CK(h, cudaStreamWaitEvent(st, h->ev_gathered[slot], 0));
         int rc = RETH_OK;
@@ -1176,8 +1219,10 @@ RETH_EXPORT int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, co
     }
     if (!serial) {
         CK(h, cudaEventRecord(h->ev_join_t, st));
-        CK(h, cudaEventRecord(h->ev_join_g, sg));
         CK(h, cudaStreamWaitEvent(s, h->ev_join_t, 0));
+        CK(h, cudaEventRecord(h->ev_join_g, h->s_gather));
+        CK(h, cudaStreamWaitEvent(s, h->ev_join_g, 0));
+        CK(h, cudaEventRecord(h->ev_join_g, h->s_gather2));
         CK(h, cudaStreamWaitEvent(s, h->ev_join_g, 0));
     }
     return RETH_OK;

@@ -213,11 +213,11 @@ struct UpdateArgs {
     double2 *agg;
     uint32_t *stamp;      // [capacity]  last-writer-wins arbitration
     uint32_t *mask;       // [n_tiles]   touched-node bits of the running update
-    int32_t *worklist;    // [kMaxTileLevels][max_n] owned tiles per tile level
     int32_t *counts;      // [kMaxTileLevels] this call
     int32_t *counts_next; // [kMaxTileLevels] zeroed for the next call
     int32_t *err;
-    int64_t n, max_n;
+    int64_t n;            // <= cluster size * kUpdateThreads (the host chunks larger batches)
+    uint32_t stamp_base;  // entry i carries stamp 1 + stamp_base + i (chunks of one batch keep batch order)
     const void *idx;
     int32_t idx_kind;     // 0 int64[], 1 int32[], 2 iota: (iota_base + i) % capacity
     int64_t iota_base;
@@ -241,18 +241,25 @@ __device__ __forceinline__ int64_t upd_index(const UpdateArgs &a, int64_t i)
 
 // (w + 1e-6) ** alpha in the dtype of the incoming array (per_sampler.py:16-17):
 // float32 in -> float32 add and a correctly rounded float32 power.
-__device__ __forceinline__ double upd_leaf(const UpdateArgs &a, int64_t i)
+__device__ __forceinline__ double upd_prio_load(const UpdateArgs &a, int64_t i)
 {
     if (a.prio_kind == 2) return 1.0;                    // prioritized_buffer.py:36-37
+    if (a.prio_kind == 0) return (double)((const float *)a.prio)[i];   // exact widening
+    return ((const double *)a.prio)[i];
+}
+
+__device__ __forceinline__ double upd_leaf(const UpdateArgs &a, double raw)
+{
+    if (a.prio_kind == 2) return 1.0;
     const bool f32 = a.prio_kind == 0;
     double base, expo = a.alpha;
     if (f32) {
-        const float w = ((const float *)a.prio)[i];
+        const float w = (float)raw;
         if (!a.transform) return (double)w;
         base = (double)(w + 1e-6f);
         expo = (double)(float)a.alpha;
     } else {
-        const double w = ((const double *)a.prio)[i];
+        const double w = raw;
         if (!a.transform) return w;
         base = w + 1e-6;
     }
@@ -269,40 +276,6 @@ __device__ __forceinline__ double2 maintain_node(double v, const double2 &Lc, co
     if (Lc.y != 0.0) mn = (Lc.y < mn) ? Lc.y : mn;
     if (Rc.y != 0.0) mn = (Rc.y < mn) ? Rc.y : mn;
     return make_double2(s, mn);
-}
-
-// Warp-cooperative repair of one tile with an arbitrary touched mask (several paths):
-// lane = node, 5 levels bottom-up through register shuffles.
-__device__ __forceinline__ void repair_tile_warp(const UpdateArgs &a, int64_t tile, int T, int lane)
-{
-    double2 ag = ldcg2(&a.agg[tile * 64 + lane]);
-    const double2 ex = ldcg2(&a.agg[tile * 64 + 32 + lane]);
-    double2 de = ldcg2(&a.desc[tile * 32 + lane]);
-    const uint32_t m = __ldcg(&a.mask[tile]);
-    const bool touched = (m >> lane) & 1u;
-#pragma unroll
-    for (int l = 4; l >= 0; --l) {
-        const int src = ((l == 4) ? 2 * (lane - 16) : 2 * lane) & 31;
-        const double sx = (l == 4) ? ex.x : ag.x, sy = (l == 4) ? ex.y : ag.y;
-        double2 Lc, Rc;
-        Lc.x = __shfl_sync(0xffffffffu, sx, src);
-        Lc.y = __shfl_sync(0xffffffffu, sy, src);
-        Rc.x = __shfl_sync(0xffffffffu, sx, src | 1);
-        Rc.y = __shfl_sync(0xffffffffu, sy, src | 1);
-        if (touched && (lane >> l) == 1) {
-            ag = maintain_node(de.y, Lc, Rc);
-            de.x = Lc.x;
-        }
-    }
-    if (touched) {
-        __stcg(&a.agg[tile * 64 + lane], ag);
-        __stcg(&a.desc[tile * 32 + lane].x, de.x);
-    }
-    if (lane == 1 && T > 0) {
-        const int64_t rel = tile - tile_base(T);
-        __stcg(&a.agg[(tile_base(T - 1) + (rel >> 5)) * 64 + 32 + (rel & 31)], ag);
-    }
-    if (lane == 0) __stcg(&a.mask[tile], 0u);
 }
 
 // One THREAD repairs one tile whose touched set is a single root-ward chain (the
@@ -349,219 +322,245 @@ __device__ __forceinline__ void repair_tile_chain(const UpdateArgs &a, int64_t t
     __stcg(&a.mask[tile], 0u);
 }
 
-// Tile levels 0 and 1 (heap depths 0..9, <= 1023 nodes) swept by one CTA in shared
-// memory, one __syncthreads per tree level.  A node is recomputed when its own mask
-// bit is set (it was written by this batch) or a child has ever been maintained
-// (child min != 0, which _numba_maintain_node guarantees for every node it visited):
-// its ancestors were maintained then too, so recomputing them is idempotent.  Deep
-// paths therefore need no marking atomics on the two top tile levels.
-__device__ __forceinline__ void repair_top(const UpdateArgs &a)
+// Warp-cooperative repair of up to K tiles of one tile level, lane = node.  The loads of ALL
+// tiles are issued before the first use (one memory round trip per call instead of one per
+// tile).  derived == false: exactly the nodes whose mask bit is set are recomputed.
+// derived == true (tile levels 0 and 1): a node is also recomputed when a child has ever been
+// maintained (child min != 0, which _numba_maintain_node guarantees for every node it visited):
+// its ancestors were maintained then too, so recomputing them is idempotent and deep paths need
+// no marking atomics on the two top tile levels.  `count` must be warp-uniform.
+template <int K>
+__device__ __forceinline__ void repair_tiles_warp(const UpdateArgs &a, const int64_t (&tile)[K], int count,
+                                                  int T, int lane, bool derived)
 {
-    __shared__ double sS[2048], sM[2048], sV[1024];
-    __shared__ uint8_t sK[1024];
-    const int NT = a.g.n_tile_levels;
-    const int D = (NT >= 2) ? 10 : 5;                    // tree levels in the sweep
-    const int nn = 1 << D;                                // nodes are heap k = 1 .. nn-1
-    const int64_t n1 = (NT >= 2) ? ((a.g.n_tiles - 1 < 32) ? a.g.n_tiles - 1 : 32) : 0;
-    // 2*nn <= 2048 entries over 512 threads: 4 per thread, all loads issued before any use
-    double2 g[4];
-    double v[4];
-    uint32_t mk[4];
+    double2 ag[K], ex[K], de[K];
+    uint32_t m[K];
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        const int k = threadIdx.x + q * kUpdateThreads;
-        g[q] = make_double2(0.0, 0.0);
-        v[q] = 0.0;
-        mk[q] = 0u;
-        if (k >= 2 * nn) continue;
-        if (k >= 1 && k < nn) {
-            const int d = 31 - __clz(k);
-            const int64_t tile = (d < 5) ? 0 : 1 + ((k >> (d - 5)) - 32);
-            const int local = (d < 5) ? k : ((1 << (d - 5)) | (k & ((1 << (d - 5)) - 1)));
-            if (tile <= n1) {
-                g[q] = ldcg2(&a.agg[tile * 64 + local]);
-                v[q] = __ldcg(&a.desc[tile * 32 + local].y);
-                mk[q] = (__ldcg(&a.mask[tile]) >> local) & 1u;
-            }
-        } else if (k >= nn) {                             // children of the last swept level
-            const int64_t tile = (NT >= 2) ? 1 + ((k >> 5) - 32) : 0;
-            if (tile <= n1) g[q] = ldcg2(&a.agg[tile * 64 + 32 + (k & 31)]);
-        }
+    for (int q = 0; q < K; ++q) {
+        if (q >= count) continue;
+        ag[q] = ldcg2(&a.agg[tile[q] * 64 + lane]);
+        ex[q] = ldcg2(&a.agg[tile[q] * 64 + 32 + lane]);
+        de[q] = ldcg2(&a.desc[tile[q] * 32 + lane]);
+        m[q] = __ldcg(&a.mask[tile[q]]);
     }
+    // level-major so that the K independent dependency chains interleave
+    bool wrote[K];
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        const int k = threadIdx.x + q * kUpdateThreads;
-        if (k >= 2 * nn) continue;
-        sS[k] = g[q].x;
-        sM[k] = g[q].y;
-        if (k < nn) { sV[k] = v[q]; sK[k] = (uint8_t)mk[q]; }
-    }
-    if (a.dbg && threadIdx.x == 0) a.dbg[23] = clock64();
-    __syncthreads();
-    for (int l = D - 1; l >= 0; --l) {
-        for (int k = (1 << l) + threadIdx.x; k < (2 << l); k += kUpdateThreads) {
-            const double2 Lc = make_double2(sS[2 * k], sM[2 * k]), Rc = make_double2(sS[2 * k + 1], sM[2 * k + 1]);
-            if (sK[k] || Lc.y != 0.0 || Rc.y != 0.0) {
-                const double2 res = maintain_node(sV[k], Lc, Rc);
-                sS[k] = res.x;
-                sM[k] = res.y;
-                sK[k] = 2;
+    for (int q = 0; q < K; ++q) wrote[q] = false;
+#pragma unroll
+    for (int l = 4; l >= 0; --l) {
+        const int src = ((l == 4) ? 2 * (lane - 16) : 2 * lane) & 31;
+#pragma unroll
+        for (int q = 0; q < K; ++q) {
+            if (q >= count) continue;
+            const double sx = (l == 4) ? ex[q].x : ag[q].x, sy = (l == 4) ? ex[q].y : ag[q].y;
+            double2 Lc, Rc;
+            Lc.x = __shfl_sync(0xffffffffu, sx, src);
+            Lc.y = __shfl_sync(0xffffffffu, sy, src);
+            Rc.x = __shfl_sync(0xffffffffu, sx, src | 1);
+            Rc.y = __shfl_sync(0xffffffffu, sy, src | 1);
+            const bool own = (m[q] >> lane) & 1u;
+            if ((lane >> l) == 1 && (own || (derived && (Lc.y != 0.0 || Rc.y != 0.0)))) {
+                ag[q] = maintain_node(de[q].y, Lc, Rc);
+                de[q].x = Lc.x;
+                wrote[q] = true;
             }
         }
-        __syncthreads();
     }
-    if (a.dbg && threadIdx.x == 0) a.dbg[24] = clock64();
-    for (int k = 1 + threadIdx.x; k < nn; k += kUpdateThreads) {
-        if (sK[k] != 2) continue;
-        const int d = 31 - __clz(k);
-        const int64_t tile = (d < 5) ? 0 : 1 + ((k >> (d - 5)) - 32);
-        const int local = (d < 5) ? k : ((1 << (d - 5)) | (k & ((1 << (d - 5)) - 1)));
-        const double2 res = make_double2(sS[k], sM[k]);
-        __stcg(&a.agg[tile * 64 + local], res);
-        __stcg(&a.desc[tile * 32 + local].x, sS[2 * k]);
-        if (d == 5) __stcg(&a.agg[32 + (k - 32)], res);  // root of a level-1 tile: copy in tile 0
+#pragma unroll
+    for (int q = 0; q < K; ++q) {
+        if (q >= count) continue;
+        if (wrote[q]) {
+            __stcg(&a.agg[tile[q] * 64 + lane], ag[q]);
+            __stcg(&a.desc[tile[q] * 32 + lane].x, de[q].x);
+        }
+        if (lane == 1 && T > 0) {
+            const int64_t rel = tile[q] - tile_base(T);
+            __stcg(&a.agg[(tile_base(T - 1) + (rel >> 5)) * 64 + 32 + (rel & 31)], ag[q]);
+        }
+        if (lane == 0 && m[q] != 0u) __stcg(&a.mask[tile[q]], 0u);
     }
-    if (threadIdx.x <= n1) __stcg(&a.mask[threadIdx.x], 0u);
 }
 
-// Batched priority write-back with tree-path repair (utils/sumtree.py:61-67,
-// 24-31).  One thread-block cluster; stages separated by cluster barriers:
-//   P0 stamp  : atomicMax(stamp[idx], 1+i) -> the last i of a duplicate index wins
-//   P1 leaves : winners write val.  For tile levels >= 2 they OR their path bits into
-//               the per-tile masks (all atomics of a path issued together); the first
-//               marker of a tile owns it: worklist[T][i] = tile (else -1).  A leaf that
-//               itself lives in tile level 0/1 only sets its own mask bit.
-//   R  repair : tile levels deepest -> 2 (skipped when nobody owns a tile there); a
-//               lane takes one owned tile: single-chain tiles are repaired by that
-//               thread alone, multi-path tiles by the whole warp; cluster barrier
-//   TOP       : tile levels 1 and 0 by CTA 0 in shared memory (repair_top)
-// The result equals the reference's sequential loop because sum/min are pure
-// functions of the final leaves on the union of touched paths.
+// Batched priority write-back with tree-path repair (utils/sumtree.py:61-67, 24-31) for
+// n <= (cluster size x 512) entries, one entry per thread.  One thread-block cluster; stages:
+//   A stamp  (dedupe 1) atomicMax(stamp[idx], 1+base+i): the last i of a duplicate index wins; barrier
+//   B leaves : winners write val and mark their root-ward path: tile levels >= 3 with a
+//              returning atomicOr per tile (the first marker OWNS the tile and keeps it in a
+//              register), tile level 2 with a fire-and-forget atomicOr, levels 0/1 not at all
+//              (a leaf living there sets its own bit); cluster barrier
+//   R sparse : tile levels deepest -> 3 (skipped when nobody owns a tile there): an owner whose
+//              tile holds a single root-ward chain repairs it alone (repair_tile_chain), tiles
+//              with several paths are repaired by the warp, two per round trip; cluster barrier
+//   D dense  : tile level 2 (<= 1024 tiles): CTA c takes the children of the level-1 tiles
+//              j = c (mod cluster), a warp repairs its touched tiles four per round trip;
+//              __syncthreads; the CTA's level-1 tiles (derived rule); cluster barrier
+//   ROOT     : tile 0 by one warp of CTA 0 (derived rule)
+// The result equals the reference's sequential loop because sum/min are pure functions of
+// the final leaves on the union of touched paths.
 __global__ void __launch_bounds__(kUpdateThreads) per_update_kernel(const UpdateArgs a)
 {
     cg::cluster_group cluster = cg::this_cluster();
     const int nblk = (int)cluster.num_blocks(), brank = (int)cluster.block_rank();
-    const int64_t nthr = (int64_t)nblk * kUpdateThreads;
-    // consecutive work items are spread over the CTAs of the cluster
-    const int64_t L = (int64_t)threadIdx.x * nblk + brank;
+    // consecutive entries are spread over the CTAs of the cluster
+    const int64_t i = (int64_t)threadIdx.x * nblk + brank;
     const int64_t cap = a.g.capacity;
-    const int lane = threadIdx.x & 31;
+    const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
+    constexpr int kWarps = kUpdateThreads / 32;
     const int NT = a.g.n_tile_levels;
 
     RETH_STAMP(0);
     if (brank == 0 && threadIdx.x < kMaxTileLevels) a.counts_next[threadIdx.x] = 0;
+    // every load that does not depend on another is issued up front
+    const bool inrange = i < a.n;
+    int64_t idx = 0, nxt = -1;
+    double raw = 0.0;
+    if (inrange) { idx = upd_index(a, i); raw = upd_prio_load(a, i); }
+    if (a.dedupe == 2 && i + 1 < a.n) nxt = upd_index(a, i + 1);
+    bool active = inrange;
+    if (active && (idx < 0 || idx >= cap)) { atomicOr(a.err, 1); active = false; }
+    const uint32_t my_stamp = 1u + a.stamp_base + (uint32_t)i;
     if (a.dedupe == 1) {
-        for (int64_t i = L; i < a.n; i += nthr) {
-            const int64_t idx = upd_index(a, i);
-            if (idx < 0 || idx >= cap) { atomicOr(a.err, 1); continue; }
-            atomicMax(&a.stamp[idx], 1u + (uint32_t)i);
-        }
+        if (active) atomicMax(&a.stamp[idx], my_stamp);
         RETH_STAMP(1);
         cluster.sync();
     }
     RETH_STAMP(2);
-    const int64_t iters = (a.n + nthr - 1) / nthr;      // warp-uniform trip count (ballots inside)
-    for (int64_t it = 0; it < iters; ++it) {
-        const int64_t i = it * nthr + L;
-        const bool inrange = i < a.n;
-        bool active = inrange;
-        int64_t idx = 0;
-        if (active) {
-            idx = upd_index(a, i);
-            if (idx < 0 || idx >= cap) { atomicOr(a.err, 1); active = false; }
-        }
-        uint32_t st = 0;
-        if (active && a.dedupe == 1) st = __ldcg(&a.stamp[idx]);
-        // dedupe 2: indices drawn by per_sample_kernel.  Stratified targets are monotone and
-        // _numba_find_index is a monotone step function of its target, so equal indices are
-        // always adjacent: the last element of a run is the sequential loop's last writer.
-        if (active && a.dedupe == 2 && i + 1 < a.n && upd_index(a, i + 1) == idx) active = false;
-        if (it == 0) RETH_STAMP(11);
-        const double leaf = active ? upd_leaf(a, i) : 0.0;       // pow overlaps the stamp load
-        if (it == 0) RETH_STAMP(12);
-        if (active && a.dedupe == 1) {
-            if (st != 1u + (uint32_t)i) active = false;
-            else if (!a.keep_stamps) __stcg(&a.stamp[idx], 0u);   // stamps are zero between launches
-        }
-        int64_t tiles[kMaxTileLevels];
-        uint32_t old[kMaxTileLevels];
-        int Tn = -1;
-        if (active) {
-            const NodeLoc n = locate(idx);
-            Tn = n.T;
-            __stcg(&a.desc[n.tile * 32 + n.local].y, leaf);
-            if (Tn <= 1) {
-                atomicOr(&a.mask[n.tile], 1u << n.local);         // own bit; ancestors are derived
-            } else {
-                uint32_t bits[kMaxTileLevels];
-                int64_t tile = n.tile;
-                int local = n.local, r = n.r;
-                uint64_t kroot = ((uint64_t)idx + 1ull) >> n.r;   // heap k of the tile root
+    uint32_t st = 0;
+    if (active && a.dedupe == 1) st = __ldcg(&a.stamp[idx]);
+    // dedupe 2: indices drawn by per_sample_kernel.  Stratified targets are monotone and
+    // _numba_find_index is a monotone step function of its target, so equal indices are
+    // always adjacent: the last element of a run is the sequential loop's last writer.
+    if (active && a.dedupe == 2 && nxt == idx) active = false;
+    const double leaf = active ? upd_leaf(a, raw) : 0.0;            // pow overlaps the stamp load
+    RETH_STAMP(12);
+    if (active && a.dedupe == 1) {
+        if (st != my_stamp) active = false;
+        else if (!a.keep_stamps) __stcg(&a.stamp[idx], 0u);       // stamps are zero between launches
+    }
+    int32_t own_tile[kMaxTileLevels];                             // tile this thread owns at level T (>= 3), else -1
 #pragma unroll
-                for (int T = kMaxTileLevels - 1; T >= 2; --T) {
-                    if (T > Tn) continue;
-                    uint32_t b = 0;
-                    for (int j = 0; j <= r; ++j) b |= 1u << (local >> (r - j));
-                    tiles[T] = tile;
-                    bits[T] = b;
-                    // parent of the tile root is a bottom-row node of the parent tile
-                    const uint64_t kp = kroot >> 1;
-                    local = 16 | (int)(kp & 15ull);
-                    r = 4;
-                    kroot = kp >> 4;
-                    tile = tile_base(T - 1) + (int64_t)(kroot - (1ull << (5 * (T - 1))));
-                }
+    for (int T = 0; T < kMaxTileLevels; ++T) own_tile[T] = -1;
+    if (active) {
+        const NodeLoc n = locate(idx);
+        __stcg(&a.desc[n.tile * 32 + n.local].y, leaf);
+        if (n.T <= 1) {
+            atomicOr(&a.mask[n.tile], 1u << n.local);             // own bit; ancestors are derived
+        } else {
+            int64_t tiles[kMaxTileLevels];
+            uint32_t bits[kMaxTileLevels], old[kMaxTileLevels];
+            int64_t tile = n.tile;
+            int local = n.local, r = n.r;
+            uint64_t kroot = ((uint64_t)idx + 1ull) >> n.r;       // heap k of the tile root
 #pragma unroll
-                for (int T = kMaxTileLevels - 1; T >= 2; --T)
-                    if (T <= Tn) old[T] = atomicOr(&a.mask[tiles[T]], bits[T]);
+            for (int T = kMaxTileLevels - 1; T >= 2; --T) {
+                if (T > n.T) continue;
+                uint32_t b = 0;
+                for (int j = 0; j <= r; ++j) b |= 1u << (local >> (r - j));
+                tiles[T] = tile;
+                bits[T] = b;
+                // parent of the tile root is a bottom-row node of the parent tile
+                const uint64_t kp = kroot >> 1;
+                local = 16 | (int)(kp & 15ull);
+                r = 4;
+                kroot = kp >> 4;
+                tile = tile_base(T - 1) + (int64_t)(kroot - (1ull << (5 * (T - 1))));
             }
-        }
-        if (it == 0) RETH_STAMP(13);
 #pragma unroll
-        for (int T = kMaxTileLevels - 1; T >= 2; --T) {
-            if (T >= NT) continue;                                // uniform
-            const bool own = active && T <= Tn && old[T] == 0u;
-            if (inrange) a.worklist[(int64_t)T * a.max_n + i] = own ? (int32_t)tiles[T] : -1;
-            const unsigned bal = __ballot_sync(0xffffffffu, own);
-            if (bal != 0u && lane == __ffs(bal) - 1) atomicOr(&a.counts[0], 1 << T);   // level has work
+            for (int T = kMaxTileLevels - 1; T >= 3; --T)
+                if (T <= n.T) old[T] = atomicOr(&a.mask[tiles[T]], bits[T]);
+            atomicOr(&a.mask[tiles[2]], bits[2]);                 // level 2 is swept densely: no owner
+#pragma unroll
+            for (int T = kMaxTileLevels - 1; T >= 3; --T)
+                if (T <= n.T && old[T] == 0u) own_tile[T] = (int32_t)tiles[T];
         }
+    }
+#pragma unroll
+    for (int T = kMaxTileLevels - 1; T >= 3; --T) {
+        if (T >= NT) continue;                                    // uniform
+        const unsigned bal = __ballot_sync(0xffffffffu, own_tile[T] >= 0);
+        if (bal != 0u && lane == __ffs(bal) - 1) atomicOr(&a.counts[0], 1 << T);   // level has work
     }
     RETH_STAMP(3);
     cluster.sync();
     RETH_STAMP(4);
 
-    const int64_t warp = (int64_t)(threadIdx.x >> 5) * nblk + brank, nwarps = nthr >> 5;
-    // entry e of a level's worklist goes to lane (e / nwarps) of warp (e % nwarps): the owned
-    // tiles are spread thinly so that multi-path tiles rarely queue up inside one warp
-    const int64_t e0 = (int64_t)lane * nwarps + warp;
-    const int flags = __ldcg(&a.counts[0]);                       // bit T: somebody owns a tile at level T
-#pragma unroll 1
-    for (int T = NT - 1; T >= 2; --T) {
-        if (!((flags >> T) & 1)) continue;                        // uniform over the cluster
-        for (int64_t base = 0; base < a.n; base += 32 * nwarps) {
-            const int64_t e = base + e0;
-            int32_t t = -1;
-            if (e < a.n) t = __ldcg(&a.worklist[(int64_t)T * a.max_n + e]);
+    // ---- R: sparse tile levels
+    if (NT > 3) {
+        const int flags = __ldcg(&a.counts[0]);                   // bit T: somebody owns a tile at level T
+#pragma unroll
+        for (int T = kMaxTileLevels - 1; T >= 3; --T) {
+            if (T >= NT || !((flags >> T) & 1)) continue;         // uniform over the cluster
+            const int32_t t = own_tile[T];
             uint32_t m = 0;
             if (t >= 0) m = __ldcg(&a.mask[t]);
-            if (m) RETH_STAMP(14 + (T & 1));
-            const bool chain = t >= 0 && __popc(m) == (31 - __clz(31 - __clz(m | 1u))) + 1 && m != 0u;
+            const bool chain = t >= 0 && m != 0u && __popc(m) == (31 - __clz(31 - __clz(m | 1u))) + 1;
             if (chain) repair_tile_chain(a, (int64_t)t, m, T);
-            RETH_STAMP(16 + (T & 1));
             unsigned rest = __ballot_sync(0xffffffffu, t >= 0 && !chain);
             while (rest) {
-                const int src = __ffs(rest) - 1;
-                rest &= rest - 1;
-                repair_tile_warp(a, (int64_t)__shfl_sync(0xffffffffu, t, src), T, lane);
+                int64_t t2[2] = {0, 0};
+                int cnt = 0;
+#pragma unroll
+                for (int q = 0; q < 2; ++q)
+                    if (rest) {
+                        const int src = __ffs(rest) - 1;
+                        rest &= rest - 1;
+                        t2[q] = (int64_t)__shfl_sync(0xffffffffu, t, src);
+                        ++cnt;
+                    }
+                repair_tiles_warp<2>(a, t2, cnt, T, lane, false);
+            }
+            RETH_STAMP(5 + 2 * (T - 3));
+            cluster.sync();
+            RETH_STAMP(6 + 2 * (T - 3));
+        }
+    }
+
+    // ---- D: tile level 2 (dense) and this CTA's level-1 tiles
+    const int64_t n1 = (NT >= 2) ? ((a.g.n_tiles - 1 < 32) ? a.g.n_tiles - 1 : 32) : 0;     // tiles at level 1
+    const int64_t n2 = (NT >= 3) ? ((a.g.n_tiles - 33 < 1024) ? a.g.n_tiles - 33 : 1024) : 0;   // tiles at level 2
+    const int my_parents = (n1 > brank) ? (int)((n1 - brank + nblk - 1) / nblk) : 0;       // level-1 tiles j = brank + q*nblk
+    if (NT >= 3) {
+        const int n_e = my_parents * 32;                          // candidate level-2 tiles of this CTA
+        for (int base = 0; base < n_e; base += 32 * kWarps) {
+            const int e = base + wic + kWarps * lane;
+            int64_t tile = -1;
+            uint32_t m = 0;
+            if (e < n_e) {
+                const int64_t rel = ((int64_t)brank + (int64_t)(e >> 5) * nblk) * 32 + (e & 31);
+                if (rel < n2) { tile = 33 + rel; m = __ldcg(&a.mask[tile]); }
+            }
+            unsigned todo = __ballot_sync(0xffffffffu, m != 0u);
+            while (todo) {
+                int64_t t4[4] = {0, 0, 0, 0};
+                int cnt = 0;
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    if (todo) {
+                        const int src = __ffs(todo) - 1;
+                        todo &= todo - 1;
+                        t4[q] = __shfl_sync(0xffffffffu, tile, src);
+                        ++cnt;
+                    }
+                repair_tiles_warp<4>(a, t4, cnt, 2, lane, false);
             }
         }
-        RETH_STAMP(5 + 2 * (T - 2));
-        cluster.sync();
-        RETH_STAMP(6 + 2 * (T - 2));
+        RETH_STAMP(20);
+        __syncthreads();
     }
-    if (brank != 0) return;
-    RETH_STAMP(20);
-    repair_top(a);
+    if (NT >= 2) {
+        for (int q = wic; q < my_parents; q += kWarps) {
+            const int64_t t1[1] = {1 + (int64_t)brank + (int64_t)q * nblk};
+            repair_tiles_warp<1>(a, t1, 1, 1, lane, true);
+        }
+        RETH_STAMP(23);
+        cluster.sync();
+        RETH_STAMP(24);
+    }
+    if (brank == 0 && wic == 0) {
+        const int64_t t0[1] = {0};
+        repair_tiles_warp<1>(a, t0, 1, 0, lane, true);
+    }
     RETH_STAMP(22);
 }
 

@@ -437,13 +437,14 @@ class ReplayShard:
         return self.stats()["tail"]
 
     def step_loop(self, steps, batch, prio_dev, uniforms_dev=None, seed=0, alpha=0.6, beta=0.4,
-                  gather=True, serial=False, time_gather=False, sample=True, update=True, group=1, stream=None):
+                  gather=True, serial=False, time_gather=False, sample=True, update=True, group=1,
+                  one_gather_stream=False, stream=None):
         pp, ploc, pdt, pcnt, pk = _ptr_loc(prio_dev)
         assert ploc == DEVICE and pdt == np.dtype(np.float32) and pcnt >= steps * batch
         up, uloc, udt, ucnt, uk = _ptr_loc(uniforms_dev)
         if uniforms_dev is not None:
             assert uloc == DEVICE and udt == np.dtype(np.float64) and ucnt >= steps * batch
-        flags = (0 if gather else 1) | (2 if serial else 0) | (4 if time_gather else 0) | (0 if sample else 8) | (0 if update else 16) | ((int(group) & 0xff) << 8)
+        flags = (0 if gather else 1) | (2 if serial else 0) | (4 if time_gather else 0) | (0 if sample else 8) | (0 if update else 16) | (32 if one_gather_stream else 0) | ((int(group) & 0xff) << 8)
         self._ck(self._lib.reth_replay_step_loop(self._h, int(steps), int(batch), pp, up,
                                                  int(seed) & (2**64 - 1), float(alpha), float(beta),
                                                  flags, self._s(stream)))

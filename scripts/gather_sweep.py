@@ -9,7 +9,7 @@ from reth_b200 import ReplayShard
 ATARI = [(np.uint8, (4, 84, 84)), (np.int64, ()), (np.float32, ()), (np.uint8, (4, 84, 84)), (np.float32, ())]
 R = 56464
 cap = int(os.environ.get("CAP", 1 << 20)); B = int(os.environ.get("B", 512)); depth = int(os.environ.get("DEPTH", 16))
-sh = ReplayShard(cap, ATARI, max_batch=B, ring_depth=depth)
+sh = ReplayShard(cap, ATARI, max_batch=B, ring_depth=depth, update_cluster=int(os.environ.get("RETH_CLUSTER", 0)))
 g = torch.Generator(device="cuda").manual_seed(0)
 chunk = 1 << 14
 for st in range(0, cap, chunk):
