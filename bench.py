@@ -190,11 +190,15 @@ def fill_shard(torch, shard, cap, seed):
     torch.cuda.synchronize()
 
 
-def timed_loop(torch, dist, shard, steps, warmup, iters, batch, prio, group, world, time_gather):
+def timed_loop(torch, dist, shard, steps, warmup, iters, batch, prio, group, world, time_gather, shard_group=None):
     def one_step(k):
         off = (k % prio_steps) * iters * batch
         shard.step_loop(iters, batch, prio[off:], seed=1234, alpha=ALPHA, beta=BETA, group=group,
                         time_gather=time_gather, one_gather_stream=time_gather)
+        if shard_group is not None:
+            # the path's only exchange: NCCL all-gather of the 16-byte shard roots {total, min}
+            # (sharded.py Mode G), once per bench step, asynchronous on the torch stream
+            shard_group.exchange_roots()
     prio_steps = prio.numel() // (iters * batch)
     for k in range(warmup):
         one_step(k)
@@ -317,17 +321,15 @@ def run_ours(args):
 
     # multi-GPU: shards are independent (reference: one server per shard, trainer.py:52-61); the only
     # exchange is the 16-byte shard root {total, min}, combined with an NCCL all-gather per bench step
-    roots = None
+    sg = None
     if world > 1:
-        roots = torch.zeros(2 * world, device="cuda", dtype=torch.float64)
+        from reth_b200.sharded import ShardGroup
+        sg = ShardGroup(shard)
 
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()
-    ms, launches, _ = timed_loop(torch, dist, shard, args.steps, args.warmup, iters, B, prio, G, world, False)
-    if world > 1:
-        mine = torch.as_tensor(shard.root_dev(), device="cuda").clone()
-        dist.all_gather_into_tensor(roots, mine)
+    ms, launches, _ = timed_loop(torch, dist, shard, args.steps, args.warmup, iters, B, prio, G, world, False, sg)
     clk = clocks.stop() if rank == 0 else None
     value = world * args.steps * iters * B / (ms / 1e3)
 
@@ -382,10 +384,10 @@ def run_ours(args):
         "hbm_gbs_whole_loop": 2 * ROW_BYTES * value / 1e9 / world,
         "strict_alternation": {"value": strict, "unit": "transitions/s", "prefetch_group": 1},
         "append": {"rows_per_s": app_rows, "gbs": app_gbs, "rows_per_call": 16384, "source": "device"},
-        "shard_mode": "independent shards; NCCL all-gather of shard {total,min} once per run" if world > 1 else "single shard",
+        "shard_mode": "one shard per GPU, no data-path collective; NCCL all-gather of the 16-byte shard roots {total,min} once per bench step inside the timed region" if world > 1 else "single shard",
     }
     if world > 1:
-        line["shard_totals"] = [float(x) for x in roots.cpu()[0::2]]
+        line["shard_totals"] = [float(x) for x in sg.all_roots.cpu()[0::2]]
     if rank == 0 and world == 1 and not args.no_cpu:
         cores = os.cpu_count() or 1
         v, dt = cpu_reference_arm(args.cpu_steps, 1, args.cpu_iters, B, cap, cores)

@@ -215,6 +215,36 @@ class OracleRing:
         return outs
 
 
+def global_sample(trees, shard, batch, u, beta, min_mode=0):
+    """Mode-G oracle: n reference trees + the range rule.  Shard `shard` serves the
+    targets of the global cdf inside [prefix, prefix + total_shard); indices come from the
+    reference descent (_numba_find_index, utils/sumtree.py:34-58) on the LOCAL target, weights use
+    the global minimum.  -> (first, indices, weights, values)."""
+    totals = [t.sum() for t in trees]
+    total, prefix = 0.0, []
+    for t in totals:
+        prefix.append(total)
+        total = total + t
+    mins = [t._min[0] for t, s in zip(trees, totals) if s != 0.0 and t._min[0] != 0.0]
+    pmin = min(mins) if mins else 1.0
+    seg = total / float(batch)
+    u = np.asarray(u, np.float64)
+    first, idx, val = None, [], []
+    for i in range(batch):
+        tgt = (float(i) + u[i]) * seg
+        lo_ok = (not prefix[shard] > 0.0) or tgt >= prefix[shard]
+        hi_ok = shard == len(trees) - 1 or not tgt >= prefix[shard] + totals[shard]
+        if lo_ok and hi_ok:
+            if first is None:
+                first = i
+            j = trees[shard].find_index(tgt - prefix[shard])
+            idx.append(j)
+            val.append(trees[shard]._val[j])
+    idx = np.asarray(idx, np.int64)
+    val = np.asarray(val, np.float64)
+    return (first if first is not None else 0), idx, is_weights(val, pmin, beta), val
+
+
 def fifo_indices(capacity, tail, n):
     """fifo_policy.py:11-18 -> (indices, new_tail)."""
     t = C.c_int64(tail)

@@ -1,0 +1,90 @@
+"""Multi-shard replay: one ReplayShard per GPU / rank.
+
+The reference shards replay by running one server per port with capacity // n and lets the
+learner poll the shards round-robin, one whole batch from one shard at a time, with no
+cross-shard normalisation (test/apex-dqn/trainer.py:33-36,52-61; actors are pinned to a shard,
+worker.py:94).  Two modes are provided:
+
+  Mode R (reference parity): step t draws its batch from shard t mod n; no collective.
+  Mode G (north_star "NCCL-reduced shard totals"): every rank contributes its 16-byte shard root
+         {total, min}; after one all-gather each rank knows the exclusive prefix of totals and
+         serves the stratified targets of the GLOBAL cdf that fall inside its range, with the
+         global minimum in the importance weights.  The rule, identical on host and device
+         (reth_b200/csrc/tree.cuh per_sample_kernel):
+             total   = ((t_0 + t_1) + ...) in rank order,  seg = total / B
+             target_i = (i + u_i) * seg
+             rank r serves i in [first_r, end_r):  first_r = min{i : target_i >= prefix_r},
+             end_r = B for the last rank, else min{i : target_i >= prefix_r + t_r}
+             local target = target_i - prefix_r;  p_min = min over non-empty shards of min_r.
+
+torch.distributed carries the exchange (NCCL on GPUs, gloo in the CPU tests); the data path has
+no other collective: frames never leave their shard unless the learner is remote.
+"""
+import numpy as np
+
+
+def owner_round_robin(step, n_shards):
+    """Mode R: the shard that serves the whole batch of learner step `step` (trainer.py:33-36)."""
+    return int(step) % int(n_shards)
+
+
+def combine_roots(all_roots):
+    """all_roots: float64[2*n] = {total_r, min_r} in rank order -> (total, prefix[n], p_min)."""
+    r = np.asarray(all_roots, dtype=np.float64).reshape(-1, 2)
+    prefix = np.empty(len(r), np.float64)
+    total = 0.0
+    mn = 0.0
+    for s, (t, m) in enumerate(r):
+        prefix[s] = total
+        total = total + t
+        if t != 0.0 and m != 0.0:
+            mn = m if (mn == 0.0 or m < mn) else mn
+    return total, prefix, (mn if mn != 0.0 else 1.0)
+
+
+def global_quota(all_roots, shard, batch, uniforms):
+    """Host statement of the Mode-G range rule for explicit uniforms u[batch]:
+    -> (first, count, local_targets float64[count], p_min)."""
+    r = np.asarray(all_roots, dtype=np.float64).reshape(-1, 2)
+    n = len(r)
+    total, prefix, pmin = combine_roots(all_roots)
+    u = np.asarray(uniforms, dtype=np.float64)
+    assert len(u) == batch
+    seg = total / float(batch)
+    targets = (np.arange(batch, dtype=np.float64) + u) * seg
+
+    def lower_bound(bound):
+        if not bound > 0.0:
+            return 0
+        return int(np.searchsorted(targets, bound, side="left"))   # targets are monotone in i
+    first = lower_bound(prefix[shard])
+    end = batch if shard == n - 1 else lower_bound(prefix[shard] + r[shard, 0])
+    end = max(end, first)
+    return first, end - first, targets[first:end] - prefix[shard], pmin
+
+
+class ShardGroup:
+    """This rank's shard inside a torch.distributed process group."""
+
+    def __init__(self, shard, group=None, device=None):
+        import torch
+        import torch.distributed as dist
+        self.shard = shard
+        self.dist = dist
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        self.device = device if device is not None else torch.device("cuda", shard.device)
+        self.all_roots = torch.zeros(2 * self.world, dtype=torch.float64, device=self.device)
+        self._mine = torch.as_tensor(shard.root_dev(), device=self.device)   # zero-copy view of {total, min}
+
+    def exchange_roots(self, async_op=False):
+        """all-gather of the 16-byte shard roots (NCCL over NVLink); -> device float64[2*world]."""
+        return self.dist.all_gather_into_tensor(self.all_roots, self._mine, group=self.group, async_op=async_op)
+
+    def sample_global(self, global_batch, beta=0.4, uniforms=None, seed=0, slot=0, stream=None):
+        """Draw this rank's part of one global stratified batch into batch slot `slot`;
+        -> (first, count) of the global batch positions it serves."""
+        self.shard.sample_global(global_batch, self.all_roots, self.world, self.rank, beta=beta,
+                                 uniforms=uniforms, seed=seed, slot=slot, stream=stream)
+        return self.shard.slot_meta(slot, stream=stream)

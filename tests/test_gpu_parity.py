@@ -285,3 +285,49 @@ def test_step_loop_matches_stepwise_calls(Shard):
             assert np.array_equal(x, y)
         for (da, ia, wa), (db, ib, wb) in zip(out[a][1], out[b][1]):
             assert np.array_equal(ia, ib) and np.array_equal(wa, wb) and np.array_equal(da[0], db[0])
+
+
+@pytest.mark.parametrize("n_shards", [2, 4])
+def test_global_mode_vs_oracle(Shard, n_shards):
+    """Mode G: n shards (emulated on one GPU), stratified targets over the global
+    cdf, each shard serves its contiguous range with the global minimum -- against n reference
+    trees + the same range rule (oracle.global_sample).  One shard is left empty."""
+    import torch
+    cap, B = 5000, 256
+    rng = np.random.default_rng(21)
+    shards, trees = [], []
+    for g in range(n_shards):
+        sh = Shard(cap, [], max_batch=B, store_rows=False)
+        t = po.OracleSumTree(cap)
+        if g != 1 or n_shards == 2:                      # with 4 shards, shard 1 stays empty
+            n = cap if g % 2 == 0 else 1234
+            p = rng.random(n) * (1 + 3 * g) + 0.01
+            sh.update(np.arange(n), p, transform=False)
+            t.update(np.arange(n), p)
+        shards.append(sh)
+        trees.append(t)
+    torch.cuda.synchronize()
+    roots = torch.cat([torch.as_tensor(sh.root_dev(), device="cuda").clone() for sh in shards])
+    for step in range(4):
+        u = rng.random(B)
+        covered = 0
+        for g, sh in enumerate(shards):
+            sh.sample_global(B, roots, n_shards, g, beta=0.5, uniforms=u, slot=step % 2)
+            first, count = sh.slot_meta(step % 2)
+            _, idx, w = sh.slot_read(step % 2)
+            ofirst, oidx, ow, _ = po.global_sample(trees, g, B, u, 0.5)
+            assert count == len(oidx) and first == covered
+            assert np.array_equal(idx[:count], oidx)
+            assert np.allclose(w[:count], ow, rtol=RTOL, atol=0)
+            covered += count
+        assert covered == B
+    # device generator: same seed and draw counter on every shard -> the slices still partition the batch
+    covered = 0
+    for g, sh in enumerate(shards):
+        sh.sample_global(B, roots, n_shards, g, beta=0.5, uniforms=None, seed=99, slot=0)
+        first, count = sh.slot_meta(0)
+        assert first == covered
+        covered += count
+    assert covered == B
+    for sh in shards:
+        sh.close()
