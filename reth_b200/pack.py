@@ -1,0 +1,200 @@
+"""Wire codec of the reth_buffer service (host side, no kernel).
+
+The byte format is the reference's (reth_buffer/reth_buffer/utils/pack.py:60-98,148-164), kept so
+that actors built against the reference can feed this server unchanged:
+
+    [4-byte big-endian header length][msgpack header][raw body]
+    header = {"meta": <tree>, "body_len": int, "time": float}
+    <tree> mirrors the python object; an ndarray becomes
+        {KEY_NUMPY: True, "header": {"shape","fortran_order","descr"}, "raw_size", "offset", "length"}
+    and a bytes-like becomes {KEY_BYTES: True, "raw_size", "offset", "length"}; offset/length
+    address the body.  An lz4-framed body is flagged by KEY_COMPRESS (utils/pack.py:67-84).
+
+Client.append sends  encode([[encode(row_0), ..., encode(row_n-1)], weights])  with one inner
+message per transition (client/client.py:26-35); `decode_append` turns that back into columns
+with one strided copy per column instead of the reference's per-row Python loop
+(client/numpy_loader.py:35-50).  This build's own clients send the columns directly
+(`encode([columns, weights])` with COLUMNAR set in the header), which skips the row split.
+"""
+import time
+
+import msgpack
+import numpy as np
+
+KEY_COMPRESS = "reth_compress_953531b51ab8"
+KEY_NUMPY = "reth_numpy_356b759ef2b3"
+KEY_BYTES = "reth_bytes_a32b00c47e72"
+KEY_COLUMNAR = "reth_b200_columnar"
+
+
+class _Body:
+    """Body segments in emission order; offsets are assigned as segments are added."""
+
+    def __init__(self):
+        self.size = 0
+        self.parts = []
+
+    def add(self, buf):
+        mv = memoryview(buf).cast("B") if not isinstance(buf, np.ndarray) else memoryview(
+            np.ascontiguousarray(buf).reshape(-1).view(np.uint8))
+        at = self.size
+        self.parts.append(mv)
+        self.size += mv.nbytes
+        return at, mv.nbytes
+
+
+def _describe(obj, body):
+    if isinstance(obj, (list, tuple)):
+        return [_describe(x, body) for x in obj]
+    if isinstance(obj, dict):
+        return {k: _describe(v, body) for k, v in obj.items()}
+    if isinstance(obj, np.ndarray):
+        node = {KEY_NUMPY: True, "header": np.lib.format.header_data_from_array_1_0(obj), "raw_size": obj.nbytes}
+        if obj.flags.f_contiguous and not obj.flags.c_contiguous:
+            at, n = body.add(obj.T)                  # fortran data is emitted in memory order
+        else:
+            at, n = body.add(obj)
+        node["offset"], node["length"] = at, n
+        return node
+    if isinstance(obj, (bytes, bytearray, memoryview)):
+        node = {KEY_BYTES: True, "raw_size": memoryview(obj).nbytes}
+        node["offset"], node["length"] = body.add(obj)
+        return node
+    if isinstance(obj, np.generic):
+        return obj.item()
+    return obj
+
+
+def encode(obj, compress=False, columnar=False, now=None):
+    """-> bytearray in the reference wire format."""
+    body = _Body()
+    meta = _describe(obj, body)
+    raw = bytearray(body.size)
+    at = 0
+    for mv in body.parts:
+        raw[at:at + mv.nbytes] = mv
+        at += mv.nbytes
+    header = {}
+    if compress:
+        try:
+            import lz4.frame
+        except ImportError as e:                      # pragma: no cover - lz4 is absent from this image
+            raise RuntimeError("compress=True needs the lz4 package") from e
+        raw = lz4.frame.compress(raw, return_bytearray=True)
+        header[KEY_COMPRESS] = True
+    header["meta"] = meta
+    header["body_len"] = len(raw)
+    header["time"] = time.time() if now is None else now
+    if columnar:
+        header[KEY_COLUMNAR] = True
+    hb = msgpack.packb(header)
+    out = bytearray(4 + len(hb) + len(raw))
+    out[:4] = len(hb).to_bytes(4, "big")
+    out[4:4 + len(hb)] = hb
+    out[4 + len(hb):] = raw
+    return out
+
+
+def _split(buf):
+    mv = memoryview(buf).cast("B")
+    hl = int.from_bytes(mv[:4], "big")
+    header = msgpack.unpackb(mv[4:4 + hl])
+    body = mv[4 + hl:]
+    if body.nbytes != header["body_len"]:
+        raise ValueError("truncated message: body_len does not match")
+    if header.get(KEY_COMPRESS):
+        try:
+            import lz4.frame
+        except ImportError as e:
+            raise RuntimeError("received an lz4-compressed message but the lz4 package is not installed") from e
+        body = memoryview(lz4.frame.decompress(body, return_bytearray=True))
+    return header, body, 4 + hl
+
+
+def _array(node, body):
+    h = node["header"]
+    dt = np.lib.format.descr_to_dtype(h["descr"])
+    a = np.frombuffer(body[node["offset"]:node["offset"] + node["length"]], dtype=dt)
+    shape = tuple(h["shape"])
+    a = a.reshape(shape[::-1]).T if h["fortran_order"] else a.reshape(shape)
+    if a.nbytes != node["raw_size"]:
+        raise ValueError("ndarray size mismatch")
+    return a
+
+
+def _rebuild(node, body):
+    if isinstance(node, (list, tuple)):
+        return [_rebuild(x, body) for x in node]
+    if isinstance(node, dict):
+        if KEY_NUMPY in node:
+            return _array(node, body)
+        if KEY_BYTES in node:
+            return body[node["offset"]:node["offset"] + node["length"]]
+        return {k: _rebuild(v, body) for k, v in node.items()}
+    return node
+
+
+def decode(buf):
+    """Inverse of encode (utils/pack.py:148-164); arrays are views into `buf` (or into the
+    decompressed body)."""
+    header, body, _ = _split(buf)
+    return _rebuild(header["meta"], body)
+
+
+def is_columnar(buf):
+    mv = memoryview(buf).cast("B")
+    hl = int.from_bytes(mv[:4], "big")
+    return bool(msgpack.unpackb(mv[4:4 + hl]).get(KEY_COLUMNAR))
+
+
+def decode_append(buf):
+    """An append message -> (columns, weights): columns[c] is a C-contiguous (n, ...) array.
+
+    Accepts the reference's row format ([[row messages], weights], client/client.py:26-35) and this
+    build's columnar format.  Row format, fast path: when all row messages have the same length and
+    the same inner header length (same struct: always, for a fixed-size transition), the rows form
+    an (n, L) byte matrix and each column is ONE strided copy out of it."""
+    header, body, _ = _split(buf)
+    meta = header["meta"]
+    if header.get(KEY_COLUMNAR):
+        cols, weights = _rebuild(meta, body)
+        return [np.ascontiguousarray(c) for c in cols], np.asarray(weights)
+    rows, wnode = meta
+    weights = _rebuild(wnode, body)
+    n = len(rows)
+    if n == 0:
+        return [], np.asarray(weights)
+    L, first = rows[0]["length"], rows[0]["offset"]
+    regular = all(r["length"] == L and r["offset"] == first + i * L for i, r in enumerate(rows))
+    if regular:
+        mat = np.frombuffer(body[first:first + n * L], np.uint8).reshape(n, L)
+        h0, _, skip = _split(mat[0])
+        hl = mat[:, :4]
+        if np.all(hl == hl[0]) and all(isinstance(x, dict) and KEY_NUMPY in x for x in h0["meta"]):
+            cols = []
+            for node in h0["meta"]:
+                hd = node["header"]
+                dt = np.lib.format.descr_to_dtype(hd["descr"])
+                if hd["fortran_order"] and len(hd["shape"]) > 1:
+                    break
+                lo = skip + node["offset"]
+                raw = np.ascontiguousarray(mat[:, lo:lo + node["length"]])
+                cols.append(raw.view(dt).reshape((n,) + tuple(hd["shape"])))
+            else:
+                return cols, np.asarray(weights)
+    # general path: decode row by row
+    per_row = [decode(body[r["offset"]:r["offset"] + r["length"]]) for r in rows]
+    ncol = len(per_row[0])
+    cols = [np.stack([np.asarray(per_row[i][c]) for i in range(n)]) for c in range(ncol)]
+    return cols, np.asarray(weights)
+
+
+def encode_append_rows(columns, weights, compress=False, now=None):
+    """What the reference's Client.append puts on the wire (client/client.py:26-35)."""
+    n = len(weights)
+    rows = [encode([col[i, ...] for col in columns], now=now) for i in range(n)]
+    return encode([rows, weights], compress=compress, now=now)
+
+
+def encode_append_columns(columns, weights, now=None):
+    return encode([list(columns), weights], columnar=True, now=now)
