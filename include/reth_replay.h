@@ -235,6 +235,26 @@ int reth_replay_update_async(reth_replay_t *h, const int64_t *idx_host, const vo
 /* wait until everything enqueued on the pipe's streams has finished */
 int reth_replay_pipe_drain(reth_replay_t *h);
 
+/* ---- batch ring across processes: the reference hands pre-gathered batches to a learner in
+ *      another process through CUDA IPC (client/torch_cuda_loader.py:58,63,114-135,157-160:
+ *      shared CUDA tensors + interprocess events).  ipc_export() fills a plain-bytes descriptor of
+ *      this shard's batch ring (one cudaIpcMemHandle per column array + indices + weights); a
+ *      consumer process on the same GPU maps it with reth_ipc_open() and reads slot pointers.
+ *      Completion is signalled by the owner process (it replies after pipe_wait()), so no
+ *      interprocess event is needed. */
+typedef struct reth_ipc_export {
+    int32_t n_columns, ring_depth, max_batch, device;
+    int64_t row_bytes[RETH_MAX_COLUMNS];
+    unsigned char col_handle[RETH_MAX_COLUMNS][64];   /* cudaIpcMemHandle_t */
+    unsigned char idx_handle[64], w_handle[64];
+} reth_ipc_export;
+typedef struct reth_ipc_view reth_ipc_view_t;
+int reth_replay_ipc_export(reth_replay_t *h, reth_ipc_export *out);
+int reth_ipc_open(const reth_ipc_export *in, reth_ipc_view_t **out);
+int reth_ipc_slot_ptrs(reth_ipc_view_t *v, int slot, void **cols_out /*[n_columns]*/, int64_t **indices_out,
+                       double **weights_out);
+int reth_ipc_close(reth_ipc_view_t *v);
+
 /* ---- measured loop (bench / learner-less soak): `steps` iterations of
  *      sample(batch) -> gather || update_slot(new priorities), the tree chain and the
  *      frame gather on two internal streams joined to `stream` at both ends, slots used

@@ -48,6 +48,12 @@ class PipeInfo(C.Structure):
                 ("upd_host", C.c_void_p)]
 
 
+class IpcExport(C.Structure):
+    _fields_ = [("n_columns", C.c_int32), ("ring_depth", C.c_int32), ("max_batch", C.c_int32), ("device", C.c_int32),
+                ("row_bytes", C.c_int64 * RETH_MAX_COLUMNS), ("col_handle", (C.c_ubyte * 64) * RETH_MAX_COLUMNS),
+                ("idx_handle", C.c_ubyte * 64), ("w_handle", C.c_ubyte * 64)]
+
+
 def _sources():
     d = os.path.join(_HERE, "csrc")
     return [os.path.join(d, f) for f in sorted(os.listdir(d))] + [HEADER]
@@ -103,6 +109,10 @@ SIGNATURES = {
     "reth_replay_pipe_update_commit": [_vp, _i32, _i64, _i32, _f64, _i32],
     "reth_replay_update_async": [_vp, _vp, _vp, _i32, _i64, _f64, _i32],
     "reth_replay_pipe_drain": [_vp],
+    "reth_replay_ipc_export": [_vp, C.POINTER(IpcExport)],
+    "reth_ipc_open": [C.POINTER(IpcExport), C.POINTER(_vp)],
+    "reth_ipc_slot_ptrs": [_vp, _i32, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp)],
+    "reth_ipc_close": [_vp],
     "reth_replay_step_loop": [_vp, _i32, _i32, _vp, _vp, _u64, _f64, _f64, _i32, _vp],
     "reth_replay_gather_time": [_vp, C.POINTER(_f64), C.POINTER(_i64)],
     "reth_replay_debug_stamps": [_vp, C.POINTER(_i64)],

@@ -1151,6 +1151,87 @@ RETH_EXPORT int reth_replay_pipe_drain(reth_replay_t *h)
     return RETH_OK;
 }
 
+// ------------------------------------------------------------ cross-process ring --
+struct reth_ipc_view {
+    reth_ipc_export ex{};
+    uint8_t *cols[kMaxCols] = {};
+    int64_t *idx = nullptr;
+    double *w = nullptr;
+};
+
+RETH_EXPORT int reth_replay_ipc_export(reth_replay_t *h, reth_ipc_export *out)
+{
+    if (!h || !out) return RETH_ERR_INVALID;
+    DeviceGuard guard(h->cfg.device);
+    memset(out, 0, sizeof *out);
+    out->n_columns = h->cfg.store_rows ? h->cfg.n_columns : 0;
+    out->ring_depth = (int32_t)h->slots.size();
+    out->max_batch = h->cfg.max_batch;
+    out->device = h->cfg.device;
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    for (int c = 0; c < out->n_columns; ++c) {
+        out->row_bytes[c] = h->cfg.row_bytes[c];
+        CK(h, cudaIpcGetMemHandle((cudaIpcMemHandle_t *)out->col_handle[c], h->slot_cols[c]));
+    }
+    CK(h, cudaIpcGetMemHandle((cudaIpcMemHandle_t *)out->idx_handle, h->slot_idx));
+    CK(h, cudaIpcGetMemHandle((cudaIpcMemHandle_t *)out->w_handle, h->slot_w));
+    return RETH_OK;
+}
+
+RETH_EXPORT int reth_ipc_open(const reth_ipc_export *in, reth_ipc_view_t **out)
+{
+    if (!in || !out) return RETH_ERR_INVALID;
+    *out = nullptr;
+    if (in->n_columns < 0 || in->n_columns > RETH_MAX_COLUMNS) return fail(nullptr, RETH_ERR_INVALID, "bad descriptor");
+    reth_ipc_view *v = new (std::nothrow) reth_ipc_view();
+    if (!v) return fail(nullptr, RETH_ERR_OOM, "host allocation failed");
+    v->ex = *in;
+    DeviceGuard guard(in->device);
+    auto open1 = [&](const unsigned char *hb, void **p) {
+        cudaIpcMemHandle_t mh;
+        memcpy(&mh, hb, sizeof mh);
+        return cudaIpcOpenMemHandle(p, mh, cudaIpcMemLazyEnablePeerAccess);
+    };
+    cudaError_t e = cudaSuccess;
+    for (int c = 0; c < in->n_columns && e == cudaSuccess; ++c) e = open1(in->col_handle[c], (void **)&v->cols[c]);
+    if (e == cudaSuccess) e = open1(in->idx_handle, (void **)&v->idx);
+    if (e == cudaSuccess) e = open1(in->w_handle, (void **)&v->w);
+    if (e != cudaSuccess) {
+        fail(nullptr, RETH_ERR_CUDA, "cudaIpcOpenMemHandle: %s", cudaGetErrorString(e));
+        cudaGetLastError();
+        reth_ipc_close(v);
+        return RETH_ERR_CUDA;
+    }
+    *out = v;
+    return RETH_OK;
+}
+
+RETH_EXPORT int reth_ipc_slot_ptrs(reth_ipc_view_t *v, int slot, void **cols_out, int64_t **indices_out,
+                                   double **weights_out)
+{
+    if (!v || slot < 0 || slot >= v->ex.ring_depth) return RETH_ERR_INVALID;
+    const size_t mb = (size_t)v->ex.max_batch;
+    if (cols_out)
+        for (int c = 0; c < v->ex.n_columns; ++c) cols_out[c] = v->cols[c] + (size_t)slot * mb * v->ex.row_bytes[c];
+    if (indices_out) *indices_out = v->idx + (size_t)slot * mb;
+    if (weights_out) *weights_out = v->w + (size_t)slot * mb;
+    return RETH_OK;
+}
+
+RETH_EXPORT int reth_ipc_close(reth_ipc_view_t *v)
+{
+    if (!v) return RETH_OK;
+    {
+        DeviceGuard guard(v->ex.device);
+        for (int c = 0; c < kMaxCols; ++c)
+            if (v->cols[c]) cudaIpcCloseMemHandle(v->cols[c]);
+        if (v->idx) cudaIpcCloseMemHandle(v->idx);
+        if (v->w) cudaIpcCloseMemHandle(v->w);
+    }
+    delete v;
+    return RETH_OK;
+}
+
 // ------------------------------------------------------------------ step loop --
 RETH_EXPORT int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, const float *prio_dev,
                                       const double *uniforms_dev, uint64_t seed, double alpha, double beta,

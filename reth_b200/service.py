@@ -150,14 +150,12 @@ class _Engine:
             self.pipe = self.shard.open_pipe(self.batch_size, self.group, seed=0x5EED)
         return self.pipe
 
-    def next_batch(self):
-        """-> (batch slot, host indices view) of the next pre-sampled batch."""
-        if self._queue:
-            return self._queue.pop()
+    def next_group(self):
+        """Take delivery of the next pre-sampled group and keep `ahead` more in flight.
+        -> (group slot g, host indices [group, batch], host weights [group, batch]); batch slots
+        g*group .. g*group+group-1 stay lent until the next call."""
         self.wait_ready()
         with self.lock:
-            if self._queue:
-                return self._queue.pop()
             pipe = self._ensure_pipe()
             self.flush()                                      # partially staged write-backs land before the draw
             beta = self.sampler["beta"].value()
@@ -169,8 +167,17 @@ class _Engine:
                 g = pipe.wait()
                 while pipe.in_flight < self.ahead and pipe.can_issue():
                     pipe.issue(beta)
+            return g, pipe.idx_host[g], pipe.w_host[g]
+
+    def next_batch(self):
+        """-> (batch slot, host indices view) of the next pre-sampled batch."""
+        if self._queue:
+            return self._queue.pop()
+        with self.lock:
+            if self._queue:
+                return self._queue.pop()
+            g, idx, _ = self.next_group()
             G = self.group
-            idx = pipe.idx_host[g]
             self._queue = [(g * G + k, idx[k]) for k in range(G - 1, -1, -1)]
             return self._queue.pop()
 
@@ -302,8 +309,19 @@ def _engine(meta_addr):
         raise ConnectionError(f"no replay engine at {meta_addr!r} in this process") from None
 
 
+def _remote(meta_addr):
+    return isinstance(meta_addr, str) and not meta_addr.startswith(_SCHEME)
+
+
 class Client:
-    """client/client.py:8-39."""
+    """client/client.py:8-39.  An address that does not name an in-process engine is a server in
+    another process (service_mp): the same class name then builds the ZeroMQ client."""
+
+    def __new__(cls, meta_addr, *args, **kwargs):
+        if cls is Client and _remote(meta_addr):
+            from . import service_mp
+            return service_mp.Client(meta_addr, *args, **kwargs)
+        return super().__new__(cls)
 
     def __init__(self, meta_addr):
         self._eng = _engine(meta_addr)
@@ -361,6 +379,12 @@ class _LoaderBase:
 class NumpyLoader(_LoaderBase):
     """client/numpy_loader.py:8-56: fresh host arrays (data, indices int64, weights float64)."""
 
+    def __new__(cls, meta_addr, *args, **kwargs):
+        if cls is NumpyLoader and _remote(meta_addr):
+            from . import service_mp
+            return service_mp.NumpyLoader(meta_addr, *args, **kwargs)
+        return super().__new__(cls)
+
     def __init__(self, meta_addr, topic="default", prefetch=1, ahead=0):
         super().__init__(meta_addr, topic, prefetch, ahead)
 
@@ -379,6 +403,12 @@ class TorchCudaLoader(_LoaderBase):
     buffer_size = batches resident in the lending ring, as in the reference; by default half of
     them form the group being consumed and the other half is drawn + gathered ahead
     (prefetch = buffer_size // 2, ahead = 1).  prefetch=1, ahead=0 is strict alternation."""
+
+    def __new__(cls, meta_addr, *args, **kwargs):
+        if cls is TorchCudaLoader and _remote(meta_addr):
+            from . import service_mp
+            return service_mp.TorchCudaLoader(meta_addr, *args, **kwargs)
+        return super().__new__(cls)
 
     def __init__(self, meta_addr, topic="default", buffer_size=8, num_procs=6, prefetch=None, ahead=None):
         eng = _engine(meta_addr)

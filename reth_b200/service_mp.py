@@ -1,0 +1,401 @@
+"""The replay server in its own process, reachable by address (SURVEY.md 7 "hard part 8").
+
+The reference's callers start the server in one process and build `Client` / loaders in others
+from the address string alone (test/apex-dqn/trainer.py:49-66, worker.py:22,
+reth_buffer/test/test_rb.py:63-85).  This module keeps that layout:
+
+  server process   owns the GPU shard (service._Engine) and runs ONE poll loop over
+                   meta   REP    tcp   -> JSON config                (server/main_loop.py:64-76)
+                   append PULL   tcp   <- reference wire format      (main_loop.py:21-61, utils/pack.py)
+                   update PULL   tcp   <- [indices, weights, step]   (main_loop.py:79-88, sampler_loop.py:29-36)
+                   loader ROUTER tcp   <-> loaders in other processes (replaces the per-sampler PUSH
+                                           sockets + the loader worker processes)
+                   A single loop = a single arrival order for appends, updates and draws, which is
+                   what the reference gets from funnelling everything through one SUB socket.
+  Client           PUSH sockets, fire-and-forget, HWM 10 like the reference (utils/__init__.py:12)
+  loaders          ask the server for the next pre-sampled GROUP; indices/weights come back in the
+                   reply, the batch itself stays in HBM and is mapped into the loader's process
+                   through CUDA IPC handles of the batch ring (reth_ipc_open) -- the mechanism of
+                   client/torch_cuda_loader.py:58,63,157-160.  NumpyLoader copies the rows D2H.
+
+Append messages may be in the reference's row format (what its Client sends) or this build's
+columnar format (what `Client(..., wire="columns")`, the default here, sends): see pack.py.
+"""
+import ctypes as C
+import json
+import multiprocessing as mp
+import os
+import signal
+import socket
+import time
+
+import numpy as np
+
+from . import pack
+
+ZMQ_DEFAULT_HWM = 10            # utils/__init__.py:12
+
+
+def _pick_port(host):
+    s = socket.socket()
+    s.bind((host, 0))
+    port = s.getsockname()[1]
+    s.close()
+    return port
+
+
+# ------------------------------------------------------------------ server --
+def server_main(capacity, batch_size, host, ports, samplers, cache_policy, device, max_ring, ready_evt):
+    """Body of the server process (main_loop.py:110-216 + append_loop + sampler_loop in one loop)."""
+    import zmq
+    from . import _cabi, service
+
+    signal.signal(signal.SIGINT, signal.SIG_IGN)
+    stop = {"flag": False}
+    signal.signal(signal.SIGTERM, lambda *_: stop.__setitem__("flag", True))
+
+    eng = service._Engine(capacity, batch_size, samplers, cache_policy, device, max_ring)
+    ctx = zmq.Context.instance()
+    ctx.setsockopt(zmq.LINGER, 0)
+    addrs = {k: f"tcp://{host}:{p}" for k, p in ports.items()}
+    meta = ctx.socket(zmq.REP)
+    meta.bind(addrs["meta"])
+    app = ctx.socket(zmq.PULL)
+    app.set_hwm(ZMQ_DEFAULT_HWM)
+    app.bind(addrs["append"])
+    upd = ctx.socket(zmq.PULL)
+    upd.set_hwm(ZMQ_DEFAULT_HWM)
+    upd.bind(addrs["update"])
+    ldr = ctx.socket(zmq.ROUTER)
+    ldr.bind(addrs["loader"])
+    config = {"engine": "reth_b200", "capacity": capacity, "batch_size": batch_size, "device": device,
+              "meta_addr": addrs["meta"], "append_addr": addrs["append"], "update_addr": addrs["update"],
+              "loader_addr": addrs["loader"], "pid": os.getpid(),
+              "sampler_info": {eng.topic: {"topic": eng.topic, "sampler_cls": "PERSampler",
+                                           "sample_start": eng.sampler["sample_start"], "batch_size": batch_size}}}
+    poller = zmq.Poller()
+    for s in (meta, app, upd, ldr):
+        poller.register(s, zmq.POLLIN)
+    waiting = []                 # loader requests parked until the buffer is ready (sampler_loop.py:25-28)
+    ready_evt.set()
+
+    def reply(ident, obj, *blobs):
+        ldr.send_multipart([ident, b"", json.dumps(obj).encode()] + list(blobs))
+
+    def serve_next(ident):
+        g, idx, w = eng.next_group()
+        reply(ident, {"ok": True, "group": int(g), "first_slot": int(g * eng.group), "n": int(eng.group)},
+              idx.tobytes(), w.tobytes())
+
+    def handle_loader(ident, req):
+        op = req.get("op")
+        if op == "open":
+            if eng.shard is None:                      # row struct unknown until the first append
+                waiting.append((ident, req))
+                return
+            eng.open_pipe(req.get("prefetch", 1), req.get("ahead", 0))
+            ex = _cabi.IpcExport()
+            eng.shard._ck(_cabi.lib().reth_replay_ipc_export(eng.shard._h, C.byref(ex)))
+            struct = [[np.dtype(dt).str, list(sh)] for dt, sh in eng.shard.struct]
+            reply(ident, {"ok": True, "struct": struct, "batch_size": batch_size, "group": eng.group,
+                          "ahead": eng.ahead, "ring_depth": eng.shard.ring_depth}, bytes(ex))
+        elif op == "next":
+            if not eng.ready():
+                waiting.append((ident, req))
+                return
+            serve_next(ident)
+        elif op == "rows":                             # NumpyLoader: rows of a lent slot, device -> host
+            data, _, _ = eng.shard.slot_read(int(req["slot"]), with_rows=True, stream=eng.stream)
+            reply(ident, {"ok": True}, *[np.ascontiguousarray(c).tobytes() for c in data])
+        elif op == "close":
+            eng.release_pipe()
+            reply(ident, {"ok": True})
+        elif op == "drain":
+            eng.drain()
+            reply(ident, {"ok": True, "cnt": eng.cnt})
+        else:
+            reply(ident, {"ok": False, "error": f"unknown op {op!r}"})
+
+    try:
+        while not stop["flag"]:
+            events = dict(poller.poll(50))
+            if meta in events:
+                meta.recv()
+                meta.send_json(config)
+            # drain every pending write before serving a draw (sampler_loop.py:29-36)
+            while app.poll(0):
+                frame = app.recv(copy=False)
+                cols, weights = pack.decode_append(frame.buffer)
+                eng.append(cols, weights)
+            while upd.poll(0):
+                frame = upd.recv(copy=False)
+                indices, weights, step = pack.decode(frame.buffer)
+                eng.update(np.asarray(indices), np.asarray(weights), bool(step))
+            if waiting and eng.shard is not None:
+                parked, waiting[:] = list(waiting), []
+                for ident, req in parked:
+                    handle_loader(ident, req)
+            while ldr.poll(0):
+                ident, _, payload = ldr.recv_multipart()
+                try:
+                    handle_loader(ident, json.loads(payload))
+                except Exception as e:                 # keep serving; the loader raises on its side
+                    reply(ident, {"ok": False, "error": f"{type(e).__name__}: {e}"})
+    finally:
+        eng.close()
+        for s in (meta, app, upd, ldr):
+            s.close(0)
+
+
+# ------------------------------------------------------------ public surface --
+def start_server(capacity, batch_size, host=None, port=None, samplers=None, cache_policy=None, device=0,
+                 max_ring=16):
+    """reth_buffer.start_server (__init__.py:11-27): spawn the server process, return
+    (proc, meta_addr).  `proc` supports terminate()/join() as callers expect (trainer.py:72-74)."""
+    host = host or "127.0.0.1"
+    ports = {"meta": port or _pick_port(host)}
+    for k in ("append", "update", "loader"):
+        ports[k] = _pick_port(host)
+    if samplers is not None:
+        samplers = [dict(s, sampler_cls=getattr(s["sampler_cls"], "__name__", str(s["sampler_cls"]))) for s in samplers]
+    ctx = mp.get_context("spawn")
+    ready = ctx.Event()
+    proc = ctx.Process(target=_server_entry, args=(capacity, batch_size, host, ports, samplers, cache_policy, device,
+                                                   max_ring, ready), daemon=True)
+    proc.start()
+    if not ready.wait(120):
+        proc.terminate()
+        raise RuntimeError("replay server did not come up")
+    return proc, f"tcp://{host}:{ports['meta']}"
+
+
+def _server_entry(capacity, batch_size, host, ports, samplers, cache_policy, device, max_ring, ready):
+    from .sampler import PERSampler
+    if samplers is not None:
+        for s in samplers:
+            if s["sampler_cls"] != "PERSampler":
+                raise NotImplementedError("only PERSampler runs on the device in this build")
+            s["sampler_cls"] = PERSampler
+    server_main(capacity, batch_size, host, ports, samplers, cache_policy, device, max_ring, ready)
+
+
+def start_per(capacity, batch_size, alpha=0.6, beta=0.4, sample_start=1000, num_sampler_procs=1,
+              host=None, port=None, cache_policy=None, device=0, max_ring=16):
+    """reth_buffer.start_per (__init__.py:30-49)."""
+    from .sampler import PERSampler
+    samplers = [{"sampler_cls": PERSampler, "num_procs": num_sampler_procs, "sample_start": sample_start,
+                 "kwargs": {"alpha": alpha, "beta": beta}}]
+    return start_server(capacity, batch_size, host, port, samplers, cache_policy, device, max_ring)
+
+
+_META_CACHE = {}
+
+
+def get_meta(meta_addr, timeout_ms=30000):
+    """utils/__init__.py:50-59 (REQ to the meta endpoint, cached per address)."""
+    if meta_addr in _META_CACHE:
+        return _META_CACHE[meta_addr]
+    import zmq
+    ctx = zmq.Context.instance()
+    sock = ctx.socket(zmq.REQ)
+    sock.setsockopt(zmq.LINGER, 0)
+    sock.setsockopt(zmq.IMMEDIATE, 1)
+    sock.connect(meta_addr)
+    sock.send(b"")
+    if not sock.poll(timeout_ms):
+        sock.close(0)
+        raise ConnectionError(f"no replay server answers at {meta_addr!r}")
+    res = sock.recv_json()
+    sock.close(0)
+    _META_CACHE[meta_addr] = res
+    return res
+
+
+class Client:
+    """client/client.py:8-39 against a server in another process.  wire="columns" (default) sends
+    the columns as they are; wire="rows" sends exactly what the reference's Client sends."""
+
+    def __init__(self, meta_addr, wire="columns"):
+        import zmq
+        self.ctx = zmq.Context.instance()
+        self.meta = get_meta(meta_addr)
+        self.wire = wire
+        self.append_sock = self.ctx.socket(zmq.PUSH)
+        self.append_sock.set_hwm(ZMQ_DEFAULT_HWM)
+        self.append_sock.connect(self.meta["append_addr"])
+        self.update_sock = self.ctx.socket(zmq.PUSH)
+        self.update_sock.set_hwm(ZMQ_DEFAULT_HWM)
+        self.update_sock.connect(self.meta["update_addr"])
+
+    def append(self, data, weights, compress=False):
+        assert isinstance(data, (list, tuple))                # client.py:22
+        for col in data:
+            assert isinstance(col, np.ndarray)                # :24
+            assert len(col) == len(weights)                   # :25
+        weights = np.asarray(weights)
+        if self.wire == "rows":
+            msg = pack.encode_append_rows(data, weights, compress=compress)
+        else:
+            msg = pack.encode_append_columns(data, weights)
+        self.append_sock.send(msg, copy=False)
+
+    def update_priorities(self, indices, weights, step=True):
+        assert len(indices) == len(weights)                   # :38
+        self.update_sock.send(pack.encode([np.asarray(indices), np.asarray(weights), step]), copy=False)
+
+    def close(self):
+        self.append_sock.close(0)
+        self.update_sock.close(0)
+
+
+class _RemoteLoader:
+    """Loader-side connection: one REQ socket; a request for the next group releases the previous one
+    (the borrow rule of client/torch_cuda_loader.py:152-163, at group granularity)."""
+
+    def __init__(self, meta_addr, topic="default", prefetch=1, ahead=0, map_ring=True, timeout_s=120.0):
+        import zmq
+        from . import _cabi
+        self.meta = get_meta(meta_addr)
+        assert topic in self.meta["sampler_info"]
+        self._zmq = zmq
+        self.sock = zmq.Context.instance().socket(zmq.REQ)
+        self.sock.setsockopt(zmq.LINGER, 0)
+        self.sock.connect(self.meta["loader_addr"])
+        self.timeout_ms = int(timeout_s * 1000)
+        self._view = None
+        self._lib = _cabi.lib()
+        self._open = False
+        self._map_ring = map_ring
+        self.prefetch, self.ahead = int(prefetch), int(ahead)
+        self.group = int(prefetch)
+        self.batch_size = self.meta["batch_size"]
+        self.device = self.meta["device"]
+        self.struct = None
+        self._queue = []
+
+    def _ensure_open(self):
+        """The row struct is only known after the first append (torch_cuda_loader.py:106-112 discovers
+        it from the first row), so the ring is opened at the first sample(), not in the constructor."""
+        if self._open:
+            return
+        from . import _cabi
+        head, blobs = self._call({"op": "open", "prefetch": self.prefetch, "ahead": self.ahead})
+        self._open = True
+        self.struct = [(np.dtype(dt), tuple(sh)) for dt, sh in head["struct"]]
+        self.group = head["group"]
+        if self._map_ring:
+            ex = _cabi.IpcExport.from_buffer_copy(blobs[0])
+            v = C.c_void_p()
+            rc = self._lib.reth_ipc_open(C.byref(ex), C.byref(v))
+            if rc != 0:
+                _cabi.check(None, rc)
+            self._view = v
+            self._ncols = ex.n_columns
+
+    def _call(self, obj):
+        self.sock.send(json.dumps(obj).encode())
+        if not self.sock.poll(self.timeout_ms):
+            raise TimeoutError("the replay server did not answer (no batch available: fewer than sample_start "
+                               "transitions were appended?)")
+        parts = self.sock.recv_multipart()
+        head = json.loads(parts[0])
+        if not head.get("ok"):
+            raise RuntimeError(f"replay server: {head.get('error')}")
+        return head, parts[1:]
+
+    def _next(self):
+        """-> (batch slot, indices int64[B], weights float64[B]) of the next pre-sampled batch."""
+        if not self._queue:
+            self._ensure_open()
+            head, blobs = self._call({"op": "next"})
+            G, B = head["n"], self.batch_size
+            idx = np.frombuffer(blobs[0], np.int64).reshape(G, B)
+            w = np.frombuffer(blobs[1], np.float64).reshape(G, B)
+            first = head["first_slot"]
+            self._queue = [(first + k, idx[k].copy(), w[k].copy()) for k in range(G - 1, -1, -1)]
+        return self._queue.pop()
+
+    def slot_pointers(self, slot):
+        cols = (C.c_void_p * max(1, self._ncols))()
+        ip, wp = C.c_void_p(), C.c_void_p()
+        rc = self._lib.reth_ipc_slot_ptrs(self._view, int(slot), cols, C.byref(ip), C.byref(wp))
+        assert rc == 0
+        return [cols[c] for c in range(self._ncols)], ip.value, wp.value
+
+    def drain(self):
+        """Block until the server has executed everything it has received so far; -> {"cnt": ...}."""
+        return self._call({"op": "drain"})[0]
+
+    def close(self):
+        if self._open:
+            self._open = False
+            try:
+                self._call({"op": "close"})
+            except Exception:
+                pass
+        if self._view is not None:
+            self._lib.reth_ipc_close(self._view)
+            self._view = None
+        self.sock.close(0)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __iter__(self):
+        return self
+
+    def __next__(self):
+        return self.sample()
+
+
+class NumpyLoader(_RemoteLoader):
+    """client/numpy_loader.py:8-56 against a server in another process: fresh host arrays."""
+
+    def __init__(self, meta_addr, topic="default", prefetch=1, ahead=0):
+        super().__init__(meta_addr, topic, prefetch, ahead, map_ring=False)
+
+    def sample(self):
+        slot, idx, w = self._next()
+        _, blobs = self._call({"op": "rows", "slot": slot})
+        B = self.batch_size
+        data = [np.frombuffer(b, dt).reshape((B,) + sh).copy() for b, (dt, sh) in zip(blobs, self.struct)]
+        return data, idx, w
+
+    def get_indices(self):
+        _, idx, w = self._next()
+        return idx, w
+
+
+class TorchCudaLoader(_RemoteLoader):
+    """client/torch_cuda_loader.py:69-163 against a server in another process on the same GPU:
+    the batch ring is mapped through CUDA IPC, data/weights are zero-copy CUDA tensors lent until
+    the group is released, indices come back on the host."""
+
+    def __init__(self, meta_addr, topic="default", buffer_size=8, num_procs=6, prefetch=None, ahead=None):
+        buffer_size = max(1, int(buffer_size))
+        if prefetch is None:
+            prefetch = max(1, buffer_size // 2)
+        if ahead is None:
+            ahead = max(0, buffer_size // int(prefetch) - 1)
+        super().__init__(meta_addr, topic, prefetch, ahead, map_ring=True)
+        self.buffer_size = buffer_size
+        self.num_procs = num_procs
+        self._views = {}
+
+    def sample(self):
+        import torch
+        from .shard import _DevArray
+        slot, idx, _ = self._next()
+        v = self._views.get(slot)
+        if v is None:
+            cols, _, wp = self.slot_pointers(slot)
+            B = self.batch_size
+            dev = torch.device("cuda", self.device)
+            data = [torch.as_tensor(_DevArray(p, (B,) + sh, dt, self), device=dev)
+                    for p, (dt, sh) in zip(cols, self.struct)]
+            weights = torch.as_tensor(_DevArray(wp, (B,), np.float64, self), device=dev)
+            v = self._views[slot] = (data, weights)
+        return v[0], idx, v[1]

@@ -13,12 +13,20 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 @pytest.fixture(scope="module")
 def reth_buffer():
+    """The shim with the engine in this process (RETH_B200_SERVER=inproc); the server-process
+    layout is covered by tests/test_service_mp_gpu.py."""
     import __graft_entry__ as entry
     entry.build()
     sys.path.insert(0, os.path.join(ROOT, "reth_b200", "compat"))
+    old = os.environ.get("RETH_B200_SERVER")
+    os.environ["RETH_B200_SERVER"] = "inproc"
     import reth_buffer
     yield reth_buffer
     sys.path.remove(os.path.join(ROOT, "reth_b200", "compat"))
+    if old is None:
+        os.environ.pop("RETH_B200_SERVER", None)
+    else:
+        os.environ["RETH_B200_SERVER"] = old
 
 
 def test_rb_basic(reth_buffer):

@@ -1,0 +1,125 @@
+"""The drop-in layout of the reference on the GPU: server in its own process, clients and
+loaders built from the address string in other processes (test/apex-dqn/trainer.py:49-66,
+reth_buffer/test/test_rb.py:12-35,63-85), ZeroMQ + the reference wire format for append/update,
+CUDA IPC for the batch ring."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def reth_buffer():
+    import __graft_entry__ as entry
+    entry.build()
+    sys.path.insert(0, os.path.join(ROOT, "reth_b200", "compat"))
+    os.environ.pop("RETH_B200_SERVER", None)
+    import reth_buffer
+    yield reth_buffer
+    sys.path.remove(os.path.join(ROOT, "reth_b200", "compat"))
+
+
+def test_rb_basic_server_process(reth_buffer):
+    """test_rb.py:12-35 against a spawned server; append in the reference's ROW wire format."""
+    from reth_b200 import service_mp
+    CAPACITY, BATCH_SIZE = 100000, 32
+    rb_proc, addr = reth_buffer.start_server(CAPACITY, BATCH_SIZE)
+    try:
+        assert addr.startswith("tcp://") and rb_proc.is_alive()
+        client = service_mp.Client(addr, wire="rows")
+        loader = reth_buffer.NumpyLoader(addr)
+        data = [np.random.rand(1000, 4, 84), np.random.rand(1000), np.arange(1000)]
+        buf_weights = np.random.rand(1000) + 1
+        for start in range(0, 1000, 100):
+            batch = [x[start:start + 100] for x in data]
+            client.append(batch, buf_weights[start:start + 100])
+        for _ in range(10):
+            batch, indices, weights = loader.sample()
+            assert indices.dtype == np.int64 and weights.dtype == np.float64
+            for i, idx in enumerate(indices):
+                assert batch[2][i] == idx
+                assert batch[1][i] == data[1][idx]
+                assert np.array_equal(batch[0][i], data[0][idx])
+        buf_weights = np.random.rand(1000) + 10
+        client.update_priorities(np.arange(1000), buf_weights)
+        assert loader.drain()["cnt"] == 2000                  # sampler_loop.py:36: appended + updated indices
+        loader.close()
+    finally:
+        rb_proc.terminate()
+        rb_proc.join()
+    assert not rb_proc.is_alive()
+
+
+def test_torch_cuda_loader_ipc(reth_buffer):
+    """trainer.py:19-36 shape: TorchCudaLoader in a process other than the server's; the lent CUDA
+    tensors are views of the server's batch ring (CUDA IPC) and hold the rows of `indices`."""
+    import torch
+    B = 64
+    proc, addr = reth_buffer.start_per(5000, B, alpha=0.5, beta="0.4,1,2000", sample_start=200)
+    try:
+        client = reth_buffer.Client(addr)                     # columnar wire format
+        rng = np.random.default_rng(0)
+        s0 = rng.integers(0, 256, (600, 4, 84, 84), dtype=np.uint8)
+        cols = [s0, rng.integers(0, 18, 600), rng.standard_normal(600).astype(np.float32), s0[::-1].copy(),
+                np.zeros(600, np.float32)]
+        for st in range(0, 600, 64):
+            client.append([c[st:st + 64] for c in cols], np.ones(len(cols[0][st:st + 64]), np.float32))
+        loader = reth_buffer.TorchCudaLoader(addr, buffer_size=4, num_procs=2)     # trainer.py:23
+        for it in range(12):
+            data, indices, weights = loader.sample()
+            assert isinstance(indices, np.ndarray) and indices.dtype == np.int64 and indices.shape == (B,)
+            assert weights.is_cuda and weights.dtype == torch.float64 and tuple(weights.shape) == (B,)
+            assert data[0].is_cuda and data[0].dtype == torch.uint8 and tuple(data[0].shape) == (B, 4, 84, 84)
+            assert np.array_equal(data[0].cpu().numpy(), s0[indices])
+            assert np.array_equal(data[1].cpu().numpy(), cols[1][indices])
+            assert np.array_equal(data[3].cpu().numpy(), cols[3][indices])
+            assert float(weights.max()) <= 1.0 + 1e-12
+            loss = np.abs(rng.standard_normal(B)).astype(np.float32)
+            client.update_priorities(np.asarray(indices), np.asarray(loss))         # trainer.py:36
+        assert loader.group == 2
+        st = loader.drain()
+        assert st["cnt"] == 600 + 12 * B
+        with pytest.raises(AssertionError):
+            client.append([c[:10] for c in cols], np.ones(9))
+        loader.close()
+    finally:
+        proc.terminate()
+        proc.join()
+
+
+def _producer(addr, n_batches, seed):
+    sys.path.insert(0, ROOT)
+    from reth_b200 import service
+    client = service.Client(addr)
+    rng = np.random.default_rng(seed)
+    for _ in range(n_batches):
+        ids = rng.integers(0, 1 << 30, 32)
+        client.append([ids, np.repeat(ids[:, None], 16, 1).astype(np.float32)], np.ones(32))
+    client.close()
+
+
+def test_mp_producers(reth_buffer):
+    """test_rb.py:63-85: several producer processes feed one server; rows stay self-consistent."""
+    import multiprocessing as mp
+    B = 32
+    proc, addr = reth_buffer.start_per(20000, B, sample_start=B)
+    try:
+        ctx = mp.get_context("spawn")
+        ps = [ctx.Process(target=_producer, args=(addr, 20, k)) for k in range(3)]
+        [p.start() for p in ps]
+        loader = reth_buffer.NumpyLoader(addr)
+        for _ in range(20):
+            data, indices, weights = loader.sample()
+            assert len(data) == 2
+            assert np.array_equal(data[1], np.repeat(data[0][:, None], 16, 1).astype(np.float32))
+        [p.join(60) for p in ps]
+        assert all(p.exitcode == 0 for p in ps)
+        assert loader.drain()["cnt"] == 3 * 20 * 32
+        loader.close()
+    finally:
+        proc.terminate()
+        proc.join()
