@@ -331,3 +331,77 @@ def test_global_mode_vs_oracle(Shard, n_shards):
     assert covered == B
     for sh in shards:
         sh.close()
+
+
+def test_config4_learner_loop_with_actor_streams(Shard):
+    """BASELINE config 4 shape (scaled): per learner step 256 actor messages of 64 rows are appended
+    (the ring wraps every 4 steps), then one batch of 512 is drawn and written back; alpha 0.5,
+    beta "0.4,1,2000000" (test/apex-dqn/config.yaml:26-27).  Leaves are copied from the engine into
+    the oracle after each write (CUDA pow vs libm pow differ in the last ulp) and
+    checked to 1e-5; everything downstream -- indices, sums, mins, gathered rows -- is exact."""
+    from reth_b200.sampler import Schedule
+    cap, B, streams, rows = 1 << 16, 512, 256, 64
+    struct = [(np.float32, (4,)), (np.int64, ()), (np.float32, ()), (np.float32, (4,)), (np.float32, ())]
+    rng = np.random.default_rng(44)
+    sh = Shard(cap, struct, max_batch=B, ring_depth=2)
+    ring = po.OracleRing(cap, struct)
+    ref = po.OracleSumTree(cap)
+    beta = Schedule.from_str("0.4,1,2000000")
+    alpha = 0.5
+    for step in range(10):
+        n = streams * rows
+        cols = [rng.standard_normal((n, 4)).astype(np.float32), rng.integers(0, 2, n),
+                rng.standard_normal(n).astype(np.float32), rng.standard_normal((n, 4)).astype(np.float32),
+                (rng.random(n) < 0.01).astype(np.float32)]
+        w = np.abs(rng.standard_normal(n)).astype(np.float32)
+        for m in range(0, n, 4096):                           # several actor messages per call
+            first = sh.append([c[m:m + 4096] for c in cols], w[m:m + 4096], alpha=alpha)
+            slots = ring.append_batch([c[m:m + 4096] for c in cols])
+            assert first == slots[0]
+        _, _, v = sh.tree_arrays()
+        slots = (ring.tail - n + np.arange(n)) % cap
+        assert np.allclose(v[slots], po.normalize_weights(w, alpha), rtol=RTOL, atol=0)
+        ref.update(slots, v[slots])
+        u = rng.random(B)
+        sh.sample(B, beta=beta.value(), uniforms=u, slot=step % 2)
+        sh.gather(step % 2)
+        data, gi, gw = sh.slot_read(step % 2, with_rows=True)
+        ri, rv = ref.sample(B, u)
+        assert np.array_equal(gi, ri), step
+        assert np.allclose(gw, po.is_weights(rv, ref.min(0), beta.value()), rtol=RTOL, atol=0)
+        for got, want in zip(data, ring.select(ri)):
+            assert np.array_equal(got, want)
+        td = np.abs(rng.standard_normal(B)).astype(np.float32)
+        sh.update(gi, td, alpha=alpha)
+        beta.step()
+        _, _, v = sh.tree_arrays()
+        ref.update(ri, v[ri])
+        assert sh.root() == (ref.sum(), ref.min(0))
+    s, m, v = sh.tree_arrays()
+    assert np.array_equal(s, ref._sum) and np.array_equal(m, ref._min)
+    sh.close()
+
+
+def test_capacity_2p24_tree_only(Shard):
+    """BASELINE config 5 upper end: capacity 2^24 (five tile levels, three sparse ones), batch 8192."""
+    cap, B = 1 << 24, 8192
+    rng = np.random.default_rng(24)
+    sh = Shard(cap, [], max_batch=B, store_rows=False)
+    ref = po.OracleSumTree(cap)
+    for st in range(0, cap, 1 << 20):
+        pw = np.abs(rng.standard_normal(1 << 20)) + 1e-3
+        sh.append([], pw, transform=False)
+        ref.update(np.arange(st, st + (1 << 20)), pw)
+    for t in range(4):
+        u = rng.random(B)
+        sh.sample(B, beta=0.4, uniforms=u, slot=t % 2)
+        _, gi, gw = sh.slot_read(t % 2)
+        ri, rv = ref.sample(B, u)
+        assert np.array_equal(gi, ri)
+        newp = np.abs(rng.standard_normal(B)) + 1e-3
+        sh.update_slot(t % 2, newp, transform=False)
+        ref.update(ri, newp)
+        assert sh.root() == (ref.sum(), ref.min(0))
+    s, m, v = sh.tree_arrays()
+    assert np.array_equal(s, ref._sum) and np.array_equal(m, ref._min)
+    sh.close()
