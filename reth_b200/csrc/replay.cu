@@ -62,6 +62,9 @@ struct reth_replay {
     int two_gather_streams = 1;
     std::vector<cudaEvent_t> ev_sampled, ev_gathered;
     cudaEvent_t ev_fork = nullptr, ev_join_t = nullptr, ev_join_g = nullptr;
+    cudaStream_t s_append = nullptr;          // large device-source appends: the row copy runs beside the tree update
+    cudaEvent_t ev_app_fork = nullptr, ev_app_done = nullptr;
+    cudaEvent_t last_gather_ev = nullptr;     // newest gather of the internal streams (appends wait for it: rows stay atomic)
     int update_cluster = 8;
     int max_dyn_smem = 0;               // opt-in shared memory per block
     bool gather_bulk = false;           // gather through row_gather_bulk_kernel (TMA bulk copies)
@@ -142,6 +145,9 @@ void free_all(reth_replay *h)
     for (auto e : h->ev_gathered) cudaEventDestroy(e);
     for (auto e : h->ev_time) cudaEventDestroy(e);
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+    if (h->ev_app_fork) cudaEventDestroy(h->ev_app_fork);
+    if (h->ev_app_done) cudaEventDestroy(h->ev_app_done);
+    if (h->s_append) cudaStreamDestroy(h->s_append);
     if (h->ev_join_t) cudaEventDestroy(h->ev_join_t);
     if (h->ev_join_g) cudaEventDestroy(h->ev_join_g);
     if (h->s_tree) cudaStreamDestroy(h->s_tree);
@@ -262,6 +268,9 @@ RETH_EXPORT int reth_replay_create(const reth_replay_config *cfg, reth_replay_t 
         CKC(cudaEventCreateWithFlags(&h->ev_gathered[i], cudaEventDisableTiming));
     }
     CKC(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
+    CKC(cudaEventCreateWithFlags(&h->ev_app_fork, cudaEventDisableTiming));
+    CKC(cudaEventCreateWithFlags(&h->ev_app_done, cudaEventDisableTiming));
+    CKC(cudaStreamCreateWithFlags(&h->s_append, cudaStreamNonBlocking));
     CKC(cudaEventCreateWithFlags(&h->ev_join_t, cudaEventDisableTiming));
     CKC(cudaEventCreateWithFlags(&h->ev_join_g, cudaEventDisableTiming));
     if (h->update_cluster > 16) h->update_cluster = 16;
@@ -418,6 +427,10 @@ RETH_EXPORT int reth_replay_append(reth_replay_t *h, const void *const *cols, in
     cudaStream_t s = S(stream);
     const int64_t cap = h->cfg.capacity;
     if (first_slot_out) *first_slot_out = h->tail;
+    // a gather still running on the internal streams must not see half-written rows (the reference's
+    // LMDB rows are replaced atomically, main_loop.py:55-57)
+    if (h->last_gather_ev && h->cfg.store_rows && n > 0) CK(h, cudaStreamWaitEvent(s, h->last_gather_ev, 0));
+    bool forked = false;
     for (int64_t off = 0; off < n; off += h->max_n) {
         const int64_t m = (n - off < h->max_n) ? n - off : h->max_n;
         const int64_t start = h->tail;
@@ -437,7 +450,16 @@ RETH_EXPORT int reth_replay_append(reth_replay_t *h, const void *const *cols, in
                 const int64_t cap_blocks = (int64_t)h->n_sms * 8;
                 if (blocks > cap_blocks) blocks = cap_blocks;
                 if (blocks < 1) blocks = 1;
-                ring_append_kernel<<<(unsigned)blocks, kCopyThreads, 0, s>>>(a);
+                cudaStream_t sc = s;
+                if (bytes >= (32ll << 20)) {           // big copy: run it beside the tree update of the same rows
+                    if (!forked) {
+                        CK(h, cudaEventRecord(h->ev_app_fork, s));
+                        CK(h, cudaStreamWaitEvent(h->s_append, h->ev_app_fork, 0));
+                        forked = true;
+                    }
+                    sc = h->s_append;
+                }
+                ring_append_kernel<<<(unsigned)blocks, kCopyThreads, 0, sc>>>(a);
                 CK(h, cudaGetLastError());
                 h->st.kernel_launches++;
             } else {
@@ -460,6 +482,10 @@ RETH_EXPORT int reth_replay_append(reth_replay_t *h, const void *const *cols, in
         h->tail = (start + m) % cap;
         h->size = (h->size + m < cap) ? h->size + m : cap;
         h->st.appended_rows += m;
+    }
+    if (forked) {
+        CK(h, cudaEventRecord(h->ev_app_done, h->s_append));
+        CK(h, cudaStreamWaitEvent(s, h->ev_app_done, 0));
     }
     h->st.tail = h->tail; h->st.size = h->size;
     return RETH_OK;
@@ -935,6 +961,7 @@ void pipe_free(reth_replay *h)
         v->clear();
     }
     if (p.s_copy) cudaStreamDestroy(p.s_copy);
+    h->last_gather_ev = nullptr;
     p = reth_replay::Pipe();
 }
 
@@ -958,6 +985,7 @@ int pipe_issue(reth_replay *h, double beta)
     rc = do_gather(h, slot, false, sg, p.G);
     if (rc) return rc;
     CK(h, cudaEventRecord(p.ev_gat[g], sg));
+    h->last_gather_ev = p.ev_gat[g];
     CK(h, cudaStreamWaitEvent(p.s_copy, p.ev_gat[g], 0));
     CK(h, cudaEventRecord(p.ev_done[g], p.s_copy));
     p.issued++;
@@ -1287,7 +1315,7 @@ RETH_EXPORT int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, co
                 CK(h, cudaEventRecord(h->ev_time[h->ev_time_used + 1], sg));
                 h->ev_time_used += 2;
             }
-            if (!serial) CK(h, cudaEventRecord(h->ev_gathered[slot], sg));
+            if (!serial) { CK(h, cudaEventRecord(h->ev_gathered[slot], sg)); h->last_gather_ev = h->ev_gathered[slot]; }
         }
         if (no_update) continue;
         UpdateArgs a = {};
