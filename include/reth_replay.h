@@ -239,7 +239,8 @@ int reth_replay_pipe_drain(reth_replay_t *h);
  *      another process through CUDA IPC (client/torch_cuda_loader.py:58,63,114-135,157-160:
  *      shared CUDA tensors + interprocess events).  ipc_export() fills a plain-bytes descriptor of
  *      this shard's batch ring (one cudaIpcMemHandle per column array + indices + weights); a
- *      consumer process on the same GPU maps it with reth_ipc_open() and reads slot pointers.
+ *      consumer process maps it with reth_ipc_open() FOR ITS CURRENT DEVICE (the same GPU, or a peer
+ *      GPU reached over NVLink) and reads slot pointers.
  *      Completion is signalled by the owner process (it replies after pipe_wait()), so no
  *      interprocess event is needed. */
 typedef struct reth_ipc_export {
@@ -254,6 +255,14 @@ int reth_ipc_open(const reth_ipc_export *in, reth_ipc_view_t **out);
 int reth_ipc_slot_ptrs(reth_ipc_view_t *v, int slot, void **cols_out /*[n_columns]*/, int64_t **indices_out,
                        double **weights_out);
 int reth_ipc_close(reth_ipc_view_t *v);
+/* Cross-shard batch assembly over NVLink (north_star "only when the learner is not
+ * co-located"): after reth_replay_sample_global() into `slot`, gather this shard's rows STRAIGHT
+ * into batch slot `dst_slot` of a peer's ring (`dst`, opened with reth_ipc_open; may live on
+ * another GPU: the stores cross NVLink from inside the gather kernel), at the global batch rows
+ * [first, first+count) the shard serves; its indices and weights go to the same rows.  dst == NULL
+ * names this shard's own ring (the learner rank's own slice; dst_slot != slot).  The
+ * reference has no counterpart (its learner polls whole batches shard by shard, trainer.py:33-36). */
+int reth_replay_gather_to(reth_replay_t *h, int slot, reth_ipc_view_t *dst, int dst_slot, void *stream);
 
 /* ---- measured loop (bench / learner-less soak): `steps` iterations of
  *      sample(batch) -> gather || update_slot(new priorities), the tree chain and the

@@ -113,6 +113,7 @@ SIGNATURES = {
     "reth_ipc_open": [C.POINTER(IpcExport), C.POINTER(_vp)],
     "reth_ipc_slot_ptrs": [_vp, _i32, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp)],
     "reth_ipc_close": [_vp],
+    "reth_replay_gather_to": [_vp, _i32, _vp, _i32, _vp],
     "reth_replay_step_loop": [_vp, _i32, _i32, _vp, _vp, _u64, _f64, _f64, _i32, _vp],
     "reth_replay_gather_time": [_vp, C.POINTER(_f64), C.POINTER(_i64)],
     "reth_replay_debug_stamps": [_vp, C.POINTER(_i64)],

@@ -95,6 +95,7 @@ struct RowArgs {
     const int64_t *idx;        // slot per batch row
     int32_t batch;
     const int64_t *meta;       // optional {first,count}: rows = meta[1]
+    int32_t dst_row_from_meta; // batch row of local row i is meta[0] + i (cross-shard assembly into a peer's batch)
     int64_t wide_items;        // items over all wide columns (batch-relative layout)
     int32_t narrow_groups;     // ceil(batch / kCopyThreads) when narrow columns exist
     // scatter only: last-writer-wins arbitration (same stamps as the tree update)
@@ -109,6 +110,7 @@ template <bool kScatter>
 __global__ void __launch_bounds__(kCopyThreads, 6) row_move_kernel(const RowArgs a)
 {
     const int rows = a.meta ? (int)a.meta[1] : a.batch;
+    const int64_t row0 = (a.meta && a.dst_row_from_meta) ? a.meta[0] : 0;
     const int64_t total = a.wide_items + a.narrow_groups;
     for (int64_t item = blockIdx.x; item < total; item += gridDim.x) {
         if (item < a.wide_items) {
@@ -127,7 +129,7 @@ __global__ void __launch_bounds__(kCopyThreads, 6) row_move_kernel(const RowArgs
             const int64_t u0 = (int64_t)chunk * col.units;
             const int64_t n = min((int64_t)col.units, upr - u0);
             const uint4 *rp = (const uint4 *)(col.ring + slot * col.rb) + u0;
-            const uint4 *bp = (const uint4 *)(col.batch + (int64_t)row * col.rb) + u0;
+            const uint4 *bp = (const uint4 *)(col.batch + ((int64_t)row + row0) * col.rb) + u0;
             const uint4 *s = kScatter ? bp : rp;
             uint4 *d = (uint4 *)(kScatter ? rp : bp);
             int64_t j = threadIdx.x;
@@ -158,10 +160,21 @@ __global__ void __launch_bounds__(kCopyThreads, 6) row_move_kernel(const RowArgs
                 const RowCol &col = a.col[c];
                 if (col.chunks != 0) continue;
                 uint8_t *rp = col.ring + slot * col.rb;
-                uint8_t *bp = col.batch + (int64_t)row * col.rb;
+                uint8_t *bp = col.batch + ((int64_t)row + row0) * col.rb;
                 span_copy(kScatter ? rp : bp, kScatter ? bp : rp, col.rb, 0, 1);
             }
         }
+    }
+}
+
+// indices / weights of a shard's slice of a global batch -> the same rows of a peer's batch slot
+__global__ void slice_copy_kernel(const int64_t *idx, const double *w, const int64_t *meta,
+                                  int64_t *dst_idx, double *dst_w)
+{
+    const int64_t first = meta[0], count = meta[1];
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (int64_t)gridDim.x * blockDim.x) {
+        dst_idx[first + i] = idx[i];
+        dst_w[first + i] = w[i];
     }
 }
 

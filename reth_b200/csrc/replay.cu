@@ -1182,6 +1182,7 @@ RETH_EXPORT int reth_replay_pipe_drain(reth_replay_t *h)
 // ------------------------------------------------------------ cross-process ring --
 struct reth_ipc_view {
     reth_ipc_export ex{};
+    int open_device = 0;          // device that was current when the ring was mapped
     uint8_t *cols[kMaxCols] = {};
     int64_t *idx = nullptr;
     double *w = nullptr;
@@ -1214,7 +1215,9 @@ RETH_EXPORT int reth_ipc_open(const reth_ipc_export *in, reth_ipc_view_t **out)
     reth_ipc_view *v = new (std::nothrow) reth_ipc_view();
     if (!v) return fail(nullptr, RETH_ERR_OOM, "host allocation failed");
     v->ex = *in;
-    DeviceGuard guard(in->device);
+    // the ring is mapped for the CALLER's current device: when that is not the exporting GPU,
+    // cudaIpcMemLazyEnablePeerAccess sets up the peer (NVLink) mapping
+    if (cudaGetDevice(&v->open_device) != cudaSuccess) v->open_device = in->device;
     auto open1 = [&](const unsigned char *hb, void **p) {
         cudaIpcMemHandle_t mh;
         memcpy(&mh, hb, sizeof mh);
@@ -1246,11 +1249,54 @@ RETH_EXPORT int reth_ipc_slot_ptrs(reth_ipc_view_t *v, int slot, void **cols_out
     return RETH_OK;
 }
 
+RETH_EXPORT int reth_replay_gather_to(reth_replay_t *h, int slot, reth_ipc_view_t *dst, int dst_slot, void *stream)
+{
+    if (!h) return RETH_ERR_INVALID;
+    if (slot_ok(h, slot)) return RETH_ERR_INVALID;
+    BatchSlot &b = h->slots[slot];
+    if (b.batch <= 0) return fail(h, RETH_ERR_STATE, "slot %d holds no sampled batch", slot);
+    const int ncols = h->cfg.store_rows ? h->cfg.n_columns : 0;
+    // dst == NULL: this shard's own ring (the learner rank's own slice of the global batch)
+    const int d_depth = dst ? dst->ex.ring_depth : (int)h->slots.size();
+    const int d_mb = dst ? dst->ex.max_batch : h->cfg.max_batch;
+    if (dst_slot < 0 || dst_slot >= d_depth || d_mb < b.batch)
+        return fail(h, RETH_ERR_INVALID, "destination slot %d does not hold a batch of %d", dst_slot, b.batch);
+    if (!dst && dst_slot == slot) return fail(h, RETH_ERR_INVALID, "assembling into the slot being read");
+    if (dst) {
+        if (dst->ex.n_columns != ncols) return fail(h, RETH_ERR_INVALID, "destination ring has another row struct");
+        for (int c = 0; c < ncols; ++c)
+            if (dst->ex.row_bytes[c] != h->cfg.row_bytes[c])
+                return fail(h, RETH_ERR_INVALID, "destination ring has another row struct");
+    }
+    DeviceGuard guard(h->cfg.device);
+    cudaStream_t s = S(stream);
+    const size_t mb = (size_t)d_mb;
+    if (ncols > 0) {
+        uint8_t *cols[kMaxCols] = {};
+        for (int c = 0; c < ncols; ++c)
+            cols[c] = (dst ? dst->cols[c] : h->slot_cols[c]) + (size_t)dst_slot * mb * h->cfg.row_bytes[c];
+        RowArgs a;
+        build_row_args(h, a, cols, b.idx, b.batch);
+        a.meta = b.meta;
+        a.dst_row_from_meta = 1;
+        int rc = launch_row_move<false>(h, a, s);
+        if (rc) return rc;
+        h->st.gathered_rows += b.batch;
+    }
+    slice_copy_kernel<<<(b.batch + 255) / 256, 256, 0, s>>>(b.idx, b.w, b.meta,
+                                                          (dst ? dst->idx : h->slot_idx) + (size_t)dst_slot * mb,
+                                                          (dst ? dst->w : h->slot_w) + (size_t)dst_slot * mb);
+    CK(h, cudaGetLastError());
+    h->st.kernel_launches++;
+    if (!dst) h->slots[dst_slot].batch = b.batch;
+    return RETH_OK;
+}
+
 RETH_EXPORT int reth_ipc_close(reth_ipc_view_t *v)
 {
     if (!v) return RETH_OK;
     {
-        DeviceGuard guard(v->ex.device);
+        DeviceGuard guard(v->open_device);
         for (int c = 0; c < kMaxCols; ++c)
             if (v->cols[c]) cudaIpcCloseMemHandle(v->cols[c]);
         if (v->idx) cudaIpcCloseMemHandle(v->idx);

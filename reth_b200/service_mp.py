@@ -284,6 +284,8 @@ class _RemoteLoader:
         self.struct = [(np.dtype(dt), tuple(sh)) for dt, sh in head["struct"]]
         self.group = head["group"]
         if self._map_ring:
+            import torch
+            torch.cuda.set_device(self.device)         # the ring is mapped for the current device
             ex = _cabi.IpcExport.from_buffer_copy(blobs[0])
             v = C.c_void_p()
             rc = self._lib.reth_ipc_open(C.byref(ex), C.byref(v))

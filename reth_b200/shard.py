@@ -144,6 +144,31 @@ class ShardPipe:
         self._h = None
 
 
+class IpcRing:
+    """A peer's batch ring mapped into this process (reth_ipc_open): same GPU in another process
+    (loader hand-off) or another GPU (cross-shard batch assembly over NVLink)."""
+
+    def __init__(self, blob):
+        self._lib = _cabi.lib()
+        self.ex = _cabi.IpcExport.from_buffer_copy(blob)
+        self._v = C.c_void_p()
+        rc = self._lib.reth_ipc_open(C.byref(self.ex), C.byref(self._v))
+        if rc != 0:
+            self._v = None
+            _cabi.check(None, rc)
+
+    def close(self):
+        if self._v is not None:
+            self._lib.reth_ipc_close(self._v)
+            self._v = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 class ReplayShard:
     """One replay shard on one GPU.
 
@@ -387,6 +412,19 @@ class ReplayShard:
         fc = (C.c_int64 * 2)()
         self._ck(self._lib.reth_replay_slot_meta(self._h, slot, fc, self._s(stream)))
         return fc[0], fc[1]
+
+    def ipc_export(self):
+        """bytes descriptor of the batch ring (CUDA IPC handles) for IpcRing in another process."""
+        ex = _cabi.IpcExport()
+        self._ck(self._lib.reth_replay_ipc_export(self._h, C.byref(ex)))
+        return bytes(ex)
+
+    def gather_to(self, slot, ring, dst_slot, stream=None):
+        """After sample_global(slot): gather this shard's rows, indices and weights straight into rows
+        [first, first+count) of batch slot `dst_slot` of a peer's ring (NVLink stores from the kernel);
+        ring=None: this shard's own ring."""
+        self._ck(self._lib.reth_replay_gather_to(self._h, int(slot), ring._v if ring is not None else None,
+                                                 int(dst_slot), self._s(stream)))
 
     def open_pipe(self, batch, group, seed=0):
         return ShardPipe(self, batch, group, seed)

@@ -82,6 +82,23 @@ class ShardGroup:
         """all-gather of the 16-byte shard roots (NCCL over NVLink); -> device float64[2*world]."""
         return self.dist.all_gather_into_tensor(self.all_roots, self._mine, group=self.group, async_op=async_op)
 
+    def connect_learner(self, learner_rank):
+        """Map the learner rank's batch ring into this process (CUDA IPC; a ring on another GPU is
+        reached over NVLink).  Collective: every rank of the group must call it."""
+        from .shard import IpcRing
+        blobs = [None] * self.world
+        self.dist.all_gather_object(blobs, self.shard.ipc_export(), group=self.group)
+        self.learner_rank = int(learner_rank)
+        self.learner_ring = None if self.rank == learner_rank else IpcRing(blobs[learner_rank])
+        return self.learner_ring
+
+    def assemble(self, slot, dst_slot, stream=None):
+        """Cross-shard batch assembly: after sample_global(slot) on every rank, each rank writes its
+        slice of the global batch into the learner rank's batch slot `dst_slot` (!= slot on the learner
+        rank) -- the learner's own slice by a local gather, the others by peer stores from the kernel.  The caller orders
+        the learner's reads after a collective on the same stream (e.g. exchange_roots())."""
+        self.shard.gather_to(slot, self.learner_ring, dst_slot, stream=stream)
+
     def sample_global(self, global_batch, beta=0.4, uniforms=None, seed=0, slot=0, stream=None):
         """Draw this rank's part of one global stratified batch into batch slot `slot`;
         -> (first, count) of the global batch positions it serves."""

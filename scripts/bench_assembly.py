@@ -1,0 +1,55 @@
+"""Mode G with cross-shard batch assembly over NVLink, one rank per GPU (torchrun).
+Per step: all-gather of shard roots -> sample_global -> gather_to(learner rank 0) on every rank
+-> all-gather (orders the learner's reads).  Reports global batches/s and the NVLink payload rate
+into the learner GPU.  Rows: Atari-u8 (56 464 B); capacity per shard CAP; global batch GB."""
+import json, os, sys, time
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import torch
+import torch.distributed as dist
+from reth_b200 import ReplayShard
+from reth_b200.sharded import ShardGroup
+
+ATARI = [(np.uint8, (4, 84, 84)), (np.int64, ()), (np.float32, ()), (np.uint8, (4, 84, 84)), (np.float32, ())]
+R = 56464
+rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(local)
+dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+cap = int(os.environ.get("CAP", 1 << 18)); GB = int(os.environ.get("GB", 4096)); steps = int(os.environ.get("STEPS", 200))
+sh = ReplayShard(cap, ATARI, max_batch=GB, ring_depth=4, device=local)
+g = torch.Generator(device="cuda").manual_seed(rank)
+for st in range(0, cap, 1 << 14):
+    n = min(1 << 14, cap - st)
+    s0 = torch.randint(0, 256, (n, 4, 84, 84), dtype=torch.uint8, device="cuda", generator=g)
+    z = torch.zeros(n, device="cuda")
+    sh.append([s0, z.long(), z, s0, z], torch.rand(n, device="cuda", generator=g) + 0.01)
+torch.cuda.synchronize()
+sg = ShardGroup(sh)
+sg.connect_learner(0)
+
+def step(k):
+    sg.exchange_roots()
+    sh.sample_global(GB, sg.all_roots, world, rank, beta=0.4, seed=7, slot=k % 2)
+    sg.assemble(slot=k % 2, dst_slot=2 + k % 2)
+
+for k in range(10):
+    step(k)
+sg.exchange_roots()
+torch.cuda.synchronize(); dist.barrier()
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record()
+for k in range(steps):
+    step(k)
+sg.exchange_roots()
+e1.record()
+torch.cuda.synchronize()
+ms = torch.tensor([e0.elapsed_time(e1)], device="cuda", dtype=torch.float64)
+dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+if rank == 0:
+    us = float(ms.item()) * 1e3 / steps
+    remote = GB * (world - 1) / world * R
+    print(json.dumps({"n_gpus": world, "global_batch": GB, "us_per_global_batch": us,
+                      "transitions_per_s": GB / us * 1e6, "nvlink_payload_GBps_into_learner": remote / us / 1e3,
+                      "note": "every rank gathers its slice straight into rank 0's batch ring (peer stores from the gather kernel)"}))
+dist.barrier()
+dist.destroy_process_group()
