@@ -38,6 +38,25 @@ def log(*a):
     print(*a, file=sys.stderr, flush=True)
 
 
+# stdout carries exactly ONE JSON line: everything else that libraries print there (NCCL prints its
+# version banner on fd 1) is sent to stderr by swapping the descriptors for the whole run.
+_REAL_STDOUT = None
+
+
+def _claim_stdout():
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit(line):
+    out = _REAL_STDOUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def measured_peak():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -162,7 +181,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": "transitions/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def workload_config(args):
@@ -397,7 +416,7 @@ def run_ours(args):
             "sample": f"{cores} replicas x {args.cpu_steps} steps x {args.cpu_iters} iterations of batch {B} "
                       f"({dt:.1f} s); tree capacity {cap}, frame ring bounded to 16384 rows (slot & mask)"}
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     proc.terminate()
     if world > 1:
         dist.barrier()
@@ -422,6 +441,7 @@ def main():
     ap.add_argument("--cpu-iters", type=int, default=64, help="iterations per step of the CPU arm (bounded sample)")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
+    _claim_stdout()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3
     if args.impl == "reference":
