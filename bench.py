@@ -301,6 +301,25 @@ def append_rate(torch, shard, n=16384, reps=10):
     return n / (ms / 1e3), 2 * n * ROW_BYTES / (ms / 1e3) / 1e9
 
 
+def append_rate_host(torch, shard, n=4096, reps=5):
+    """Host-producer variant (config 4): the same append from PINNED host columns, i.e. what an actor
+    message costs once decoded -- PCIe-bound, reported beside the HBM-bound device-source figure."""
+    cols = [torch.randint(0, 256, (n, 4, 84, 84), dtype=torch.uint8).pin_memory(),
+            torch.zeros(n, dtype=torch.int64).pin_memory(), torch.zeros(n).pin_memory(),
+            torch.randint(0, 256, (n, 4, 84, 84), dtype=torch.uint8).pin_memory(), torch.zeros(n).pin_memory()]
+    w = torch.rand(n).pin_memory()
+    shard.append(cols, w, alpha=ALPHA)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        shard.append(cols, w, alpha=ALPHA)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    return n / (ms / 1e3), n * ROW_BYTES / (ms / 1e3) / 1e9
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -365,6 +384,7 @@ def run_ours(args):
     e2e, h2d, d2h = e2e_loop(torch, dist, service, addr, e2e_iters, 64, B, world, G, args.ahead)
     e2e_strict, _, _ = e2e_loop(torch, dist, service, addr, min(1000, e2e_iters), 16, B, world, 1, 0)
     app_rows, app_gbs = append_rate(torch, shard) if rank == 0 or world == 1 else (None, None)
+    apph_rows, apph_gbs = append_rate_host(torch, shard) if rank == 0 and world == 1 else (None, None)
 
     peak, peak_src = measured_peak()
     rows_per_launch = G * B
@@ -403,6 +423,7 @@ def run_ours(args):
         "hbm_gbs_whole_loop": 2 * ROW_BYTES * value / 1e9 / world,
         "strict_alternation": {"value": strict, "unit": "transitions/s", "prefetch_group": 1},
         "append": {"rows_per_s": app_rows, "gbs": app_gbs, "rows_per_call": 16384, "source": "device"},
+        "append_host": {"rows_per_s": apph_rows, "pcie_gbs": apph_gbs, "rows_per_call": 4096, "source": "pinned host"},
         "shard_mode": "one shard per GPU, no data-path collective; NCCL all-gather of the 16-byte shard roots {total,min} once per bench step inside the timed region" if world > 1 else "single shard",
     }
     if world > 1:
