@@ -63,7 +63,15 @@ typedef struct reth_replay_config {
                                                2 = TMA bulk copies (cp.async.bulk + mbarrier ring) */
     int32_t store_rows;                     /* 0 = tree only (no frame ring; config 5 "tree-only") */
     int32_t reserved[5];
+    /* per column, what the GATHER emits into the learner batch (ring storage is unchanged):
+     * 0 raw bytes; 1 uint8 -> float32; 2 uint8 -> float32 / 255.  Replaces the learner's first pass
+     * over the batch, ensure_tensor(s0, torch.float, ...) in reth/reth/algorithm/dqn/dqn_solver.py:71-75
+     * (reth/reth/algorithm/util.py:5-12) and ScaledFloatFrame (reth/reth/env/util.py:219): frames stay
+     * uint8 in HBM (4x the capacity of the float32 rows test/apex-dqn/worker.py:47-51 stores) and the
+     * batch column is float32[row_bytes] per row. */
+    int32_t out_cast[RETH_MAX_COLUMNS];
 } reth_replay_config;
+typedef enum reth_cast { RETH_CAST_NONE = 0, RETH_CAST_U8_F32 = 1, RETH_CAST_U8_F32_UNIT = 2 } reth_cast;
 
 /* counters for the throughput report (SURVEY.md 5 "Metrics") */
 typedef struct reth_replay_stats {

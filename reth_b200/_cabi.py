@@ -34,7 +34,7 @@ class Config(C.Structure):
                 ("row_bytes", C.c_int64 * RETH_MAX_COLUMNS), ("max_batch", C.c_int32),
                 ("ring_depth", C.c_int32), ("device", C.c_int32), ("min_mode", C.c_int32),
                 ("update_cluster", C.c_int32), ("gather_mode", C.c_int32), ("store_rows", C.c_int32),
-                ("reserved", C.c_int32 * 5)]
+                ("reserved", C.c_int32 * 5), ("out_cast", C.c_int32 * RETH_MAX_COLUMNS)]
 
 
 class Stats(C.Structure):

@@ -23,6 +23,21 @@ __device__ __forceinline__ uint4 ld_stream(const uint4 *p)
                  : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
     return r;
 }
+// 4 packed uint8 -> 4 float32 (exact); unit: IEEE division by 255 like numpy's float32 x / 255.0
+__device__ __forceinline__ uint4 u8x4_to_f32(uint32_t w, bool unit)
+{
+    float f0 = (float)(w & 0xffu), f1 = (float)((w >> 8) & 0xffu), f2 = (float)((w >> 16) & 0xffu), f3 = (float)(w >> 24);
+    if (unit) {
+        f0 = __fdiv_rn(f0, 255.0f); f1 = __fdiv_rn(f1, 255.0f); f2 = __fdiv_rn(f2, 255.0f); f3 = __fdiv_rn(f3, 255.0f);
+    }
+    return make_uint4(__float_as_uint(f0), __float_as_uint(f1), __float_as_uint(f2), __float_as_uint(f3));
+}
+__device__ __forceinline__ uint32_t ld_stream32(const uint32_t *p)
+{
+    uint32_t r;
+    asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(r) : "l"(p));
+    return r;
+}
 __device__ __forceinline__ void st_stream(uint4 *p, const uint4 &v)
 {
     asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};"
@@ -86,6 +101,7 @@ struct RowCol {
     int64_t rb;           // row bytes
     int32_t chunks;       // work items per row (wide columns), 0 = narrow column
     int32_t units;        // 16 B units per chunk
+    int32_t cast;         // gather only: 0 raw, 1 u8 -> f32, 2 u8 -> f32 / 255 (batch rows are 4*rb bytes)
     int64_t item_base;    // first work item of this column
 };
 
@@ -106,8 +122,10 @@ struct RowArgs {
 
 // kScatter=false: batch[i] <- ring[idx[i]]   (numpy_loader.py:35-50, buffer.py:92-93)
 // kScatter=true : ring[idx[i]] <- batch[i]   (append to policy-chosen slots)
-template <bool kScatter>
-__global__ void __launch_bounds__(kCopyThreads, 6) row_move_kernel(const RowArgs a)
+// kWiden (gather only): some column is emitted as float32 (RowCol::cast); a separate instantiation so
+// that the plain byte mover keeps its register budget.
+template <bool kScatter, bool kWiden = false>
+__global__ void __launch_bounds__(kCopyThreads, kWiden ? 4 : 6) row_move_kernel(const RowArgs a)
 {
     const int rows = a.meta ? (int)a.meta[1] : a.batch;
     const int64_t row0 = (a.meta && a.dst_row_from_meta) ? a.meta[0] : 0;
@@ -130,6 +148,25 @@ __global__ void __launch_bounds__(kCopyThreads, 6) row_move_kernel(const RowArgs
             const int64_t n = min((int64_t)col.units, upr - u0);
             const uint4 *rp = (const uint4 *)(col.ring + slot * col.rb) + u0;
             const uint4 *bp = (const uint4 *)(col.batch + ((int64_t)row + row0) * col.rb) + u0;
+            if (kWiden && !kScatter && col.cast) {
+                // widening gather: lane = one 32-bit word (4 uint8) in, one 16 B vector (4 float32) out,
+                // so a warp reads 128 contiguous bytes and writes 512 contiguous bytes per instruction
+                uint4 *d4 = (uint4 *)(col.batch + ((int64_t)row + row0) * col.rb * 4) + u0 * 4;
+                const uint32_t *w32 = (const uint32_t *)rp;
+                const bool unit = col.cast == 2;
+                const int64_t n4 = n * 4;
+                int64_t j = threadIdx.x;
+                for (; j + 3 * kCopyThreads < n4; j += 4 * kCopyThreads) {
+                    const uint32_t a0 = ld_stream32(w32 + j), a1 = ld_stream32(w32 + j + kCopyThreads);
+                    const uint32_t a2 = ld_stream32(w32 + j + 2 * kCopyThreads), a3 = ld_stream32(w32 + j + 3 * kCopyThreads);
+                    st_stream(d4 + j, u8x4_to_f32(a0, unit));
+                    st_stream(d4 + j + kCopyThreads, u8x4_to_f32(a1, unit));
+                    st_stream(d4 + j + 2 * kCopyThreads, u8x4_to_f32(a2, unit));
+                    st_stream(d4 + j + 3 * kCopyThreads, u8x4_to_f32(a3, unit));
+                }
+                for (; j < n4; j += kCopyThreads) st_stream(d4 + j, u8x4_to_f32(ld_stream32(w32 + j), unit));
+                continue;
+            }
             const uint4 *s = kScatter ? bp : rp;
             uint4 *d = (uint4 *)(kScatter ? rp : bp);
             int64_t j = threadIdx.x;
@@ -160,6 +197,12 @@ __global__ void __launch_bounds__(kCopyThreads, 6) row_move_kernel(const RowArgs
                 const RowCol &col = a.col[c];
                 if (col.chunks != 0) continue;
                 uint8_t *rp = col.ring + slot * col.rb;
+                if (kWiden && !kScatter && col.cast) {
+                    float *fp = (float *)(col.batch + ((int64_t)row + row0) * col.rb * 4);
+                    for (int64_t q = 0; q < col.rb; ++q)
+                        fp[q] = col.cast == 2 ? __fdiv_rn((float)rp[q], 255.0f) : (float)rp[q];
+                    continue;
+                }
                 uint8_t *bp = col.batch + ((int64_t)row + row0) * col.rb;
                 span_copy(kScatter ? rp : bp, kScatter ? bp : rp, col.rb, 0, 1);
             }

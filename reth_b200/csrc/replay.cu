@@ -66,6 +66,7 @@ struct reth_replay {
     cudaEvent_t ev_app_fork = nullptr, ev_app_done = nullptr;
     cudaEvent_t last_gather_ev = nullptr;     // newest gather of the internal streams (appends wait for it: rows stay atomic)
     int update_cluster = 8;
+    int64_t out_rb[kMaxCols] = {};      // bytes of one row of each BATCH column (4x row_bytes when the gather widens)
     int max_dyn_smem = 0;               // opt-in shared memory per block
     bool gather_bulk = false;           // gather through row_gather_bulk_kernel (TMA bulk copies)
     int bulk_grid_cap = 0;              // RETH_BULK_GRID at create time: cap on the persistent grid (tests)
@@ -157,7 +158,7 @@ void free_all(reth_replay *h)
 
 }  // namespace
 
-RETH_EXPORT int reth_replay_abi_version(void) { return 1; }
+RETH_EXPORT int reth_replay_abi_version(void) { return 2; }
 
 RETH_EXPORT const char *reth_replay_last_error(const reth_replay_t *h)
 {
@@ -185,6 +186,10 @@ RETH_EXPORT int reth_replay_create(const reth_replay_config *cfg, reth_replay_t 
     h->cfg = *cfg;
     if (h->cfg.ring_depth < 1) h->cfg.ring_depth = 2;
     h->geom = make_geom(cfg->capacity);
+    for (int c = 0; c < cfg->n_columns; ++c) {
+        if (cfg->out_cast[c] < 0 || cfg->out_cast[c] > 2) { delete h; return fail(nullptr, RETH_ERR_INVALID, "out_cast[%d] invalid", c); }
+        h->out_rb[c] = cfg->row_bytes[c] * (cfg->out_cast[c] ? 4 : 1);
+    }
     h->update_cluster = cfg->update_cluster > 0 ? cfg->update_cluster : 8;
     DeviceGuard guard(cfg->device);
     auto bail = [&](int code) { free_all(h); g_create_error = h->error; delete h; return code; };
@@ -210,6 +215,8 @@ RETH_EXPORT int reth_replay_create(const reth_replay_config *cfg, reth_replay_t 
         bool any_wide = false;
         for (int c = 0; c < cfg->n_columns; ++c)
             if (cfg->row_bytes[c] % 16 == 0 && cfg->row_bytes[c] >= 256) any_wide = true;
+        for (int c = 0; c < cfg->n_columns; ++c)
+            if (cfg->out_cast[c]) any_wide = false;          // the DMA gather cannot widen: LDG/STG kernel
         h->gather_bulk = (mode == 2) && any_wide;   // auto = LDG/STG.128: measured faster (profiles/r01_gather_sweep.log)
         if (const char *e = getenv("RETH_BULK_GRID")) h->bulk_grid_cap = atoi(e);
         if (h->gather_bulk)
@@ -239,8 +246,8 @@ RETH_EXPORT int reth_replay_create(const reth_replay_config *cfg, reth_replay_t 
     const size_t depth = (size_t)h->cfg.ring_depth, mb = (size_t)cfg->max_batch;
     if (cfg->store_rows)
         for (int c = 0; c < cfg->n_columns; ++c) {
-            CKC(cudaMalloc((void **)&h->slot_cols[c], depth * mb * cfg->row_bytes[c]));
-            *acct += (int64_t)(depth * mb * cfg->row_bytes[c]);
+            CKC(cudaMalloc((void **)&h->slot_cols[c], depth * mb * h->out_rb[c]));
+            *acct += (int64_t)(depth * mb * h->out_rb[c]);
         }
     CKC(dalloc_zero(&h->slot_idx, depth * mb, acct));
     CKC(dalloc_zero(&h->slot_w, depth * mb, acct));
@@ -249,7 +256,7 @@ RETH_EXPORT int reth_replay_create(const reth_replay_config *cfg, reth_replay_t 
     for (size_t i = 0; i < depth; ++i) {
         BatchSlot &s = h->slots[i];
         for (int c = 0; c < cfg->n_columns; ++c)
-            s.cols[c] = h->slot_cols[c] ? h->slot_cols[c] + i * mb * cfg->row_bytes[c] : nullptr;
+            s.cols[c] = h->slot_cols[c] ? h->slot_cols[c] + i * mb * h->out_rb[c] : nullptr;
         s.idx = h->slot_idx + i * mb;
         s.w = h->slot_w + i * mb;
         s.prio = h->slot_prio + i * mb;
@@ -554,7 +561,7 @@ int gather_units_target()
 
 // Work decomposition of a row move over `batch` rows (gather or scatter).
 void build_row_args(reth_replay *h, RowArgs &a, uint8_t *const *batch_cols, const int64_t *idx, int batch,
-                    int units_target = 0)
+                    int units_target = 0, bool widen = false)
 {
     if (units_target <= 0) units_target = gather_units_target();
     a = RowArgs{};
@@ -570,6 +577,7 @@ void build_row_args(reth_replay *h, RowArgs &a, uint8_t *const *batch_cols, cons
         col.ring = h->ring[c];
         col.batch = batch_cols[c];
         col.rb = h->cfg.row_bytes[c];
+        col.cast = widen ? h->cfg.out_cast[c] : 0;
         const bool wide = (col.rb % 16 == 0) && col.rb >= 256 && ((uintptr_t)col.batch % 16 == 0);
         if (wide) {
             const int64_t upr = col.rb / 16;
@@ -589,11 +597,14 @@ void build_row_args(reth_replay *h, RowArgs &a, uint8_t *const *batch_cols, cons
 template <bool kScatter>
 int launch_row_move(reth_replay *h, const RowArgs &a, cudaStream_t s)
 {
+    bool widen = false;
+    for (int c = 0; c < a.ncols; ++c) widen |= a.col[c].cast != 0;
     int64_t total = a.wide_items + a.narrow_groups;
     if (total <= 0) return RETH_OK;
     const int64_t maxg = (int64_t)h->n_sms * 6 * 64;
     const unsigned grid = (unsigned)(total < maxg ? total : maxg);
-    row_move_kernel<kScatter><<<grid, kCopyThreads, 0, s>>>(a);
+    if (!kScatter && widen) row_move_kernel<false, true><<<grid, kCopyThreads, 0, s>>>(a);
+    else row_move_kernel<kScatter><<<grid, kCopyThreads, 0, s>>>(a);
     CK(h, cudaGetLastError());
     h->st.kernel_launches++;
     return RETH_OK;
@@ -685,7 +696,7 @@ int do_gather(reth_replay *h, int slot, bool use_meta, cudaStream_t s, int group
         rc = launch_gather_bulk(h, b.cols, b.idx, b.batch * groups, meta, s);
     } else {
         RowArgs a;
-        build_row_args(h, a, b.cols, b.idx, b.batch * groups);
+        build_row_args(h, a, b.cols, b.idx, b.batch * groups, 0, true);
         a.meta = meta;
         rc = launch_row_move<false>(h, a, s);
     }
@@ -846,7 +857,7 @@ RETH_EXPORT int reth_replay_slot_read(reth_replay_t *h, int slot, int64_t *indic
     if (cols && h->cfg.store_rows)
         for (int c = 0; c < h->cfg.n_columns; ++c)
             if (cols[c])
-                CK(h, cudaMemcpyAsync(cols[c], b.cols[c], n * h->cfg.row_bytes[c], cudaMemcpyDeviceToHost, s));
+                CK(h, cudaMemcpyAsync(cols[c], b.cols[c], n * h->out_rb[c], cudaMemcpyDeviceToHost, s));
     return check_device_err(h, s);
 }
 
@@ -1199,7 +1210,7 @@ RETH_EXPORT int reth_replay_ipc_export(reth_replay_t *h, reth_ipc_export *out)
     out->device = h->cfg.device;
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
     for (int c = 0; c < out->n_columns; ++c) {
-        out->row_bytes[c] = h->cfg.row_bytes[c];
+        out->row_bytes[c] = h->out_rb[c];               // rows of the BATCH ring
         CK(h, cudaIpcGetMemHandle((cudaIpcMemHandle_t *)out->col_handle[c], h->slot_cols[c]));
     }
     CK(h, cudaIpcGetMemHandle((cudaIpcMemHandle_t *)out->idx_handle, h->slot_idx));
@@ -1265,7 +1276,7 @@ RETH_EXPORT int reth_replay_gather_to(reth_replay_t *h, int slot, reth_ipc_view_
     if (dst) {
         if (dst->ex.n_columns != ncols) return fail(h, RETH_ERR_INVALID, "destination ring has another row struct");
         for (int c = 0; c < ncols; ++c)
-            if (dst->ex.row_bytes[c] != h->cfg.row_bytes[c])
+            if (dst->ex.row_bytes[c] != h->out_rb[c])
                 return fail(h, RETH_ERR_INVALID, "destination ring has another row struct");
     }
     DeviceGuard guard(h->cfg.device);
@@ -1274,9 +1285,9 @@ RETH_EXPORT int reth_replay_gather_to(reth_replay_t *h, int slot, reth_ipc_view_
     if (ncols > 0) {
         uint8_t *cols[kMaxCols] = {};
         for (int c = 0; c < ncols; ++c)
-            cols[c] = (dst ? dst->cols[c] : h->slot_cols[c]) + (size_t)dst_slot * mb * h->cfg.row_bytes[c];
+            cols[c] = (dst ? dst->cols[c] : h->slot_cols[c]) + (size_t)dst_slot * mb * h->out_rb[c];
         RowArgs a;
-        build_row_args(h, a, cols, b.idx, b.batch);
+        build_row_args(h, a, cols, b.idx, b.batch, 0, true);
         a.meta = b.meta;
         a.dst_row_from_meta = 1;
         int rc = launch_row_move<false>(h, a, s);

@@ -43,7 +43,9 @@ class _Engine:
     (sampler_loop.py:30-36).  Nothing here waits for the device except a loader taking delivery
     of a pre-sampled group (ShardPipe.wait)."""
 
-    def __init__(self, capacity, batch_size, samplers=None, cache_policy=None, device=0, max_ring=16):
+    def __init__(self, capacity, batch_size, samplers=None, cache_policy=None, device=0, max_ring=16,
+                 float_frames=None):
+        self.float_frames = float_frames                      # None | "f32" | "f32/255": see ReplayShard(out_cast=)
         self.capacity = int(capacity)
         self.batch_size = int(batch_size)
         self.device = device
@@ -94,8 +96,12 @@ class _Engine:
         if self.shard is not None:
             return
         self.struct = struct or [(np.asarray(col).dtype, tuple(np.asarray(col).shape[1:])) for col in data]
+        # float_frames: image-like uint8 columns (rank >= 2 per row) are handed to the learner as float32,
+        # the conversion DQNSolver does first (reth/reth/algorithm/dqn/dqn_solver.py:71-75), fused into the gather
+        cast = [self.float_frames if (np.dtype(dt) == np.uint8 and len(sh) >= 2) else None for dt, sh in self.struct]
         self.shard = ReplayShard(self.capacity, self.struct, max_batch=self.batch_size,
-                                 ring_depth=self.max_ring, device=self.device, min_mode=MIN_SERVICE)
+                                 ring_depth=self.max_ring, device=self.device, min_mode=MIN_SERVICE,
+                                 out_cast=cast if self.float_frames else None)
         self.stream = self.shard.pipe_stream
 
     def append(self, data, weights):
@@ -286,20 +292,20 @@ class _ServerHandle:
 
 
 def start_server(capacity, batch_size, host=None, port=None, samplers=None, cache_policy=None, device=0,
-                 max_ring=16):
+                 max_ring=16, float_frames=None):
     """reth_buffer.start_server (__init__.py:11-27).  host/port are accepted for signature
     compatibility; the engine is reached through the returned in-process address."""
     addr = f"{_SCHEME}{next(_COUNTER)}"
-    _ENGINES[addr] = _Engine(capacity, batch_size, samplers, cache_policy, device, max_ring)
+    _ENGINES[addr] = _Engine(capacity, batch_size, samplers, cache_policy, device, max_ring, float_frames)
     return _ServerHandle(addr), addr
 
 
 def start_per(capacity, batch_size, alpha=0.6, beta=0.4, sample_start=1000, num_sampler_procs=1,
-              host=None, port=None, cache_policy=None, device=0, max_ring=16):
+              host=None, port=None, cache_policy=None, device=0, max_ring=16, float_frames=None):
     """reth_buffer.start_per (__init__.py:30-49)."""
     samplers = [{"sampler_cls": PERSampler, "num_procs": num_sampler_procs, "sample_start": sample_start,
                  "kwargs": {"alpha": alpha, "beta": beta}}]
-    return start_server(capacity, batch_size, host, port, samplers, cache_policy, device, max_ring)
+    return start_server(capacity, batch_size, host, port, samplers, cache_policy, device, max_ring, float_frames)
 
 
 def _engine(meta_addr):

@@ -177,7 +177,7 @@ class ReplayShard:
     """
 
     def __init__(self, capacity, struct, max_batch, ring_depth=2, device=0, min_mode=MIN_SERVICE,
-                 store_rows=True, update_cluster=0, gather_mode=0):
+                 store_rows=True, update_cluster=0, gather_mode=0, out_cast=None):
         self._h = None
         self._lib = _cabi.lib()
         self.capacity = int(capacity)
@@ -198,6 +198,18 @@ class ReplayShard:
         cfg.min_mode = int(min_mode)
         cfg.update_cluster = int(update_cluster)
         cfg.store_rows = int(self.store_rows)
+        # out_cast[c]: None | "f32" | "f32/255": the gather widens a uint8 column to float32 for the learner
+        codes = {None: 0, 0: 0, "f32": 1, 1: 1, "f32/255": 2, 2: 2}
+        self.out_cast = [codes[x] for x in (out_cast or [None] * len(self.struct))]
+        if len(self.out_cast) != len(self.struct):
+            raise ValueError("out_cast needs one entry per column")
+        for i, code in enumerate(self.out_cast):
+            if code and self.struct[i][0] != np.dtype(np.uint8):
+                raise ValueError(f"column {i}: only uint8 columns can be widened to float32")
+            cfg.out_cast[i] = code
+        # what a batch slot holds (struct is what the ring stores)
+        self.out_struct = [((np.dtype(np.float32) if code else dt), sh)
+                           for (dt, sh), code in zip(self.struct, self.out_cast)]
         cfg.gather_mode = int(gather_mode)      # 0 auto (TMA bulk when a column is wide), 1 LDG/STG, 2 TMA bulk
         h = C.c_void_p()
         rc = self._lib.reth_replay_create(C.byref(cfg), C.byref(h))
@@ -371,7 +383,7 @@ class ReplayShard:
         n = b.value if rows is None else int(rows)
         data = []
         if self.store_rows:
-            data = [_DevArray(cols[i], (n,) + sh, dt, self) for i, (dt, sh) in enumerate(self.struct)]
+            data = [_DevArray(cols[i], (n,) + sh, dt, self) for i, (dt, sh) in enumerate(self.out_struct)]
         return (data, _DevArray(ip.value, (n,), np.int64, self), _DevArray(wp.value, (n,), np.float64, self),
                 _DevArray(pp.value, (n,), np.float64, self))
 
@@ -390,7 +402,7 @@ class ReplayShard:
         w = np.empty(n, np.float64)
         ptrs, outs = None, None
         if with_rows and self.store_rows:
-            outs = [np.empty((n,) + sh, dt) for dt, sh in self.struct]
+            outs = [np.empty((n,) + sh, dt) for dt, sh in self.out_struct]
             ptrs = (C.c_void_p * len(outs))(*[o.ctypes.data for o in outs])
         self._ck(self._lib.reth_replay_slot_read(self._h, slot, idx.ctypes.data, w.ctypes.data, ptrs,
                                                  self._s(stream)))

@@ -30,7 +30,7 @@ def test_header_symbols_exported_and_bound():
         assert re.search(rf"\bT {n}\b", syms), f"{n} not exported"
         assert hasattr(L, n)
         assert n in _cabi.SIGNATURES or n == "reth_replay_last_error", f"{n} has no ctypes signature"
-    assert L.reth_replay_abi_version() == 1
+    assert L.reth_replay_abi_version() == 2
 
 
 def test_library_is_sm100a_with_lineinfo():
@@ -40,7 +40,7 @@ def test_library_is_sm100a_with_lineinfo():
 
 def test_config_struct_matches_header():
     # 8 + 4(+4 pad) + 16*8 + 7*4 + 5*4 = 192
-    assert C.sizeof(_cabi.Config) == 192
+    assert C.sizeof(_cabi.Config) == 256      # 192 + out_cast[16]
     assert C.sizeof(_cabi.Stats) == 64
 
 

@@ -174,3 +174,42 @@ def test_gather_property_full_size(Shard):
         assert w.max() <= 1.0 + 1e-12                  # p_min normalisation: max weight is 1
     assert len(seen) > 5 * B * 0.9                     # spread over the whole ring
     sh.close()
+
+
+@pytest.mark.parametrize("mode", ["f32", "f32/255"])
+def test_widening_gather_u8_to_f32(Shard, mode):
+    """The gather hands uint8 frame columns to the learner as float32 (optionally / 255): what
+    DQNSolver does first with every batch (reth/reth/algorithm/dqn/dqn_solver.py:71-75,
+    reth/reth/algorithm/util.py:5-12; scaling as reth/reth/env/util.py:219).  Bit-exact against
+    numpy's astype(float32) [/ 255.0]; the ring keeps the uint8 bytes."""
+    import torch
+    cap, B, G = 2000, 160, 2
+    struct = [(np.uint8, (4, 84, 84)), (np.int64, ()), (np.float32, ()), (np.uint8, (4, 84, 84)), (np.uint8, (5,))]
+    rng = np.random.default_rng(13)
+    sh = Shard(cap, struct, max_batch=B, ring_depth=2 * G, out_cast=[mode, None, None, mode, mode])
+    ring = po.OracleRing(cap, struct)
+    cols = _rows(rng, struct, 1500)
+    cols[0][:] = rng.integers(0, 256, cols[0].shape, dtype=np.uint8)
+    cols[3][:, :, :2] = 255
+    sh.append(cols, rng.random(1500).astype(np.float32) + 0.1)
+    ring.append_batch(cols)
+    assert np.array_equal(sh.ring_read(0, 0, 1500), cols[0])           # storage stays uint8
+    conv = (lambda a: a.astype(np.float32)) if mode == "f32" else (lambda a: a.astype(np.float32) / 255.0)
+    sh.sample(B, uniforms=rng.random(B), slot=0)
+    sh.gather(0)
+    data, idx, _ = sh.slot_read(0, with_rows=True)
+    want = ring.select(idx)
+    assert data[0].dtype == np.float32 and data[0].shape == (B, 4, 84, 84)
+    for c in (0, 3, 4):
+        assert np.array_equal(data[c], conv(want[c])), c
+    assert np.array_equal(data[1], want[1]) and np.array_equal(data[2], want[2])
+    sh.sample_multi(B, 0, G, seed=3)
+    sh.gather_multi(0, G)
+    for g in range(G):
+        t, ti, _, _ = sh.slot_tensors(g)
+        assert t[0].dtype == torch.float32 and tuple(t[0].shape) == (B, 4, 84, 84)
+        w2 = ring.select(ti.cpu().numpy())
+        assert np.array_equal(t[0].cpu().numpy(), conv(w2[0])) and np.array_equal(t[4].cpu().numpy(), conv(w2[4]))
+    with pytest.raises(ValueError):
+        Shard(10, [(np.float32, (4,))], max_batch=2, out_cast=["f32"])
+    sh.close()
