@@ -200,6 +200,31 @@ int reth_replay_sample_global(reth_replay_t *h, int global_batch, const double *
 int reth_replay_slot_meta(reth_replay_t *h, int slot, int64_t *first_count, void *stream);
 
 
+/* ---- the other sampler plugins of start_server(samplers=[...]) (server/main_loop.py:135-159) on the
+ *      same shard: batches are drawn into the same batch slots and gathered by the same kernel.
+ *  UniformSampler (sampler/uniform_sampler.py:6-25): uniform_note() is its update(): the first
+ *  `capacity` notified indices are logged in arrival order (appends AND priority updates notify, as
+ *  in the reference where both travel the update channel, main_loop.py:58); the reference raises
+ *  IndexError when a message crosses the capacity of the log, here the excess is dropped.
+ *  append_note != 0 on reth_replay_append-style FIFO slots: idx == NULL, slots first_slot.. mod capacity.
+ *  sample_uniform(): positions = draws[n] in [0, tail) (parity: the reference uses
+ *  np.random.choice(tail, batch)) or NULL = device generator; weights are 1.
+ *  FIFOSampler (sampler/fifo_sampler.py:8-29): fifo_push() is its update() (a bounded queue,
+ *  deque(maxlen=capacity).appendleft: the oldest entry is dropped when full); sample_fifo() pops the
+ *  `batch` oldest entries, RETH_ERR_STATE unless len > batch (ready_sample, :17-18).
+ *  Both write n_slots consecutive batch slots in one launch (batch == max_batch when n_slots > 1). */
+int reth_replay_uniform_note(reth_replay_t *h, const void *idx, int idx_dtype, int idx_loc, int64_t first_slot,
+                             int64_t n, void *stream);
+int reth_replay_sample_uniform(reth_replay_t *h, int batch, int first_slot, int n_slots, const int64_t *draws,
+                               int draws_loc, uint64_t seed, void *stream);
+int reth_replay_fifo_push(reth_replay_t *h, const void *idx, int idx_dtype, int idx_loc, int64_t first_slot,
+                          const void *w, int w_dtype, int w_loc, int64_t n, void *stream);
+int reth_replay_sample_fifo(reth_replay_t *h, int batch, int first_slot, int n_slots, void *stream);
+/* host int64[4] = {uniform tail, fifo length, fifo head, 0} */
+int reth_replay_sampler_state(reth_replay_t *h, int64_t *out);
+/* which sampler reth_replay_pipe_issue() draws with: 0 PER (default), 1 uniform, 2 fifo */
+int reth_replay_pipe_sampler(reth_replay_t *h, int kind);
+
 /* ---- asynchronous loader pipeline (the end-to-end path with HOST index / priority buffers).
  *      Replaces, in one process, what the reference spreads over sampler_loop (pre-sampled batch
  *      behind a HWM-1 PUSH socket, server/sampler_loop.py:14,25-28,37-39), the TorchCudaLoader

@@ -272,3 +272,55 @@ def step_loop(tree, ring, slot_mask, steps, batch, u, new_prio, alpha, beta, min
                              float(alpha), float(beta), min_mode, _ptr(idx), _ptr(val), _ptr(w),
                              _ptr(p), ptrs)
     return acc, idx, w, outs
+
+
+class OracleUniformSampler:
+    """sampler/uniform_sampler.py:6-25: a log of the first `capacity` notified indices; sample =
+    log[draws], draws in [0, tail) (the reference draws them with np.random.choice(tail, batch)),
+    weights are int64 ones.  The reference raises IndexError when one message crosses the end of
+    the log (:21-22 writes indices[capacity]); the restatement (and the engine) drop the excess."""
+
+    def __init__(self, capacity):
+        self.indices = np.zeros(capacity, dtype="i8")
+        self.capacity = capacity
+        self.tail = 0
+
+    def update(self, indices, weights=None):
+        if self.tail == self.capacity:                       # :18-19
+            return
+        idx = np.asarray(indices, dtype=np.int64)
+        m = min(len(idx), self.capacity - self.tail)
+        self.indices[self.tail:self.tail + m] = idx[:m]
+        self.tail += m
+
+    def sample(self, draws):
+        draws = np.asarray(draws, dtype=np.int64)
+        assert np.all((draws >= 0) & (draws < self.tail))
+        return self.indices[draws], np.ones(len(draws), dtype="i8")
+
+    def clear(self):
+        self.indices[:] = 0
+        self.tail = 0
+
+
+class OracleFIFOSampler:
+    """sampler/fifo_sampler.py:8-29: deque(maxlen=capacity); update appends on the left (a full
+    queue drops its oldest entry), sample pops the oldest entries from the right."""
+
+    def __init__(self, capacity):
+        from collections import deque
+        self.buffer = deque(maxlen=capacity)
+
+    def ready_sample(self, batch_size):
+        return len(self.buffer) > batch_size                 # :17-18
+
+    def update(self, indices, weights):
+        for i, idx in enumerate(indices):
+            self.buffer.appendleft((int(idx), float(weights[i])))
+
+    def sample(self, batch_size):
+        out = [self.buffer.pop() for _ in range(batch_size)]
+        return np.array([o[0] for o in out], np.int64), np.array([o[1] for o in out], np.float64)
+
+    def clear(self):
+        self.buffer.clear()

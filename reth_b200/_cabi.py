@@ -99,6 +99,12 @@ SIGNATURES = {
     "reth_replay_root_dev": [_vp, C.POINTER(_vp)],
     "reth_replay_sample_global": [_vp, _i32, _vp, _i32, _i32, _vp, _i32, _u64, _f64, _i32, _vp],
     "reth_replay_slot_meta": [_vp, _i32, C.POINTER(_i64), _vp],
+    "reth_replay_uniform_note": [_vp, _vp, _i32, _i32, _i64, _i64, _vp],
+    "reth_replay_sample_uniform": [_vp, _i32, _i32, _i32, _vp, _i32, _u64, _vp],
+    "reth_replay_fifo_push": [_vp, _vp, _i32, _i32, _i64, _vp, _i32, _i32, _i64, _vp],
+    "reth_replay_sample_fifo": [_vp, _i32, _i32, _i32, _vp],
+    "reth_replay_sampler_state": [_vp, C.POINTER(_i64)],
+    "reth_replay_pipe_sampler": [_vp, _i32],
     "reth_replay_pipe_open": [_vp, _i32, _i32, _u64, C.POINTER(PipeInfo)],
     "reth_replay_pipe_close": [_vp],
     "reth_replay_pipe_stream": [_vp, C.POINTER(_vp)],

@@ -73,6 +73,11 @@ struct reth_replay {
     long long *dbg = nullptr;           // RETH_DEBUG_TIMING=1: stage clocks of the last update launch
     std::vector<cudaEvent_t> ev_time;   // pairs (start, stop) around timed gather launches
     size_t ev_time_used = 0;
+    // non-PER sampler plugins (allocated on first use)
+    int64_t *uni_log = nullptr, *fifo_idx = nullptr;
+    double *fifo_w = nullptr;
+    int64_t uni_tail = 0, fifo_head = 0, fifo_len = 0;
+    int pipe_kind = 0;                  // sampler of pipe_issue: 0 PER, 1 uniform, 2 fifo
     // asynchronous loader pipeline (reth_replay_pipe_*)
     struct Pipe {
         bool open = false;
@@ -136,6 +141,7 @@ void free_all(reth_replay *h)
 {
     cudaFree(h->desc); cudaFree(h->agg); cudaFree(h->stamp); cudaFree(h->mask);
     cudaFree(h->counts); cudaFree(h->err);
+    cudaFree(h->uni_log); cudaFree(h->fifo_idx); cudaFree(h->fifo_w);
     cudaFree(h->dbg);
     cudaFree(h->stage_idx); cudaFree(h->stage_prio); cudaFree(h->stage_u);
     if (h->host_pin) cudaFreeHost(h->host_pin);
@@ -419,6 +425,7 @@ RETH_EXPORT int reth_replay_clear(reth_replay_t *h, void *stream)
     CK(h, cudaMemsetAsync(h->counts, 0, 2 * kMaxTileLevels * sizeof(int32_t), s));
     h->tail = 0;
     h->size = 0;
+    h->uni_tail = h->fifo_head = h->fifo_len = 0;   // UniformSampler.clear / FIFOSampler.clear
     return RETH_OK;
 }
 
@@ -956,6 +963,167 @@ RETH_EXPORT int reth_replay_stats_get(reth_replay_t *h, reth_replay_stats *out)
 }
 
 
+// ------------------------------------------------------- non-PER sampler plugins --
+namespace {
+
+// entries [skip, n) of (idx, w) -> dst[(dst_pos + i) % dst_cap]; host arrays go through the staging buffers
+int note_entries(reth_replay *h, const void *idx, int idx_dtype, int idx_loc, int64_t first_slot, const void *w,
+                 int w_dtype, int w_loc, int64_t n, int64_t skip, int64_t *dst_idx, double *dst_w, int64_t dst_pos,
+                 int64_t dst_cap, cudaStream_t s)
+{
+    if (idx && idx_dtype != RETH_I32 && idx_dtype != RETH_I64) return fail(h, RETH_ERR_INVALID, "indices must be int32 or int64");
+    if (w && w_dtype != RETH_F32 && w_dtype != RETH_F64) return fail(h, RETH_ERR_INVALID, "weights must be float32 or float64");
+    const size_t is = idx ? dtype_size(idx_dtype) : 0, ws = w ? dtype_size(w_dtype) : 0;
+    for (int64_t off = skip; off < n; off += h->max_n) {
+        const int64_t m = (n - off < h->max_n) ? n - off : h->max_n;
+        NoteArgs a = {};
+        a.capacity = h->cfg.capacity;
+        a.n = m; a.skip = 0;
+        a.dst_idx = dst_idx; a.dst_w = w ? dst_w : nullptr;
+        a.dst_pos = (dst_pos + off) % dst_cap; a.dst_cap = dst_cap;
+        if (idx) {
+            a.idx_kind = idx_dtype == RETH_I64 ? 0 : 1;
+            int rc = to_device(h, (const uint8_t *)idx + off * is, idx_loc, m * is, h->stage_idx, s, &a.idx);
+            if (rc) return rc;
+        } else {
+            a.idx_kind = 2; a.iota_base = first_slot + off;
+        }
+        a.w_kind = 2;
+        if (w) {
+            a.w_kind = w_dtype == RETH_F32 ? 0 : 1;
+            int rc = to_device(h, (const uint8_t *)w + off * ws, w_loc, m * ws, h->stage_prio, s, &a.w);
+            if (rc) return rc;
+        }
+        sampler_note_kernel<<<(unsigned)((m + 255) / 256), 256, 0, s>>>(a);
+        CK(h, cudaGetLastError());
+        h->st.kernel_launches++;
+    }
+    return RETH_OK;
+}
+
+int pick_into_slots(reth_replay *h, PickArgs &a, int batch, int first_slot, int n_slots, cudaStream_t s)
+{
+    BatchSlot &b = h->slots[first_slot];
+    a.n = (int64_t)batch * n_slots;
+    a.idx_out = b.idx; a.w_out = b.w; a.prio_out = b.prio; a.meta = b.meta; a.batch = batch; a.err = h->err;
+    sampler_pick_kernel<<<(unsigned)((a.n + 255) / 256), 256, 0, s>>>(a);
+    CK(h, cudaGetLastError());
+    h->st.kernel_launches++;
+    h->st.sampled_rows += a.n;
+    for (int g = 0; g < n_slots; ++g) h->slots[first_slot + g].batch = batch;
+    return RETH_OK;
+}
+
+int slots_ok(reth_replay *h, int batch, int first_slot, int n_slots)
+{
+    if (batch < 1 || batch > h->cfg.max_batch) return fail(h, RETH_ERR_INVALID, "batch %d outside [1, max_batch=%d]", batch, h->cfg.max_batch);
+    if (n_slots < 1 || first_slot < 0 || first_slot + n_slots > (int)h->slots.size())
+        return fail(h, RETH_ERR_INVALID, "slots %d..%d outside the batch ring", first_slot, first_slot + n_slots - 1);
+    if (n_slots > 1 && batch != h->cfg.max_batch) return fail(h, RETH_ERR_INVALID, "multi-slot draws need batch == max_batch");
+    return RETH_OK;
+}
+
+int do_sample_uniform(reth_replay *h, int batch, int first_slot, int n_slots, const int64_t *draws, int draws_loc,
+                      uint64_t seed, cudaStream_t s)
+{
+    if (slots_ok(h, batch, first_slot, n_slots)) return RETH_ERR_INVALID;
+    if (h->uni_tail <= 0) return fail(h, RETH_ERR_STATE, "uniform sampler: nothing has been notified yet");
+    PickArgs a = {};
+    a.uniform = 1; a.src_idx = h->uni_log; a.tail = h->uni_tail; a.seed = seed; a.draw_base = h->draw_counter;
+    h->draw_counter += (uint64_t)batch * n_slots;
+    if (draws) {
+        if ((int64_t)batch * n_slots > h->max_n) return fail(h, RETH_ERR_INVALID, "too many explicit draws");
+        const void *d = nullptr;
+        int rc = to_device(h, draws, draws_loc, (size_t)batch * n_slots * 8, h->stage_idx, s, &d);
+        if (rc) return rc;
+        a.draws = (const int64_t *)d;
+    }
+    return pick_into_slots(h, a, batch, first_slot, n_slots, s);
+}
+
+int do_sample_fifo(reth_replay *h, int batch, int first_slot, int n_slots, cudaStream_t s)
+{
+    if (slots_ok(h, batch, first_slot, n_slots)) return RETH_ERR_INVALID;
+    const int64_t n = (int64_t)batch * n_slots;
+    if (!(h->fifo_len > n)) return fail(h, RETH_ERR_STATE, "fifo sampler: %lld queued, need more than %lld", (long long)h->fifo_len, (long long)n);
+    PickArgs a = {};
+    a.uniform = 0; a.src_idx = h->fifo_idx; a.src_w = h->fifo_w; a.src_cap = h->cfg.capacity; a.head = h->fifo_head;
+    int rc = pick_into_slots(h, a, batch, first_slot, n_slots, s);
+    if (rc) return rc;
+    h->fifo_head = (h->fifo_head + n) % h->cfg.capacity;
+    h->fifo_len -= n;
+    return RETH_OK;
+}
+
+}  // namespace
+
+RETH_EXPORT int reth_replay_uniform_note(reth_replay_t *h, const void *idx, int idx_dtype, int idx_loc,
+                                         int64_t first_slot, int64_t n, void *stream)
+{
+    if (!h || n < 0) return RETH_ERR_INVALID;
+    DeviceGuard guard(h->cfg.device);
+    const int64_t cap = h->cfg.capacity;
+    if (!h->uni_log) CK(h, dalloc_zero(&h->uni_log, (size_t)cap, &h->st.hbm_bytes));
+    if (h->uni_tail >= cap) return RETH_OK;                       // uniform_sampler.py:18-19
+    const int64_t m = n < cap - h->uni_tail ? n : cap - h->uni_tail;
+    int rc = note_entries(h, idx, idx_dtype, idx_loc, first_slot, nullptr, 0, 0, m, 0, h->uni_log, nullptr,
+                          h->uni_tail, cap + 1, S(stream));     // dst_cap > any position: no wrap
+    if (rc) return rc;
+    h->uni_tail += m;
+    return RETH_OK;
+}
+
+RETH_EXPORT int reth_replay_sample_uniform(reth_replay_t *h, int batch, int first_slot, int n_slots,
+                                           const int64_t *draws, int draws_loc, uint64_t seed, void *stream)
+{
+    if (!h) return RETH_ERR_INVALID;
+    DeviceGuard guard(h->cfg.device);
+    return do_sample_uniform(h, batch, first_slot, n_slots, draws, draws_loc, seed, S(stream));
+}
+
+RETH_EXPORT int reth_replay_fifo_push(reth_replay_t *h, const void *idx, int idx_dtype, int idx_loc, int64_t first_slot,
+                                      const void *w, int w_dtype, int w_loc, int64_t n, void *stream)
+{
+    if (!h || n < 0 || !w) return RETH_ERR_INVALID;
+    DeviceGuard guard(h->cfg.device);
+    const int64_t cap = h->cfg.capacity;
+    if (!h->fifo_idx) {
+        CK(h, dalloc_zero(&h->fifo_idx, (size_t)cap, &h->st.hbm_bytes));
+        CK(h, dalloc_zero(&h->fifo_w, (size_t)cap, &h->st.hbm_bytes));
+    }
+    // deque(maxlen=capacity).appendleft: a full queue drops its oldest entry; a push longer than the
+    // queue keeps only its last `capacity` entries
+    const int64_t skip = n > cap ? n - cap : 0;
+    int rc = note_entries(h, idx, idx_dtype, idx_loc, first_slot, w, w_dtype, w_loc, n, skip, h->fifo_idx, h->fifo_w,
+                          (h->fifo_head + h->fifo_len) % cap, cap, S(stream));
+    if (rc) return rc;
+    const int64_t total = h->fifo_len + n;
+    if (total > cap) { h->fifo_head = (h->fifo_head + (total - cap)) % cap; h->fifo_len = cap; }
+    else h->fifo_len = total;
+    return RETH_OK;
+}
+
+RETH_EXPORT int reth_replay_sample_fifo(reth_replay_t *h, int batch, int first_slot, int n_slots, void *stream)
+{
+    if (!h) return RETH_ERR_INVALID;
+    DeviceGuard guard(h->cfg.device);
+    return do_sample_fifo(h, batch, first_slot, n_slots, S(stream));
+}
+
+RETH_EXPORT int reth_replay_sampler_state(reth_replay_t *h, int64_t *out)
+{
+    if (!h || !out) return RETH_ERR_INVALID;
+    out[0] = h->uni_tail; out[1] = h->fifo_len; out[2] = h->fifo_head; out[3] = 0;
+    return RETH_OK;
+}
+
+RETH_EXPORT int reth_replay_pipe_sampler(reth_replay_t *h, int kind)
+{
+    if (!h || kind < 0 || kind > 2) return RETH_ERR_INVALID;
+    h->pipe_kind = kind;
+    return RETH_OK;
+}
+
 // ------------------------------------------------------- asynchronous pipeline --
 namespace {
 
@@ -983,7 +1151,10 @@ int pipe_issue(reth_replay *h, double beta)
     if (p.issued - p.waited + (p.waited > 0 ? 1 : 0) >= p.n_groups)
         return fail(h, RETH_ERR_STATE, "all %d group slots are issued or lent", p.n_groups);
     const int g = (int)(p.issued % p.n_groups), slot = g * p.G;
-    int rc = do_sample(h, p.batch, nullptr, RETH_DEVICE, p.seed, beta, slot, nullptr, 1, 0, h->s_tree, p.G);
+    int rc;
+    if (h->pipe_kind == 1) rc = do_sample_uniform(h, p.batch, slot, p.G, nullptr, RETH_DEVICE, p.seed, h->s_tree);
+    else if (h->pipe_kind == 2) rc = do_sample_fifo(h, p.batch, slot, p.G, h->s_tree);
+    else rc = do_sample(h, p.batch, nullptr, RETH_DEVICE, p.seed, beta, slot, nullptr, 1, 0, h->s_tree, p.G);
     if (rc) return rc;
     CK(h, cudaEventRecord(p.ev_smp[g], h->s_tree));
     CK(h, cudaStreamWaitEvent(p.s_copy, p.ev_smp[g], 0));

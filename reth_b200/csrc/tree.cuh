@@ -571,6 +571,77 @@ __global__ void stamp_clear_kernel(uint32_t *stamp, const int64_t *slots, int64_
     if (i < n && slots[i] >= 0 && slots[i] < cap) stamp[slots[i]] = 0u;
 }
 
+
+// ------------------------------------------------ non-PER samplers (plugin surface) --
+// UniformSampler (reth_buffer/reth_buffer/sampler/uniform_sampler.py:6-25): a log of the first
+// `capacity` notified slot indices; sample = log[randint(0, tail)], weights all one.
+// FIFOSampler (sampler/fifo_sampler.py:8-29): a bounded queue of (index, weight); sample pops the
+// oldest entries.  Host code owns the cursors (tail / head / count), kernels move the entries.
+struct NoteArgs {
+    const void *idx;
+    int32_t idx_kind;          // 0 int64[], 1 int32[], 2 iota (iota_base + i) % capacity
+    int64_t iota_base, capacity;
+    const void *w;
+    int32_t w_kind;            // 0 float32[], 1 float64[], 2 none
+    int64_t n, skip;           // entries skip..n-1 are written (a push longer than the queue keeps its tail)
+    int64_t *dst_idx;
+    double *dst_w;
+    int64_t dst_pos, dst_cap;  // entry i -> (dst_pos + i) % dst_cap
+};
+
+__global__ void sampler_note_kernel(const NoteArgs a)
+{
+    for (int64_t i = a.skip + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.n;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        int64_t v;
+        if (a.idx_kind == 0) v = ((const int64_t *)a.idx)[i];
+        else if (a.idx_kind == 1) v = (int64_t)((const int32_t *)a.idx)[i];
+        else v = (a.iota_base + i) % a.capacity;
+        const int64_t p = (a.dst_pos + i) % a.dst_cap;
+        a.dst_idx[p] = v;
+        if (a.dst_w) a.dst_w[p] = a.w_kind == 0 ? (double)((const float *)a.w)[i] : ((const double *)a.w)[i];
+    }
+}
+
+struct PickArgs {
+    const int64_t *src_idx;
+    const double *src_w;       // nullptr: weights are 1.0 (uniform)
+    int64_t src_cap, head;     // fifo: entry i = src[(head + i) % src_cap]
+    const int64_t *draws;      // uniform: explicit positions in [0, tail) or nullptr (device generator)
+    int64_t tail;
+    uint64_t seed, draw_base;
+    int32_t uniform;
+    int64_t n;
+    int64_t *idx_out;
+    double *w_out, *prio_out;
+    int64_t *meta;             // {first, count} per batch slot
+    int32_t batch;
+    int32_t *err;
+};
+
+__global__ void sampler_pick_kernel(const PickArgs a)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.n) return;
+    if (i % a.batch == 0) { a.meta[2 * (i / a.batch)] = 0; a.meta[2 * (i / a.batch) + 1] = a.batch; }
+    int64_t p;
+    if (a.uniform) {
+        if (a.draws) {
+            p = a.draws[i];
+            if (p < 0 || p >= a.tail) { atomicOr(a.err, 1); p = 0; }
+        } else {
+            p = (int64_t)(uniform53(a.seed, a.draw_base + (uint64_t)i) * (double)a.tail);
+            if (p >= a.tail) p = a.tail - 1;
+        }
+    } else {
+        p = (a.head + i) % a.src_cap;
+    }
+    a.idx_out[i] = a.src_idx[p];
+    const double w = a.src_w ? a.src_w[p] : 1.0;
+    a.w_out[i] = w;
+    a.prio_out[i] = w;
+}
+
 // ---------------------------------------------------------------- readback --
 // Tiled -> heap order (the three arrays of NumbaSumTree, utils/sumtree.py:85-88).
 __global__ void tree_read_kernel(TreeGeom g, const double2 *desc, const double2 *agg,

@@ -125,3 +125,61 @@ class PERSampler(BaseSampler):
 
     def update(self, indices, weights):
         self.shard.update(indices, weights, alpha=self.alpha.value(), transform=True)
+
+
+class UniformSampler(BaseSampler):
+    """sampler/uniform_sampler.py:6-25 on a ReplayShard: the index log and the draw live on the
+    device; sample() returns host (indices int64, weights int64 ones) like the reference."""
+
+    def __init__(self, capacity, shard=None, max_batch=8192, device=0, seed=0):
+        from .shard import ReplayShard
+        self.shard = shard if shard is not None else ReplayShard(capacity, [], max_batch=max_batch,
+                                                                 store_rows=False, device=device)
+        self.capacity = capacity
+        self.seed = seed
+        self.last_slot = 0
+
+    @property
+    def tail(self):
+        return self.shard.sampler_state()["uniform_tail"]
+
+    def sample(self, batch_size, draws=None):
+        slot = self.last_slot = (self.last_slot + 1) % self.shard.ring_depth
+        self.shard.sample_uniform(batch_size, slot, 1, draws=draws, seed=self.seed)
+        _, indices, _ = self.shard.slot_read(slot)
+        return indices, np.ones(batch_size, dtype="i8")
+
+    def update(self, indices, weights):
+        self.shard.uniform_note(indices)
+
+    def clear(self):
+        self.shard.clear()
+
+
+class FIFOSampler(BaseSampler):
+    """sampler/fifo_sampler.py:8-29 on a ReplayShard (an on-policy queue: every entry is handed
+    out once, oldest first)."""
+
+    def __init__(self, capacity, shard=None, max_batch=8192, device=0):
+        from .shard import ReplayShard
+        self.shard = shard if shard is not None else ReplayShard(capacity, [], max_batch=max_batch,
+                                                                 store_rows=False, device=device)
+        self.last_slot = 0
+
+    def __len__(self):
+        return self.shard.sampler_state()["fifo_len"]
+
+    def ready_sample(self, batch_size):
+        return len(self) > batch_size
+
+    def sample(self, batch_size):
+        slot = self.last_slot = (self.last_slot + 1) % self.shard.ring_depth
+        self.shard.sample_fifo(batch_size, slot, 1)
+        _, indices, weights = self.shard.slot_read(slot)
+        return indices, weights
+
+    def update(self, indices, weights):
+        self.shard.fifo_push(indices, weights)
+
+    def clear(self):
+        self.shard.clear()

@@ -27,7 +27,7 @@ import time
 
 import numpy as np
 
-from .sampler import FIFOPolicy, PERSampler, Schedule  # noqa: F401  (re-exported like reth_buffer does)
+from .sampler import FIFOPolicy, FIFOSampler, PERSampler, Schedule, UniformSampler  # noqa: F401  (re-exported like reth_buffer does)
 from .shard import MIN_SERVICE, ReplayShard
 
 _ENGINES = {}
@@ -58,9 +58,12 @@ class _Engine:
             assert topic not in topics                        # main_loop.py:137
             kwargs = dict(item.get("kwargs", {}))
             cls = item["sampler_cls"]
-            if cls is not PERSampler and getattr(cls, "__name__", "") != "PERSampler":
-                raise NotImplementedError("only PERSampler runs on the device in this build (SURVEY.md 8f row 3)")
+            name = cls if isinstance(cls, str) else getattr(cls, "__name__", "")
+            kinds = {"PERSampler": "per", "UniformSampler": "uniform", "FIFOSampler": "fifo"}
+            if name not in kinds:
+                raise NotImplementedError(f"sampler {name!r} has no device implementation in this build")
             topics[topic] = {
+                "kind": kinds[name],
                 "alpha": Schedule.from_str(kwargs.get("alpha", 0.6)),
                 "beta": Schedule.from_str(kwargs.get("beta", 0.4)),
                 "sample_start": max(item.get("sample_start", 1000), self.batch_size),   # main_loop.py:144-145
@@ -69,6 +72,7 @@ class _Engine:
         if len(topics) != 1:
             raise NotImplementedError("one sampler topic per buffer in this build")
         self.topic, self.sampler = next(iter(topics.items()))
+        self.kind = self.sampler["kind"]                      # "per" | "uniform" | "fifo"
         # a custom cache policy keeps deciding slots on the host (BasePolicy.get_indices);
         # the default FIFO cursor lives in the shard
         self.cache_policy = cache_policy
@@ -103,13 +107,18 @@ class _Engine:
                                  ring_depth=self.max_ring, device=self.device, min_mode=MIN_SERVICE,
                                  out_cast=cast if self.float_frames else None)
         self.stream = self.shard.pipe_stream
+        self.shard.pipe_sampler(self.kind)
 
     def append(self, data, weights):
         with self.lock:
             self._ensure_shard(data)
             alpha = self.sampler["alpha"].value()
             if self.cache_policy is None:
-                self.shard.append(list(data), weights, alpha=alpha, transform=True, stream=self.stream)
+                first = self.shard.append(list(data), weights, alpha=alpha, transform=True, stream=self.stream)
+                if self.kind == "uniform":                    # the append notice every sampler receives (main_loop.py:58)
+                    self.shard.uniform_note(None, first_slot=first, n=len(weights), stream=self.stream)
+                elif self.kind == "fifo":
+                    self.shard.fifo_push(None, weights, first_slot=first, stream=self.stream)
             else:
                 import torch
                 slots = np.asarray(self.cache_policy.get_indices(len(weights)), dtype=np.int64)
@@ -117,6 +126,10 @@ class _Engine:
                        for c, (dt, _) in zip(data, self.struct)]
                 torch.cuda.current_stream(self.device).synchronize()
                 self.shard.append_at(slots, dev, weights, alpha=alpha, transform=True, stream=self.stream)
+                if self.kind == "uniform":
+                    self.shard.uniform_note(slots, stream=self.stream)
+                elif self.kind == "fifo":
+                    self.shard.fifo_push(slots, weights, stream=self.stream)
             self.cnt += len(weights)
 
     # -- loader pipeline --------------------------------------------------
@@ -202,6 +215,12 @@ class _Engine:
                 self.sampler["beta"].step()
             n = len(indices)
             self.cnt += n
+            if self.kind != "per":                            # sampler.update() of the plugin (sampler_loop.py:35)
+                if self.kind == "uniform":
+                    self.shard.uniform_note(np.asarray(indices), stream=self.stream)
+                else:
+                    self.shard.fifo_push(np.asarray(indices), np.asarray(weights), stream=self.stream)
+                return
             pipe = self.pipe
             B = self.batch_size
             w = weights if isinstance(weights, np.ndarray) else np.asarray(weights)
@@ -246,7 +265,11 @@ class _Engine:
                 self.shard._ck(self.shard._lib.reth_replay_pipe_drain(self.shard._h))
 
     def ready(self):
-        return self.shard is not None and self.cnt >= self.sampler["sample_start"]
+        if self.shard is None or self.cnt < self.sampler["sample_start"]:
+            return False
+        if self.kind == "fifo":                               # FIFOSampler.ready_sample (fifo_sampler.py:17-18)
+            return self.shard.sampler_state()["fifo_len"] > self.batch_size * self.group
+        return True
 
     def wait_ready(self, timeout=60.0):
         if self.ready():

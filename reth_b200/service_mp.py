@@ -71,7 +71,7 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
     config = {"engine": "reth_b200", "capacity": capacity, "batch_size": batch_size, "device": device,
               "meta_addr": addrs["meta"], "append_addr": addrs["append"], "update_addr": addrs["update"],
               "loader_addr": addrs["loader"], "pid": os.getpid(),
-              "sampler_info": {eng.topic: {"topic": eng.topic, "sampler_cls": "PERSampler",
+              "sampler_info": {eng.topic: {"topic": eng.topic, "sampler_cls": eng.kind,
                                            "sample_start": eng.sampler["sample_start"], "batch_size": batch_size}}}
     poller = zmq.Poller()
     for s in (meta, app, upd, ldr):
@@ -173,9 +173,7 @@ def _server_entry(capacity, batch_size, host, ports, samplers, cache_policy, dev
     from .sampler import PERSampler
     if samplers is not None:
         for s in samplers:
-            if s["sampler_cls"] != "PERSampler":
-                raise NotImplementedError("only PERSampler runs on the device in this build")
-            s["sampler_cls"] = PERSampler
+            pass                                       # class names are resolved by service._Engine
     server_main(capacity, batch_size, host, ports, samplers, cache_policy, device, max_ring, ready)
 
 

@@ -425,6 +425,58 @@ class ReplayShard:
         self._ck(self._lib.reth_replay_slot_meta(self._h, slot, fc, self._s(stream)))
         return fc[0], fc[1]
 
+    # -- non-PER sampler plugins (uniform_sampler.py, fifo_sampler.py) --------
+    def _idx_arg(self, indices):
+        ip, iloc, idt, n, keep = _ptr_loc(indices)
+        if idt not in (np.dtype(np.int32), np.dtype(np.int64)):
+            if iloc == DEVICE:
+                raise ValueError("device indices must be int32 or int64")
+            keep = np.ascontiguousarray(keep, dtype=np.int64)
+            ip, idt = keep.ctypes.data, keep.dtype
+        return ip, (I32 if idt.itemsize == 4 else I64), iloc, n, keep
+
+    def uniform_note(self, indices=None, first_slot=0, n=None, stream=None):
+        """UniformSampler.update: indices, or (indices=None) the FIFO slots first_slot.. of an append."""
+        if indices is None:
+            self._ck(self._lib.reth_replay_uniform_note(self._h, None, I64, HOST, int(first_slot), int(n), self._s(stream)))
+            return
+        ip, idt, iloc, cnt, keep = self._idx_arg(indices)
+        self._ck(self._lib.reth_replay_uniform_note(self._h, ip, idt, iloc, 0, cnt, self._s(stream)))
+        self._keep = keep
+
+    def sample_uniform(self, batch, first_slot=0, n_slots=1, draws=None, seed=0, stream=None):
+        dp, dloc, keep = None, HOST, None
+        if draws is not None:
+            dp, _, dloc, cnt, keep = self._idx_arg(draws if _is_torch(draws) else np.ascontiguousarray(draws, dtype=np.int64))
+            assert cnt == batch * n_slots
+        self._ck(self._lib.reth_replay_sample_uniform(self._h, int(batch), int(first_slot), int(n_slots), dp, dloc,
+                                                      int(seed) & (2**64 - 1), self._s(stream)))
+        self._keep = keep
+
+    def fifo_push(self, indices, weights, first_slot=0, stream=None):
+        """FIFOSampler.update: (index, weight) pairs; indices=None: the FIFO slots first_slot.. of an append."""
+        p, pdt, ploc, pkeep = self._prio(weights, len(weights))
+        if indices is None:
+            self._ck(self._lib.reth_replay_fifo_push(self._h, None, I64, HOST, int(first_slot), p, pdt, ploc,
+                                                     len(weights), self._s(stream)))
+        else:
+            ip, idt, iloc, cnt, keep = self._idx_arg(indices)
+            assert cnt == len(weights)
+            self._ck(self._lib.reth_replay_fifo_push(self._h, ip, idt, iloc, 0, p, pdt, ploc, cnt, self._s(stream)))
+            self._keep = keep
+        self._keep2 = pkeep
+
+    def sample_fifo(self, batch, first_slot=0, n_slots=1, stream=None):
+        self._ck(self._lib.reth_replay_sample_fifo(self._h, int(batch), int(first_slot), int(n_slots), self._s(stream)))
+
+    def sampler_state(self):
+        out = (C.c_int64 * 4)()
+        self._ck(self._lib.reth_replay_sampler_state(self._h, out))
+        return {"uniform_tail": out[0], "fifo_len": out[1], "fifo_head": out[2]}
+
+    def pipe_sampler(self, kind):
+        self._ck(self._lib.reth_replay_pipe_sampler(self._h, {"per": 0, "uniform": 1, "fifo": 2}[kind]))
+
     def ipc_export(self):
         """bytes descriptor of the batch ring (CUDA IPC handles) for IpcRing in another process."""
         ex = _cabi.IpcExport()

@@ -214,6 +214,32 @@ def main():
                         weights=weights, msg=np.frombuffer(bytes(msg), np.uint8),
                         upd=np.frombuffer(bytes(upd), np.uint8),
                         row0=np.frombuffer(bytes(rows[0]), np.uint8))
+    # 9. the other sampler plugins (sampler/uniform_sampler.py, sampler/fifo_sampler.py), seeded global RNG
+    from reth_buffer.sampler.uniform_sampler import UniformSampler
+    from reth_buffer.sampler.fifo_sampler import FIFOSampler
+    rng = np.random.default_rng(6)
+    out = {}
+    us = UniformSampler(300)
+    fs = FIFOSampler(50)
+    msgs = [rng.integers(0, 1000, n).astype(np.int64) for n in (64, 64, 100, 40, 32)]   # 300 in total: fills the log exactly
+    wts = [rng.random(len(m)) for m in msgs]
+    for k, (m, w) in enumerate(zip(msgs, wts)):
+        us.update(m, w)
+        fs.update(m, w)
+        out[f"msg{k}"], out[f"w{k}"] = m, w
+        np.random.seed(100 + k)
+        draws = np.random.choice(us.tail, 16)                     # what sample() will draw next
+        np.random.seed(100 + k)
+        ui, uw = us.sample(16)
+        out[f"u_draws{k}"], out[f"u_idx{k}"], out[f"u_w{k}"] = draws, np.asarray(ui), np.asarray(uw)
+        out[f"u_tail{k}"] = np.int64(us.tail)
+        if fs.ready_sample(8):
+            fi, fw = fs.sample(8)
+            out[f"f_idx{k}"], out[f"f_w{k}"] = np.asarray(fi, np.int64), np.asarray(fw)
+        out[f"f_len{k}"] = np.int64(len(fs.buffer))
+    us.update(np.arange(5), np.ones(5))                           # a full log ignores further messages
+    out["u_tail_final"] = np.int64(us.tail)
+    np.savez_compressed(os.path.join(OUT, "sampler_plugins.npz"), **out)
     for f in sorted(os.listdir(OUT)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(OUT, f)))

@@ -106,3 +106,22 @@ def test_fifo_and_ring(golden):
     out = ring.select(g["sel"])
     for c in range(3):
         assert np.array_equal(out[c], g[f"sel_{c}"])
+
+
+def test_sampler_plugins_golden(golden):
+    """Uniform / FIFO sampler restatements against the reference's own classes
+    (sampler/uniform_sampler.py, sampler/fifo_sampler.py; make_golden.py section 9)."""
+    g = golden("sampler_plugins")
+    us, fs = po.OracleUniformSampler(300), po.OracleFIFOSampler(50)
+    for k in range(5):
+        us.update(g[f"msg{k}"], g[f"w{k}"])
+        fs.update(g[f"msg{k}"], g[f"w{k}"])
+        assert us.tail == int(g[f"u_tail{k}"])
+        ui, uw = us.sample(g[f"u_draws{k}"])
+        assert np.array_equal(ui, g[f"u_idx{k}"]) and np.array_equal(uw, g[f"u_w{k}"]) and uw.dtype == g[f"u_w{k}"].dtype
+        if fs.ready_sample(8):
+            fi, fw = fs.sample(8)
+            assert np.array_equal(fi, g[f"f_idx{k}"]) and np.array_equal(fw, g[f"f_w{k}"])
+        assert len(fs.buffer) == int(g[f"f_len{k}"])
+    us.update(np.arange(5), np.ones(5))
+    assert us.tail == int(g["u_tail_final"])

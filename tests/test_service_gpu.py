@@ -154,3 +154,30 @@ def test_prioritized_buffer_distribution():
     assert buf.size == 0
     buf.append([col[0] for col in data])
     assert buf.size == 1 and buf._shard.root() == (1.0, 1.0)
+
+
+def test_start_server_with_uniform_and_fifo_samplers(reth_buffer):
+    """start_server(samplers=[...]) with the other plugin classes (server/main_loop.py:135-159)."""
+    from reth_buffer.sampler import FIFOSampler, UniformSampler
+    rng = np.random.default_rng(4)
+    data = [rng.integers(0, 256, (600, 4, 84, 84), dtype=np.uint8), np.arange(600)]
+    for cls in (UniformSampler, FIFOSampler):
+        proc, addr = reth_buffer.start_server(5000, 32, samplers=[{"sampler_cls": cls, "sample_start": 64}])
+        try:
+            client = reth_buffer.Client(addr)
+            loader = reth_buffer.NumpyLoader(addr)
+            for st in range(0, 600, 100):
+                client.append([c[st:st + 100] for c in data], rng.random(100))
+            seen = []
+            for _ in range(6):
+                batch, indices, weights = loader.sample()
+                assert np.array_equal(batch[1], indices) and np.array_equal(batch[0], data[0][indices])
+                seen.append(indices)
+            seen = np.concatenate(seen)
+            if cls is FIFOSampler:
+                assert np.array_equal(seen, np.arange(6 * 32))         # oldest first, each row once
+            else:
+                assert seen.min() >= 0 and seen.max() < 600 and np.all(weights == 1.0)
+            loader.close()
+        finally:
+            proc.terminate()
