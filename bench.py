@@ -417,9 +417,10 @@ def run_ours(args):
                      "kernel": "row_move_kernel<false> (frame gather)", "rows_per_launch": rows_per_launch,
                      "algorithmic_bytes_per_launch": 2 * rows_per_launch * ROW_BYTES, "avg_launch_us": gather_us,
                      "launches_timed": int(gt_n),
-                     "how": "CUDA events around every gather launch on its own stream, in a second pass of the same "
-                            "loop with all gathers on one stream (tree kernels concurrent); the headline loop "
-                            "alternates two gather streams, see hbm_gbs_whole_loop for its aggregate"},
+                     "how": "second pass of the same loop with all gathers on ONE stream (tree kernels concurrent): per "
+                            "bench step one CUDA-event bracket on the gather stream from the first to the last gather "
+                            "launch, divided by the launches it spans (includes the gaps between launches); the "
+                            "headline loop alternates two gather streams, see hbm_gbs_whole_loop for its aggregate"},
         "hbm_gbs_whole_loop": 2 * ROW_BYTES * value / 1e9 / world,
         "strict_alternation": {"value": strict, "unit": "transitions/s", "prefetch_group": 1},
         "append": {"rows_per_s": app_rows, "gbs": app_gbs, "rows_per_call": 16384, "source": "device"},

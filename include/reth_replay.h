@@ -303,7 +303,8 @@ int reth_replay_gather_to(reth_replay_t *h, int slot, reth_ipc_view_t *dst, int 
  *      round-robin.  prio_dev: device float32[steps*batch] new |TD| priorities;
  *      uniforms_dev: device double[steps*batch] or NULL (device generator).
  *      flags bit0: skip gather (tree only); bit1: serialise everything on one stream;
- *      bit2: bracket every gather launch with CUDA events on its own stream (see gather_time);
+ *      bit2: time the gathers with CUDA events on their own stream (see gather_time): one bracket
+ *      around the first..last gather of the call when they share a stream (bit5 or bit1), else one per launch;
  *      bit3 / bit4: skip the sample / the update launch (kernel micro-timing only);
  *      bit5: all gathers on ONE internal stream (default: consecutive gathers alternate between two
  *      streams so the tail of one overlaps the ramp-up of the next; bit2 timings are only per-kernel

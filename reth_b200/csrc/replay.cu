@@ -73,6 +73,7 @@ struct reth_replay {
     long long *dbg = nullptr;           // RETH_DEBUG_TIMING=1: stage clocks of the last update launch
     std::vector<cudaEvent_t> ev_time;   // pairs (start, stop) around timed gather launches
     size_t ev_time_used = 0;
+    int64_t ev_time_launches = 0;       // gather launches covered by the recorded brackets
     // non-PER sampler plugins (allocated on first use)
     int64_t *uni_log = nullptr, *fifo_idx = nullptr;
     double *fifo_w = nullptr;
@@ -1529,7 +1530,12 @@ RETH_EXPORT int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, co
                 CK(h, cudaEventRecord(h->ev_sampled[slot], st));
                 CK(h, cudaStreamWaitEvent(sg, h->ev_sampled[slot], 0));
             }
-            if (timed) {
+            // timing: with all gathers on one stream ONE bracket spans the first..last gather of this call
+            // (a timing event per launch would serialise the stream and stretch every launch); with two
+            // gather streams every launch gets its own bracket
+            const bool span = timed && (one_gather_stream || serial);
+            const bool open_bracket = timed && (!span || k == 0), close_bracket = timed && (!span || k + G >= steps);
+            if (open_bracket) {
                 while (h->ev_time.size() < h->ev_time_used + 2) {
                     cudaEvent_t e;
                     CK(h, cudaEventCreate(&e));
@@ -1539,7 +1545,8 @@ RETH_EXPORT int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, co
             }
             rc = do_gather(h, slot, false, sg, G);
             if (rc) return rc;
-            if (timed) {
+            if (timed) h->ev_time_launches++;
+            if (close_bracket) {
                 CK(h, cudaEventRecord(h->ev_time[h->ev_time_used + 1], sg));
                 h->ev_time_used += 2;
             }
@@ -1577,8 +1584,9 @@ RETH_EXPORT int reth_replay_gather_time(reth_replay_t *h, double *total_ms, int6
         tot += ms;
     }
     if (total_ms) *total_ms = tot;
-    if (launches) *launches = (int64_t)(h->ev_time_used / 2);
+    if (launches) *launches = h->ev_time_launches;
     h->ev_time_used = 0;
+    h->ev_time_launches = 0;
     return RETH_OK;
 }
 
