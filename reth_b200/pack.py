@@ -25,6 +25,7 @@ KEY_COMPRESS = "reth_compress_953531b51ab8"
 KEY_NUMPY = "reth_numpy_356b759ef2b3"
 KEY_BYTES = "reth_bytes_a32b00c47e72"
 KEY_COLUMNAR = "reth_b200_columnar"
+KEY_SHM = "reth_b200_shm"              # [descriptor of columns in a shared-memory ring, weights]
 
 
 class _Body:
@@ -66,33 +67,42 @@ def _describe(obj, body):
 
 
 def encode(obj, compress=False, columnar=False, now=None):
-    """-> bytearray in the reference wire format."""
+    """-> bytes-like (a uint8 numpy buffer) in the reference wire format.  The body segments are
+    copied ONCE, straight into the output buffer."""
     body = _Body()
     meta = _describe(obj, body)
-    raw = bytearray(body.size)
-    at = 0
-    for mv in body.parts:
-        raw[at:at + mv.nbytes] = mv
-        at += mv.nbytes
     header = {}
+    raw = None
     if compress:
         try:
             import lz4.frame
         except ImportError as e:                      # pragma: no cover - lz4 is absent from this image
             raise RuntimeError("compress=True needs the lz4 package") from e
-        raw = lz4.frame.compress(raw, return_bytearray=True)
+        flat = np.empty(body.size, np.uint8)
+        at = 0
+        for mv in body.parts:
+            flat[at:at + mv.nbytes] = np.frombuffer(mv, np.uint8)
+            at += mv.nbytes
+        raw = lz4.frame.compress(flat, return_bytearray=True)
         header[KEY_COMPRESS] = True
     header["meta"] = meta
-    header["body_len"] = len(raw)
+    header["body_len"] = len(raw) if raw is not None else body.size
     header["time"] = time.time() if now is None else now
     if columnar:
         header[KEY_COLUMNAR] = True
     hb = msgpack.packb(header)
-    out = bytearray(4 + len(hb) + len(raw))
-    out[:4] = len(hb).to_bytes(4, "big")
-    out[4:4 + len(hb)] = hb
-    out[4 + len(hb):] = raw
-    return out
+    out = np.empty(4 + len(hb) + header["body_len"], np.uint8)
+    out[:4] = np.frombuffer(len(hb).to_bytes(4, "big"), np.uint8)
+    out[4:4 + len(hb)] = np.frombuffer(hb, np.uint8)
+    at = 4 + len(hb)
+    if raw is not None:
+        out[at:] = np.frombuffer(raw, np.uint8)
+    else:
+        for mv in body.parts:
+            if mv.nbytes:
+                out[at:at + mv.nbytes] = np.frombuffer(mv, np.uint8)
+            at += mv.nbytes
+    return out.data
 
 
 def _split(buf):
@@ -145,6 +155,14 @@ def is_columnar(buf):
     mv = memoryview(buf).cast("B")
     hl = int.from_bytes(mv[:4], "big")
     return bool(msgpack.unpackb(mv[4:4 + hl]).get(KEY_COLUMNAR))
+
+
+def is_shm(buf):
+    """True for an append whose columns sit in a shared-memory ring (service_mp._ShmRing)."""
+    mv = memoryview(buf).cast("B")
+    hl = int.from_bytes(mv[:4], "big")
+    meta = msgpack.unpackb(mv[4:4 + hl])["meta"]
+    return isinstance(meta, list) and len(meta) == 2 and isinstance(meta[0], dict) and KEY_SHM in meta[0]
 
 
 def decode_append(buf):

@@ -27,6 +27,7 @@ import multiprocessing as mp
 import os
 import signal
 import socket
+import sys
 import time
 
 import numpy as np
@@ -70,14 +71,35 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
     ldr.bind(addrs["loader"])
     config = {"engine": "reth_b200", "capacity": capacity, "batch_size": batch_size, "device": device,
               "meta_addr": addrs["meta"], "append_addr": addrs["append"], "update_addr": addrs["update"],
-              "loader_addr": addrs["loader"], "pid": os.getpid(),
+              "loader_addr": addrs["loader"], "pid": os.getpid(), "host_id": _host_id(),
               "sampler_info": {eng.topic: {"topic": eng.topic, "sampler_cls": eng.kind,
                                            "sample_start": eng.sampler["sample_start"], "batch_size": batch_size}}}
     poller = zmq.Poller()
     for s in (meta, app, upd, ldr):
         poller.register(s, zmq.POLLIN)
     waiting = []                 # loader requests parked until the buffer is ready (sampler_loop.py:25-28)
+    segments = {}                # shared-memory ingest rings of same-host clients: name -> _ShmSegment
+    pending = []                 # (cuda event, segment, seq): H2D copies out of a ring still in flight
     ready_evt.set()
+
+    def append_from_ring(head, weights):
+        import torch
+        seg = segments.get(head[pack.KEY_SHM])
+        if seg is None:
+            seg = segments[head[pack.KEY_SHM]] = _ShmSegment(head[pack.KEY_SHM], head["size"], device)
+        cols = [seg.buf[at:at + nb].view(np.dtype(dt)).reshape(sh) for dt, sh, at, nb in head["cols"]]
+        eng.append(cols, weights)
+        if seg.pinned:                                  # the copies run asynchronously out of the ring
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.ExternalStream(eng.stream, device=device))
+            pending.append((ev, seg, int(head["seq"])))
+        else:                                           # pageable source: staged before the call returned
+            seg.consumed[0] = int(head["seq"])
+
+    def retire_ring_copies():
+        while pending and pending[0][0].query():
+            _, seg, seq = pending.pop(0)
+            seg.consumed[0] = seq
 
     def reply(ident, obj, *blobs):
         ldr.send_multipart([ident, b"", json.dumps(obj).encode()] + list(blobs))
@@ -118,15 +140,25 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
 
     try:
         while not stop["flag"]:
-            events = dict(poller.poll(50))
+            events = dict(poller.poll(1 if pending else 50))
             if meta in events:
                 meta.recv()
                 meta.send_json(config)
             # drain every pending write before serving a draw (sampler_loop.py:29-36)
             while app.poll(0):
                 frame = app.recv(copy=False)
-                cols, weights = pack.decode_append(frame.buffer)
-                eng.append(cols, weights)
+                if pack.is_shm(frame.buffer):
+                    head, weights = pack.decode(frame.buffer)
+                    try:
+                        append_from_ring(head, np.asarray(weights))
+                    except FileNotFoundError:          # the producer vanished with its ring: the rows are lost
+                        print(f"reth_b200 server: ingest ring {head[pack.KEY_SHM]} is gone, message dropped",
+                              file=sys.stderr, flush=True)
+                else:
+                    cols, weights = pack.decode_append(frame.buffer)
+                    eng.append(cols, weights)
+                retire_ring_copies()
+            retire_ring_copies()
             while upd.poll(0):
                 frame = upd.recv(copy=False)
                 indices, weights, step = pack.decode(frame.buffer)
@@ -143,8 +175,43 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
                     reply(ident, {"ok": False, "error": f"{type(e).__name__}: {e}"})
     finally:
         eng.close()
+        for seg in segments.values():
+            seg.close()
         for s in (meta, app, upd, ldr):
             s.close(0)
+
+
+class _ShmSegment:
+    """Server side of a client's shared-memory ingest ring: attached once, registered with CUDA so the
+    host->device copies of the rows are true asynchronous DMA out of the ring."""
+
+    def __init__(self, name, size, device):
+        from multiprocessing import resource_tracker, shared_memory
+        self.shm = shared_memory.SharedMemory(name=name)
+        try:                                            # the client owns (and unlinks) the segment
+            resource_tracker.unregister(self.shm._name, "shared_memory")
+        except Exception:
+            pass
+        self.buf = np.frombuffer(self.shm.buf, np.uint8)
+        self.consumed = np.frombuffer(self.shm.buf, np.uint64, count=1)
+        self.pinned = False
+        try:
+            import torch
+            torch.cuda.set_device(device)
+            rc = torch.cuda.cudart().cudaHostRegister(self.buf.ctypes.data, self.buf.nbytes, 0)
+            self.pinned = int(rc) == 0
+        except Exception:
+            self.pinned = False
+
+    def close(self):
+        try:
+            if self.pinned:
+                import torch
+                torch.cuda.cudart().cudaHostUnregister(self.buf.ctypes.data)
+            self.buf = self.consumed = None
+            self.shm.close()
+        except Exception:
+            pass
 
 
 # ------------------------------------------------------------ public surface --
@@ -209,21 +276,118 @@ def get_meta(meta_addr, timeout_ms=30000):
     return res
 
 
-class Client:
-    """client/client.py:8-39 against a server in another process.  wire="columns" (default) sends
-    the columns as they are; wire="rows" sends exactly what the reference's Client sends."""
+def _host_id():
+    """Identifies the machine (same value in every process of one host / container)."""
+    try:
+        with open("/proc/sys/kernel/random/boot_id") as f:
+            return socket.gethostname() + ":" + f.read().strip()
+    except OSError:
+        return socket.gethostname()
 
-    def __init__(self, meta_addr, wire="columns"):
+
+class _ShmRing:
+    """Client side of the shared-memory ingest ring: a POSIX shm segment owned by one client.
+    Bytes 0..7 hold the number of messages the server has finished copying out (written by the
+    server); message bodies are bump-allocated after a 64-byte header and reused once consumed.
+    The reference is an "intra-node shared-mem based" service too (rows live in an LMDB file in
+    /dev/shm, main_loop.py:128-132); here shared memory carries the rows straight to the H2D copy."""
+
+    def __init__(self, size):
+        from multiprocessing import shared_memory
+        self.shm = shared_memory.SharedMemory(create=True, size=int(size))
+        self.buf = np.frombuffer(self.shm.buf, np.uint8)
+        self.consumed = np.frombuffer(self.shm.buf, np.uint64, count=1)
+        self.consumed[0] = 0
+        self.size = int(size)
+        self.cur = 64
+        self.seq = 0                      # messages produced
+        self.inflight = []                # (seq, start, end) not yet known to be consumed
+        self._closed = False
+        import atexit
+        atexit.register(self.close)       # before interpreter teardown: views must go before the mapping
+
+    def _retire(self):
+        done = int(self.consumed[0])
+        self.inflight = [m for m in self.inflight if m[0] > done]
+
+    def reserve(self, nbytes, timeout=120.0):
+        """-> offset of a free contiguous region (blocks while the server still reads an overlapping one)."""
+        nbytes = (int(nbytes) + 63) & ~63
+        if nbytes + 64 > self.size:
+            return None
+        if self.cur + nbytes > self.size:
+            self.cur = 64
+        a, b = self.cur, self.cur + nbytes
+        t0 = time.time()
+        while True:
+            self._retire()
+            if not any(s < b and a < e for _, s, e in self.inflight):
+                break
+            if time.time() - t0 > timeout:
+                raise TimeoutError("shared-memory ingest ring: the server does not drain it")
+            time.sleep(0.0002)
+        self.cur = b
+        self.seq += 1
+        self.inflight.append((self.seq, a, b))
+        return a
+
+    def close(self, timeout=30.0):
+        """Fire-and-forget appends may still sit in the ring: wait until the server has copied them out
+        (or `timeout`), then unlink the segment."""
+        if self._closed:
+            return
+        self._closed = True
+        try:
+            t0 = time.time()
+            while self.consumed is not None and int(self.consumed[0]) < self.seq and time.time() - t0 < timeout:
+                time.sleep(0.001)
+            self.buf = self.consumed = None
+            self.shm.close()
+            self.shm.unlink()
+        except Exception:
+            pass
+
+
+class Client:
+    """client/client.py:8-39 against a server in another process.  wire:
+      "rows"    exactly what the reference's Client sends (one inner message per transition);
+      "columns" the columns as they are, in one ZeroMQ frame;
+      "shm"     same-host fast path: the columns are written once into a shared-memory ring the
+                server copies host->device from, only a small descriptor travels over ZeroMQ;
+      "auto"    (default) "shm" when the server runs on this host, else "columns"."""
+
+    def __init__(self, meta_addr, wire="auto", shm_mb=None):
         import zmq
         self.ctx = zmq.Context.instance()
         self.meta = get_meta(meta_addr)
+        if wire == "auto":
+            wire = "shm" if self.meta.get("host_id") == _host_id() else "columns"
         self.wire = wire
+        self._ring = None
+        self._shm_bytes = int(shm_mb if shm_mb is not None else os.environ.get("RETH_B200_SHM_MB", 512)) << 20
         self.append_sock = self.ctx.socket(zmq.PUSH)
         self.append_sock.set_hwm(ZMQ_DEFAULT_HWM)
         self.append_sock.connect(self.meta["append_addr"])
         self.update_sock = self.ctx.socket(zmq.PUSH)
         self.update_sock.set_hwm(ZMQ_DEFAULT_HWM)
         self.update_sock.connect(self.meta["update_addr"])
+
+    def _append_shm(self, data, weights):
+        if self._ring is None:
+            self._ring = _ShmRing(self._shm_bytes)
+        cols = [np.ascontiguousarray(c) for c in data]
+        total = sum((c.nbytes + 63) & ~63 for c in cols)
+        at = self._ring.reserve(total)
+        if at is None:
+            return False                                      # larger than the ring: fall back to one frame
+        desc = []
+        for c in cols:
+            self._ring.buf[at:at + c.nbytes] = c.reshape(-1).view(np.uint8)
+            desc.append([c.dtype.str, list(c.shape), at, c.nbytes])
+            at += (c.nbytes + 63) & ~63
+        head = {pack.KEY_SHM: self._ring.shm.name, "size": self._ring.size, "seq": self._ring.seq, "cols": desc}
+        self.append_sock.send(pack.encode([head, weights]), copy=False)
+        return True
 
     def append(self, data, weights, compress=False):
         assert isinstance(data, (list, tuple))                # client.py:22
@@ -233,6 +397,8 @@ class Client:
         weights = np.asarray(weights)
         if self.wire == "rows":
             msg = pack.encode_append_rows(data, weights, compress=compress)
+        elif self.wire == "shm" and self._append_shm(data, weights):
+            return
         else:
             msg = pack.encode_append_columns(data, weights)
         self.append_sock.send(msg, copy=False)
@@ -244,6 +410,16 @@ class Client:
     def close(self):
         self.append_sock.close(0)
         self.update_sock.close(0)
+        if self._ring is not None:
+            self._ring.close()
+            self._ring = None
+
+    def __del__(self):
+        try:
+            if self._ring is not None:
+                self._ring.close()
+        except Exception:
+            pass
 
 
 class _RemoteLoader:

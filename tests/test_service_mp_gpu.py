@@ -54,14 +54,17 @@ def test_rb_basic_server_process(reth_buffer):
     assert not rb_proc.is_alive()
 
 
-def test_torch_cuda_loader_ipc(reth_buffer):
+@pytest.mark.parametrize("wire", ["shm", "columns"])
+def test_torch_cuda_loader_ipc(reth_buffer, wire):
     """trainer.py:19-36 shape: TorchCudaLoader in a process other than the server's; the lent CUDA
     tensors are views of the server's batch ring (CUDA IPC) and hold the rows of `indices`."""
     import torch
     B = 64
     proc, addr = reth_buffer.start_per(5000, B, alpha=0.5, beta="0.4,1,2000", sample_start=200)
     try:
-        client = reth_buffer.Client(addr)                     # columnar wire format
+        from reth_b200 import service_mp
+        client = service_mp.Client(addr, wire=wire, shm_mb=8) # 8 MB ring: 64 Atari rows x 2 frames wrap it often
+        assert reth_buffer.Client(addr).wire == "shm"         # same host: the default picks the shared-memory ring
         rng = np.random.default_rng(0)
         s0 = rng.integers(0, 256, (600, 4, 84, 84), dtype=np.uint8)
         cols = [s0, rng.integers(0, 18, 600), rng.standard_normal(600).astype(np.float32), s0[::-1].copy(),
