@@ -18,12 +18,12 @@ def built():
 def _declared():
     text = open(_cabi.HEADER).read()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
-    return sorted(set(re.findall(r"\b(reth_replay_[a-z_]+)\s*\(", text)))
+    return sorted(set(re.findall(r"\b(reth_(?:replay|ipc)_[a-z_]+)\s*\(", text)))
 
 
 def test_header_symbols_exported_and_bound():
     names = _declared()
-    assert len(names) >= 20
+    assert len(names) >= 45 and "reth_ipc_open" in names
     syms = subprocess.check_output(["nm", "-D", "--defined-only", _cabi.LIB_PATH]).decode()
     L = _cabi.lib()
     for n in names:
