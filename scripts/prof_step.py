@@ -7,7 +7,7 @@ from reth_b200 import ReplayShard
 ATARI = [(np.uint8, (4, 84, 84)), (np.int64, ()), (np.float32, ()), (np.uint8, (4, 84, 84)), (np.float32, ())]
 cap = int(os.environ.get("CAP", 1 << 20)); B = int(os.environ.get("B", 512)); steps = int(os.environ.get("STEPS", 20))
 G = int(os.environ.get("GROUP", 1))
-sh = ReplayShard(cap, ATARI, max_batch=B, ring_depth=max(4, 2 * G), update_cluster=int(os.environ.get("CLUSTER", 8)))
+sh = ReplayShard(cap, ATARI, max_batch=B, ring_depth=max(4, 2 * G), update_cluster=int(os.environ.get("CLUSTER", 0)))
 g = torch.Generator(device="cuda").manual_seed(0)
 chunk = 1 << 14
 for st in range(0, cap, chunk):
