@@ -455,10 +455,12 @@ def main():
     ap.add_argument("--batch", type=int, default=512)
     ap.add_argument("--iters", type=int, default=128, help="learner iterations per bench step")
     ap.add_argument("--group", type=int, default=8,
-                    help="prefetch group: batches drawn per launch; with --ahead 1 the lending ring holds 16 batches, the "
-                         "number the reference keeps in flight by default (TorchCudaLoader buffer_size=8 + num_procs=6 "
-                         "worker batches + 2 on the sampler side, torch_cuda_loader.py:70, sampler_loop.py:14)")
-    ap.add_argument("--ahead", type=int, default=1, help="e2e loader: groups drawn ahead of the one being consumed")
+                    help="prefetch group: batches drawn per launch (one draw kernel, one gather launch, one write-back)")
+    ap.add_argument("--ahead", type=int, default=2,
+                    help="e2e loader: groups drawn ahead of the one being consumed; the lending ring holds "
+                         "(ahead + 1) * group batches.  The reference keeps buffer_size + num_procs + 2 batches in "
+                         "flight (TorchCudaLoader ring + one per worker + sampler side: 16 at its defaults, "
+                         "torch_cuda_loader.py:70, sampler_loop.py:14); 8 x (2 + 1) = 24 here, --ahead 1 = 16")
     ap.add_argument("--cpu-steps", type=int, default=24)
     ap.add_argument("--cpu-iters", type=int, default=64, help="iterations per step of the CPU arm (bounded sample)")
     ap.add_argument("--no-cpu", action="store_true")

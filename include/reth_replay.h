@@ -257,7 +257,9 @@ int reth_replay_pipe_stream(reth_replay_t *h, void **stream_out);
 int reth_replay_pipe_issue(reth_replay_t *h, double beta);
 /* group_out: group slot g -> batch slots g*group .. g*group+group-1, host rows idx_host[g], w_host[g] */
 int reth_replay_pipe_wait(reth_replay_t *h, int32_t *group_out);
-/* pipe_wait() of the oldest group followed by pipe_issue() of a new one, in one call */
+/* steady-state call: hands the lent group back, pipe_issue()s a new group into its slots and then
+ * pipe_wait()s for the oldest group in flight.  Issuing BEFORE blocking keeps a draw + gather
+ * queued behind the group in flight, so the device does not idle while the host wakes up. */
 int reth_replay_pipe_next(reth_replay_t *h, double beta, int32_t *group_out);
 int reth_replay_pipe_update_begin(reth_replay_t *h, int32_t *entry_out);
 int reth_replay_pipe_update_commit(reth_replay_t *h, int entry, int64_t n, int prio_dtype, double alpha,

@@ -1145,11 +1145,13 @@ void pipe_free(reth_replay *h)
     p = reth_replay::Pipe();
 }
 
-int pipe_issue(reth_replay *h, double beta)
+// give_up_lent: the caller hands the lent group back with this call (pipe_next), so its slots may
+// be drawn into before the wait for the next delivery -- the device then never idles between groups.
+int pipe_issue(reth_replay *h, double beta, bool give_up_lent = false)
 {
     auto &p = h->pipe;
     if (!p.open) return fail(h, RETH_ERR_STATE, "no pipe is open");
-    if (p.issued - p.waited + (p.waited > 0 ? 1 : 0) >= p.n_groups)
+    if (p.issued - p.waited + (p.waited > 0 && !give_up_lent ? 1 : 0) >= p.n_groups)
         return fail(h, RETH_ERR_STATE, "all %d group slots are issued or lent", p.n_groups);
     const int g = (int)(p.issued % p.n_groups), slot = g * p.G;
     int rc;
@@ -1277,9 +1279,14 @@ RETH_EXPORT int reth_replay_pipe_next(reth_replay_t *h, double beta, int32_t *gr
 {
     if (!h) return RETH_ERR_INVALID;
     DeviceGuard guard(h->cfg.device);
-    int rc = pipe_wait(h, group_out);
+    auto &p = h->pipe;
+    if (!p.open) return fail(h, RETH_ERR_STATE, "no pipe is open");
+    if (p.issued <= p.waited) return fail(h, RETH_ERR_STATE, "pipe_next: no group has been issued");
+    // the group lent so far is handed back by this call: draw into its slots FIRST, so that the new
+    // draw + gather queue up behind the group in flight, and only then block for the delivery
+    int rc = pipe_issue(h, beta, true);
     if (rc) return rc;
-    return pipe_issue(h, beta);
+    return pipe_wait(h, group_out);
 }
 
 RETH_EXPORT int reth_replay_pipe_update_begin(reth_replay_t *h, int32_t *entry_out)
