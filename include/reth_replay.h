@@ -324,6 +324,19 @@ int reth_replay_gather_time(reth_replay_t *h, double *total_ms, int64_t *launche
  * tree-repair launch; needs RETH_DEBUG_TIMING=1 in the environment at create time. */
 int reth_replay_debug_stamps(reth_replay_t *h, int64_t *out);
 
+/* ---- lz4 frame codec of the ingest wire format (host code, no handle).
+ *      The reference's actors send compress=True bodies (test/apex-dqn/worker.py:60 ->
+ *      utils/pack.py:63-84 lz4.frame.compress) and the server undoes them (utils/pack.py:152-156
+ *      lz4.frame.decompress).  These replace the two calls of the `lz4` package (absent here):
+ *      any conforming LZ4 frame is decoded (linked or independent blocks, optional checksums,
+ *      skippable and concatenated frames); the compressor writes independent 64 KB blocks with the
+ *      content size stored.  All four return a byte count, or a negative value:
+ *      -1 truncated, -2 malformed, -3 checksum mismatch, -4 output too small, -5 dictionary id. */
+int64_t reth_lz4f_content_size(const void *src, int64_t n);   /* -1: the frame does not store it */
+int64_t reth_lz4f_decompress(const void *src, int64_t n, void *dst, int64_t cap);
+int64_t reth_lz4f_compress_bound(int64_t n);
+int64_t reth_lz4f_compress(const void *src, int64_t n, void *dst, int64_t cap);
+
 #ifdef __cplusplus
 }
 #endif

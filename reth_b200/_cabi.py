@@ -128,6 +128,14 @@ SIGNATURES = {
 _lib = None
 
 
+LZ4F_SIGNATURES = {                      # return a byte count (int64) or a negative error
+    "reth_lz4f_content_size": [_vp, _i64],
+    "reth_lz4f_decompress": [_vp, _i64, _vp, _i64],
+    "reth_lz4f_compress_bound": [_i64],
+    "reth_lz4f_compress": [_vp, _i64, _vp, _i64],
+}
+
+
 def lib():
     """Load the C-ABI library; raises if it has not been built (no fallback)."""
     global _lib
@@ -144,6 +152,10 @@ def lib():
         fn.restype = C.c_int
     L.reth_replay_last_error.argtypes = [_vp]
     L.reth_replay_last_error.restype = C.c_char_p
+    for name, args in LZ4F_SIGNATURES.items():
+        fn = getattr(L, name)
+        fn.argtypes = args
+        fn.restype = C.c_int64
     _lib = L
     return L
 

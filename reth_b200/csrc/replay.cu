@@ -11,6 +11,7 @@
 
 #include "../../include/reth_replay.h"
 #include "copy.cuh"
+#include "lz4f.h"
 #include "tree.cuh"
 
 using namespace reth;
@@ -166,6 +167,24 @@ void free_all(reth_replay *h)
 }  // namespace
 
 RETH_EXPORT int reth_replay_abi_version(void) { return 2; }
+
+// lz4 frame codec (host code, lz4f.h)
+RETH_EXPORT int64_t reth_lz4f_content_size(const void *src, int64_t n)
+{
+    if (!src || n < 0) return lz4f::kErrFormat;
+    return lz4f::content_size((const uint8_t *)src, n);
+}
+RETH_EXPORT int64_t reth_lz4f_decompress(const void *src, int64_t n, void *dst, int64_t cap)
+{
+    if (!src || n < 0 || cap < 0 || (!dst && cap > 0)) return lz4f::kErrFormat;
+    return lz4f::decompress((const uint8_t *)src, n, (uint8_t *)dst, cap);
+}
+RETH_EXPORT int64_t reth_lz4f_compress_bound(int64_t n) { return n < 0 ? lz4f::kErrFormat : lz4f::compress_bound(n); }
+RETH_EXPORT int64_t reth_lz4f_compress(const void *src, int64_t n, void *dst, int64_t cap)
+{
+    if (n < 0 || (!src && n > 0) || !dst) return lz4f::kErrFormat;
+    return lz4f::compress((const uint8_t *)src, n, (uint8_t *)dst, cap);
+}
 
 RETH_EXPORT const char *reth_replay_last_error(const reth_replay_t *h)
 {

@@ -8,7 +8,10 @@ that actors built against the reference can feed this server unchanged:
     <tree> mirrors the python object; an ndarray becomes
         {KEY_NUMPY: True, "header": {"shape","fortran_order","descr"}, "raw_size", "offset", "length"}
     and a bytes-like becomes {KEY_BYTES: True, "raw_size", "offset", "length"}; offset/length
-    address the body.  An lz4-framed body is flagged by KEY_COMPRESS (utils/pack.py:67-84).
+    address the body.  An lz4-framed body is flagged by KEY_COMPRESS (utils/pack.py:67-84); the
+    reference's actors use it (test/apex-dqn/worker.py:60).  The frame codec is the `lz4` package
+    when it is installed, else the C implementation in this build's library
+    (reth_lz4f_*, include/reth_replay.h; reth_b200/csrc/lz4f.h).
 
 Client.append sends  encode([[encode(row_0), ..., encode(row_n-1)], weights])  with one inner
 message per transition (client/client.py:26-35); `decode_append` turns that back into columns
@@ -26,6 +29,55 @@ KEY_NUMPY = "reth_numpy_356b759ef2b3"
 KEY_BYTES = "reth_bytes_a32b00c47e72"
 KEY_COLUMNAR = "reth_b200_columnar"
 KEY_SHM = "reth_b200_shm"              # [descriptor of columns in a shared-memory ring, weights]
+
+
+def _native():
+    from . import _cabi
+    return _cabi.lib()
+
+
+def lz4_compress(buf):
+    """lz4.frame.compress(buf) (utils/pack.py:69) -> uint8 array holding one LZ4 frame."""
+    try:
+        import lz4.frame
+        return np.frombuffer(lz4.frame.compress(buf, return_bytearray=True), np.uint8)
+    except ImportError:
+        pass
+    src = np.ascontiguousarray(np.frombuffer(buf, np.uint8))
+    L = _native()
+    out = np.empty(L.reth_lz4f_compress_bound(src.size), np.uint8)
+    n = L.reth_lz4f_compress(src.ctypes.data, src.size, out.ctypes.data, out.size)
+    if n < 0:
+        raise ValueError(f"lz4 frame compression failed ({n})")
+    return out[:n]
+
+
+_LZ4F_ERR = {-1: "truncated frame", -2: "malformed frame", -3: "checksum mismatch", -4: "output too small",
+             -5: "frames with a dictionary id are not supported"}
+
+
+def lz4_decompress(buf):
+    """lz4.frame.decompress(buf) (utils/pack.py:155) -> uint8 array."""
+    try:
+        import lz4.frame
+        return np.frombuffer(lz4.frame.decompress(buf, return_bytearray=True), np.uint8)
+    except ImportError:
+        pass
+    src = np.ascontiguousarray(np.frombuffer(buf, np.uint8))
+    L = _native()
+    size = L.reth_lz4f_content_size(src.ctypes.data, src.size)
+    if size < -1:
+        raise ValueError(f"lz4 frame: {_LZ4F_ERR.get(size, size)}")
+    cap = size if size >= 0 else max(4 * src.size, 1 << 16)
+    while True:
+        out = np.empty(cap, np.uint8)
+        n = L.reth_lz4f_decompress(src.ctypes.data, src.size, out.ctypes.data, cap)
+        if n == -4 and cap < (1 << 40):                       # size not stored / concatenated frames: grow
+            cap = max(4 * cap, 1 << 16)
+            continue
+        if n < 0:
+            raise ValueError(f"lz4 frame: {_LZ4F_ERR.get(n, n)}")
+        return out[:n]
 
 
 class _Body:
@@ -74,16 +126,12 @@ def encode(obj, compress=False, columnar=False, now=None):
     header = {}
     raw = None
     if compress:
-        try:
-            import lz4.frame
-        except ImportError as e:                      # pragma: no cover - lz4 is absent from this image
-            raise RuntimeError("compress=True needs the lz4 package") from e
         flat = np.empty(body.size, np.uint8)
         at = 0
         for mv in body.parts:
             flat[at:at + mv.nbytes] = np.frombuffer(mv, np.uint8)
             at += mv.nbytes
-        raw = lz4.frame.compress(flat, return_bytearray=True)
+        raw = lz4_compress(flat)
         header[KEY_COMPRESS] = True
     header["meta"] = meta
     header["body_len"] = len(raw) if raw is not None else body.size
@@ -113,11 +161,7 @@ def _split(buf):
     if body.nbytes != header["body_len"]:
         raise ValueError("truncated message: body_len does not match")
     if header.get(KEY_COMPRESS):
-        try:
-            import lz4.frame
-        except ImportError as e:
-            raise RuntimeError("received an lz4-compressed message but the lz4 package is not installed") from e
-        body = memoryview(lz4.frame.decompress(body, return_bytearray=True))
+        body = memoryview(lz4_decompress(body))
     return header, body, 4 + hl
 
 
@@ -214,5 +258,5 @@ def encode_append_rows(columns, weights, compress=False, now=None):
     return encode([rows, weights], compress=compress, now=now)
 
 
-def encode_append_columns(columns, weights, now=None):
-    return encode([list(columns), weights], columnar=True, now=now)
+def encode_append_columns(columns, weights, compress=False, now=None):
+    return encode([list(columns), weights], compress=compress, columnar=True, now=now)

@@ -398,9 +398,9 @@ class Client:
         if self.wire == "rows":
             msg = pack.encode_append_rows(data, weights, compress=compress)
         elif self.wire == "shm" and self._append_shm(data, weights):
-            return
+            return                                            # same host: nothing to gain from compress
         else:
-            msg = pack.encode_append_columns(data, weights)
+            msg = pack.encode_append_columns(data, weights, compress=compress)
         self.append_sock.send(msg, copy=False)
 
     def update_priorities(self, indices, weights, step=True):

@@ -18,18 +18,18 @@ def built():
 def _declared():
     text = open(_cabi.HEADER).read()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
-    return sorted(set(re.findall(r"\b(reth_(?:replay|ipc)_[a-z_]+)\s*\(", text)))
+    return sorted(set(re.findall(r"\b(reth_(?:replay|ipc|lz4f)_[a-z0-9_]+)\s*\(", text)))
 
 
 def test_header_symbols_exported_and_bound():
     names = _declared()
-    assert len(names) >= 45 and "reth_ipc_open" in names
+    assert len(names) >= 49 and "reth_ipc_open" in names and "reth_lz4f_decompress" in names
     syms = subprocess.check_output(["nm", "-D", "--defined-only", _cabi.LIB_PATH]).decode()
     L = _cabi.lib()
     for n in names:
         assert re.search(rf"\bT {n}\b", syms), f"{n} not exported"
         assert hasattr(L, n)
-        assert n in _cabi.SIGNATURES or n == "reth_replay_last_error", f"{n} has no ctypes signature"
+        assert n in _cabi.SIGNATURES or n in _cabi.LZ4F_SIGNATURES or n == "reth_replay_last_error", f"{n} has no ctypes signature"
     assert L.reth_replay_abi_version() == 2
 
 

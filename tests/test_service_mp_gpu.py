@@ -23,8 +23,10 @@ def reth_buffer():
     sys.path.remove(os.path.join(ROOT, "reth_b200", "compat"))
 
 
-def test_rb_basic_server_process(reth_buffer):
-    """test_rb.py:12-35 against a spawned server; append in the reference's ROW wire format."""
+@pytest.mark.parametrize("compress", [False, True])
+def test_rb_basic_server_process(reth_buffer, compress):
+    """test_rb.py:12-35 against a spawned server; append in the reference's ROW wire format, plain
+    and with the lz4-framed body the Ape-X workers send (worker.py:60 compress=True)."""
     from reth_b200 import service_mp
     CAPACITY, BATCH_SIZE = 100000, 32
     rb_proc, addr = reth_buffer.start_server(CAPACITY, BATCH_SIZE)
@@ -36,7 +38,7 @@ def test_rb_basic_server_process(reth_buffer):
         buf_weights = np.random.rand(1000) + 1
         for start in range(0, 1000, 100):
             batch = [x[start:start + 100] for x in data]
-            client.append(batch, buf_weights[start:start + 100])
+            client.append(batch, buf_weights[start:start + 100], compress=compress)
         for _ in range(10):
             batch, indices, weights = loader.sample()
             assert indices.dtype == np.int64 and weights.dtype == np.float64
