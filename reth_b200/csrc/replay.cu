@@ -29,6 +29,7 @@ struct BatchSlot {
     double *prio = nullptr;
     int64_t *meta = nullptr;   // {first, count}
     int32_t batch = 0;
+    bool partial = false;      // Mode G draw: only meta[1] of the `batch` entries belong to this shard
 };
 
 }  // namespace
@@ -375,6 +376,7 @@ int launch_update(reth_replay *h, UpdateArgs &a, cudaStream_t s)
     const size_t is = a.idx_kind == 0 ? 8 : 4, ps = a.prio_kind == 0 ? 4 : 8;
     for (int64_t off = 0; off < n; off += per) {
         a.n = n - off < per ? n - off : per;
+        a.n_off = off;
         a.stamp_base = (uint32_t)off;
         if (a.idx_kind != 2) a.idx = idx0 + off * is;
         if (a.prio_kind != 2) a.prio = prio0 + off * ps;
@@ -564,6 +566,7 @@ RETH_EXPORT int reth_replay_update_slot(reth_replay_t *h, int slot, const void *
     if (b.batch <= 0) return fail(h, RETH_ERR_STATE, "slot %d holds no sampled batch", slot);
     UpdateArgs a = {};
     a.n = b.batch; a.idx = b.idx; a.idx_kind = 0;
+    if (b.partial) a.n_dev = b.meta + 1;                      // Mode G: this shard's share of the global batch
     a.alpha = alpha; a.transform = transform; a.dedupe = 2;   // own stratified draw: duplicates are adjacent
     int rc = set_prio(h, a, prio, prio_dtype, prio_loc, 0, b.batch, S(stream));
     if (rc) return rc;
@@ -707,7 +710,7 @@ int do_sample(reth_replay *h, int batch, const double *uniforms, int uniforms_lo
     CK(h, cudaGetLastError());
     h->st.kernel_launches++;
     h->st.sampled_rows += (int64_t)batch * groups;
-    for (int g = 0; g < groups; ++g) h->slots[slot + g].batch = batch;
+    for (int g = 0; g < groups; ++g) { h->slots[slot + g].batch = batch; h->slots[slot + g].partial = n_shards > 1; }
     return RETH_OK;
 }
 
@@ -1030,7 +1033,7 @@ int pick_into_slots(reth_replay *h, PickArgs &a, int batch, int first_slot, int 
     CK(h, cudaGetLastError());
     h->st.kernel_launches++;
     h->st.sampled_rows += a.n;
-    for (int g = 0; g < n_slots; ++g) h->slots[first_slot + g].batch = batch;
+    for (int g = 0; g < n_slots; ++g) { h->slots[first_slot + g].batch = batch; h->slots[first_slot + g].partial = false; }
     return RETH_OK;
 }
 

@@ -217,6 +217,8 @@ struct UpdateArgs {
     int32_t *counts_next; // [kMaxTileLevels] zeroed for the next call
     int32_t *err;
     int64_t n;            // <= cluster size * kUpdateThreads (the host chunks larger batches)
+    const int64_t *n_dev; // optional: the entry count lives on the device (Mode G slot); this launch
+    int64_t n_off;        //           covers entries [n_off, min(n_off + n, *n_dev))
     uint32_t stamp_base;  // entry i carries stamp 1 + stamp_base + i (chunks of one batch keep batch order)
     const void *idx;
     int32_t idx_kind;     // 0 int64[], 1 int32[], 2 iota: (iota_base + i) % capacity
@@ -412,11 +414,16 @@ __global__ void __launch_bounds__(kUpdateThreads) per_update_kernel(const Update
     RETH_STAMP(0);
     if (brank == 0 && threadIdx.x < kMaxTileLevels) a.counts_next[threadIdx.x] = 0;
     // every load that does not depend on another is issued up front
-    const bool inrange = i < a.n;
+    int64_t n = a.n;
+    if (a.n_dev) {
+        const int64_t m = __ldcg(a.n_dev) - a.n_off;
+        n = m < n ? (m < 0 ? 0 : m) : n;
+    }
+    const bool inrange = i < n;
     int64_t idx = 0, nxt = -1;
     double raw = 0.0;
     if (inrange) { idx = upd_index(a, i); raw = upd_prio_load(a, i); }
-    if (a.dedupe == 2 && i + 1 < a.n) nxt = upd_index(a, i + 1);
+    if (a.dedupe == 2 && i + 1 < n) nxt = upd_index(a, i + 1);
     bool active = inrange;
     if (active && (idx < 0 || idx >= cap)) { atomicOr(a.err, 1); active = false; }
     const uint32_t my_stamp = 1u + a.stamp_base + (uint32_t)i;

@@ -15,8 +15,12 @@ R = 56464
 rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
 torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-cap = int(os.environ.get("CAP", 1 << 18)); GB = int(os.environ.get("GB", 4096)); steps = int(os.environ.get("STEPS", 200))
-sh = ReplayShard(cap, ATARI, max_batch=GB, ring_depth=4, device=local)
+cap = int(os.environ.get("CAP", 1 << 18)); steps = int(os.environ.get("STEPS", 200))
+# CASES: comma-separated mode:global_batch.  assemble = single learner on rank 0 (slices travel over
+# NVLink); local = data-parallel learners, each rank consumes its own slice (gather + write-back stay local)
+CASES = [(c.split(":")[0], int(c.split(":")[1])) for c in os.environ.get("CASES", "assemble:4096").split(",")]
+GBMAX = max(gb for _, gb in CASES)
+sh = ReplayShard(cap, ATARI, max_batch=GBMAX, ring_depth=4, device=local)
 g = torch.Generator(device="cuda").manual_seed(rank)
 for st in range(0, cap, 1 << 14):
     n = min(1 << 14, cap - st)
@@ -26,30 +30,41 @@ for st in range(0, cap, 1 << 14):
 torch.cuda.synchronize()
 sg = ShardGroup(sh)
 sg.connect_learner(0)
+newp = torch.rand(GBMAX, device="cuda", generator=g) + 0.01
 
-def step(k):
+for mode, GB in CASES:
+    def step(k):
+        sg.exchange_roots()
+        sh.sample_global(GB, sg.all_roots, world, rank, beta=0.4, seed=7, slot=k % 2)
+        if mode == "assemble":
+            sg.assemble(slot=k % 2, dst_slot=2 + k % 2)
+        else:
+            sh.gather(k % 2)
+            sh.update_slot(k % 2, newp[:GB], alpha=0.6)
+
+    for k in range(10):
+        step(k)
     sg.exchange_roots()
-    sh.sample_global(GB, sg.all_roots, world, rank, beta=0.4, seed=7, slot=k % 2)
-    sg.assemble(slot=k % 2, dst_slot=2 + k % 2)
-
-for k in range(10):
-    step(k)
-sg.exchange_roots()
-torch.cuda.synchronize(); dist.barrier()
-e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-e0.record()
-for k in range(steps):
-    step(k)
-sg.exchange_roots()
-e1.record()
-torch.cuda.synchronize()
-ms = torch.tensor([e0.elapsed_time(e1)], device="cuda", dtype=torch.float64)
-dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-if rank == 0:
-    us = float(ms.item()) * 1e3 / steps
-    remote = GB * (world - 1) / world * R
-    print(json.dumps({"n_gpus": world, "global_batch": GB, "us_per_global_batch": us,
-                      "transitions_per_s": GB / us * 1e6, "nvlink_payload_GBps_into_learner": remote / us / 1e3,
-                      "note": "every rank gathers its slice straight into rank 0's batch ring (peer stores from the gather kernel)"}))
+    torch.cuda.synchronize(); dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for k in range(steps):
+        step(k)
+    sg.exchange_roots()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1)], device="cuda", dtype=torch.float64)
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        us = float(ms.item()) * 1e3 / steps
+        out = {"n_gpus": world, "mode": mode, "global_batch": GB, "capacity_per_shard": cap, "us_per_global_batch": us,
+               "transitions_per_s": GB / us * 1e6}
+        if mode == "assemble":
+            out["nvlink_payload_GBps_into_learner"] = GB * (world - 1) / world * R / us / 1e3
+            out["note"] = "every rank gathers its slice straight into rank 0's batch ring (peer stores from the gather kernel)"
+        else:
+            out["note"] = ("per step: all-gather of shard roots, draw of this shard's share of the global stratified batch, "
+                           "local gather, priority write-back of the share")
+        print(json.dumps(out), flush=True)
 dist.barrier()
 dist.destroy_process_group()

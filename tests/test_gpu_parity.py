@@ -333,6 +333,53 @@ def test_global_mode_vs_oracle(Shard, n_shards):
         sh.close()
 
 
+def test_global_mode_learner_loop_update_slot(Shard):
+    """Mode G learner loop: every step the shard roots are re-read, each shard draws its share of the
+    global batch and writes new priorities back with update_slot -- which must touch only the
+    `count` entries of the slot that belong to the shard (the rest of the slot is stale)."""
+    import torch
+    cap, B, n_shards = 3000, 512, 3
+    rng = np.random.default_rng(5)
+    shards, trees = [], []
+    for g in range(n_shards):
+        sh = Shard(cap, [], max_batch=B, store_rows=False)
+        t = po.OracleSumTree(cap)
+        p = rng.random(cap) * (1 + 5 * g) + 0.01
+        sh.update(np.arange(cap), p, transform=False)
+        t.update(np.arange(cap), p)
+        shards.append(sh)
+        trees.append(t)
+    for sh in shards:                                    # a stale full-size local draw in both slots
+        sh.sample(B, uniforms=rng.random(B), slot=0)
+        sh.sample(B, uniforms=rng.random(B), slot=1)
+    for step in range(6):
+        torch.cuda.synchronize()
+        roots = torch.cat([torch.as_tensor(sh.root_dev(), device="cuda").clone() for sh in shards])
+        u = rng.random(B)
+        newp = rng.random(B) * 4 + 0.01
+        for g, sh in enumerate(shards):
+            sh.sample_global(B, roots, n_shards, g, beta=0.5, uniforms=u, slot=step % 2)
+            ofirst, oidx, ow, _ = po.global_sample(trees, g, B, u, 0.5)
+            first, count = sh.slot_meta(step % 2)
+            assert (first, count) == (ofirst, len(oidx))
+        for g, sh in enumerate(shards):                  # write-back after every shard has drawn
+            ofirst, oidx, _, _ = po.global_sample(trees, g, B, u, 0.5)
+            mine = np.zeros(B)
+            mine[:len(oidx)] = newp[ofirst:ofirst + len(oidx)]
+            sh.update_slot(step % 2, mine, transform=False)
+        # oracle write-back (indices recomputed before any oracle tree changes)
+        draws = [po.global_sample(trees, g, B, u, 0.5) for g in range(n_shards)]
+        for g, (ofirst, oidx, _, _) in enumerate(draws):
+            trees[g].update(oidx, newp[ofirst:ofirst + len(oidx)])
+        for g, sh in enumerate(shards):
+            s_, m_, v_ = sh.tree_arrays()
+            assert np.array_equal(v_, trees[g]._val), (step, g)
+            assert np.array_equal(s_, trees[g]._sum), (step, g)
+            assert np.array_equal(m_, trees[g]._min), (step, g)
+    for sh in shards:
+        sh.close()
+
+
 def test_config4_learner_loop_with_actor_streams(Shard):
     """BASELINE config 4 shape (scaled): per learner step 256 actor messages of 64 rows are appended
     (the ring wraps every 4 steps), then one batch of 512 is drawn and written back; alpha 0.5,
