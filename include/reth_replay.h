@@ -261,6 +261,14 @@ int reth_replay_pipe_wait(reth_replay_t *h, int32_t *group_out);
  * pipe_wait()s for the oldest group in flight.  Issuing BEFORE blocking keeps a draw + gather
  * queued behind the group in flight, so the device does not idle while the host wakes up. */
 int reth_replay_pipe_next(reth_replay_t *h, double beta, int32_t *group_out);
+/* Lending depth: the newest `groups` delivered groups stay valid (default 1; call before the first
+ * pipe_issue).  A consumer in ANOTHER process asks for group k+1 when it starts on group k, so the
+ * request that reaches the owner hands back group k-1: two groups are lent at a time there. */
+int reth_replay_pipe_hold(reth_replay_t *h, int groups);
+/* hand the oldest lent group back and pipe_issue() a new group into its slots; does not block */
+int reth_replay_pipe_advance(reth_replay_t *h, double beta);
+/* *ready_out = 1 when pipe_wait() would return without blocking */
+int reth_replay_pipe_ready(reth_replay_t *h, int32_t *ready_out);
 int reth_replay_pipe_update_begin(reth_replay_t *h, int32_t *entry_out);
 int reth_replay_pipe_update_commit(reth_replay_t *h, int entry, int64_t n, int prio_dtype, double alpha,
                                    int transform);

@@ -111,6 +111,9 @@ SIGNATURES = {
     "reth_replay_pipe_issue": [_vp, _f64],
     "reth_replay_pipe_wait": [_vp, C.POINTER(C.c_int32)],
     "reth_replay_pipe_next": [_vp, _f64, C.POINTER(C.c_int32)],
+    "reth_replay_pipe_hold": [_vp, _i32],
+    "reth_replay_pipe_advance": [_vp, _f64],
+    "reth_replay_pipe_ready": [_vp, C.POINTER(_i32)],
     "reth_replay_pipe_update_begin": [_vp, C.POINTER(C.c_int32)],
     "reth_replay_pipe_update_commit": [_vp, _i32, _i64, _i32, _f64, _i32],
     "reth_replay_update_async": [_vp, _vp, _vp, _i32, _i64, _f64, _i32],

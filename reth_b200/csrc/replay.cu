@@ -96,6 +96,7 @@ struct reth_replay {
         std::vector<cudaEvent_t> ev_smp, ev_gat, ev_done, ev_upd;
         std::vector<char> upd_used;
         int64_t issued = 0, waited = 0, upd_next = 0;
+        int hold = 1;             // delivered groups that stay lent (the newest `hold` of them)
     } pipe;
     std::string error;
 };
@@ -1173,7 +1174,9 @@ int pipe_issue(reth_replay *h, double beta, bool give_up_lent = false)
 {
     auto &p = h->pipe;
     if (!p.open) return fail(h, RETH_ERR_STATE, "no pipe is open");
-    if (p.issued - p.waited + (p.waited > 0 && !give_up_lent ? 1 : 0) >= p.n_groups)
+    int64_t lent = p.waited < p.hold ? p.waited : p.hold;
+    if (give_up_lent && lent == p.hold) lent -= 1;          // fewer delivered than `hold`: nothing to hand back yet
+    if (p.issued - p.waited + lent >= p.n_groups)
         return fail(h, RETH_ERR_STATE, "all %d group slots are issued or lent", p.n_groups);
     const int g = (int)(p.issued % p.n_groups), slot = g * p.G;
     int rc;
@@ -1309,6 +1312,38 @@ RETH_EXPORT int reth_replay_pipe_next(reth_replay_t *h, double beta, int32_t *gr
     int rc = pipe_issue(h, beta, true);
     if (rc) return rc;
     return pipe_wait(h, group_out);
+}
+
+RETH_EXPORT int reth_replay_pipe_hold(reth_replay_t *h, int groups)
+{
+    if (!h) return RETH_ERR_INVALID;
+    auto &p = h->pipe;
+    if (!p.open) return fail(h, RETH_ERR_STATE, "no pipe is open");
+    if (groups < 1 || groups >= p.n_groups) return fail(h, RETH_ERR_INVALID, "hold %d outside [1, n_groups - 1 = %d]", groups, p.n_groups - 1);
+    if (p.issued) return fail(h, RETH_ERR_STATE, "pipe_hold must precede the first pipe_issue");
+    p.hold = groups;
+    return RETH_OK;
+}
+
+RETH_EXPORT int reth_replay_pipe_advance(reth_replay_t *h, double beta)
+{
+    if (!h) return RETH_ERR_INVALID;
+    DeviceGuard guard(h->cfg.device);
+    return pipe_issue(h, beta, true);
+}
+
+RETH_EXPORT int reth_replay_pipe_ready(reth_replay_t *h, int32_t *ready_out)
+{
+    if (!h || !ready_out) return RETH_ERR_INVALID;
+    auto &p = h->pipe;
+    if (!p.open) return fail(h, RETH_ERR_STATE, "no pipe is open");
+    *ready_out = 0;
+    if (p.issued <= p.waited) return RETH_OK;
+    DeviceGuard guard(h->cfg.device);
+    const cudaError_t e = cudaEventQuery(p.ev_done[p.waited % p.n_groups]);
+    if (e == cudaSuccess) *ready_out = 1;
+    else if (e != cudaErrorNotReady) return fail(h, RETH_ERR_CUDA, "cudaEventQuery: %s", cudaGetErrorString(e));
+    return RETH_OK;
 }
 
 RETH_EXPORT int reth_replay_pipe_update_begin(reth_replay_t *h, int32_t *entry_out)

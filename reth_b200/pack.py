@@ -29,6 +29,8 @@ KEY_NUMPY = "reth_numpy_356b759ef2b3"
 KEY_BYTES = "reth_bytes_a32b00c47e72"
 KEY_COLUMNAR = "reth_b200_columnar"
 KEY_SHM = "reth_b200_shm"              # [descriptor of columns in a shared-memory ring, weights]
+KEY_SRC = "reth_b200_src"              # [client id, message number]: lets the server order a loader's
+                                       # request after the writes the same process sent on other sockets
 
 
 def _native():
@@ -118,9 +120,10 @@ def _describe(obj, body):
     return obj
 
 
-def encode(obj, compress=False, columnar=False, now=None):
+def encode(obj, compress=False, columnar=False, now=None, extra=None):
     """-> bytes-like (a uint8 numpy buffer) in the reference wire format.  The body segments are
-    copied ONCE, straight into the output buffer."""
+    copied ONCE, straight into the output buffer.  extra: additional header fields (the reference's
+    deserialize ignores header keys it does not know)."""
     body = _Body()
     meta = _describe(obj, body)
     header = {}
@@ -138,6 +141,8 @@ def encode(obj, compress=False, columnar=False, now=None):
     header["time"] = time.time() if now is None else now
     if columnar:
         header[KEY_COLUMNAR] = True
+    if extra:
+        header.update(extra)
     hb = msgpack.packb(header)
     out = np.empty(4 + len(hb) + header["body_len"], np.uint8)
     out[:4] = np.frombuffer(len(hb).to_bytes(4, "big"), np.uint8)
@@ -209,6 +214,21 @@ def is_shm(buf):
     return isinstance(meta, list) and len(meta) == 2 and isinstance(meta[0], dict) and KEY_SHM in meta[0]
 
 
+def open_append(buf):
+    """An append message, header parsed once -> (kind, payload, weights, src):
+    kind "shm": payload = descriptor of columns in a shared-memory ring (service_mp._ShmRing);
+    kind "columns": payload = list of C-contiguous (n, ...) arrays (row or columnar wire format);
+    src = the sender's [client id, message number] or None (a reference client)."""
+    header, body, _ = _split(buf)
+    meta = header["meta"]
+    src = header.get(KEY_SRC)
+    if isinstance(meta, list) and len(meta) == 2 and isinstance(meta[0], dict) and KEY_SHM in meta[0]:
+        head, weights = _rebuild(meta, body)
+        return "shm", head, np.asarray(weights), src
+    cols, weights = _decode_append(header, body)
+    return "columns", cols, weights, src
+
+
 def decode_append(buf):
     """An append message -> (columns, weights): columns[c] is a C-contiguous (n, ...) array.
 
@@ -217,6 +237,10 @@ def decode_append(buf):
     the same inner header length (same struct: always, for a fixed-size transition), the rows form
     an (n, L) byte matrix and each column is ONE strided copy out of it."""
     header, body, _ = _split(buf)
+    return _decode_append(header, body)
+
+
+def _decode_append(header, body):
     meta = header["meta"]
     if header.get(KEY_COLUMNAR):
         cols, weights = _rebuild(meta, body)
@@ -251,12 +275,12 @@ def decode_append(buf):
     return cols, np.asarray(weights)
 
 
-def encode_append_rows(columns, weights, compress=False, now=None):
+def encode_append_rows(columns, weights, compress=False, now=None, extra=None):
     """What the reference's Client.append puts on the wire (client/client.py:26-35)."""
     n = len(weights)
     rows = [encode([col[i, ...] for col in columns], now=now) for i in range(n)]
-    return encode([rows, weights], compress=compress, now=now)
+    return encode([rows, weights], compress=compress, now=now, extra=extra)
 
 
-def encode_append_columns(columns, weights, compress=False, now=None):
-    return encode([list(columns), weights], compress=compress, columnar=True, now=now)
+def encode_append_columns(columns, weights, compress=False, now=None, extra=None):
+    return encode([list(columns), weights], compress=compress, columnar=True, now=now, extra=extra)

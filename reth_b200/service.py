@@ -88,6 +88,8 @@ class _Engine:
         self.pipe = None
         self.group = 1
         self.ahead = 0
+        self.lend = 1                                         # delivered groups that stay lent (2: loader in another process)
+        self._want = 0                                        # deliveries a remote loader has asked for
         self.loaders = 0
         self._queue = []                                      # delivered, not yet consumed: (slot, indices)
         # priority write-backs being coalesced into one staging entry
@@ -133,19 +135,25 @@ class _Engine:
             self.cnt += len(weights)
 
     # -- loader pipeline --------------------------------------------------
-    def open_pipe(self, group, ahead):
+    def open_pipe(self, group, ahead, lend=1):
         """Called by a loader: `group` batches per launch group, `ahead` groups in flight beyond
-        the one being consumed (ahead 0 = strict alternation: a draw sees every earlier update)."""
+        the one being consumed (ahead 0 = strict alternation: a draw sees every earlier update).
+        lend = delivered groups that stay valid: 1 for a loader in this process; 2 for a loader in
+        another process that asks for the next group when it STARTS on the current one (the request
+        then hands back the group before)."""
         with self.lock:
             group = max(1, int(group))
             ahead = max(0, int(ahead))
+            lend = 2 if (int(lend) >= 2 and ahead > 0) else 1
+            if lend == 2 and max(ahead + 1, 3) * group > self.max_ring:
+                lend = 1                                      # the batch ring holds fewer than 3 groups: lazy requests
             if self.pipe is not None:
-                if (group, ahead) != (self.group, self.ahead):
+                if (group, ahead, lend) != (self.group, self.ahead, self.lend):
                     if self.loaders > 0:
                         raise ValueError(f"this buffer already serves loaders with prefetch group {self.group} / "
                                          f"{self.ahead} ahead")
                     self._close_pipe()
-            self.group, self.ahead = group, ahead
+            self.group, self.ahead, self.lend = group, ahead, lend
             self.loaders += 1
 
     def _close_pipe(self):
@@ -154,6 +162,7 @@ class _Engine:
             self.pipe.close()
             self.pipe = None
             self._queue = []
+            self._want = 0
 
     def release_pipe(self):
         with self.lock:
@@ -163,11 +172,49 @@ class _Engine:
 
     def _ensure_pipe(self):
         if self.pipe is None:
-            need = (self.ahead + 1) * self.group
+            need = max(self.ahead + 1, self.lend + 1) * self.group
             if need > self.shard.ring_depth:
                 raise ValueError(f"prefetch of {need} batches exceeds the batch ring ({self.shard.ring_depth})")
             self.pipe = self.shard.open_pipe(self.batch_size, self.group, seed=0x5EED)
+            if self.lend > 1:
+                self.pipe.hold(self.lend)
         return self.pipe
+
+    # -- loader in another process (service_mp): request and delivery are separate, nothing blocks --
+    def request_group(self):
+        """A remote loader asked for one more group: hand back the oldest lent group once `lend`
+        groups are out, keep `ahead` groups in flight, and remember that a delivery is owed."""
+        with self.lock:
+            pipe = self._ensure_pipe()
+            self.flush()                                      # staged write-backs land before the draw
+            beta = self.sampler["beta"].value()
+            handed_back = False
+            while pipe.in_flight < max(1, self.ahead):
+                if pipe.can_issue():
+                    pipe.issue(beta)
+                elif pipe.waited >= pipe.lend and not handed_back:
+                    pipe.advance(beta)                        # the request hands ONE group back: draw into its slots
+                    handed_back = True
+                else:
+                    break
+            self._want += 1
+
+    def try_deliver(self):
+        """-> (group slot g, host indices [group, batch], host weights [group, batch]) when a requested
+        group is complete, else None.  Never blocks."""
+        with self.lock:
+            pipe = self.pipe
+            if pipe is None or self._want <= 0:
+                return None
+            if pipe.in_flight == 0:                           # e.g. the ring was full when the request came
+                if not pipe.can_issue():
+                    return None
+                pipe.issue(self.sampler["beta"].value())
+            if not pipe.ready():
+                return None
+            g = pipe.wait()
+            self._want -= 1
+            return g, pipe.idx_host[g], pipe.w_host[g]
 
     def next_group(self):
         """Take delivery of the next pre-sampled group and keep `ahead` more in flight.
@@ -247,6 +294,43 @@ class _Engine:
             self._upd_k = k + 1
             if k + 1 >= self.group:
                 self.flush()
+
+    def update_block(self, indices, weights, sizes, steps):
+        """Several update_priorities messages that arrived in one frame (service_mp): indices / weights
+        are the messages' arrays back to back.  Same effect as update() per message, in order; whole
+        runs of learner-batch messages are staged with one copy each."""
+        with self.lock:
+            B, pipe = self.batch_size, self.pipe
+            if (self.shard is None or self.kind != "per" or pipe is None or not all(steps)
+                    or any(n != B for n in sizes)):
+                at = 0
+                for n, st in zip(sizes, steps):
+                    self.update(indices[at:at + n], weights[at:at + n], bool(st))
+                    at += n
+                return
+            f32 = weights.dtype == np.float32
+            alpha, beta = self.sampler["alpha"], self.sampler["beta"]
+            K, pos = len(sizes), 0
+            while pos < K:
+                k = self._upd_k
+                if k and f32 != self._upd_f32:
+                    self.flush()
+                    k = 0
+                if k == 0:
+                    self._upd_e = pipe.update_begin()
+                    self._upd_f32 = f32
+                take = min(self.group - k, K - pos)
+                for _ in range(take):                         # sampler_loop.py:33-34, once per message
+                    alpha.step()
+                    beta.step()
+                e = self._upd_e
+                pipe.upd_idx[e, k * B:(k + take) * B] = indices[pos * B:(pos + take) * B]
+                (pipe.upd_p32 if f32 else pipe.upd_p64)[e, k * B:(k + take) * B] = weights[pos * B:(pos + take) * B]
+                self._upd_k = k + take
+                self.cnt += take * B
+                pos += take
+                if self._upd_k >= self.group:
+                    self.flush()
 
     def flush(self):
         with self.lock:

@@ -27,14 +27,24 @@ import multiprocessing as mp
 import os
 import signal
 import socket
+import struct
 import sys
+import threading
 import time
+import weakref
 
 import numpy as np
 
 from . import pack
 
 ZMQ_DEFAULT_HWM = 10            # utils/__init__.py:12
+
+# compact priority write-back frame of this build's own Client:
+#   [magic, client id, frame number, count] [step, float32?, reserved, n] * count
+#   [int64 indices of all messages] [float32|float64 priorities of all messages]  (one dtype per frame)
+_UPD_MAGIC = b"RBU1"            # a reference-format message starts with a big-endian header length: first byte 0
+_UPD_FRAME = struct.Struct("<4s8sQI")
+_UPD_HEAD = struct.Struct("<BBHI")
 
 
 def _pick_port(host):
@@ -78,6 +88,8 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
     for s in (meta, app, upd, ldr):
         poller.register(s, zmq.POLLIN)
     waiting = []                 # loader requests parked until the buffer is ready (sampler_loop.py:25-28)
+    owed = []                    # loaders that asked for a group which is still being drawn / gathered
+    seen = {}                    # client id -> [last append message, last update frame] taken in
     segments = {}                # shared-memory ingest rings of same-host clients: name -> _ShmSegment
     pending = []                 # (cuda event, segment, seq): H2D copies out of a ring still in flight
     ready_evt.set()
@@ -104,75 +116,150 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
     def reply(ident, obj, *blobs):
         ldr.send_multipart([ident, b"", json.dumps(obj).encode()] + list(blobs))
 
-    def serve_next(ident):
-        g, idx, w = eng.next_group()
-        reply(ident, {"ok": True, "group": int(g), "first_slot": int(g * eng.group), "n": int(eng.group)},
-              idx.tobytes(), w.tobytes())
+    def deliver():
+        """Send every group that is owed and complete; nothing here blocks on the device."""
+        while owed:
+            got = eng.try_deliver()
+            if got is None:
+                return
+            g, idx, w = got
+            reply(owed.pop(0), {"ok": True, "op": "next", "group": int(g), "first_slot": int(g * eng.group),
+                                "n": int(eng.group)}, idx.tobytes(), w.tobytes())
+
+    def apply_updates(buf):
+        """One update frame: the reference's [indices, weights, step] message (client.py:37-39), or this
+        build's compact frame holding one or more such messages back to back."""
+        mv = memoryview(buf)
+        if mv[:4] != _UPD_MAGIC:
+            indices, weights, step = pack.decode(mv)
+            eng.update(np.asarray(indices), np.asarray(weights), bool(step))
+            return
+        _, cid, seq, count = _UPD_FRAME.unpack_from(mv, 0)
+        at = _UPD_FRAME.size
+        sizes, steps, f32 = [], [], 1
+        for _ in range(count):
+            step, f32, _, n = _UPD_HEAD.unpack_from(mv, at)
+            at += _UPD_HEAD.size
+            sizes.append(n)
+            steps.append(step)
+        total = sum(sizes)
+        idx = np.frombuffer(mv, np.int64, total, at)
+        w = np.frombuffer(mv, np.float32 if f32 else np.float64, total, at + 8 * total)
+        eng.update_block(idx, w, sizes, steps)
+        seen.setdefault(cid.hex(), [0, 0])[1] = seq
+
+    def drain_appends():
+        while True:
+            try:
+                frame = app.recv(zmq.NOBLOCK, copy=False)
+            except zmq.Again:
+                break
+            kind, payload, weights, src = pack.open_append(frame.buffer)
+            if kind == "shm":
+                try:
+                    append_from_ring(payload, weights)
+                except FileNotFoundError:              # the producer vanished with its ring: the rows are lost
+                    print(f"reth_b200 server: ingest ring {payload[pack.KEY_SHM]} is gone, message dropped",
+                          file=sys.stderr, flush=True)
+            else:
+                eng.append(payload, weights)
+            if src:
+                seen.setdefault(src[0], [0, 0])[0] = int(src[1])
+            retire_ring_copies()
+        retire_ring_copies()
+
+    def drain_updates():
+        while True:
+            try:
+                frame = upd.recv(zmq.NOBLOCK, copy=False)
+            except zmq.Again:
+                break
+            apply_updates(frame.buffer)
+
+    def await_writes(after, timeout=2.0):
+        """A loader's request names the appends / write-backs its own process sent before it (they
+        travel on other sockets): take them in first, so the request sees them -- the arrival order
+        the reference gets from one SUB socket (sampler_loop.py:29-36)."""
+        def behind():
+            return any(seen.get(c, (0, 0))[0] < a or seen.get(c, (0, 0))[1] < u for c, (a, u) in after.items())
+        if not after or not behind():
+            return
+        t0 = time.time()
+        while behind() and time.time() - t0 < timeout:
+            poller.poll(1)
+            drain_appends()
+            drain_updates()
 
     def handle_loader(ident, req):
         op = req.get("op")
+        await_writes(req.get("after"))
         if op == "open":
             if eng.shard is None:                      # row struct unknown until the first append
                 waiting.append((ident, req))
                 return
-            eng.open_pipe(req.get("prefetch", 1), req.get("ahead", 0))
+            # fit the loader's geometry into the batch ring: three groups when it asks ahead
+            group = max(1, int(req.get("prefetch", 1)))
+            ahead = max(0, int(req.get("ahead", 0)))
+            if ahead > 0 and 3 * group > eng.max_ring:
+                group = max(1, eng.max_ring // 3)
+            ahead = min(ahead, max(0, eng.max_ring // group - 1))
+            eng.open_pipe(group, ahead, req.get("lend", 1))
             ex = _cabi.IpcExport()
             eng.shard._ck(_cabi.lib().reth_replay_ipc_export(eng.shard._h, C.byref(ex)))
             struct = [[np.dtype(dt).str, list(sh)] for dt, sh in eng.shard.struct]
-            reply(ident, {"ok": True, "struct": struct, "batch_size": batch_size, "group": eng.group,
-                          "ahead": eng.ahead, "ring_depth": eng.shard.ring_depth}, bytes(ex))
+            reply(ident, {"ok": True, "op": "open", "struct": struct, "batch_size": batch_size, "group": eng.group,
+                          "ahead": eng.ahead, "lend": eng.lend, "ring_depth": eng.shard.ring_depth}, bytes(ex))
         elif op == "next":
             if not eng.ready():
                 waiting.append((ident, req))
                 return
-            serve_next(ident)
+            eng.request_group()
+            owed.append(ident)
+            deliver()
         elif op == "rows":                             # NumpyLoader: rows of a lent slot, device -> host
             data, _, _ = eng.shard.slot_read(int(req["slot"]), with_rows=True, stream=eng.stream)
-            reply(ident, {"ok": True}, *[np.ascontiguousarray(c).tobytes() for c in data])
+            reply(ident, {"ok": True, "op": "rows"}, *[np.ascontiguousarray(c).tobytes() for c in data])
         elif op == "close":
+            owed[:] = [i for i in owed if i != ident]
             eng.release_pipe()
-            reply(ident, {"ok": True})
+            reply(ident, {"ok": True, "op": "close"})
         elif op == "drain":
             eng.drain()
-            reply(ident, {"ok": True, "cnt": eng.cnt})
+            reply(ident, {"ok": True, "op": "drain", "cnt": eng.cnt})
         else:
-            reply(ident, {"ok": False, "error": f"unknown op {op!r}"})
+            reply(ident, {"ok": False, "op": op, "error": f"unknown op {op!r}"})
 
+    last_traffic = 0.0
     try:
         while not stop["flag"]:
-            events = dict(poller.poll(1 if pending else 50))
+            # a delivery is owed, or traffic within the last 2 ms: spin (a blocking poll costs a scheduler
+            # wake-up per message; the reference's sampler loop spins in zmq.select too, sampler_loop.py:22-24)
+            busy = owed or (eng.loaders > 0 and time.perf_counter() - last_traffic < 0.002)
+            events = dict(poller.poll(0 if busy else (1 if pending else 50)))
+            if events:
+                last_traffic = time.perf_counter()
             if meta in events:
                 meta.recv()
                 meta.send_json(config)
             # drain every pending write before serving a draw (sampler_loop.py:29-36)
-            while app.poll(0):
-                frame = app.recv(copy=False)
-                if pack.is_shm(frame.buffer):
-                    head, weights = pack.decode(frame.buffer)
-                    try:
-                        append_from_ring(head, np.asarray(weights))
-                    except FileNotFoundError:          # the producer vanished with its ring: the rows are lost
-                        print(f"reth_b200 server: ingest ring {head[pack.KEY_SHM]} is gone, message dropped",
-                              file=sys.stderr, flush=True)
-                else:
-                    cols, weights = pack.decode_append(frame.buffer)
-                    eng.append(cols, weights)
-                retire_ring_copies()
-            retire_ring_copies()
-            while upd.poll(0):
-                frame = upd.recv(copy=False)
-                indices, weights, step = pack.decode(frame.buffer)
-                eng.update(np.asarray(indices), np.asarray(weights), bool(step))
+            drain_appends()
+            drain_updates()
             if waiting and eng.shard is not None:
                 parked, waiting[:] = list(waiting), []
                 for ident, req in parked:
                     handle_loader(ident, req)
-            while ldr.poll(0):
-                ident, _, payload = ldr.recv_multipart()
+            while True:
                 try:
-                    handle_loader(ident, json.loads(payload))
+                    ident, _, payload = ldr.recv_multipart(zmq.NOBLOCK)
+                except zmq.Again:
+                    break
+                req = {}
+                try:
+                    req = json.loads(payload)
+                    handle_loader(ident, req)
                 except Exception as e:                 # keep serving; the loader raises on its side
-                    reply(ident, {"ok": False, "error": f"{type(e).__name__}: {e}"})
+                    reply(ident, {"ok": False, "op": req.get("op"), "error": f"{type(e).__name__}: {e}"})
+            deliver()
     finally:
         eng.close()
         for seg in segments.values():
@@ -216,7 +303,7 @@ class _ShmSegment:
 
 # ------------------------------------------------------------ public surface --
 def start_server(capacity, batch_size, host=None, port=None, samplers=None, cache_policy=None, device=0,
-                 max_ring=16):
+                 max_ring=32):
     """reth_buffer.start_server (__init__.py:11-27): spawn the server process, return
     (proc, meta_addr).  `proc` supports terminate()/join() as callers expect (trainer.py:72-74)."""
     host = host or "127.0.0.1"
@@ -241,11 +328,26 @@ def _server_entry(capacity, batch_size, host, ports, samplers, cache_policy, dev
     if samplers is not None:
         for s in samplers:
             pass                                       # class names are resolved by service._Engine
-    server_main(capacity, batch_size, host, ports, samplers, cache_policy, device, max_ring, ready)
+    prof_path = os.environ.get("RETH_B200_SERVER_PROFILE")      # diagnostic: cProfile of the server loop
+    if not prof_path:
+        server_main(capacity, batch_size, host, ports, samplers, cache_policy, device, max_ring, ready)
+        return
+    import cProfile
+    import io
+    import pstats
+    pr = cProfile.Profile()
+    try:
+        pr.runcall(server_main, capacity, batch_size, host, ports, samplers, cache_policy, device, max_ring, ready)
+    finally:
+        out = io.StringIO()
+        pstats.Stats(pr, stream=out).sort_stats("tottime").print_stats(25)
+        pstats.Stats(pr, stream=out).sort_stats("cumtime").print_stats("reth_b200", 40)
+        with open(prof_path, "w") as f:
+            f.write(out.getvalue())
 
 
 def start_per(capacity, batch_size, alpha=0.6, beta=0.4, sample_start=1000, num_sampler_procs=1,
-              host=None, port=None, cache_policy=None, device=0, max_ring=16):
+              host=None, port=None, cache_policy=None, device=0, max_ring=32):
     """reth_buffer.start_per (__init__.py:30-49)."""
     from .sampler import PERSampler
     samplers = [{"sampler_cls": PERSampler, "num_procs": num_sampler_procs, "sample_start": sample_start,
@@ -356,10 +458,22 @@ class Client:
                 server copies host->device from, only a small descriptor travels over ZeroMQ;
       "auto"    (default) "shm" when the server runs on this host, else "columns"."""
 
-    def __init__(self, meta_addr, wire="auto", shm_mb=None):
+    def __init__(self, meta_addr, wire="auto", shm_mb=None, coalesce=None):
         import zmq
         self.ctx = zmq.Context.instance()
         self.meta = get_meta(meta_addr)
+        # priority write-backs are fire-and-forget (client.py:37-39); up to `coalesce` consecutive messages
+        # share one ZeroMQ frame (each keeps its own step flag and is applied separately, in order).  A
+        # partial frame is sent before this process asks for a new group, at append(), close(), and by a
+        # timer once it is 2 ms old.  coalesce=1 (and wire="rows") sends every message on its own.
+        self.coalesce = max(1, int(coalesce if coalesce is not None else os.environ.get("RETH_B200_UPDATE_COALESCE", 8)))
+        self._lock = threading.Lock()
+        self._id = os.urandom(8)
+        self._aseq = self._useq = 0                            # append messages / update frames sent so far
+        self._heads, self._idxs, self._ws, self._held, self._held_t0, self._held_f32 = [], [], [], 0, 0.0, True
+        self._timer = None
+        self._closed = False
+        _CLIENTS.setdefault(self.meta["meta_addr"], weakref.WeakSet()).add(self)
         if wire == "auto":
             wire = "shm" if self.meta.get("host_id") == _host_id() else "columns"
         self.wire = wire
@@ -386,8 +500,12 @@ class Client:
             desc.append([c.dtype.str, list(c.shape), at, c.nbytes])
             at += (c.nbytes + 63) & ~63
         head = {pack.KEY_SHM: self._ring.shm.name, "size": self._ring.size, "seq": self._ring.seq, "cols": desc}
-        self.append_sock.send(pack.encode([head, weights]), copy=False)
+        self.append_sock.send(pack.encode([head, weights], extra=self._next_append()), copy=False)
         return True
+
+    def _next_append(self):
+        self._aseq += 1
+        return {pack.KEY_SRC: [self._id.hex(), self._aseq]}
 
     def append(self, data, weights, compress=False):
         assert isinstance(data, (list, tuple))                # client.py:22
@@ -395,36 +513,113 @@ class Client:
             assert isinstance(col, np.ndarray)                # :24
             assert len(col) == len(weights)                   # :25
         weights = np.asarray(weights)
+        self.flush()                                          # keep write-backs ahead of later appends
         if self.wire == "rows":
-            msg = pack.encode_append_rows(data, weights, compress=compress)
+            msg = pack.encode_append_rows(data, weights, compress=compress, extra=self._next_append())
         elif self.wire == "shm" and self._append_shm(data, weights):
             return                                            # same host: nothing to gain from compress
         else:
-            msg = pack.encode_append_columns(data, weights, compress=compress)
+            msg = pack.encode_append_columns(data, weights, compress=compress, extra=self._next_append())
         self.append_sock.send(msg, copy=False)
 
     def update_priorities(self, indices, weights, step=True):
         assert len(indices) == len(weights)                   # :38
-        self.update_sock.send(pack.encode([np.asarray(indices), np.asarray(weights), step]), copy=False)
+        if self.wire == "rows":                               # exactly the reference's message
+            self.update_sock.send(pack.encode([np.asarray(indices), np.asarray(weights), step]), copy=False)
+            return
+        idx = indices if (type(indices) is np.ndarray and indices.dtype == np.int64) else np.asarray(indices, dtype=np.int64)
+        w = weights if type(weights) is np.ndarray else np.asarray(weights)
+        f32 = w.dtype == np.float32
+        if not f32 and w.dtype != np.float64:
+            w = w.astype(np.float64)
+        with self._lock:
+            if self._held and f32 != self._held_f32:           # one priority dtype per frame
+                self._flush_locked()
+            self._held_f32 = f32
+            self._heads.append(_UPD_HEAD.pack(1 if step else 0, 1 if f32 else 0, 0, idx.size))
+            self._idxs.append(idx.tobytes())                  # copies: the caller may reuse its arrays
+            self._ws.append(w.tobytes())
+            self._held += 1
+            if self._held >= self.coalesce:
+                self._flush_locked()
+            elif self._held == 1:
+                self._held_t0 = time.perf_counter()
+                if self._timer is None:
+                    self._timer = threading.Thread(target=_flush_timer, args=(weakref.ref(self),), daemon=True)
+                    self._timer.start()
+
+    def _flush_locked(self):
+        if self._held:
+            self._useq += 1
+            frame = b"".join([_UPD_FRAME.pack(_UPD_MAGIC, self._id, self._useq, self._held)] + self._heads
+                             + self._idxs + self._ws)
+            self._heads, self._idxs, self._ws, self._held = [], [], [], 0
+            self.update_sock.send(frame, copy=False)
+
+    def flush(self):
+        """Send the write-backs held back for coalescing.  -> (append messages, update frames) sent so far."""
+        with self._lock:
+            if not self._closed:
+                self._flush_locked()
+            return self._aseq, self._useq
 
     def close(self):
-        self.append_sock.close(0)
-        self.update_sock.close(0)
+        with self._lock:
+            if self._closed:
+                return
+            self._flush_locked()
+            self._closed = True
+            self.append_sock.close(0)
+            self.update_sock.close(2000)                      # let the last write-backs leave
         if self._ring is not None:
             self._ring.close()
             self._ring = None
 
     def __del__(self):
         try:
+            self.flush()
             if self._ring is not None:
                 self._ring.close()
         except Exception:
             pass
 
 
+_CLIENTS = {}                    # meta address -> clients of this process (flushed before a loader asks for a group)
+
+
+def _flush_clients(meta_addr):
+    """-> {client id: [append messages, update frames]} sent by this process: a loader request carries it
+    so that the server takes those writes in before it acts on the request."""
+    after = {}
+    for c in list(_CLIENTS.get(meta_addr, ())):
+        a, u = c.flush()
+        if c.wire != "rows" or a:                             # reference-format update messages carry no number
+            after[c._id.hex()] = [a, u if c.wire != "rows" else 0]
+    return after
+
+
+def _flush_timer(ref):
+    """Bounds how long a partial frame of write-backs may wait: 2 ms."""
+    while True:
+        time.sleep(0.002)
+        c = ref()
+        if c is None or c._closed:
+            return
+        with c._lock:
+            if c._held and time.perf_counter() - c._held_t0 > 0.002 and not c._closed:
+                try:
+                    c._flush_locked()
+                except Exception:
+                    return
+        del c
+
+
 class _RemoteLoader:
-    """Loader-side connection: one REQ socket; a request for the next group releases the previous one
-    (the borrow rule of client/torch_cuda_loader.py:152-163, at group granularity)."""
+    """Loader-side connection: one DEALER socket.  With ahead >= 1 the request for group k+1 leaves
+    when group k ARRIVES (so the server draws and gathers while this process consumes group k); it
+    hands back group k-1, and groups k and k+1 may both be lent meanwhile.  With ahead == 0 (strict
+    alternation) the request leaves when the next group is needed and hands back the previous one --
+    the borrow rule of client/torch_cuda_loader.py:152-163 at group granularity."""
 
     def __init__(self, meta_addr, topic="default", prefetch=1, ahead=0, map_ring=True, timeout_s=120.0):
         import zmq
@@ -432,7 +627,7 @@ class _RemoteLoader:
         self.meta = get_meta(meta_addr)
         assert topic in self.meta["sampler_info"]
         self._zmq = zmq
-        self.sock = zmq.Context.instance().socket(zmq.REQ)
+        self.sock = zmq.Context.instance().socket(zmq.DEALER)
         self.sock.setsockopt(zmq.LINGER, 0)
         self.sock.connect(self.meta["loader_addr"])
         self.timeout_ms = int(timeout_s * 1000)
@@ -446,6 +641,9 @@ class _RemoteLoader:
         self.device = self.meta["device"]
         self.struct = None
         self._queue = []
+        self._asked = False          # a "next" request is outstanding
+        self._ask_ahead = False
+        self._stash = []             # "next" replies that arrived while another call was waiting
 
     def _ensure_open(self):
         """The row struct is only known after the first append (torch_cuda_loader.py:106-112 discovers
@@ -453,10 +651,12 @@ class _RemoteLoader:
         if self._open:
             return
         from . import _cabi
-        head, blobs = self._call({"op": "open", "prefetch": self.prefetch, "ahead": self.ahead})
+        head, blobs = self._call({"op": "open", "prefetch": self.prefetch, "ahead": self.ahead,
+                                  "lend": 2 if self.ahead > 0 else 1})
         self._open = True
         self.struct = [(np.dtype(dt), tuple(sh)) for dt, sh in head["struct"]]
         self.group = head["group"]
+        self._ask_ahead = head.get("lend", 1) >= 2     # else the ring is too small to lend two groups
         if self._map_ring:
             import torch
             torch.cuda.set_device(self.device)         # the ring is mapped for the current device
@@ -468,27 +668,60 @@ class _RemoteLoader:
             self._view = v
             self._ncols = ex.n_columns
 
+    def _send(self, obj):
+        self.sock.send_multipart([b"", json.dumps(obj).encode()])
+
+    def _recv(self, op):
+        """The reply to request `op`; replies to an outstanding "next" that arrive first are kept."""
+        if op == "next" and self._stash:
+            return self._stash.pop(0)
+        zmq = self._zmq
+        while True:
+            spin_until = time.perf_counter() + 0.0005          # a blocking poll costs a scheduler wake-up
+            while True:
+                try:
+                    parts = self.sock.recv_multipart(zmq.NOBLOCK)
+                    break
+                except zmq.Again:
+                    if time.perf_counter() < spin_until:
+                        continue
+                    if not self.sock.poll(self.timeout_ms):
+                        raise TimeoutError("the replay server did not answer (no batch available: fewer than "
+                                           "sample_start transitions were appended?)") from None
+            head = json.loads(parts[1])
+            if head.get("op") == "next" and op != "next" and head.get("ok"):
+                self._stash.append((head, parts[2:]))
+                continue
+            if not head.get("ok"):
+                if head.get("op") == "next":
+                    self._asked = False
+                raise RuntimeError(f"replay server: {head.get('error')}")
+            return head, parts[2:]
+
     def _call(self, obj):
-        self.sock.send(json.dumps(obj).encode())
-        if not self.sock.poll(self.timeout_ms):
-            raise TimeoutError("the replay server did not answer (no batch available: fewer than sample_start "
-                               "transitions were appended?)")
-        parts = self.sock.recv_multipart()
-        head = json.loads(parts[0])
-        if not head.get("ok"):
-            raise RuntimeError(f"replay server: {head.get('error')}")
-        return head, parts[1:]
+        self._send(obj)
+        return self._recv(obj["op"])
+
+    def _ask(self):
+        # this process's appends and write-backs are taken in before the draw
+        self._send({"op": "next", "after": _flush_clients(self.meta["meta_addr"])})
+        self._asked = True
 
     def _next(self):
         """-> (batch slot, indices int64[B], weights float64[B]) of the next pre-sampled batch."""
         if not self._queue:
             self._ensure_open()
-            head, blobs = self._call({"op": "next"})
+            if not self._asked:
+                self._ask()
+            head, blobs = self._recv("next")
+            self._asked = False
+            if self._ask_ahead:
+                self._ask()                            # the server works on the next group while this one is consumed
             G, B = head["n"], self.batch_size
-            idx = np.frombuffer(blobs[0], np.int64).reshape(G, B)
-            w = np.frombuffer(blobs[1], np.float64).reshape(G, B)
+            idx = np.frombuffer(blobs[0], np.int64).reshape(G, B).copy()      # writable, like the reference's
+            w = np.frombuffer(blobs[1], np.float64).reshape(G, B).copy()
             first = head["first_slot"]
-            self._queue = [(first + k, idx[k].copy(), w[k].copy()) for k in range(G - 1, -1, -1)]
+            self._queue = [(first + k, idx[k], w[k]) for k in range(G - 1, -1, -1)]
         return self._queue.pop()
 
     def slot_pointers(self, slot):
@@ -500,7 +733,7 @@ class _RemoteLoader:
 
     def drain(self):
         """Block until the server has executed everything it has received so far; -> {"cnt": ...}."""
-        return self._call({"op": "drain"})[0]
+        return self._call({"op": "drain", "after": _flush_clients(self.meta["meta_addr"])})[0]
 
     def close(self):
         if self._open:
@@ -551,11 +784,14 @@ class TorchCudaLoader(_RemoteLoader):
     the group is released, indices come back on the host."""
 
     def __init__(self, meta_addr, topic="default", buffer_size=8, num_procs=6, prefetch=None, ahead=None):
+        # across processes every group costs a request/reply exchange (~100 us of host work on each
+        # side), so the default group is the whole buffer_size and two more groups are kept in flight;
+        # the server shrinks the group if its batch ring (start_server(max_ring=32)) cannot hold three
         buffer_size = max(1, int(buffer_size))
         if prefetch is None:
-            prefetch = max(1, buffer_size // 2)
+            prefetch = buffer_size
         if ahead is None:
-            ahead = max(0, buffer_size // int(prefetch) - 1)
+            ahead = 2 if buffer_size > 1 else 0
         super().__init__(meta_addr, topic, prefetch, ahead, map_ring=True)
         self.buffer_size = buffer_size
         self.num_procs = num_procs

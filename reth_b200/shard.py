@@ -89,6 +89,7 @@ class ShardPipe:
         self.upd_p32 = raw[:, E * 8:E * 12].view(np.float32)      # [entry][E]
         self.upd_p64 = raw[:, E * 8:].view(np.float64)            # [entry][E]
         self.issued = self.waited = 0
+        self.lend = 1                                             # delivered groups that stay lent
         self._g = C.c_int32()
         self._e = C.c_int32()
         p = C.c_void_p()
@@ -100,7 +101,22 @@ class ShardPipe:
         return self.issued - self.waited
 
     def can_issue(self):
-        return self.in_flight + (1 if self.waited else 0) < self.n_groups
+        return self.in_flight + min(self.waited, self.lend) < self.n_groups
+
+    def hold(self, groups):
+        """Keep the newest `groups` delivered groups lent (reth_replay_pipe_hold); before the first issue."""
+        self.shard._ck(self._lib.reth_replay_pipe_hold(self._h, int(groups)))
+        self.lend = int(groups)
+
+    def advance(self, beta):
+        """Hand the oldest lent group back and issue a new group into its slots; never blocks."""
+        self.shard._ck(self._lib.reth_replay_pipe_advance(self._h, float(beta)))
+        self.issued += 1
+
+    def ready(self):
+        """True when wait() would not block."""
+        self.shard._ck(self._lib.reth_replay_pipe_ready(self._h, C.byref(self._g)))
+        return bool(self._g.value)
 
     def issue(self, beta):
         self.shard._ck(self._lib.reth_replay_pipe_issue(self._h, float(beta)))

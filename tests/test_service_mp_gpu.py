@@ -85,12 +85,42 @@ def test_torch_cuda_loader_ipc(reth_buffer, wire):
             assert float(weights.max()) <= 1.0 + 1e-12
             loss = np.abs(rng.standard_normal(B)).astype(np.float32)
             client.update_priorities(np.asarray(indices), np.asarray(loss))         # trainer.py:36
-        assert loader.group == 2
+        assert loader.group == 4                              # the whole buffer_size is one group across processes
         st = loader.drain()
         assert st["cnt"] == 600 + 12 * B
         with pytest.raises(AssertionError):
             client.append([c[:10] for c in cols], np.ones(9))
         loader.close()
+    finally:
+        proc.terminate()
+        proc.join()
+
+
+@pytest.mark.parametrize("wire", ["columns", "rows"])
+def test_draw_sees_earlier_writes_of_the_same_process(reth_buffer, wire):
+    """Appends, write-backs and loader requests travel on three sockets; a strict-alternation loader
+    (prefetch 1, nothing ahead) must still see every write its own process made before sample():
+    the request names the writes and the server takes them in first."""
+    from reth_b200 import service_mp
+    B, n = 32, 512
+    proc, addr = reth_buffer.start_per(4096, B, alpha=1.0, beta=0.4, sample_start=B)
+    try:
+        client = service_mp.Client(addr, wire=wire, coalesce=8 if wire == "columns" else 1)
+        loader = service_mp.NumpyLoader(addr)                 # prefetch 1 / ahead 0
+        ids = np.arange(n, dtype=np.int64)
+        client.append([ids, ids.astype(np.float32)], np.full(n, 1e-3, np.float32))
+        rng = np.random.default_rng(0)
+        for it in range(30):
+            hot = int(rng.integers(0, n))
+            client.update_priorities(np.array([hot]), np.array([1e9], np.float32))   # held back for coalescing
+            data, indices, weights = loader.sample()
+            if wire == "columns":                             # numbered frames: exact ordering
+                assert np.all(indices == hot), (it, hot, indices[:8])
+                assert np.array_equal(data[0], indices)
+            client.update_priorities(np.array([hot]), np.array([1e-3], np.float32))
+        assert loader.drain()["cnt"] == n + 60
+        loader.close()
+        client.close()
     finally:
         proc.terminate()
         proc.join()
