@@ -261,6 +261,9 @@ int reth_replay_pipe_wait(reth_replay_t *h, int32_t *group_out);
  * pipe_wait()s for the oldest group in flight.  Issuing BEFORE blocking keeps a draw + gather
  * queued behind the group in flight, so the device does not idle while the host wakes up. */
 int reth_replay_pipe_next(reth_replay_t *h, double beta, int32_t *group_out);
+/* Keep the last n_slots batch slots of the ring out of the pipe (they serve other sampler topics
+ * through gather_from()); call before pipe_open. */
+int reth_replay_pipe_reserve(reth_replay_t *h, int n_slots);
 /* Lending depth: the newest `groups` delivered groups stay valid (default 1; call before the first
  * pipe_issue).  A consumer in ANOTHER process asks for group k+1 when it starts on group k, so the
  * request that reaches the owner hands back group k-1: two groups are lent at a time there. */
@@ -306,6 +309,14 @@ int reth_ipc_close(reth_ipc_view_t *v);
  * names this shard's own ring (the learner rank's own slice; dst_slot != slot).  The
  * reference has no counterpart (its learner polls whole batches shard by shard, trainer.py:33-36). */
 int reth_replay_gather_to(reth_replay_t *h, int slot, reth_ipc_view_t *dst, int dst_slot, void *stream);
+
+/* ---- several sampler topics over one row store (start_server(samplers=[...]), server/main_loop.py:135-159:
+ *      every sampler sees every append and every update, loaders pick a topic).  The first topic
+ *      uses the row shard's own tree; each further topic is a tree-only handle (store_rows = 0, same
+ *      capacity, same device) that receives the same appends / updates.  gather_from() fills batch
+ *      slot dst_slot of the ROW shard `h` with the rows, indices and weights of the batch the index
+ *      shard `src` drew into its slot src_slot. */
+int reth_replay_gather_from(reth_replay_t *h, int dst_slot, reth_replay_t *src, int src_slot, void *stream);
 
 /* ---- measured loop (bench / learner-less soak): `steps` iterations of
  *      sample(batch) -> gather || update_slot(new priorities), the tree chain and the

@@ -111,6 +111,8 @@ SIGNATURES = {
     "reth_replay_pipe_issue": [_vp, _f64],
     "reth_replay_pipe_wait": [_vp, C.POINTER(C.c_int32)],
     "reth_replay_pipe_next": [_vp, _f64, C.POINTER(C.c_int32)],
+    "reth_replay_gather_from": [_vp, _i32, _vp, _i32, _vp],
+    "reth_replay_pipe_reserve": [_vp, _i32],
     "reth_replay_pipe_hold": [_vp, _i32],
     "reth_replay_pipe_advance": [_vp, _f64],
     "reth_replay_pipe_ready": [_vp, C.POINTER(_i32)],

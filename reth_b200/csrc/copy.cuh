@@ -212,9 +212,10 @@ __global__ void __launch_bounds__(kCopyThreads, kWiden ? 4 : 6) row_move_kernel(
 
 // indices / weights of a shard's slice of a global batch -> the same rows of a peer's batch slot
 __global__ void slice_copy_kernel(const int64_t *idx, const double *w, const int64_t *meta,
-                                  int64_t *dst_idx, double *dst_w)
+                                  int64_t *dst_idx, double *dst_w, int64_t *dst_meta = nullptr)
 {
     const int64_t first = meta[0], count = meta[1];
+    if (dst_meta && blockIdx.x == 0 && threadIdx.x == 0) { dst_meta[0] = first; dst_meta[1] = count; }
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (int64_t)gridDim.x * blockDim.x) {
         dst_idx[first + i] = idx[i];
         dst_w[first + i] = w[i];

@@ -98,6 +98,7 @@ struct reth_replay {
         int64_t issued = 0, waited = 0, upd_next = 0;
         int hold = 1;             // delivered groups that stay lent (the newest `hold` of them)
     } pipe;
+    int pipe_reserved = 0;        // batch slots at the end of the ring that a pipe never uses (other sampler topics)
     std::string error;
 };
 
@@ -1225,7 +1226,7 @@ RETH_EXPORT int reth_replay_pipe_open(reth_replay_t *h, int batch, int group, ui
     if (!h) return RETH_ERR_INVALID;
     auto &p = h->pipe;
     if (p.open) return fail(h, RETH_ERR_STATE, "a pipe is already open");
-    const int depth = (int)h->slots.size();
+    const int depth = (int)h->slots.size() - h->pipe_reserved;
     if (group < 1 || batch < 1 || batch > h->cfg.max_batch || (group > 1 && batch != h->cfg.max_batch))
         return fail(h, RETH_ERR_INVALID, "pipe: batch %d / group %d invalid (group > 1 needs batch == max_batch)", batch, group);
     if (depth / group < 2) return fail(h, RETH_ERR_INVALID, "pipe: ring_depth %d holds fewer than 2 groups of %d", depth, group);
@@ -1312,6 +1313,15 @@ RETH_EXPORT int reth_replay_pipe_next(reth_replay_t *h, double beta, int32_t *gr
     int rc = pipe_issue(h, beta, true);
     if (rc) return rc;
     return pipe_wait(h, group_out);
+}
+
+RETH_EXPORT int reth_replay_pipe_reserve(reth_replay_t *h, int n_slots)
+{
+    if (!h) return RETH_ERR_INVALID;
+    if (h->pipe.open) return fail(h, RETH_ERR_STATE, "pipe_reserve must precede pipe_open");
+    if (n_slots < 0 || n_slots > (int)h->slots.size() - 2) return fail(h, RETH_ERR_INVALID, "cannot reserve %d of %d batch slots", n_slots, (int)h->slots.size());
+    h->pipe_reserved = n_slots;
+    return RETH_OK;
 }
 
 RETH_EXPORT int reth_replay_pipe_hold(reth_replay_t *h, int groups)
@@ -1536,6 +1546,37 @@ RETH_EXPORT int reth_replay_gather_to(reth_replay_t *h, int slot, reth_ipc_view_
     CK(h, cudaGetLastError());
     h->st.kernel_launches++;
     if (!dst) h->slots[dst_slot].batch = b.batch;
+    return RETH_OK;
+}
+
+RETH_EXPORT int reth_replay_gather_from(reth_replay_t *h, int dst_slot, reth_replay_t *src, int src_slot, void *stream)
+{
+    if (!h || !src) return RETH_ERR_INVALID;
+    if (slot_ok(h, dst_slot)) return RETH_ERR_INVALID;
+    if (src_slot < 0 || src_slot >= (int)src->slots.size()) return fail(h, RETH_ERR_INVALID, "source slot %d outside the index shard's ring", src_slot);
+    if (src->cfg.device != h->cfg.device || src->cfg.capacity != h->cfg.capacity)
+        return fail(h, RETH_ERR_INVALID, "the index shard must live on the same device and span the same slots");
+    const BatchSlot &b = src->slots[src_slot];
+    if (b.batch <= 0) return fail(h, RETH_ERR_STATE, "source slot %d holds no sampled batch", src_slot);
+    if (b.batch > h->cfg.max_batch) return fail(h, RETH_ERR_INVALID, "batch of %d exceeds max_batch %d", b.batch, h->cfg.max_batch);
+    if (src == h && src_slot == dst_slot) return reth_replay_gather(h, dst_slot, stream);
+    DeviceGuard guard(h->cfg.device);
+    cudaStream_t s = S(stream);
+    BatchSlot &d = h->slots[dst_slot];
+    if (h->cfg.store_rows && h->cfg.n_columns > 0) {
+        RowArgs a;
+        build_row_args(h, a, d.cols, b.idx, b.batch, 0, true);
+        a.meta = b.meta;
+        a.dst_row_from_meta = 1;
+        int rc = launch_row_move<false>(h, a, s);
+        if (rc) return rc;
+        h->st.gathered_rows += b.batch;
+    }
+    slice_copy_kernel<<<(b.batch + 255) / 256, 256, 0, s>>>(b.idx, b.w, b.meta, d.idx, d.w, d.meta);
+    CK(h, cudaGetLastError());
+    h->st.kernel_launches++;
+    d.batch = b.batch;
+    d.partial = b.partial;
     return RETH_OK;
 }
 

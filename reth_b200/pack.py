@@ -200,6 +200,12 @@ def decode(buf):
     return _rebuild(header["meta"], body)
 
 
+def decode_src(buf):
+    """decode() plus the sender's [client id, message number] header field (None from a reference client)."""
+    header, body, _ = _split(buf)
+    return _rebuild(header["meta"], body), header.get(KEY_SRC)
+
+
 def is_columnar(buf):
     mv = memoryview(buf).cast("B")
     hl = int.from_bytes(mv[:4], "big")

@@ -69,10 +69,14 @@ class _Engine:
                 "sample_start": max(item.get("sample_start", 1000), self.batch_size),   # main_loop.py:144-145
                 "num_procs": item.get("num_procs", 1),
             }
-        if len(topics) != 1:
-            raise NotImplementedError("one sampler topic per buffer in this build")
+        # Several topics share the row store; every sampler sees every append and update
+        # (main_loop.py:58,79-88).  The first topic is served by the row shard's own tree and the
+        # prefetch pipeline; each further topic gets a tree-only index shard over the same slots and
+        # one reserved batch slot, and is served draw by draw (sample_topic).
+        self.topics = topics
         self.topic, self.sampler = next(iter(topics.items()))
         self.kind = self.sampler["kind"]                      # "per" | "uniform" | "fifo"
+        self.secondary = [t for t in topics if t != self.topic]
         # a custom cache policy keeps deciding slots on the host (BasePolicy.get_indices);
         # the default FIFO cursor lives in the shard
         self.cache_policy = cache_policy
@@ -106,10 +110,79 @@ class _Engine:
         # the conversion DQNSolver does first (reth/reth/algorithm/dqn/dqn_solver.py:71-75), fused into the gather
         cast = [self.float_frames if (np.dtype(dt) == np.uint8 and len(sh) >= 2) else None for dt, sh in self.struct]
         self.shard = ReplayShard(self.capacity, self.struct, max_batch=self.batch_size,
-                                 ring_depth=self.max_ring, device=self.device, min_mode=MIN_SERVICE,
-                                 out_cast=cast if self.float_frames else None)
+                                 ring_depth=self.max_ring + len(self.secondary), device=self.device,
+                                 min_mode=MIN_SERVICE, out_cast=cast if self.float_frames else None)
         self.stream = self.shard.pipe_stream
         self.shard.pipe_sampler(self.kind)
+        if self.secondary:
+            self.shard.pipe_reserve(len(self.secondary))
+        for j, t in enumerate(self.secondary):
+            st = self.topics[t]
+            st["shard"] = ReplayShard(self.capacity, [], max_batch=self.batch_size, ring_depth=2, device=self.device,
+                                      min_mode=MIN_SERVICE, store_rows=False)
+            st["slot"] = self.max_ring + j                     # its batch slot in the row shard's ring
+
+    def _notify_append(self, first, slots, weights):
+        """The append notice of the other topics' samplers (main_loop.py:58 -> sampler.update)."""
+        for t in self.secondary:
+            st = self.topics[t]
+            sh = st["shard"]
+            if slots is None:
+                sh.append([], weights, alpha=st["alpha"].value(), transform=True, stream=self.stream)
+            else:
+                sh.append_at(slots, [], weights, alpha=st["alpha"].value(), transform=True, stream=self.stream)
+            if st["kind"] == "uniform":
+                sh.uniform_note(slots, first_slot=first, n=len(weights), stream=self.stream)
+            elif st["kind"] == "fifo":
+                sh.fifo_push(slots, weights, first_slot=first, stream=self.stream)
+
+    def _notify_update(self, indices, weights, step):
+        for t in self.secondary:
+            st = self.topics[t]
+            if step:
+                st["alpha"].step()
+                st["beta"].step()
+            sh = st["shard"]
+            if st["kind"] == "per":
+                sh.update(np.asarray(indices), np.asarray(weights), alpha=st["alpha"].value(), transform=True,
+                          stream=self.stream)
+            elif st["kind"] == "uniform":
+                sh.uniform_note(np.asarray(indices), stream=self.stream)
+            else:
+                sh.fifo_push(np.asarray(indices), np.asarray(weights), stream=self.stream)
+
+    def topic_ready(self, topic):
+        st = self.topics[topic]
+        if self.shard is None or self.cnt < st["sample_start"]:
+            return False
+        if st["kind"] == "fifo":
+            return st["shard"].sampler_state()["fifo_len"] > self.batch_size
+        return True
+
+    def sample_topic(self, topic, timeout=60.0):
+        """One batch of a topic other than the first: drawn by its index shard, rows gathered from the
+        shared row store into the topic's batch slot (lent until the topic's next draw).
+        -> (batch slot, host indices int64[B], host weights float64[B])."""
+        t0 = time.time()
+        while not self.topic_ready(topic):
+            if self.closed:
+                raise RuntimeError("replay buffer terminated")
+            if time.time() - t0 > timeout:
+                raise TimeoutError("no batch available: fewer than sample_start transitions were appended")
+            time.sleep(0.001)
+        with self.lock:
+            self.flush()
+            st = self.topics[topic]
+            sh, B = st["shard"], self.batch_size
+            if st["kind"] == "per":
+                sh.sample(B, beta=st["beta"].value(), seed=0x70C1, slot=0, stream=self.stream)
+            elif st["kind"] == "uniform":
+                sh.sample_uniform(B, first_slot=0, n_slots=1, seed=0x70C1, stream=self.stream)
+            else:
+                sh.sample_fifo(B, first_slot=0, n_slots=1, stream=self.stream)
+            self.shard.gather_from(st["slot"], sh, 0, stream=self.stream)
+            _, idx, w = self.shard.slot_read(st["slot"], stream=self.stream)
+            return st["slot"], idx, w
 
     def append(self, data, weights):
         with self.lock:
@@ -121,6 +194,7 @@ class _Engine:
                     self.shard.uniform_note(None, first_slot=first, n=len(weights), stream=self.stream)
                 elif self.kind == "fifo":
                     self.shard.fifo_push(None, weights, first_slot=first, stream=self.stream)
+                self._notify_append(first, None, weights)
             else:
                 import torch
                 slots = np.asarray(self.cache_policy.get_indices(len(weights)), dtype=np.int64)
@@ -132,6 +206,7 @@ class _Engine:
                     self.shard.uniform_note(slots, stream=self.stream)
                 elif self.kind == "fifo":
                     self.shard.fifo_push(slots, weights, stream=self.stream)
+                self._notify_append(0, slots, weights)
             self.cnt += len(weights)
 
     # -- loader pipeline --------------------------------------------------
@@ -262,6 +337,8 @@ class _Engine:
                 self.sampler["beta"].step()
             n = len(indices)
             self.cnt += n
+            if self.secondary:
+                self._notify_update(indices, weights, step)
             if self.kind != "per":                            # sampler.update() of the plugin (sampler_loop.py:35)
                 if self.kind == "uniform":
                     self.shard.uniform_note(np.asarray(indices), stream=self.stream)
@@ -301,7 +378,7 @@ class _Engine:
         runs of learner-batch messages are staged with one copy each."""
         with self.lock:
             B, pipe = self.batch_size, self.pipe
-            if (self.shard is None or self.kind != "per" or pipe is None or not all(steps)
+            if (self.shard is None or self.kind != "per" or pipe is None or self.secondary or not all(steps)
                     or any(n != B for n in sizes)):
                 at = 0
                 for n, st in zip(sizes, steps):
@@ -372,6 +449,10 @@ class _Engine:
             if self.pipe is not None:
                 self.pipe.close()
                 self.pipe = None
+            for t in self.secondary:
+                sh = self.topics[t].pop("shard", None)
+                if sh is not None:
+                    sh.close()
             if self.shard is not None:
                 self.shard.close()
                 self.shard = None
@@ -458,11 +539,14 @@ class _LoaderBase:
 
     def __init__(self, meta_addr, topic="default", prefetch=1, ahead=0):
         self._eng = _engine(meta_addr)
-        assert topic == self._eng.topic
+        assert topic in self._eng.topics
+        self.topic = topic
+        self._primary = topic == self._eng.topic             # other topics are served draw by draw
         self.meta = {"capacity": self._eng.capacity, "batch_size": self._eng.batch_size}
         self.prefetch = max(1, int(prefetch))
         self.ahead = max(0, int(ahead))
-        self._eng.open_pipe(self.prefetch, self.ahead)
+        if self._primary:
+            self._eng.open_pipe(self.prefetch, self.ahead)
         self._open = True
 
     def __iter__(self):
@@ -471,16 +555,24 @@ class _LoaderBase:
     def __next__(self):
         return self.sample()
 
-    def get_indices(self):
-        """numpy_loader.py:53-56: (indices, weights) of the next batch."""
+    def _next(self):
+        """-> (batch slot, indices, weights) on the host."""
+        if not self._primary:
+            return self._eng.sample_topic(self.topic)
         slot, idx = self._eng.next_batch()
         pipe = self._eng.pipe
-        return np.array(idx), np.array(pipe.w_host[slot // pipe.group, slot % pipe.group])
+        return slot, np.array(idx), np.array(pipe.w_host[slot // pipe.group, slot % pipe.group])
+
+    def get_indices(self):
+        """numpy_loader.py:53-56: (indices, weights) of the next batch."""
+        _, idx, w = self._next()
+        return idx, w
 
     def close(self):
         if self._open:
             self._open = False
-            self._eng.release_pipe()
+            if self._primary:
+                self._eng.release_pipe()
 
     def __del__(self):
         try:
@@ -503,11 +595,10 @@ class NumpyLoader(_LoaderBase):
 
     def sample(self):
         eng = self._eng
-        slot, idx = eng.next_batch()
+        slot, idx, w = self._next()
         with eng.lock:
             data, _, _ = eng.shard.slot_read(slot, with_rows=True, stream=eng.stream)
-            pipe = eng.pipe
-            return data, np.array(idx), np.array(pipe.w_host[slot // pipe.group, slot % pipe.group])
+            return data, idx, w
 
 
 class TorchCudaLoader(_LoaderBase):
@@ -537,7 +628,10 @@ class TorchCudaLoader(_LoaderBase):
         self._views = {}                                      # slot -> cached zero-copy torch views
 
     def sample(self):
-        slot, idx = self._eng.next_batch()
+        if self._primary:
+            slot, idx = self._eng.next_batch()
+        else:
+            slot, idx, _ = self._eng.sample_topic(self.topic)
         v = self._views.get(slot)
         if v is None:
             data, _, weights, _ = self._eng.shard.slot_tensors(slot)

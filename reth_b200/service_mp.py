@@ -82,8 +82,9 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
     config = {"engine": "reth_b200", "capacity": capacity, "batch_size": batch_size, "device": device,
               "meta_addr": addrs["meta"], "append_addr": addrs["append"], "update_addr": addrs["update"],
               "loader_addr": addrs["loader"], "pid": os.getpid(), "host_id": _host_id(),
-              "sampler_info": {eng.topic: {"topic": eng.topic, "sampler_cls": eng.kind,
-                                           "sample_start": eng.sampler["sample_start"], "batch_size": batch_size}}}
+              "sampler_info": {t: {"topic": t, "sampler_cls": st["kind"], "sample_start": st["sample_start"],
+                                   "batch_size": batch_size, "primary": t == eng.topic}
+                               for t, st in eng.topics.items()}}
     poller = zmq.Poller()
     for s in (meta, app, upd, ldr):
         poller.register(s, zmq.POLLIN)
@@ -131,8 +132,10 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
         build's compact frame holding one or more such messages back to back."""
         mv = memoryview(buf)
         if mv[:4] != _UPD_MAGIC:
-            indices, weights, step = pack.decode(mv)
+            (indices, weights, step), src = pack.decode_src(mv)
             eng.update(np.asarray(indices), np.asarray(weights), bool(step))
+            if src:
+                seen.setdefault(src[0], [0, 0])[1] = int(src[1])
             return
         _, cid, seq, count = _UPD_FRAME.unpack_from(mv, 0)
         at = _UPD_FRAME.size
@@ -197,6 +200,13 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
             if eng.shard is None:                      # row struct unknown until the first append
                 waiting.append((ident, req))
                 return
+            ex = _cabi.IpcExport()
+            eng.shard._ck(_cabi.lib().reth_replay_ipc_export(eng.shard._h, C.byref(ex)))
+            struct = [[np.dtype(dt).str, list(sh)] for dt, sh in eng.shard.struct]
+            if req.get("topic", eng.topic) != eng.topic:   # another sampler topic: served draw by draw
+                reply(ident, {"ok": True, "op": "open", "struct": struct, "batch_size": batch_size, "group": 1,
+                              "ahead": 0, "lend": 1, "ring_depth": eng.shard.ring_depth}, bytes(ex))
+                return
             # fit the loader's geometry into the batch ring: three groups when it asks ahead
             group = max(1, int(req.get("prefetch", 1)))
             ahead = max(0, int(req.get("ahead", 0)))
@@ -204,11 +214,16 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
                 group = max(1, eng.max_ring // 3)
             ahead = min(ahead, max(0, eng.max_ring // group - 1))
             eng.open_pipe(group, ahead, req.get("lend", 1))
-            ex = _cabi.IpcExport()
-            eng.shard._ck(_cabi.lib().reth_replay_ipc_export(eng.shard._h, C.byref(ex)))
-            struct = [[np.dtype(dt).str, list(sh)] for dt, sh in eng.shard.struct]
             reply(ident, {"ok": True, "op": "open", "struct": struct, "batch_size": batch_size, "group": eng.group,
                           "ahead": eng.ahead, "lend": eng.lend, "ring_depth": eng.shard.ring_depth}, bytes(ex))
+        elif op == "next" and req.get("topic", eng.topic) != eng.topic:
+            topic = req["topic"]
+            if not eng.topic_ready(topic):
+                waiting.append((ident, req))
+                return
+            slot, idx, w = eng.sample_topic(topic)
+            reply(ident, {"ok": True, "op": "next", "group": -1, "first_slot": int(slot), "n": 1},
+                  np.ascontiguousarray(idx[:batch_size]).tobytes(), np.ascontiguousarray(w[:batch_size]).tobytes())
         elif op == "next":
             if not eng.ready():
                 waiting.append((ident, req))
@@ -221,7 +236,8 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
             reply(ident, {"ok": True, "op": "rows"}, *[np.ascontiguousarray(c).tobytes() for c in data])
         elif op == "close":
             owed[:] = [i for i in owed if i != ident]
-            eng.release_pipe()
+            if req.get("topic", eng.topic) == eng.topic:
+                eng.release_pipe()
             reply(ident, {"ok": True, "op": "close"})
         elif op == "drain":
             eng.drain()
@@ -524,8 +540,11 @@ class Client:
 
     def update_priorities(self, indices, weights, step=True):
         assert len(indices) == len(weights)                   # :38
-        if self.wire == "rows":                               # exactly the reference's message
-            self.update_sock.send(pack.encode([np.asarray(indices), np.asarray(weights), step]), copy=False)
+        if self.wire == "rows":                               # the reference's message (+ a header field it ignores)
+            with self._lock:
+                self._useq += 1
+                self.update_sock.send(pack.encode([np.asarray(indices), np.asarray(weights), step],
+                                                  extra={pack.KEY_SRC: [self._id.hex(), self._useq]}), copy=False)
             return
         idx = indices if (type(indices) is np.ndarray and indices.dtype == np.int64) else np.asarray(indices, dtype=np.int64)
         w = weights if type(weights) is np.ndarray else np.asarray(weights)
@@ -592,9 +611,7 @@ def _flush_clients(meta_addr):
     so that the server takes those writes in before it acts on the request."""
     after = {}
     for c in list(_CLIENTS.get(meta_addr, ())):
-        a, u = c.flush()
-        if c.wire != "rows" or a:                             # reference-format update messages carry no number
-            after[c._id.hex()] = [a, u if c.wire != "rows" else 0]
+        after[c._id.hex()] = list(c.flush())
     return after
 
 
@@ -626,6 +643,7 @@ class _RemoteLoader:
         from . import _cabi
         self.meta = get_meta(meta_addr)
         assert topic in self.meta["sampler_info"]
+        self.topic = topic
         self._zmq = zmq
         self.sock = zmq.Context.instance().socket(zmq.DEALER)
         self.sock.setsockopt(zmq.LINGER, 0)
@@ -651,7 +669,7 @@ class _RemoteLoader:
         if self._open:
             return
         from . import _cabi
-        head, blobs = self._call({"op": "open", "prefetch": self.prefetch, "ahead": self.ahead,
+        head, blobs = self._call({"op": "open", "topic": self.topic, "prefetch": self.prefetch, "ahead": self.ahead,
                                   "lend": 2 if self.ahead > 0 else 1})
         self._open = True
         self.struct = [(np.dtype(dt), tuple(sh)) for dt, sh in head["struct"]]
@@ -704,7 +722,7 @@ class _RemoteLoader:
 
     def _ask(self):
         # this process's appends and write-backs are taken in before the draw
-        self._send({"op": "next", "after": _flush_clients(self.meta["meta_addr"])})
+        self._send({"op": "next", "topic": self.topic, "after": _flush_clients(self.meta["meta_addr"])})
         self._asked = True
 
     def _next(self):
@@ -739,7 +757,7 @@ class _RemoteLoader:
         if self._open:
             self._open = False
             try:
-                self._call({"op": "close"})
+                self._call({"op": "close", "topic": self.topic})
             except Exception:
                 pass
         if self._view is not None:

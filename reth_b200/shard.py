@@ -506,6 +506,15 @@ class ReplayShard:
         self._ck(self._lib.reth_replay_gather_to(self._h, int(slot), ring._v if ring is not None else None,
                                                  int(dst_slot), self._s(stream)))
 
+    def gather_from(self, dst_slot, index_shard, src_slot, stream=None):
+        """Rows, indices and weights of the batch `index_shard` (a tree-only shard over the same slots:
+        another sampler topic) drew into its slot src_slot -> this shard's batch slot dst_slot."""
+        self._ck(self._lib.reth_replay_gather_from(self._h, int(dst_slot), index_shard._h, int(src_slot), self._s(stream)))
+
+    def pipe_reserve(self, n_slots):
+        """Keep the last n_slots batch slots out of the loader pipe (other sampler topics use them)."""
+        self._ck(self._lib.reth_replay_pipe_reserve(self._h, int(n_slots)))
+
     def open_pipe(self, batch, group, seed=0):
         return ShardPipe(self, batch, group, seed)
 

@@ -181,3 +181,63 @@ def test_start_server_with_uniform_and_fifo_samplers(reth_buffer):
             loader.close()
         finally:
             proc.terminate()
+
+
+def test_several_topics_over_one_row_store(reth_buffer):
+    """start_server(samplers=[...]) with three topics (server/main_loop.py:135-159): every sampler
+    sees every append and update, loaders pick a topic, all read the same rows."""
+    from reth_buffer.sampler import FIFOSampler, UniformSampler
+    from reth_b200 import service
+    B, n = 64, 1024
+    samplers = [{"sampler_cls": reth_buffer.PERSampler, "sample_start": B, "kwargs": {"alpha": 1.0, "beta": 0.4}},
+                {"sampler_cls": reth_buffer.PERSampler, "topic": "soft", "sample_start": B,
+                 "kwargs": {"alpha": 0.5, "beta": 1.0}},
+                {"sampler_cls": UniformSampler, "topic": "uni", "sample_start": B},
+                {"sampler_cls": FIFOSampler, "topic": "queue", "sample_start": B}]
+    proc, addr = reth_buffer.start_server(4096, B, samplers=samplers)
+    try:
+        client = reth_buffer.Client(addr)
+        rng = np.random.default_rng(8)
+        ids = np.arange(n)
+        frames = rng.integers(0, 256, (n, 2, 21, 21), dtype=np.uint8)
+        w0 = (rng.random(n) + 0.5).astype(np.float32)
+        for st in range(0, n, 256):
+            client.append([frames[st:st + 256], ids[st:st + 256]], w0[st:st + 256])
+        main = reth_buffer.TorchCudaLoader(addr, buffer_size=4)
+        soft = reth_buffer.TorchCudaLoader(addr, topic="soft")
+        uni = reth_buffer.NumpyLoader(addr, topic="uni")
+        queue = reth_buffer.NumpyLoader(addr, topic="queue")
+        with pytest.raises(AssertionError):
+            reth_buffer.NumpyLoader(addr, topic="nope")
+        eng = service._ENGINES[addr]
+        # the second PER topic keeps its own tree: (w + 1e-6)^0.5 over the same slots
+        total, _ = eng.topics["soft"]["shard"].root()
+        assert np.isclose(total, np.sum((w0.astype(np.float32) + np.float32(1e-6)) ** np.float32(0.5), dtype=np.float64), rtol=1e-6)
+        total, _ = eng.shard.root()
+        assert np.isclose(total, np.sum(w0 + np.float32(1e-6), dtype=np.float64), rtol=1e-6)
+        for it in range(4):
+            data, indices, weights = soft.sample()
+            assert np.array_equal(data[1].cpu().numpy(), indices) and np.array_equal(data[0].cpu().numpy(), frames[indices])
+            p = (w0 + np.float32(1e-6)) ** np.float32(0.5)          # beta 1.0: weight = p_min / p
+            assert np.allclose(weights.cpu().numpy(), p.min() / p[indices], rtol=1e-5)
+            assert float(weights.max()) <= 1.0 + 1e-12
+            batch, indices, weights = uni.sample()
+            assert np.array_equal(batch[1], indices) and np.array_equal(batch[0], frames[indices]) and np.all(weights == 1.0)
+            batch, indices, weights = queue.sample()
+            assert np.array_equal(indices, np.arange(it * B, (it + 1) * B)) and np.array_equal(batch[0], frames[indices])
+            data, indices, weights = main.sample()
+            assert np.array_equal(data[1].cpu().numpy(), indices)
+        # an update reaches every PER tree: one slot takes (almost) all the mass on both topics
+        client.update_priorities(ids, np.full(n, 1e-4, np.float32))
+        client.update_priorities(np.array([77]), np.array([1e8], np.float32))
+        eng.drain()
+        main.close()                                          # drop the groups drawn ahead of the update
+        main = reth_buffer.TorchCudaLoader(addr, buffer_size=1)
+        for ld in (main, soft):
+            data, indices, weights = ld.sample()
+            assert np.mean(indices == 77) > 0.9
+            assert np.array_equal(data[0].cpu().numpy(), frames[indices])
+        for ld in (main, soft, uni, queue):
+            ld.close()
+    finally:
+        proc.terminate()

@@ -126,6 +126,38 @@ def test_draw_sees_earlier_writes_of_the_same_process(reth_buffer, wire):
         proc.join()
 
 
+def test_second_topic_across_processes(reth_buffer):
+    """Two sampler topics on a spawned server: the loader of the second topic gets its batches in the
+    topic's reserved slot of the shared batch ring (CUDA IPC), rows consistent with its indices."""
+    from reth_buffer.sampler import UniformSampler
+    B, n = 32, 512
+    samplers = [{"sampler_cls": reth_buffer.PERSampler, "sample_start": B},
+                {"sampler_cls": UniformSampler, "topic": "uni", "sample_start": B}]
+    proc, addr = reth_buffer.start_server(2048, B, samplers=samplers)
+    try:
+        client = reth_buffer.Client(addr)
+        ids = np.arange(n)
+        feat = np.repeat(ids[:, None], 8, 1).astype(np.float32)
+        client.append([ids, feat], np.ones(n, np.float32))
+        per = reth_buffer.TorchCudaLoader(addr, buffer_size=2)
+        uni = reth_buffer.TorchCudaLoader(addr, topic="uni")
+        uni_np = reth_buffer.NumpyLoader(addr, topic="uni")
+        for _ in range(5):
+            for ld in (per, uni):
+                data, indices, weights = ld.sample()
+                assert np.array_equal(data[0].cpu().numpy(), indices)
+                assert np.array_equal(data[1].cpu().numpy(), feat[indices])
+            batch, indices, weights = uni_np.sample()
+            assert np.array_equal(batch[0], indices) and np.all(weights == 1.0)
+            client.update_priorities(indices, np.ones(B, np.float32))
+        assert per.drain()["cnt"] == n + 5 * B
+        for ld in (per, uni, uni_np):
+            ld.close()
+    finally:
+        proc.terminate()
+        proc.join()
+
+
 def _producer(addr, n_batches, seed):
     sys.path.insert(0, ROOT)
     from reth_b200 import service
