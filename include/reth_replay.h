@@ -61,8 +61,10 @@ typedef struct reth_replay_config {
     int32_t update_cluster;                 /* CTAs per cluster of the tree-repair kernel (0 = default: 16, or 8 if the device cannot host 16) */
     int32_t gather_mode;                    /* 0 = auto (= 1, the faster one on B200), 1 = LDG/STG.128,
                                                2 = TMA bulk copies (cp.async.bulk + mbarrier ring) */
-    int32_t store_rows;                     /* 0 = tree only (no frame ring; config 5 "tree-only") */
-    int32_t reserved[5];
+    int32_t store_rows;                     /* 0 = tree only (no row storage; config 5 "tree-only") */
+    int32_t frame_bytes;                    /* frame de-duplication: bytes of one frame (multiple of 16) and */
+    int32_t frame_capacity;                 /* frames in the frame ring; used by RETH_COL_FRAMES columns */
+    int32_t reserved[3];
     /* per column, what the GATHER emits into the learner batch (ring storage is unchanged):
      * 0 raw bytes; 1 uint8 -> float32; 2 uint8 -> float32 / 255.  Replaces the learner's first pass
      * over the batch, ensure_tensor(s0, torch.float, ...) in reth/reth/algorithm/dqn/dqn_solver.py:71-75
@@ -72,6 +74,13 @@ typedef struct reth_replay_config {
     int32_t out_cast[RETH_MAX_COLUMNS];
 } reth_replay_config;
 typedef enum reth_cast { RETH_CAST_NONE = 0, RETH_CAST_U8_F32 = 1, RETH_CAST_U8_F32_UNIT = 2 } reth_cast;
+/* out_cast[c] |= RETH_COL_FRAMES: column c is a FRAME-REFERENCE column.  Its stored row is K = row_bytes[c] / 4
+ * int32 slots of the shard's frame ring (reth_replay_append_frames); the gather expands it to the K frames
+ * themselves, K * frame_bytes per batch row (x4 as float32 with a cast).  Single frames are then stored once
+ * instead of once per stack position and per s0/s1 (the reference's FrameStack concatenates k frames into every
+ * observation, reth/reth/env/util.py:179-209; its LazyFrames remedy is commented out at :207): an Atari
+ * transition costs 7 KB of HBM instead of 56 KB, so a GPU holds 8x the transitions. */
+#define RETH_COL_FRAMES 0x100
 
 /* counters for the throughput report (SURVEY.md 5 "Metrics") */
 typedef struct reth_replay_stats {
@@ -106,6 +115,15 @@ int reth_replay_clear(reth_replay_t *h, void *stream);
 int reth_replay_append(reth_replay_t *h, const void *const *cols, int cols_loc,
                        const void *prio, int prio_dtype, int prio_loc, int64_t n,
                        double alpha, int transform, int64_t *first_slot_out, void *stream);
+
+/* Frame ring of a shard with RETH_COL_FRAMES columns: n frames of frame_bytes, stored at frame slots
+ * tail, tail+1, ... mod frame_capacity; first_frame_out (host, may be NULL) gets `tail`.  The caller writes
+ * those slots into the frame-reference columns of the transitions it appends afterwards.  A frame slot is
+ * reused after frame_capacity later frames: size the ring for the frames `capacity` transitions span. */
+int reth_replay_append_frames(reth_replay_t *h, const void *frames, int frames_loc, int64_t n,
+                              int64_t *first_frame_out, void *stream);
+/* parity / debug: frames [first_frame, first_frame + n) of the ring -> host */
+int reth_replay_frame_read(reth_replay_t *h, int64_t first_frame, int64_t n, void *out_host, void *stream);
 
 /* Plugin cache policies (cache_policy/base_policy.py:4-7): rows go to caller-chosen slots.
  * slots: int64[n] on slots_loc; duplicates resolve to the last row in batch order. */

@@ -34,7 +34,10 @@ class Config(C.Structure):
                 ("row_bytes", C.c_int64 * RETH_MAX_COLUMNS), ("max_batch", C.c_int32),
                 ("ring_depth", C.c_int32), ("device", C.c_int32), ("min_mode", C.c_int32),
                 ("update_cluster", C.c_int32), ("gather_mode", C.c_int32), ("store_rows", C.c_int32),
-                ("reserved", C.c_int32 * 5), ("out_cast", C.c_int32 * RETH_MAX_COLUMNS)]
+                ("frame_bytes", C.c_int32), ("frame_capacity", C.c_int32), ("reserved", C.c_int32 * 3),
+                ("out_cast", C.c_int32 * RETH_MAX_COLUMNS)]
+
+COL_FRAMES = 0x100                       # RETH_COL_FRAMES
 
 
 class Stats(C.Structure):
@@ -113,6 +116,8 @@ SIGNATURES = {
     "reth_replay_pipe_next": [_vp, _f64, C.POINTER(C.c_int32)],
     "reth_replay_gather_from": [_vp, _i32, _vp, _i32, _vp],
     "reth_replay_pipe_reserve": [_vp, _i32],
+    "reth_replay_append_frames": [_vp, _vp, _i32, _i64, C.POINTER(_i64), _vp],
+    "reth_replay_frame_read": [_vp, _i64, _i64, _vp, _vp],
     "reth_replay_pipe_hold": [_vp, _i32],
     "reth_replay_pipe_advance": [_vp, _f64],
     "reth_replay_pipe_ready": [_vp, C.POINTER(_i32)],

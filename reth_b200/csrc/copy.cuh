@@ -210,6 +210,102 @@ __global__ void __launch_bounds__(kCopyThreads, kWiden ? 4 : 6) row_move_kernel(
     }
 }
 
+// ------------------------------------------- gather of frame-reference columns --
+// Frame de-duplication (the reference's FrameStack re-stores every frame k times,
+// reth/reth/env/util.py:179-209, its LazyFrames remedy is commented out): single frames live ONCE in
+// a frame ring; a frame-reference column of the row struct stores K int32 frame slots per
+// transition and the gather expands them into the K-frame stack the learner expects:
+//   batch[row][k] = frames[ ring_refs[idx[row]][k] ]      (optionally widened to float32)
+// One work item = (column, row, k, chunk of the frame), 256 threads moving 16-byte vectors.
+struct FrameCol {
+    const uint8_t *refs;  // ring column of the references: int32[K] per slot
+    uint8_t *batch;       // batch column base: K * fb (x4 when cast) bytes per row
+    int64_t rb;           // bytes per slot of the reference column = 4 * K
+    int32_t K;
+    int32_t cast;         // 0 raw, 1 u8 -> f32, 2 u8 -> f32 / 255
+    int32_t split;        // pieces per frame: K * split pieces are dealt to the warps of the CTA
+};
+
+struct FrameArgs {
+    FrameCol col[kMaxCols];
+    int32_t ncols;
+    const uint8_t *frames;     // frame ring
+    int64_t fb;                // bytes per frame (multiple of 16)
+    int64_t fcap;              // frames in the ring
+    const int64_t *idx;
+    int32_t batch;
+    const int64_t *meta;
+    int32_t dst_row_from_meta;
+    int64_t capacity;
+    int32_t *err;
+};
+
+// One work item = the K-frame stack of (batch row, frame column); items of the same row are adjacent in
+// the grid, so the s0 and s1 stacks of a transition (which share K - 1 frames) are read at about the same
+// time and the second read of a shared frame hits L2.  Inside an item every warp owns (frame k, part of
+// it): the reference is one uniform load per warp, then 32 lanes stream 16-byte vectors, 4 in flight each.
+__global__ void __launch_bounds__(kCopyThreads, 6) frame_gather_kernel(const FrameArgs a)
+{
+    constexpr int kWarps = kCopyThreads / 32;
+    const int rows = a.meta ? (int)a.meta[1] : a.batch;
+    const int64_t row0 = (a.meta && a.dst_row_from_meta) ? a.meta[0] : 0;
+    const int upf = (int)(a.fb >> 4);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t items = (int64_t)a.batch * a.ncols;
+    for (int64_t item = blockIdx.x; item < items; item += gridDim.x) {
+        const int row = (int)(item / a.ncols);
+        const FrameCol &col = a.col[(int)(item - (int64_t)row * a.ncols)];
+        if (row >= rows) continue;
+        const int64_t slot = a.idx[row];
+        if (slot < 0 || slot >= a.capacity) { if (threadIdx.x == 0) atomicOr(a.err, 1); continue; }
+        const int32_t *refs = (const int32_t *)(col.refs + slot * col.rb);
+        const int64_t out_row = (int64_t)row + row0;
+        const int pieces = col.K * col.split;
+        for (int p = warp; p < pieces; p += kWarps) {
+            const int k = p / col.split, part = p - k * col.split;
+            const int64_t ref = __ldg(refs + k);
+            if (ref < 0 || ref >= a.fcap) { if (lane == 0) atomicOr(a.err, 1); continue; }
+            const int u0 = (int)((int64_t)upf * part / col.split), u1 = (int)((int64_t)upf * (part + 1) / col.split);
+            if (col.cast) {
+                // lane = one 32-bit word (4 uint8) in, one 16 B vector (4 float32) out
+                const uint32_t *w32 = (const uint32_t *)(a.frames + ref * a.fb) + u0 * 4;
+                uint4 *d4 = (uint4 *)(col.batch + (out_row * col.K + k) * a.fb * 4) + u0 * 4;
+                const bool unit = col.cast == 2;
+                const int n4 = (u1 - u0) * 4;
+                int j = lane;
+                for (; j + 96 < n4; j += 128) {
+                    const uint32_t a0 = ld_stream32(w32 + j), a1 = ld_stream32(w32 + j + 32);
+                    const uint32_t a2 = ld_stream32(w32 + j + 64), a3 = ld_stream32(w32 + j + 96);
+                    st_stream(d4 + j, u8x4_to_f32(a0, unit));
+                    st_stream(d4 + j + 32, u8x4_to_f32(a1, unit));
+                    st_stream(d4 + j + 64, u8x4_to_f32(a2, unit));
+                    st_stream(d4 + j + 96, u8x4_to_f32(a3, unit));
+                }
+                for (; j < n4; j += 32) st_stream(d4 + j, u8x4_to_f32(ld_stream32(w32 + j), unit));
+                continue;
+            }
+            const uint4 *sp = (const uint4 *)(a.frames + ref * a.fb) + u0;
+            uint4 *d = (uint4 *)(col.batch + (out_row * col.K + k) * a.fb) + u0;
+            const int n = u1 - u0;
+            int j = lane;
+            for (; j + 96 < n; j += 128) {
+                const uint4 v0 = ld_stream(sp + j), v1 = ld_stream(sp + j + 32);
+                const uint4 v2 = ld_stream(sp + j + 64), v3 = ld_stream(sp + j + 96);
+                st_stream(d + j, v0); st_stream(d + j + 32, v1);
+                st_stream(d + j + 64, v2); st_stream(d + j + 96, v3);
+            }
+            uint4 v[3];
+            int cnt = 0;
+#pragma unroll
+            for (int q = 0; q < 3; ++q)
+                if (j + q * 32 < n) { v[q] = ld_stream(sp + j + q * 32); cnt = q + 1; }
+#pragma unroll
+            for (int q = 0; q < 3; ++q)
+                if (q < cnt) st_stream(d + j + q * 32, v[q]);
+        }
+    }
+}
+
 // indices / weights of a shard's slice of a global batch -> the same rows of a peer's batch slot
 __global__ void slice_copy_kernel(const int64_t *idx, const double *w, const int64_t *meta,
                                   int64_t *dst_idx, double *dst_w, int64_t *dst_meta = nullptr)

@@ -69,6 +69,10 @@ struct reth_replay {
     cudaEvent_t last_gather_ev = nullptr;     // newest gather of the internal streams (appends wait for it: rows stay atomic)
     int update_cluster = 8;
     int64_t out_rb[kMaxCols] = {};      // bytes of one row of each BATCH column (4x row_bytes when the gather widens)
+    int col_frames[kMaxCols] = {};      // K > 0: the column stores K int32 frame references per row
+    int n_frame_cols = 0;
+    uint8_t *frames = nullptr;          // frame ring: frame_capacity x frame_bytes
+    int64_t frame_tail = 0, frames_appended = 0;
     int max_dyn_smem = 0;               // opt-in shared memory per block
     bool gather_bulk = false;           // gather through row_gather_bulk_kernel (TMA bulk copies)
     int bulk_grid_cap = 0;              // RETH_BULK_GRID at create time: cap on the persistent grid (tests)
@@ -151,6 +155,7 @@ void free_all(reth_replay *h)
     cudaFree(h->stage_idx); cudaFree(h->stage_prio); cudaFree(h->stage_u);
     if (h->host_pin) cudaFreeHost(h->host_pin);
     for (int c = 0; c < kMaxCols; ++c) cudaFree(h->ring[c]);
+    cudaFree(h->frames);
     for (int c = 0; c < kMaxCols; ++c) cudaFree(h->slot_cols[c]);
     cudaFree(h->slot_idx); cudaFree(h->slot_w); cudaFree(h->slot_prio); cudaFree(h->slot_meta);
     for (auto e : h->ev_sampled) cudaEventDestroy(e);
@@ -216,8 +221,20 @@ RETH_EXPORT int reth_replay_create(const reth_replay_config *cfg, reth_replay_t 
     if (h->cfg.ring_depth < 1) h->cfg.ring_depth = 2;
     h->geom = make_geom(cfg->capacity);
     for (int c = 0; c < cfg->n_columns; ++c) {
-        if (cfg->out_cast[c] < 0 || cfg->out_cast[c] > 2) { delete h; return fail(nullptr, RETH_ERR_INVALID, "out_cast[%d] invalid", c); }
-        h->out_rb[c] = cfg->row_bytes[c] * (cfg->out_cast[c] ? 4 : 1);
+        const int cast = cfg->out_cast[c] & ~RETH_COL_FRAMES;
+        if (cfg->out_cast[c] < 0 || cast > 2) { delete h; return fail(nullptr, RETH_ERR_INVALID, "out_cast[%d] invalid", c); }
+        h->cfg.out_cast[c] = cast;                          // the cast alone from here on
+        if (cfg->out_cast[c] & RETH_COL_FRAMES) {
+            if (cfg->frame_bytes < 16 || cfg->frame_bytes % 16 || cfg->frame_capacity < 1 || cfg->row_bytes[c] % 4 || !cfg->store_rows) {
+                delete h;
+                return fail(nullptr, RETH_ERR_INVALID, "frame column %d needs frame_bytes %% 16 == 0, frame_capacity >= 1, row_bytes = 4 * K", c);
+            }
+            h->col_frames[c] = (int)(cfg->row_bytes[c] / 4);
+            h->n_frame_cols++;
+            h->out_rb[c] = (int64_t)h->col_frames[c] * cfg->frame_bytes * (cast ? 4 : 1);
+        } else {
+            h->out_rb[c] = cfg->row_bytes[c] * (cast ? 4 : 1);
+        }
     }
     h->update_cluster = cfg->update_cluster > 0 ? cfg->update_cluster : 8;
     DeviceGuard guard(cfg->device);
@@ -245,7 +262,7 @@ RETH_EXPORT int reth_replay_create(const reth_replay_config *cfg, reth_replay_t 
         for (int c = 0; c < cfg->n_columns; ++c)
             if (cfg->row_bytes[c] % 16 == 0 && cfg->row_bytes[c] >= 256) any_wide = true;
         for (int c = 0; c < cfg->n_columns; ++c)
-            if (cfg->out_cast[c]) any_wide = false;          // the DMA gather cannot widen: LDG/STG kernel
+            if (cfg->out_cast[c]) any_wide = false;          // the DMA gather cannot widen (or expand frame references): LDG/STG kernel
         h->gather_bulk = (mode == 2) && any_wide;   // auto = LDG/STG.128: measured faster (profiles/r01_gather_sweep.log)
         if (const char *e = getenv("RETH_BULK_GRID")) h->bulk_grid_cap = atoi(e);
         if (h->gather_bulk)
@@ -271,6 +288,10 @@ RETH_EXPORT int reth_replay_create(const reth_replay_config *cfg, reth_replay_t 
             CKC(cudaMalloc((void **)&h->ring[c], (size_t)cfg->capacity * cfg->row_bytes[c]));
             *acct += cfg->capacity * cfg->row_bytes[c];
         }
+    if (h->n_frame_cols) {
+        CKC(cudaMalloc((void **)&h->frames, (size_t)cfg->frame_capacity * cfg->frame_bytes));
+        *acct += (int64_t)cfg->frame_capacity * cfg->frame_bytes;
+    }
     h->slots.resize(h->cfg.ring_depth);
     const size_t depth = (size_t)h->cfg.ring_depth, mb = (size_t)cfg->max_batch;
     if (cfg->store_rows)
@@ -453,6 +474,41 @@ RETH_EXPORT int reth_replay_clear(reth_replay_t *h, void *stream)
     return RETH_OK;
 }
 
+RETH_EXPORT int reth_replay_append_frames(reth_replay_t *h, const void *frames, int frames_loc, int64_t n,
+                                          int64_t *first_frame_out, void *stream)
+{
+    if (!h) return RETH_ERR_INVALID;
+    if (!h->frames) return fail(h, RETH_ERR_STATE, "this shard has no frame ring (no frame-reference column)");
+    const int64_t cap = h->cfg.frame_capacity, fb = h->cfg.frame_bytes;
+    if (n < 0 || n > cap) return fail(h, RETH_ERR_INVALID, "append of %lld frames exceeds the frame ring (%lld)", (long long)n, (long long)cap);
+    if (n > 0 && !frames) return fail(h, RETH_ERR_INVALID, "frames is null");
+    if (first_frame_out) *first_frame_out = h->frame_tail;
+    if (n == 0) return RETH_OK;
+    DeviceGuard guard(h->cfg.device);
+    cudaStream_t s = S(stream);
+    if (h->last_gather_ev) CK(h, cudaStreamWaitEvent(s, h->last_gather_ev, 0));   // a running gather may still read the slots
+    const cudaMemcpyKind kind = frames_loc == RETH_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+    const int64_t len1 = n < cap - h->frame_tail ? n : cap - h->frame_tail, len2 = n - len1;
+    CK(h, cudaMemcpyAsync(h->frames + h->frame_tail * fb, frames, (size_t)(len1 * fb), kind, s));
+    if (len2 > 0) CK(h, cudaMemcpyAsync(h->frames, (const uint8_t *)frames + len1 * fb, (size_t)(len2 * fb), kind, s));
+    h->frame_tail = (h->frame_tail + n) % cap;
+    h->frames_appended += n;
+    return RETH_OK;
+}
+
+RETH_EXPORT int reth_replay_frame_read(reth_replay_t *h, int64_t first_frame, int64_t n, void *out_host, void *stream)
+{
+    if (!h || !out_host) return RETH_ERR_INVALID;
+    if (!h->frames) return fail(h, RETH_ERR_STATE, "this shard has no frame ring");
+    const int64_t cap = h->cfg.frame_capacity, fb = h->cfg.frame_bytes;
+    if (first_frame < 0 || n < 0 || first_frame + n > cap) return fail(h, RETH_ERR_INVALID, "frames %lld..%lld outside the ring", (long long)first_frame, (long long)(first_frame + n));
+    DeviceGuard guard(h->cfg.device);
+    cudaStream_t s = S(stream);
+    CK(h, cudaMemcpyAsync(out_host, h->frames + first_frame * fb, (size_t)(n * fb), cudaMemcpyDeviceToHost, s));
+    CK(h, cudaStreamSynchronize(s));
+    return RETH_OK;
+}
+
 RETH_EXPORT int reth_replay_append(reth_replay_t *h, const void *const *cols, int cols_loc,
                                    const void *prio, int prio_dtype, int prio_loc, int64_t n,
                                    double alpha, int transform, int64_t *first_slot_out, void *stream)
@@ -610,6 +666,11 @@ void build_row_args(reth_replay *h, RowArgs &a, uint8_t *const *batch_cols, cons
         col.batch = batch_cols[c];
         col.rb = h->cfg.row_bytes[c];
         col.cast = widen ? h->cfg.out_cast[c] : 0;
+        if (widen && h->col_frames[c]) {                    // gather: expanded by frame_gather_kernel instead
+            col.chunks = -1;
+            col.cast = 0;
+            continue;
+        }
         const bool wide = (col.rb % 16 == 0) && col.rb >= 256 && ((uintptr_t)col.batch % 16 == 0);
         if (wide) {
             const int64_t upr = col.rb / 16;
@@ -637,6 +698,31 @@ int launch_row_move(reth_replay *h, const RowArgs &a, cudaStream_t s)
     const unsigned grid = (unsigned)(total < maxg ? total : maxg);
     if (!kScatter && widen) row_move_kernel<false, true><<<grid, kCopyThreads, 0, s>>>(a);
     else row_move_kernel<kScatter><<<grid, kCopyThreads, 0, s>>>(a);
+    CK(h, cudaGetLastError());
+    h->st.kernel_launches++;
+    return RETH_OK;
+}
+
+// Frame-reference columns of a gather (frame_gather_kernel); no-op when the struct has none.
+int launch_frame_gather(reth_replay *h, uint8_t *const *batch_cols, const int64_t *idx, int batch,
+                        const int64_t *meta, int dst_row_from_meta, cudaStream_t s)
+{
+    if (!h->n_frame_cols) return RETH_OK;
+    FrameArgs a = {};
+    a.frames = h->frames; a.fb = h->cfg.frame_bytes; a.fcap = h->cfg.frame_capacity;
+    a.idx = idx; a.batch = batch; a.meta = meta; a.dst_row_from_meta = dst_row_from_meta;
+    a.capacity = h->cfg.capacity; a.err = h->err;
+    for (int c = 0; c < h->cfg.n_columns; ++c) {
+        if (!h->col_frames[c]) continue;
+        FrameCol &col = a.col[a.ncols++];
+        col.refs = h->ring[c]; col.batch = batch_cols[c]; col.rb = h->cfg.row_bytes[c];
+        col.K = h->col_frames[c]; col.cast = h->cfg.out_cast[c];
+        col.split = col.K >= 8 ? 1 : (8 + col.K - 1) / col.K;      // K * split >= the 8 warps of a CTA
+    }
+    const int64_t items = (int64_t)batch * a.ncols;
+    if (items <= 0) return RETH_OK;
+    const int64_t maxg = (int64_t)h->n_sms * 6 * 64;
+    frame_gather_kernel<<<(unsigned)(items < maxg ? items : maxg), kCopyThreads, 0, s>>>(a);
     CK(h, cudaGetLastError());
     h->st.kernel_launches++;
     return RETH_OK;
@@ -731,6 +817,7 @@ int do_gather(reth_replay *h, int slot, bool use_meta, cudaStream_t s, int group
         build_row_args(h, a, b.cols, b.idx, b.batch * groups, 0, true);
         a.meta = meta;
         rc = launch_row_move<false>(h, a, s);
+        if (!rc) rc = launch_frame_gather(h, b.cols, b.idx, b.batch * groups, meta, 0, s);
     }
     if (rc) return rc;
     h->st.gathered_rows += (int64_t)b.batch * groups;
@@ -1537,6 +1624,7 @@ RETH_EXPORT int reth_replay_gather_to(reth_replay_t *h, int slot, reth_ipc_view_
         a.meta = b.meta;
         a.dst_row_from_meta = 1;
         int rc = launch_row_move<false>(h, a, s);
+        if (!rc) rc = launch_frame_gather(h, cols, b.idx, b.batch, b.meta, 1, s);
         if (rc) return rc;
         h->st.gathered_rows += b.batch;
     }
@@ -1569,6 +1657,7 @@ RETH_EXPORT int reth_replay_gather_from(reth_replay_t *h, int dst_slot, reth_rep
         a.meta = b.meta;
         a.dst_row_from_meta = 1;
         int rc = launch_row_move<false>(h, a, s);
+        if (!rc) rc = launch_frame_gather(h, d.cols, b.idx, b.batch, b.meta, 1, s);
         if (rc) return rc;
         h->st.gathered_rows += b.batch;
     }

@@ -193,11 +193,27 @@ class ReplayShard:
     """
 
     def __init__(self, capacity, struct, max_batch, ring_depth=2, device=0, min_mode=MIN_SERVICE,
-                 store_rows=True, update_cluster=0, gather_mode=0, out_cast=None):
+                 store_rows=True, update_cluster=0, gather_mode=0, out_cast=None, frames=None):
+        """frames: {"shape": per-frame shape, "capacity": frames in the frame ring, "columns": [column
+        indices]} turns those columns of `struct` -- uint8 stacks of shape (K,) + frame shape -- into
+        frame-reference columns: a transition stores K int32 frame slots (append_frames() returns the
+        slots), the gather hands the learner the K-frame stack.  Frames are stored once (8x less HBM per
+        Atari transition than re-storing 4-stacks for s0 and s1)."""
         self._h = None
         self._lib = _cabi.lib()
         self.capacity = int(capacity)
         self.struct = [(np.dtype(dt), tuple(int(s) for s in sh)) for dt, sh in (struct or [])]
+        self.frame_cols, self.frame_shape, self.frame_capacity = {}, None, 0
+        logical = list(self.struct)
+        if frames:
+            self.frame_shape = tuple(int(x) for x in frames["shape"])
+            self.frame_capacity = int(frames["capacity"])
+            for c in frames["columns"]:
+                dt, sh = self.struct[c]
+                if dt != np.dtype(np.uint8) or sh[1:] != self.frame_shape or len(sh) != len(self.frame_shape) + 1:
+                    raise ValueError(f"column {c}: a frame column is uint8 of shape (K,) + {self.frame_shape}")
+                self.frame_cols[c] = sh[0]
+                self.struct[c] = (np.dtype(np.int32), (sh[0],))       # what the ring stores
         self.row_bytes = [dt.itemsize * int(np.prod(sh, dtype=np.int64)) for dt, sh in self.struct]
         self.max_batch = int(max_batch)
         self.ring_depth = int(ring_depth)
@@ -220,12 +236,15 @@ class ReplayShard:
         if len(self.out_cast) != len(self.struct):
             raise ValueError("out_cast needs one entry per column")
         for i, code in enumerate(self.out_cast):
-            if code and self.struct[i][0] != np.dtype(np.uint8):
+            if code and logical[i][0] != np.dtype(np.uint8):
                 raise ValueError(f"column {i}: only uint8 columns can be widened to float32")
-            cfg.out_cast[i] = code
+            cfg.out_cast[i] = code | (_cabi.COL_FRAMES if i in self.frame_cols else 0)
+        if self.frame_cols:
+            cfg.frame_bytes = int(np.prod(self.frame_shape, dtype=np.int64))
+            cfg.frame_capacity = self.frame_capacity
         # what a batch slot holds (struct is what the ring stores)
         self.out_struct = [((np.dtype(np.float32) if code else dt), sh)
-                           for (dt, sh), code in zip(self.struct, self.out_cast)]
+                           for (dt, sh), code in zip(logical, self.out_cast)]
         cfg.gather_mode = int(gather_mode)      # 0 auto (TMA bulk when a column is wide), 1 LDG/STG, 2 TMA bulk
         h = C.c_void_p()
         rc = self._lib.reth_replay_create(C.byref(cfg), C.byref(h))
@@ -300,6 +319,23 @@ class ReplayShard:
                                               int(bool(transform)), C.byref(first), self._s(stream)))
         self._keep = (keep, pkeep)
         return first.value
+
+    def append_frames(self, frames, stream=None):
+        """n frames -> the frame ring; returns the first frame slot (slots are first, first+1, ... mod
+        frame_capacity).  Write these slots into the frame-reference columns of later appends."""
+        p, loc, dt, cnt, keep = _ptr_loc(frames)
+        fb = int(np.prod(self.frame_shape, dtype=np.int64))
+        if dt != np.dtype(np.uint8) or cnt % fb:
+            raise ValueError("frames must be uint8 with the shard's frame shape")
+        first = C.c_int64()
+        self._ck(self._lib.reth_replay_append_frames(self._h, p, loc, cnt // fb, C.byref(first), self._s(stream)))
+        self._keep = keep
+        return first.value
+
+    def frame_read(self, first, n, stream=None):
+        out = np.empty((int(n),) + self.frame_shape, np.uint8)
+        self._ck(self._lib.reth_replay_frame_read(self._h, int(first), int(n), out.ctypes.data, self._s(stream)))
+        return out
 
     def append_at(self, slots, cols, prio=None, alpha=0.6, transform=True, stream=None):
         sp, sloc, sdt, n, skeep = _ptr_loc(slots)
