@@ -218,9 +218,13 @@ __global__ void __launch_bounds__(kCopyThreads, kWiden ? 4 : 6) row_move_kernel(
 //   batch[row][k] = frames[ ring_refs[idx[row]][k] ]      (optionally widened to float32)
 // One work item = (column, row, k, chunk of the frame), 256 threads moving 16-byte vectors.
 struct FrameCol {
-    const uint8_t *refs;  // ring column of the references: int32[K] per slot
+    const uint8_t *refs;  // ring column of the references: int32[K] per slot (direct: unused)
+    const uint8_t *src;   // the frame ring; direct: the column's own ring, "frame" = the stored row
     uint8_t *batch;       // batch column base: K * fb (x4 when cast) bytes per row
     int64_t rb;           // bytes per slot of the reference column = 4 * K
+    int64_t fb;           // bytes per frame (multiple of 16)
+    int64_t fcap;         // frames in the source ring
+    int32_t direct;       // 1: no indirection, frame slot = row slot, K = 1 (a stored wide column being widened)
     int32_t K;
     int32_t cast;         // 0 raw, 1 u8 -> f32, 2 u8 -> f32 / 255
     int32_t split;        // pieces per frame: K * split pieces are dealt to the warps of the CTA
@@ -229,9 +233,6 @@ struct FrameCol {
 struct FrameArgs {
     FrameCol col[kMaxCols];
     int32_t ncols;
-    const uint8_t *frames;     // frame ring
-    int64_t fb;                // bytes per frame (multiple of 16)
-    int64_t fcap;              // frames in the ring
     const int64_t *idx;
     int32_t batch;
     const int64_t *meta;
@@ -240,6 +241,8 @@ struct FrameArgs {
     int32_t *err;
 };
 
+// Also the widening gather of stored wide columns (direct = 1): the same warp-per-part streaming, which
+// keeps 6 CTAs per SM resident where the general row mover's widening path manages 4.
 // One work item = the K-frame stack of (batch row, frame column); items of the same row are adjacent in
 // the grid, so the s0 and s1 stacks of a transition (which share K - 1 frames) are read at about the same
 // time and the second read of a shared frame hits L2.  Inside an item every warp owns (frame k, part of
@@ -249,7 +252,6 @@ __global__ void __launch_bounds__(kCopyThreads, 6) frame_gather_kernel(const Fra
     constexpr int kWarps = kCopyThreads / 32;
     const int rows = a.meta ? (int)a.meta[1] : a.batch;
     const int64_t row0 = (a.meta && a.dst_row_from_meta) ? a.meta[0] : 0;
-    const int upf = (int)(a.fb >> 4);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int64_t items = (int64_t)a.batch * a.ncols;
     for (int64_t item = blockIdx.x; item < items; item += gridDim.x) {
@@ -261,15 +263,16 @@ __global__ void __launch_bounds__(kCopyThreads, 6) frame_gather_kernel(const Fra
         const int32_t *refs = (const int32_t *)(col.refs + slot * col.rb);
         const int64_t out_row = (int64_t)row + row0;
         const int pieces = col.K * col.split;
+        const int upf = (int)(col.fb >> 4);
         for (int p = warp; p < pieces; p += kWarps) {
             const int k = p / col.split, part = p - k * col.split;
-            const int64_t ref = __ldg(refs + k);
-            if (ref < 0 || ref >= a.fcap) { if (lane == 0) atomicOr(a.err, 1); continue; }
+            const int64_t ref = col.direct ? slot : (int64_t)__ldg(refs + k);
+            if (ref < 0 || ref >= col.fcap) { if (lane == 0) atomicOr(a.err, 1); continue; }
             const int u0 = (int)((int64_t)upf * part / col.split), u1 = (int)((int64_t)upf * (part + 1) / col.split);
             if (col.cast) {
                 // lane = one 32-bit word (4 uint8) in, one 16 B vector (4 float32) out
-                const uint32_t *w32 = (const uint32_t *)(a.frames + ref * a.fb) + u0 * 4;
-                uint4 *d4 = (uint4 *)(col.batch + (out_row * col.K + k) * a.fb * 4) + u0 * 4;
+                const uint32_t *w32 = (const uint32_t *)(col.src + ref * col.fb) + u0 * 4;
+                uint4 *d4 = (uint4 *)(col.batch + (out_row * col.K + k) * col.fb * 4) + u0 * 4;
                 const bool unit = col.cast == 2;
                 const int n4 = (u1 - u0) * 4;
                 int j = lane;
@@ -284,8 +287,8 @@ __global__ void __launch_bounds__(kCopyThreads, 6) frame_gather_kernel(const Fra
                 for (; j < n4; j += 32) st_stream(d4 + j, u8x4_to_f32(ld_stream32(w32 + j), unit));
                 continue;
             }
-            const uint4 *sp = (const uint4 *)(a.frames + ref * a.fb) + u0;
-            uint4 *d = (uint4 *)(col.batch + (out_row * col.K + k) * a.fb) + u0;
+            const uint4 *sp = (const uint4 *)(col.src + ref * col.fb) + u0;
+            uint4 *d = (uint4 *)(col.batch + (out_row * col.K + k) * col.fb) + u0;
             const int n = u1 - u0;
             int j = lane;
             for (; j + 96 < n; j += 128) {

@@ -647,6 +647,13 @@ int gather_units_target()
     return v;
 }
 
+// experiment switch: plain wide columns through the warp-per-part kernel as well
+int gather_warp_mode()
+{
+    static int v = [] { const char *e = getenv("RETH_GATHER_WARP"); return e ? atoi(e) : 0; }();
+    return v;
+}
+
 // Work decomposition of a row move over `batch` rows (gather or scatter).
 void build_row_args(reth_replay *h, RowArgs &a, uint8_t *const *batch_cols, const int64_t *idx, int batch,
                     int units_target = 0, bool widen = false)
@@ -666,12 +673,13 @@ void build_row_args(reth_replay *h, RowArgs &a, uint8_t *const *batch_cols, cons
         col.batch = batch_cols[c];
         col.rb = h->cfg.row_bytes[c];
         col.cast = widen ? h->cfg.out_cast[c] : 0;
-        if (widen && h->col_frames[c]) {                    // gather: expanded by frame_gather_kernel instead
+        const bool wide = (col.rb % 16 == 0) && col.rb >= 256 && ((uintptr_t)col.batch % 16 == 0);
+        if (widen && (h->col_frames[c] || ((col.cast || gather_warp_mode()) && wide))) {
+            // gather: frame-reference columns and widened wide columns go through frame_gather_kernel
             col.chunks = -1;
             col.cast = 0;
             continue;
         }
-        const bool wide = (col.rb % 16 == 0) && col.rb >= 256 && ((uintptr_t)col.batch % 16 == 0);
         if (wide) {
             const int64_t upr = col.rb / 16;
             col.chunks = (int32_t)((upr + units_target - 1) / units_target);
@@ -707,16 +715,21 @@ int launch_row_move(reth_replay *h, const RowArgs &a, cudaStream_t s)
 int launch_frame_gather(reth_replay *h, uint8_t *const *batch_cols, const int64_t *idx, int batch,
                         const int64_t *meta, int dst_row_from_meta, cudaStream_t s)
 {
-    if (!h->n_frame_cols) return RETH_OK;
     FrameArgs a = {};
-    a.frames = h->frames; a.fb = h->cfg.frame_bytes; a.fcap = h->cfg.frame_capacity;
     a.idx = idx; a.batch = batch; a.meta = meta; a.dst_row_from_meta = dst_row_from_meta;
     a.capacity = h->cfg.capacity; a.err = h->err;
     for (int c = 0; c < h->cfg.n_columns; ++c) {
-        if (!h->col_frames[c]) continue;
+        const int64_t rb = h->cfg.row_bytes[c];
+        const bool direct = !h->col_frames[c] && (h->cfg.out_cast[c] || gather_warp_mode()) && rb % 16 == 0 && rb >= 256 &&
+                            ((uintptr_t)batch_cols[c] % 16 == 0);
+        if (!h->col_frames[c] && !direct) continue;
         FrameCol &col = a.col[a.ncols++];
-        col.refs = h->ring[c]; col.batch = batch_cols[c]; col.rb = h->cfg.row_bytes[c];
-        col.K = h->col_frames[c]; col.cast = h->cfg.out_cast[c];
+        col.refs = h->ring[c]; col.batch = batch_cols[c]; col.rb = rb; col.cast = h->cfg.out_cast[c];
+        if (direct) {
+            col.direct = 1; col.src = h->ring[c]; col.fb = rb; col.fcap = h->cfg.capacity; col.K = 1;
+        } else {
+            col.src = h->frames; col.fb = h->cfg.frame_bytes; col.fcap = h->cfg.frame_capacity; col.K = h->col_frames[c];
+        }
         col.split = col.K >= 8 ? 1 : (8 + col.K - 1) / col.K;      // K * split >= the 8 warps of a CTA
     }
     const int64_t items = (int64_t)batch * a.ncols;
