@@ -70,6 +70,8 @@ def lz4_decompress(buf):
     size = L.reth_lz4f_content_size(src.ctypes.data, src.size)
     if size < -1:
         raise ValueError(f"lz4 frame: {_LZ4F_ERR.get(size, size)}")
+    if size > 256 * src.size + (1 << 16):                     # LZ4 cannot expand more than ~255:1
+        raise ValueError("lz4 frame: the stored content size is not credible")
     cap = size if size >= 0 else max(4 * src.size, 1 << 16)
     while True:
         out = np.empty(cap, np.uint8)

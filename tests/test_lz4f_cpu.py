@@ -124,3 +124,20 @@ def test_compressed_append_message(wire):
     assert np.array_equal(gw, w)
     for a, b in zip(got, cols):
         assert a.dtype == b.dtype and np.array_equal(a, b)
+
+
+def test_sanitizer_fuzz(tmp_path):
+    """The codec under AddressSanitizer + UBSan: round trips and mutated frames (tests/native/fuzz_lz4f.cpp)."""
+    import shutil
+    import subprocess
+    if shutil.which("g++") is None:
+        pytest.skip("g++ not available")
+    src = os.path.join(os.path.dirname(__file__), "native", "fuzz_lz4f.cpp")
+    exe = str(tmp_path / "fuzz_lz4f")
+    build = subprocess.run(["g++", "-O1", "-g", "-std=c++17", "-fsanitize=address,undefined", src, "-o", exe],
+                           capture_output=True, text=True)
+    if build.returncode != 0 and "sanitize" in build.stderr:
+        pytest.skip("sanitizer runtime not available")
+    assert build.returncode == 0, build.stderr
+    run = subprocess.run([exe, "600"], capture_output=True, text=True, timeout=300)
+    assert run.returncode == 0 and run.stdout.startswith("ok"), run.stdout + run.stderr
