@@ -702,7 +702,8 @@ int launch_row_move(reth_replay *h, const RowArgs &a, cudaStream_t s)
     for (int c = 0; c < a.ncols; ++c) widen |= a.col[c].cast != 0;
     int64_t total = a.wide_items + a.narrow_groups;
     if (total <= 0) return RETH_OK;
-    const int64_t maxg = (int64_t)h->n_sms * 6 * 64;
+    static const int waves = [] { const char *e = getenv("RETH_GATHER_WAVES"); int v = e ? atoi(e) : 64; return v < 1 ? 1 : v; }();
+    const int64_t maxg = (int64_t)h->n_sms * 6 * waves;     // resident CTAs x waves; beyond that CTAs stride over the items
     const unsigned grid = (unsigned)(total < maxg ? total : maxg);
     if (!kScatter && widen) row_move_kernel<false, true><<<grid, kCopyThreads, 0, s>>>(a);
     else row_move_kernel<kScatter><<<grid, kCopyThreads, 0, s>>>(a);
