@@ -101,8 +101,17 @@ struct reth_replay {
         std::vector<char> upd_used;
         int64_t issued = 0, waited = 0, upd_next = 0;
         int hold = 1;             // delivered groups that stay lent (the newest `hold` of them)
+        // experiment (RETH_PIPE_ZEROCOPY=1): kernels write deliveries to / read write-backs from mapped pinned
+        // host memory instead of using the copy engines.  Measured slower on B200 (strict alternation
+        // 7.7 vs 8.1 M transitions/s, group 8 / one ahead 39.6 vs 43.6 M): PCIe round trips inside the
+        // update kernel's dependent chain cost more than the copy operations they save.
+        bool zero_copy = false;
     } pipe;
     int pipe_reserved = 0;        // batch slots at the end of the ring that a pipe never uses (other sampler topics)
+    // set by pipe_issue around its draw: the sampling kernel also writes into mapped pinned host memory
+    int64_t *mirror_idx = nullptr;
+    double *mirror_w = nullptr;
+    int32_t *mirror_err = nullptr;
     std::string error;
 };
 
@@ -806,6 +815,7 @@ int do_sample(reth_replay *h, int batch, const double *uniforms, int uniforms_lo
     a.groups = groups; a.out_stride = h->cfg.max_batch;
     a.beta = beta; a.min_mode = h->cfg.min_mode;
     a.idx_out = b.idx; a.w_out = b.w; a.prio_out = b.prio; a.meta = b.meta;
+    a.idx_mirror = h->mirror_idx; a.w_mirror = h->mirror_w; a.err_mirror = h->mirror_err; a.err = h->err;
     a.all_roots = all_roots; a.n_shards = n_shards; a.shard = shard;
     const int wpb = 4;
     per_sample_kernel<<<(batch * groups + wpb - 1) / wpb, wpb * 32, 0, s>>>(a);
@@ -1132,6 +1142,7 @@ int pick_into_slots(reth_replay *h, PickArgs &a, int batch, int first_slot, int 
     BatchSlot &b = h->slots[first_slot];
     a.n = (int64_t)batch * n_slots;
     a.idx_out = b.idx; a.w_out = b.w; a.prio_out = b.prio; a.meta = b.meta; a.batch = batch; a.err = h->err;
+    a.idx_mirror = h->mirror_idx; a.w_mirror = h->mirror_w; a.err_mirror = h->mirror_err;
     sampler_pick_kernel<<<(unsigned)((a.n + 255) / 256), 256, 0, s>>>(a);
     CK(h, cudaGetLastError());
     h->st.kernel_launches++;
@@ -1281,25 +1292,31 @@ int pipe_issue(reth_replay *h, double beta, bool give_up_lent = false)
     if (p.issued - p.waited + lent >= p.n_groups)
         return fail(h, RETH_ERR_STATE, "all %d group slots are issued or lent", p.n_groups);
     const int g = (int)(p.issued % p.n_groups), slot = g * p.G;
+    const size_t E = (size_t)p.E;
     int rc;
+    if (p.zero_copy) { h->mirror_idx = p.idx_host + g * E; h->mirror_w = p.w_host + g * E; h->mirror_err = p.err_host + g; }
     if (h->pipe_kind == 1) rc = do_sample_uniform(h, p.batch, slot, p.G, nullptr, RETH_DEVICE, p.seed, h->s_tree);
     else if (h->pipe_kind == 2) rc = do_sample_fifo(h, p.batch, slot, p.G, h->s_tree);
     else rc = do_sample(h, p.batch, nullptr, RETH_DEVICE, p.seed, beta, slot, nullptr, 1, 0, h->s_tree, p.G);
+    h->mirror_idx = nullptr; h->mirror_w = nullptr; h->mirror_err = nullptr;
     if (rc) return rc;
     CK(h, cudaEventRecord(p.ev_smp[g], h->s_tree));
-    CK(h, cudaStreamWaitEvent(p.s_copy, p.ev_smp[g], 0));
-    const size_t E = (size_t)p.E;
-    CK(h, cudaMemcpyAsync(p.idx_host + g * E, h->slots[slot].idx, E * 8, cudaMemcpyDeviceToHost, p.s_copy));
-    CK(h, cudaMemcpyAsync(p.w_host + g * E, h->slots[slot].w, E * 8, cudaMemcpyDeviceToHost, p.s_copy));
-    CK(h, cudaMemcpyAsync(p.err_host + g, h->err, sizeof(int32_t), cudaMemcpyDeviceToHost, p.s_copy));
+    if (!p.zero_copy) {
+        CK(h, cudaStreamWaitEvent(p.s_copy, p.ev_smp[g], 0));
+        CK(h, cudaMemcpyAsync(p.idx_host + g * E, h->slots[slot].idx, E * 8, cudaMemcpyDeviceToHost, p.s_copy));
+        CK(h, cudaMemcpyAsync(p.w_host + g * E, h->slots[slot].w, E * 8, cudaMemcpyDeviceToHost, p.s_copy));
+        CK(h, cudaMemcpyAsync(p.err_host + g, h->err, sizeof(int32_t), cudaMemcpyDeviceToHost, p.s_copy));
+    }
     cudaStream_t sg = (h->two_gather_streams && (p.issued & 1)) ? h->s_gather2 : h->s_gather;
     CK(h, cudaStreamWaitEvent(sg, p.ev_smp[g], 0));
     rc = do_gather(h, slot, false, sg, p.G);
     if (rc) return rc;
     CK(h, cudaEventRecord(p.ev_gat[g], sg));
     h->last_gather_ev = p.ev_gat[g];
-    CK(h, cudaStreamWaitEvent(p.s_copy, p.ev_gat[g], 0));
-    CK(h, cudaEventRecord(p.ev_done[g], p.s_copy));
+    if (!p.zero_copy) {
+        CK(h, cudaStreamWaitEvent(p.s_copy, p.ev_gat[g], 0));
+        CK(h, cudaEventRecord(p.ev_done[g], p.s_copy));
+    }
     p.issued++;
     return RETH_OK;
 }
@@ -1310,7 +1327,8 @@ int pipe_wait(reth_replay *h, int32_t *group_out)
     if (!p.open) return fail(h, RETH_ERR_STATE, "no pipe is open");
     if (p.issued <= p.waited) return fail(h, RETH_ERR_STATE, "pipe_wait: no group has been issued");
     const int g = (int)(p.waited % p.n_groups);
-    CK(h, cudaEventSynchronize(p.ev_done[g]));
+    // zero copy: the gather stream waited for the draw, so its event covers the indices in host memory too
+    CK(h, cudaEventSynchronize(p.zero_copy ? p.ev_gat[g] : p.ev_done[g]));
     p.waited++;
     if (group_out) *group_out = g;
     if (p.err_host[g]) {
@@ -1339,11 +1357,21 @@ RETH_EXPORT int reth_replay_pipe_open(reth_replay_t *h, int batch, int group, ui
     const size_t E = (size_t)p.E;
     auto bail = [&](int code) { pipe_free(h); return code; };
 #define CKP(expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) return bail(fail(h, RETH_ERR_CUDA, "%s: %s", #expr, cudaGetErrorString(e__))); } while (0)
-    CKP(cudaMallocHost((void **)&p.idx_host, p.n_groups * E * 8));
-    CKP(cudaMallocHost((void **)&p.w_host, p.n_groups * E * 8));
-    CKP(cudaMallocHost((void **)&p.err_host, p.n_groups * sizeof(int32_t)));
+    if (const char *e = getenv("RETH_PIPE_ZEROCOPY")) p.zero_copy = atoi(e) != 0;
+    // mapped + portable: with unified addressing the device uses the same pointers
+    const unsigned hf = cudaHostAllocMapped | cudaHostAllocPortable;
+    CKP(cudaHostAlloc((void **)&p.idx_host, p.n_groups * E * 8, hf));
+    CKP(cudaHostAlloc((void **)&p.w_host, p.n_groups * E * 8, hf));
+    CKP(cudaHostAlloc((void **)&p.err_host, p.n_groups * sizeof(int32_t), hf));
     memset(p.err_host, 0, p.n_groups * sizeof(int32_t));
-    CKP(cudaMallocHost((void **)&p.upd_host, p.upd_entries * E * 16));
+    CKP(cudaHostAlloc((void **)&p.upd_host, p.upd_entries * E * 16, hf));
+    if (p.zero_copy) {
+        void *dp = nullptr;
+        if (cudaHostGetDevicePointer(&dp, p.idx_host, 0) != cudaSuccess || dp != (void *)p.idx_host) {
+            cudaGetLastError();
+            p.zero_copy = false;              // no unified addressing for pinned memory: copy engines instead
+        }
+    }
     CKP(cudaMalloc((void **)&p.upd_dev, E * 16));
     CKP(cudaStreamCreateWithFlags(&p.s_copy, cudaStreamNonBlocking));
     for (auto *v : {&p.ev_smp, &p.ev_gat, &p.ev_done})
@@ -1451,7 +1479,8 @@ RETH_EXPORT int reth_replay_pipe_ready(reth_replay_t *h, int32_t *ready_out)
     *ready_out = 0;
     if (p.issued <= p.waited) return RETH_OK;
     DeviceGuard guard(h->cfg.device);
-    const cudaError_t e = cudaEventQuery(p.ev_done[p.waited % p.n_groups]);
+    const int gq = (int)(p.waited % p.n_groups);
+    const cudaError_t e = cudaEventQuery(p.zero_copy ? p.ev_gat[gq] : p.ev_done[gq]);
     if (e == cudaSuccess) *ready_out = 1;
     else if (e != cudaErrorNotReady) return fail(h, RETH_ERR_CUDA, "cudaEventQuery: %s", cudaGetErrorString(e));
     return RETH_OK;
@@ -1485,20 +1514,24 @@ RETH_EXPORT int reth_replay_pipe_update_commit(reth_replay_t *h, int entry, int6
     DeviceGuard guard(h->cfg.device);
     const size_t E = (size_t)p.E, ps = dtype_size(prio_dtype);
     const uint8_t *src = p.upd_host + (size_t)entry * E * 16;
-    if ((size_t)n == E) {
-        CK(h, cudaMemcpyAsync(p.upd_dev, src, E * 8 + E * ps, cudaMemcpyHostToDevice, h->s_tree));
-    } else {
-        CK(h, cudaMemcpyAsync(p.upd_dev, src, (size_t)n * 8, cudaMemcpyHostToDevice, h->s_tree));
-        CK(h, cudaMemcpyAsync(p.upd_dev + E * 8, src + E * 8, (size_t)n * ps, cudaMemcpyHostToDevice, h->s_tree));
+    const uint8_t *in = p.zero_copy ? src : p.upd_dev;   // zero copy: the kernel reads the staging entry itself
+    if (!p.zero_copy) {
+        if ((size_t)n == E) {
+            CK(h, cudaMemcpyAsync(p.upd_dev, src, E * 8 + E * ps, cudaMemcpyHostToDevice, h->s_tree));
+        } else {
+            CK(h, cudaMemcpyAsync(p.upd_dev, src, (size_t)n * 8, cudaMemcpyHostToDevice, h->s_tree));
+            CK(h, cudaMemcpyAsync(p.upd_dev + E * 8, src + E * 8, (size_t)n * ps, cudaMemcpyHostToDevice, h->s_tree));
+        }
+        CK(h, cudaEventRecord(p.ev_upd[entry], h->s_tree));
     }
-    CK(h, cudaEventRecord(p.ev_upd[entry], h->s_tree));
     p.upd_used[entry] = 1;
     p.upd_next++;
     UpdateArgs a = {};
-    a.n = n; a.idx = p.upd_dev; a.idx_kind = 0;
-    a.prio = p.upd_dev + E * 8; a.prio_kind = prio_dtype == RETH_F32 ? 0 : 1;
+    a.n = n; a.idx = in; a.idx_kind = 0;
+    a.prio = in + E * 8; a.prio_kind = prio_dtype == RETH_F32 ? 0 : 1;
     a.alpha = alpha; a.transform = transform; a.dedupe = 1;
     int rc = launch_update(h, a, h->s_tree);
+    if (p.zero_copy) CK(h, cudaEventRecord(p.ev_upd[entry], h->s_tree));   // the entry is free once the kernel has read it
     if (rc) return rc;
     h->st.updated_rows += n;
     return RETH_OK;

@@ -103,6 +103,12 @@ struct SampleArgs {
     int32_t n_shards, shard;
     int32_t groups;            // independent stratified draws of `batch` in one launch (>= 1)
     int32_t out_stride;        // elements between the outputs of consecutive draws
+    // loader pipeline: indices / weights are also written straight into pinned host memory mapped into
+    // the device address space (no device->host copy operation), and the error flag is mirrored
+    int64_t *idx_mirror;
+    double *w_mirror;
+    int32_t *err_mirror;
+    const int32_t *err;
 };
 
 __device__ __forceinline__ double draw_u(const SampleArgs &a, int64_t i)
@@ -137,6 +143,7 @@ __global__ void __launch_bounds__(256) per_sample_kernel(const SampleArgs a)
     const int lane = threadIdx.x & 31;
     const int64_t W = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (W >= (int64_t)a.batch * a.groups) return;
+    if (a.err_mirror && W == 0 && lane == 0) *a.err_mirror = *a.err;   // set by earlier launches of the stream
     const int64_t grp = W / a.batch, i = W - grp * a.batch;   // draw `grp`, stratum i
     const int64_t cap = a.g.capacity;
 
@@ -200,9 +207,11 @@ __global__ void __launch_bounds__(256) per_sample_kernel(const SampleArgs a)
     }
     if (lane == 0) {
         const int64_t o = grp * a.out_stride + i - first;
+        const double wt = pow(val / pmin, -a.beta);  // per_sampler.py:26
         a.idx_out[o] = idx;
         a.prio_out[o] = val;
-        a.w_out[o] = pow(val / pmin, -a.beta);      // per_sampler.py:26
+        a.w_out[o] = wt;
+        if (a.idx_mirror) { a.idx_mirror[o] = idx; a.w_mirror[o] = wt; }
     }
 }
 
@@ -624,12 +633,16 @@ struct PickArgs {
     int64_t *meta;             // {first, count} per batch slot
     int32_t batch;
     int32_t *err;
+    int64_t *idx_mirror;       // loader pipeline: mapped pinned host copies (see SampleArgs)
+    double *w_mirror;
+    int32_t *err_mirror;
 };
 
 __global__ void sampler_pick_kernel(const PickArgs a)
 {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= a.n) return;
+    if (a.err_mirror && i == 0) *a.err_mirror = *a.err;
     if (i % a.batch == 0) { a.meta[2 * (i / a.batch)] = 0; a.meta[2 * (i / a.batch) + 1] = a.batch; }
     int64_t p;
     if (a.uniform) {
@@ -643,10 +656,12 @@ __global__ void sampler_pick_kernel(const PickArgs a)
     } else {
         p = (a.head + i) % a.src_cap;
     }
-    a.idx_out[i] = a.src_idx[p];
+    const int64_t v = a.src_idx[p];
+    a.idx_out[i] = v;
     const double w = a.src_w ? a.src_w[p] : 1.0;
     a.w_out[i] = w;
     a.prio_out[i] = w;
+    if (a.idx_mirror) { a.idx_mirror[i] = v; a.w_mirror[i] = w; }
 }
 
 // ---------------------------------------------------------------- readback --
