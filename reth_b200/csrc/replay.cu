@@ -562,9 +562,45 @@ RETH_EXPORT int reth_replay_append(reth_replay_t *h, const void *const *cols, in
                     }
                     sc = h->s_append;
                 }
-                ring_append_kernel<<<(unsigned)blocks, kCopyThreads, 0, sc>>>(a);
-                CK(h, cudaGetLastError());
-                h->st.kernel_launches++;
+                static const int use_memcpy = [] { const char *e = getenv("RETH_APPEND_MEMCPY"); return e ? atoi(e) : 0; }();
+                if (use_memcpy && bytes >= (32ll << 20)) {
+                    // experiment: the driver's device-to-device copy per column span instead of the append kernel
+                    for (int c = 0; c < a.ncols; ++c) {
+                        CK(h, cudaMemcpyAsync(a.ring[c] + start * a.rb[c], a.src[c], (size_t)(len1 * a.rb[c]), cudaMemcpyDeviceToDevice, sc));
+                        if (len2 > 0)
+                            CK(h, cudaMemcpyAsync(a.ring[c], a.src[c] + len1 * a.rb[c], (size_t)(len2 * a.rb[c]), cudaMemcpyDeviceToDevice, sc));
+                    }
+                } else {
+                    // 16-byte-aligned spans: one CTA per contiguous 16 KB tile; otherwise the grid-strided kernel
+                    AppendTiledArgs t = {};
+                    bool aligned = true;
+                    for (int c = 0; c < a.ncols && aligned; ++c) {
+                        const int64_t rb = a.rb[c];
+                        uint8_t *d1 = a.ring[c] + start * rb;
+                        const uint8_t *s1 = a.src[c], *s2 = a.src[c] + len1 * rb;
+                        if ((((uintptr_t)d1 | (uintptr_t)s1 | (uint64_t)(len1 * rb)) & 15) ||
+                            (len2 > 0 && (((uintptr_t)a.ring[c] | (uintptr_t)s2 | (uint64_t)(len2 * rb)) & 15))) { aligned = false; break; }
+                        if (len1 > 0) {
+                            AppendSeg &g = t.seg[t.nseg++];
+                            g.dst = d1; g.src = s1; g.units = len1 * rb / 16; g.tile_base = t.tiles;
+                            t.tiles += (g.units + kAppendTileUnits - 1) / kAppendTileUnits;
+                        }
+                        if (len2 > 0) {
+                            AppendSeg &g = t.seg[t.nseg++];
+                            g.dst = a.ring[c]; g.src = s2; g.units = len2 * rb / 16; g.tile_base = t.tiles;
+                            t.tiles += (g.units + kAppendTileUnits - 1) / kAppendTileUnits;
+                        }
+                    }
+                    static const int tiled = [] { const char *e = getenv("RETH_APPEND_TILED"); return e ? atoi(e) : 1; }();
+                    if (aligned && tiled && t.tiles > 0) {
+                        const int64_t maxg = (int64_t)h->n_sms * 8 * 64;
+                        ring_append_tiled_kernel<<<(unsigned)(t.tiles < maxg ? t.tiles : maxg), kCopyThreads, 0, sc>>>(t);
+                    } else {
+                        ring_append_kernel<<<(unsigned)blocks, kCopyThreads, 0, sc>>>(a);
+                    }
+                    CK(h, cudaGetLastError());
+                    h->st.kernel_launches++;
+                }
             } else {
                 for (int c = 0; c < h->cfg.n_columns; ++c) {
                     const int64_t rb = h->cfg.row_bytes[c];
