@@ -29,6 +29,7 @@ KEY_NUMPY = "reth_numpy_356b759ef2b3"
 KEY_BYTES = "reth_bytes_a32b00c47e72"
 KEY_COLUMNAR = "reth_b200_columnar"
 KEY_SHM = "reth_b200_shm"              # [descriptor of columns in a shared-memory ring, weights]
+KEY_STEPS = "reth_b200_steps"          # [head, frames, other columns, weights]: frame-de-duplicated ingest
 KEY_SRC = "reth_b200_src"              # [client id, message number]: lets the server order a loader's
                                        # request after the writes the same process sent on other sockets
 
@@ -233,6 +234,9 @@ def open_append(buf):
     if isinstance(meta, list) and len(meta) == 2 and isinstance(meta[0], dict) and KEY_SHM in meta[0]:
         head, weights = _rebuild(meta, body)
         return "shm", head, np.asarray(weights), src
+    if isinstance(meta, list) and len(meta) == 4 and isinstance(meta[0], dict) and KEY_STEPS in meta[0]:
+        head, frames, others, weights = _rebuild(meta, body)
+        return "steps", (head, frames, others), np.asarray(weights), src
     cols, weights = _decode_append(header, body)
     return "columns", cols, weights, src
 

@@ -44,8 +44,12 @@ class _Engine:
     of a pre-sampled group (ShardPipe.wait)."""
 
     def __init__(self, capacity, batch_size, samplers=None, cache_policy=None, device=0, max_ring=16,
-                 float_frames=None):
+                 float_frames=None, frames=None):
         self.float_frames = float_frames                      # None | "f32" | "f32/255": see ReplayShard(out_cast=)
+        # frames = {"k": stack depth, "shape": frame shape, "capacity": frames in the frame ring,
+        #           "columns": (0, 3)}: frame-de-duplicated rows, fed through append_steps()
+        self.frames = dict(frames) if frames else None
+        self._writer = None
         self.capacity = int(capacity)
         self.batch_size = int(batch_size)
         self.device = device
@@ -109,9 +113,13 @@ class _Engine:
         # float_frames: image-like uint8 columns (rank >= 2 per row) are handed to the learner as float32,
         # the conversion DQNSolver does first (reth/reth/algorithm/dqn/dqn_solver.py:71-75), fused into the gather
         cast = [self.float_frames if (np.dtype(dt) == np.uint8 and len(sh) >= 2) else None for dt, sh in self.struct]
+        fr = None
+        if self.frames:
+            fr = {"shape": tuple(self.frames["shape"]), "capacity": int(self.frames["capacity"]),
+                  "columns": list(self.frames.get("columns", (0, 3)))}
         self.shard = ReplayShard(self.capacity, self.struct, max_batch=self.batch_size,
                                  ring_depth=self.max_ring + len(self.secondary), device=self.device,
-                                 min_mode=MIN_SERVICE, out_cast=cast if self.float_frames else None)
+                                 min_mode=MIN_SERVICE, out_cast=cast if self.float_frames else None, frames=fr)
         self.stream = self.shard.pipe_stream
         self.shard.pipe_sampler(self.kind)
         if self.secondary:
@@ -183,6 +191,48 @@ class _Engine:
             self.shard.gather_from(st["slot"], sh, 0, stream=self.stream)
             _, idx, w = self.shard.slot_read(st["slot"], stream=self.stream)
             return st["slot"], idx, w
+
+    def append_steps(self, stream_key, frames, others, weights, reset=None):
+        """Frame-de-duplicated ingest (this build's extension; the reference stores the full k-stacks):
+        `frames[i]` is the observation frame after step i of environment stream `stream_key`, `others`
+        the non-frame columns of the n transitions, `reset` the first frame of an episode when the
+        stream starts one.  Stacks are formed like FrameStack does (reth/reth/env/util.py:179-209)."""
+        from .frames import FrameRefWriter
+        with self.lock:
+            if self.frames is None:
+                raise ValueError("this buffer was not started with frames=...")
+            k, shape = int(self.frames["k"]), tuple(self.frames["shape"])
+            cols = tuple(self.frames.get("columns", (0, 3)))
+            if self.shard is None:
+                it = iter(others)
+                struct = []
+                for c in range(len(others) + len(cols)):
+                    if c in cols:
+                        struct.append((np.uint8, (k,) + shape))
+                    else:
+                        o = np.asarray(next(it))
+                        struct.append((o.dtype, tuple(o.shape[1:])))
+                self._ensure_shard(None, struct=struct)
+            if self._writer is None:
+                self._writer = FrameRefWriter(self.shard, k=k, frame_cols=cols)
+            w = self._writer
+            if reset is not None:
+                w.reset(stream_key, reset)
+            n = len(weights)
+            frames = np.asarray(frames).reshape((n,) + shape) if n else frames
+            others = [np.asarray(o) for o in others]
+            for i in range(n):
+                w.step(stream_key, frames[i], [o[i] for o in others], prio=float(weights[i]))
+            w.alpha = self.sampler["alpha"].value()
+            first = w.flush(stream=self.stream)
+            if n:
+                wts = np.asarray(weights, dtype=np.float32)
+                if self.kind == "uniform":
+                    self.shard.uniform_note(None, first_slot=first, n=n, stream=self.stream)
+                elif self.kind == "fifo":
+                    self.shard.fifo_push(None, wts, first_slot=first, stream=self.stream)
+                self._notify_append(first, None, wts)
+                self.cnt += n
 
     def append(self, data, weights):
         with self.lock:
@@ -480,20 +530,20 @@ class _ServerHandle:
 
 
 def start_server(capacity, batch_size, host=None, port=None, samplers=None, cache_policy=None, device=0,
-                 max_ring=16, float_frames=None):
+                 max_ring=16, float_frames=None, frames=None):
     """reth_buffer.start_server (__init__.py:11-27).  host/port are accepted for signature
     compatibility; the engine is reached through the returned in-process address."""
     addr = f"{_SCHEME}{next(_COUNTER)}"
-    _ENGINES[addr] = _Engine(capacity, batch_size, samplers, cache_policy, device, max_ring, float_frames)
+    _ENGINES[addr] = _Engine(capacity, batch_size, samplers, cache_policy, device, max_ring, float_frames, frames)
     return _ServerHandle(addr), addr
 
 
 def start_per(capacity, batch_size, alpha=0.6, beta=0.4, sample_start=1000, num_sampler_procs=1,
-              host=None, port=None, cache_policy=None, device=0, max_ring=16, float_frames=None):
+              host=None, port=None, cache_policy=None, device=0, max_ring=16, float_frames=None, frames=None):
     """reth_buffer.start_per (__init__.py:30-49)."""
     samplers = [{"sampler_cls": PERSampler, "num_procs": num_sampler_procs, "sample_start": sample_start,
                  "kwargs": {"alpha": alpha, "beta": beta}}]
-    return start_server(capacity, batch_size, host, port, samplers, cache_policy, device, max_ring, float_frames)
+    return start_server(capacity, batch_size, host, port, samplers, cache_policy, device, max_ring, float_frames, frames)
 
 
 def _engine(meta_addr):
@@ -527,6 +577,11 @@ class Client:
             assert isinstance(col, np.ndarray)                # :24
             assert len(col) == len(weights)                   # :25
         self._eng.append(data, np.asarray(weights))
+
+    def append_steps(self, env, frames, others, weights, reset=None):
+        """Frame-de-duplicated ingest for a buffer started with frames=...: see _Engine.append_steps."""
+        assert len(frames) == len(weights) and all(len(o) == len(weights) for o in others)
+        self._eng.append_steps((id(self), env), frames, others, np.asarray(weights), reset)
 
     def update_priorities(self, indices, weights, step=True):
         assert len(indices) == len(weights)                   # :38

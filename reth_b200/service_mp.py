@@ -56,7 +56,7 @@ def _pick_port(host):
 
 
 # ------------------------------------------------------------------ server --
-def server_main(capacity, batch_size, host, ports, samplers, cache_policy, device, max_ring, ready_evt):
+def server_main(capacity, batch_size, host, ports, samplers, cache_policy, device, max_ring, ready_evt, frames=None, float_frames=None):
     """Body of the server process (main_loop.py:110-216 + append_loop + sampler_loop in one loop)."""
     import zmq
     from . import _cabi, service
@@ -65,7 +65,7 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
     stop = {"flag": False}
     signal.signal(signal.SIGTERM, lambda *_: stop.__setitem__("flag", True))
 
-    eng = service._Engine(capacity, batch_size, samplers, cache_policy, device, max_ring)
+    eng = service._Engine(capacity, batch_size, samplers, cache_policy, device, max_ring, float_frames=float_frames, frames=frames)
     ctx = zmq.Context.instance()
     ctx.setsockopt(zmq.LINGER, 0)
     addrs = {k: f"tcp://{host}:{p}" for k, p in ports.items()}
@@ -158,7 +158,12 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
             except zmq.Again:
                 break
             kind, payload, weights, src = pack.open_append(frame.buffer)
-            if kind == "shm":
+            if kind == "steps":
+                head, frames, others = payload
+                reset = head.get("reset")
+                eng.append_steps((src[0] if src else "", head[pack.KEY_STEPS]), frames, others, weights,
+                                 None if reset is None else np.asarray(reset))
+            elif kind == "shm":
                 try:
                     append_from_ring(payload, weights)
                 except FileNotFoundError:              # the producer vanished with its ring: the rows are lost
@@ -202,7 +207,7 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
                 return
             ex = _cabi.IpcExport()
             eng.shard._ck(_cabi.lib().reth_replay_ipc_export(eng.shard._h, C.byref(ex)))
-            struct = [[np.dtype(dt).str, list(sh)] for dt, sh in eng.shard.struct]
+            struct = [[np.dtype(dt).str, list(sh)] for dt, sh in eng.shard.out_struct]
             if req.get("topic", eng.topic) != eng.topic:   # another sampler topic: served draw by draw
                 reply(ident, {"ok": True, "op": "open", "struct": struct, "batch_size": batch_size, "group": 1,
                               "ahead": 0, "lend": 1, "ring_depth": eng.shard.ring_depth}, bytes(ex))
@@ -319,7 +324,7 @@ class _ShmSegment:
 
 # ------------------------------------------------------------ public surface --
 def start_server(capacity, batch_size, host=None, port=None, samplers=None, cache_policy=None, device=0,
-                 max_ring=32):
+                 max_ring=32, frames=None, float_frames=None):
     """reth_buffer.start_server (__init__.py:11-27): spawn the server process, return
     (proc, meta_addr).  `proc` supports terminate()/join() as callers expect (trainer.py:72-74)."""
     host = host or "127.0.0.1"
@@ -331,7 +336,7 @@ def start_server(capacity, batch_size, host=None, port=None, samplers=None, cach
     ctx = mp.get_context("spawn")
     ready = ctx.Event()
     proc = ctx.Process(target=_server_entry, args=(capacity, batch_size, host, ports, samplers, cache_policy, device,
-                                                   max_ring, ready), daemon=True)
+                                                   max_ring, ready, frames, float_frames), daemon=True)
     proc.start()
     if not ready.wait(120):
         proc.terminate()
@@ -339,21 +344,23 @@ def start_server(capacity, batch_size, host=None, port=None, samplers=None, cach
     return proc, f"tcp://{host}:{ports['meta']}"
 
 
-def _server_entry(capacity, batch_size, host, ports, samplers, cache_policy, device, max_ring, ready):
+def _server_entry(capacity, batch_size, host, ports, samplers, cache_policy, device, max_ring, ready, frames=None,
+                  float_frames=None):
     from .sampler import PERSampler
     if samplers is not None:
         for s in samplers:
             pass                                       # class names are resolved by service._Engine
     prof_path = os.environ.get("RETH_B200_SERVER_PROFILE")      # diagnostic: cProfile of the server loop
     if not prof_path:
-        server_main(capacity, batch_size, host, ports, samplers, cache_policy, device, max_ring, ready)
+        server_main(capacity, batch_size, host, ports, samplers, cache_policy, device, max_ring, ready, frames, float_frames)
         return
     import cProfile
     import io
     import pstats
     pr = cProfile.Profile()
     try:
-        pr.runcall(server_main, capacity, batch_size, host, ports, samplers, cache_policy, device, max_ring, ready)
+        pr.runcall(server_main, capacity, batch_size, host, ports, samplers, cache_policy, device, max_ring, ready, frames,
+                   float_frames)
     finally:
         out = io.StringIO()
         pstats.Stats(pr, stream=out).sort_stats("tottime").print_stats(25)
@@ -363,12 +370,12 @@ def _server_entry(capacity, batch_size, host, ports, samplers, cache_policy, dev
 
 
 def start_per(capacity, batch_size, alpha=0.6, beta=0.4, sample_start=1000, num_sampler_procs=1,
-              host=None, port=None, cache_policy=None, device=0, max_ring=32):
+              host=None, port=None, cache_policy=None, device=0, max_ring=32, frames=None, float_frames=None):
     """reth_buffer.start_per (__init__.py:30-49)."""
     from .sampler import PERSampler
     samplers = [{"sampler_cls": PERSampler, "num_procs": num_sampler_procs, "sample_start": sample_start,
                  "kwargs": {"alpha": alpha, "beta": beta}}]
-    return start_server(capacity, batch_size, host, port, samplers, cache_policy, device, max_ring)
+    return start_server(capacity, batch_size, host, port, samplers, cache_policy, device, max_ring, frames, float_frames)
 
 
 _META_CACHE = {}
@@ -536,6 +543,18 @@ class Client:
             return                                            # same host: nothing to gain from compress
         else:
             msg = pack.encode_append_columns(data, weights, compress=compress, extra=self._next_append())
+        self.append_sock.send(msg, copy=False)
+
+    def append_steps(self, env, frames, others, weights, reset=None):
+        """Frame-de-duplicated ingest for a server started with frames=...: the observation frame after
+        each of n steps of environment stream `env`, the other columns of the n transitions, |TD|
+        weights; `reset` = first frame of an episode the stream starts.  Each frame travels once."""
+        weights = np.asarray(weights)
+        assert len(frames) == len(weights) and all(len(o) == len(weights) for o in others)
+        self.flush()
+        head = {pack.KEY_STEPS: str(env), "reset": None if reset is None else np.ascontiguousarray(reset, dtype=np.uint8)}
+        msg = pack.encode([head, np.ascontiguousarray(frames, dtype=np.uint8), [np.ascontiguousarray(o) for o in others],
+                           weights], extra=self._next_append())
         self.append_sock.send(msg, copy=False)
 
     def update_priorities(self, indices, weights, step=True):

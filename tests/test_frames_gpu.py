@@ -119,3 +119,51 @@ def test_frame_column_errors(mods):
     with pytest.raises(Exception):
         sh.slot_read(0, with_rows=True)
     sh.close()
+
+
+@pytest.mark.parametrize("layout", ["inproc", "process"])
+def test_service_append_steps(layout):
+    """The frame-de-duplicated layout behind the service surface: actors send one new frame per step
+    (Client.append_steps), loaders hand out the same k-stacks FrameStack would have produced."""
+    import __graft_entry__ as entry
+    entry.build()
+    from reth_b200 import service, service_mp
+    mod = service if layout == "inproc" else service_mp
+    B, k = 32, K
+    frames_cfg = {"k": k, "shape": FRAME, "capacity": 2048, "columns": (0, 3)}
+    proc, addr = mod.start_per(1024, B, alpha=0.6, beta=0.4, sample_start=B, frames=frames_cfg)
+    try:
+        client = mod.Client(addr)
+        rng = np.random.default_rng(23)
+        full = []                                           # transitions in arrival order, full stacks
+        stacks = {}
+        for env in range(2):
+            f0 = rng.integers(0, 256, FRAME, dtype=np.uint8)
+            stacks[env] = deque([f0] * k, maxlen=k)
+            client.append_steps(env, np.zeros((0,) + FRAME, np.uint8), [np.zeros(0, np.int64), np.zeros(0, np.float32),
+                                np.zeros(0, np.float32)], np.zeros(0, np.float32), reset=f0)
+        for rnd in range(6):
+            for env in range(2):
+                n = 40
+                fr = rng.integers(0, 256, (n,) + FRAME, dtype=np.uint8)
+                a = rng.integers(0, 18, n)
+                r = rng.standard_normal(n).astype(np.float32)
+                d = np.zeros(n, np.float32)
+                for i in range(n):
+                    s0 = np.stack(stacks[env])
+                    stacks[env].append(fr[i])
+                    full.append((s0, int(a[i]), r[i], np.stack(stacks[env])))
+                client.append_steps(env, fr, [a, r, d], rng.random(n).astype(np.float32) + 0.1)
+        loader = mod.TorchCudaLoader(addr, buffer_size=2)
+        for _ in range(6):
+            data, indices, weights = loader.sample()
+            assert tuple(data[0].shape) == (B, k) + FRAME
+            s0, s1 = data[0].cpu().numpy(), data[3].cpu().numpy()
+            for j, i in enumerate(indices):
+                assert np.array_equal(s0[j], full[i][0]) and np.array_equal(s1[j], full[i][3])
+            assert np.array_equal(data[1].cpu().numpy(), [full[i][1] for i in indices])
+            client.update_priorities(indices, np.ones(B, np.float32))
+        loader.close()
+    finally:
+        proc.terminate()
+        proc.join()
