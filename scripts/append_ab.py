@@ -4,7 +4,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import bench
 from reth_b200 import ReplayShard
-sh = ReplayShard(1 << 18, bench.ATARI, max_batch=512, ring_depth=2)
+sh = ReplayShard(int(os.environ.get("CAP", 1 << 18)), bench.ATARI, max_batch=512, ring_depth=2)
 out = {"memcpy": os.environ.get("RETH_APPEND_MEMCPY", "0")}
 for n in (4096, 16384, 65536):
     torch.cuda.synchronize()
