@@ -38,7 +38,7 @@ if __name__ == "__main__":
         for i in range(64):
             data, idx, w = loader.sample(); client.update_priorities(idx, newp[i % 64])
         loader.drain()
-        iters = 2000
+        iters = int(os.environ.get("ITERS", 2000))
         pr = None
         if os.environ.get("PROFILE"):
             import cProfile

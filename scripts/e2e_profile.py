@@ -24,7 +24,7 @@ eng.cnt = CAP
 client = service.Client(addr)
 loader = service.TorchCudaLoader(addr, buffer_size=(A + 1) * G, prefetch=G, ahead=A)
 newp = np.abs(np.random.default_rng(3).standard_normal((64, B))).astype(np.float32)
-N = 4000
+N = int(os.environ.get("ITERS", 4000))
 ts = np.zeros((N, 3))
 for i in range(200):
     d, idx, w = loader.sample()

@@ -5,12 +5,12 @@ import numpy as np, torch
 from reth_b200 import ReplayShard
 cap, B = int(os.environ.get("CAP", 1 << 20)), 512
 KEYS = tuple(range(1, 32))
-for cluster in (8, 16):
-    for G in (1, 4):
+for cluster in (16,):
+    for G in (1, 4, 8):
         sh = ReplayShard(cap, [], max_batch=B, store_rows=False, update_cluster=cluster, ring_depth=2 * G)
         w = torch.randn(cap, device="cuda").abs().float() + 0.01
         for st in range(0, cap, 16384): sh.append([], w[st:st+16384])
-        prio = torch.rand(128 * B, device="cuda")
+        prio = torch.rand(256 * B, device="cuda")
         sh.step_loop(20 * G, B, prio, gather=False, serial=True, group=G)
         torch.cuda.synchronize()
         acc = {}
