@@ -69,7 +69,7 @@ def measured_peak():
 
 # ------------------------------------------------------------------ clocks --
 class ClockSampler:
-    """nvidia-smi clocks/throttle reasons sampled every 200 ms during the timed region."""
+    """nvidia-smi clocks/throttle reasons sampled every 50 ms during the timed region."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
          "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
@@ -82,7 +82,7 @@ class ClockSampler:
     def start(self):
         try:
             self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                       "-lms", "200", "-i", str(self.gpu)], stdout=self.f, stderr=subprocess.DEVNULL)
+                                       "-lms", "50", "-i", str(self.gpu)], stdout=self.f, stderr=subprocess.DEVNULL)
         except Exception:
             self.p = None
 
@@ -379,10 +379,10 @@ def run_ours(args):
     ms1, _, _ = timed_loop(torch, dist, shard, max(1, args.steps // 2), 1, iters, B, prio, 1, world, False)
     strict = world * max(1, args.steps // 2) * iters * B / (ms1 / 1e3)
     # end to end through the public API with host buffers
-    e2e_iters = min(4000, max(400, args.steps * iters))
+    e2e_iters = min(20480, max(400, args.steps * iters))
     e2e_iters -= e2e_iters % G
     e2e, h2d, d2h = e2e_loop(torch, dist, service, addr, e2e_iters, 64, B, world, G, args.ahead)
-    e2e_strict, _, _ = e2e_loop(torch, dist, service, addr, min(1000, e2e_iters), 16, B, world, 1, 0)
+    e2e_strict, _, _ = e2e_loop(torch, dist, service, addr, min(4000, e2e_iters), 16, B, world, 1, 0)
     app_rows, app_gbs = append_rate(torch, shard) if rank == 0 or world == 1 else (None, None)
     apph_rows, apph_gbs = append_rate_host(torch, shard) if rank == 0 and world == 1 else (None, None)
 
@@ -453,7 +453,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--capacity", type=int, default=1 << 20)
     ap.add_argument("--batch", type=int, default=512)
-    ap.add_argument("--iters", type=int, default=128, help="learner iterations per bench step")
+    ap.add_argument("--iters", type=int, default=2048,
+                    help="learner iterations per bench step (2048 x batch 512 = 1 M sampled transitions, about 20 ms on one "
+                         "B200: the default 10 timed steps then span several clock samples)")
     ap.add_argument("--group", type=int, default=8,
                     help="prefetch group: batches drawn per launch (one draw kernel, one gather launch, one write-back)")
     ap.add_argument("--ahead", type=int, default=2,
