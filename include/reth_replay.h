@@ -328,6 +328,31 @@ int reth_ipc_close(reth_ipc_view_t *v);
  * reference has no counterpart (its learner polls whole batches shard by shard, trainer.py:33-36). */
 int reth_replay_gather_to(reth_replay_t *h, int slot, reth_ipc_view_t *dst, int dst_slot, void *stream);
 
+/* ---- shard roots over NVLink (SURVEY.md 8e "read peers' totals via NVLink-mapped memory"; the
+ *      reference has no counterpart: its shards never normalise against each other, trainer.py:33-36).
+ *      Mode G needs every shard's root {total, min} on every rank before a global draw.  Instead of a
+ *      host-driven collective per step, each shard owns a small "roots board" in its HBM; peers map it
+ *      (CUDA IPC from another process, peer access inside one process) and roots_exchange() launches
+ *      ONE kernel on `stream` that (phase 1) stores this shard's root into every peer's board over
+ *      NVLink and (phase 2) waits on its own board until all n_shards roots of this exchange number
+ *      have arrived, then snapshots them into the device array all_roots_dev() returns
+ *      (double[2*n_shards], the all_roots argument of reth_replay_sample_global).  Collective in the
+ *      NCCL sense: every shard of the group must issue the same sequence of exchanges; a peer that
+ *      never publishes ends the wait after RETH_BOARD_TIMEOUT_MS (default 2000) and the next
+ *      synchronising call returns RETH_ERR_STATE.  phases: 1 publish, 2 wait, 3 both in one launch
+ *      (shards driven by ONE host thread on one stream must publish all before any waits). */
+#define RETH_MAX_SHARDS 64
+typedef struct reth_board_export {
+    int32_t device, pid;
+    uint64_t local_ptr;                 /* the board's address inside the exporting process */
+    unsigned char handle[64];           /* cudaIpcMemHandle_t */
+} reth_board_export;
+int reth_replay_board_export(reth_replay_t *h, reth_board_export *out);
+int reth_replay_board_connect(reth_replay_t *h, const reth_board_export *boards /*[n_shards], rank order*/,
+                              int n_shards, int shard);
+int reth_replay_roots_exchange(reth_replay_t *h, int phases, void *stream);
+int reth_replay_all_roots_dev(reth_replay_t *h, double **all_roots_dev_out);
+
 /* ---- several sampler topics over one row store (start_server(samplers=[...]), server/main_loop.py:135-159:
  *      every sampler sees every append and every update, loaders pick a topic).  The first topic
  *      uses the row shard's own tree; each further topic is a tree-only handle (store_rows = 0, same
@@ -348,6 +373,10 @@ int reth_replay_gather_from(reth_replay_t *h, int dst_slot, reth_replay_t *src, 
  *      bit5: all gathers on ONE internal stream (default: consecutive gathers alternate between two
  *      streams so the tail of one overlaps the ramp-up of the next; bit2 timings are only per-kernel
  *      durations with bit5 set);
+ *      bit6: Mode G (after reth_replay_board_connect; group 1): every iteration starts with
+ *      roots_exchange(3) on the tree stream, draws this shard's share of a GLOBAL stratified batch of
+ *      `batch`, gathers and writes back that share (prio_dev: the first share-count values of each
+ *      step's `batch`); every shard of the group must run the same number of steps;
  *      bits 8..15: prefetch group G (0/1 = strict alternation): sample_multi / gather_multi /
  *      update_slots over G slots per iteration (steps must be a multiple of G). */
 int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, const float *prio_dev,

@@ -57,6 +57,10 @@ class IpcExport(C.Structure):
                 ("idx_handle", C.c_ubyte * 64), ("w_handle", C.c_ubyte * 64)]
 
 
+class BoardExport(C.Structure):
+    _fields_ = [("device", C.c_int32), ("pid", C.c_int32), ("local_ptr", C.c_uint64), ("handle", C.c_ubyte * 64)]
+
+
 def _sources():
     d = os.path.join(_HERE, "csrc")
     return [os.path.join(d, f) for f in sorted(os.listdir(d))] + [HEADER]
@@ -130,6 +134,10 @@ SIGNATURES = {
     "reth_ipc_slot_ptrs": [_vp, _i32, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp)],
     "reth_ipc_close": [_vp],
     "reth_replay_gather_to": [_vp, _i32, _vp, _i32, _vp],
+    "reth_replay_board_export": [_vp, C.POINTER(BoardExport)],
+    "reth_replay_board_connect": [_vp, C.POINTER(BoardExport), _i32, _i32],
+    "reth_replay_roots_exchange": [_vp, _i32, _vp],
+    "reth_replay_all_roots_dev": [_vp, C.POINTER(_vp)],
     "reth_replay_step_loop": [_vp, _i32, _i32, _vp, _vp, _u64, _f64, _f64, _i32, _vp],
     "reth_replay_gather_time": [_vp, C.POINTER(_f64), C.POINTER(_i64)],
     "reth_replay_debug_stamps": [_vp, C.POINTER(_i64)],

@@ -9,6 +9,8 @@
 #include <string>
 #include <vector>
 
+#include <unistd.h>
+
 #include "../../include/reth_replay.h"
 #include "copy.cuh"
 #include "lz4f.h"
@@ -107,6 +109,13 @@ struct reth_replay {
         // update kernel's dependent chain cost more than the copy operations they save.
         bool zero_copy = false;
     } pipe;
+    // shard roots over NVLink (reth_replay_board_*): own board, peers' boards as mapped here, exchange number
+    BoardEntry *board = nullptr;
+    BoardEntry *peer_board[kMaxShards] = {};
+    bool peer_ipc[kMaxShards] = {};   // opened with cudaIpcOpenMemHandle (to close at destroy)
+    double *all_roots = nullptr;
+    int board_shards = 0, board_shard = 0;
+    unsigned long long board_seq = 0;
     int pipe_reserved = 0;        // batch slots at the end of the ring that a pipe never uses (other sampler topics)
     // set by pipe_issue around its draw: the sampling kernel also writes into mapped pinned host memory
     int64_t *mirror_idx = nullptr;
@@ -161,6 +170,9 @@ void free_all(reth_replay *h)
     cudaFree(h->counts); cudaFree(h->err);
     cudaFree(h->uni_log); cudaFree(h->fifo_idx); cudaFree(h->fifo_w);
     cudaFree(h->dbg);
+    for (int i = 0; i < kMaxShards; ++i)
+        if (h->peer_ipc[i] && h->peer_board[i]) cudaIpcCloseMemHandle(h->peer_board[i]);
+    cudaFree(h->board); cudaFree(h->all_roots);
     cudaFree(h->stage_idx); cudaFree(h->stage_prio); cudaFree(h->stage_u);
     if (h->host_pin) cudaFreeHost(h->host_pin);
     for (int c = 0; c < kMaxCols; ++c) cudaFree(h->ring[c]);
@@ -453,6 +465,8 @@ int check_device_err(reth_replay *h, cudaStream_t s)
     CK(h, cudaStreamSynchronize(s));
     if (*flag) {
         cudaMemsetAsync(h->err, 0, sizeof(int32_t), s);
+        if (*flag & kErrBoardTimeout)
+            return fail(h, RETH_ERR_STATE, "roots exchange timed out: a peer shard did not publish its root");
         return fail(h, RETH_ERR_RANGE, "an index outside [0, capacity) was passed to the shard");
     }
     return RETH_OK;
@@ -1766,6 +1780,110 @@ RETH_EXPORT int reth_ipc_close(reth_ipc_view_t *v)
     return RETH_OK;
 }
 
+// ------------------------------------------------------ shard roots over NVLink --
+namespace {
+
+int board_alloc(reth_replay *h)
+{
+    if (h->board) return RETH_OK;
+    CK(h, dalloc_zero(&h->board, (size_t)kBoardEntries, &h->st.hbm_bytes));
+    CK(h, dalloc_zero(&h->all_roots, (size_t)2 * kMaxShards, &h->st.hbm_bytes));
+    return RETH_OK;
+}
+
+int launch_roots_exchange(reth_replay *h, int phases, cudaStream_t s)
+{
+    if (h->board_shards < 1) return fail(h, RETH_ERR_STATE, "roots exchange before reth_replay_board_connect");
+    const int timeout_ms = env_int("RETH_BOARD_TIMEOUT_MS", 2000);
+    if (phases & 1) h->board_seq++;
+    if (h->board_seq == 0) return fail(h, RETH_ERR_STATE, "roots exchange: wait before the first publish");
+    RootsArgs a = {};
+    a.agg = h->agg;
+    for (int i = 0; i < h->board_shards; ++i) a.board[i] = h->peer_board[i];
+    a.all_roots = h->all_roots;
+    a.n_shards = h->board_shards; a.shard = h->board_shard; a.phases = phases;
+    a.seq = h->board_seq;
+    a.timeout_ns = (unsigned long long)timeout_ms * 1000000ull;
+    a.err = h->err;
+    roots_exchange_kernel<<<1, kMaxShards, 0, s>>>(a);
+    CK(h, cudaGetLastError());
+    h->st.kernel_launches++;
+    return RETH_OK;
+}
+
+}  // namespace
+
+RETH_EXPORT int reth_replay_board_export(reth_replay_t *h, reth_board_export *out)
+{
+    if (!h || !out) return RETH_ERR_INVALID;
+    DeviceGuard guard(h->cfg.device);
+    int rc = board_alloc(h);
+    if (rc) return rc;
+    memset(out, 0, sizeof *out);
+    out->device = h->cfg.device;
+    out->pid = (int32_t)getpid();
+    out->local_ptr = (uint64_t)(uintptr_t)h->board;
+    CK(h, cudaIpcGetMemHandle((cudaIpcMemHandle_t *)out->handle, h->board));
+    return RETH_OK;
+}
+
+RETH_EXPORT int reth_replay_board_connect(reth_replay_t *h, const reth_board_export *boards, int n_shards, int shard)
+{
+    if (!h || !boards) return RETH_ERR_INVALID;
+    if (n_shards < 1 || n_shards > kMaxShards || shard < 0 || shard >= n_shards)
+        return fail(h, RETH_ERR_INVALID, "board_connect: shard %d of %d (at most %d shards)", shard, n_shards, kMaxShards);
+    if (h->board_shards) return fail(h, RETH_ERR_STATE, "the roots board is already connected");
+    DeviceGuard guard(h->cfg.device);
+    int rc = board_alloc(h);
+    if (rc) return rc;
+    for (int i = 0; i < n_shards; ++i) {
+        const reth_board_export &b = boards[i];
+        if (i == shard) { h->peer_board[i] = h->board; continue; }
+        if (b.pid == (int32_t)getpid()) {
+            // same process: the pointer is valid here; another device needs peer access (NVLink)
+            if (b.device != h->cfg.device) {
+                cudaError_t e = cudaDeviceEnablePeerAccess(b.device, 0);
+                if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+                else if (e != cudaSuccess)
+                    return fail(h, RETH_ERR_CUDA, "peer access %d -> %d: %s", h->cfg.device, b.device, cudaGetErrorString(e));
+            }
+            h->peer_board[i] = (BoardEntry *)(uintptr_t)b.local_ptr;
+        } else {
+            cudaIpcMemHandle_t mh;
+            memcpy(&mh, b.handle, sizeof mh);
+            void *p = nullptr;
+            cudaError_t e = cudaIpcOpenMemHandle(&p, mh, cudaIpcMemLazyEnablePeerAccess);
+            if (e != cudaSuccess) {
+                cudaGetLastError();
+                return fail(h, RETH_ERR_CUDA, "cudaIpcOpenMemHandle (board of shard %d): %s", i, cudaGetErrorString(e));
+            }
+            h->peer_board[i] = (BoardEntry *)p;
+            h->peer_ipc[i] = true;
+        }
+    }
+    h->board_shards = n_shards;
+    h->board_shard = shard;
+    return RETH_OK;
+}
+
+RETH_EXPORT int reth_replay_roots_exchange(reth_replay_t *h, int phases, void *stream)
+{
+    if (!h) return RETH_ERR_INVALID;
+    if (phases < 1 || phases > 3) return fail(h, RETH_ERR_INVALID, "phases must be 1 (publish), 2 (wait) or 3 (both)");
+    DeviceGuard guard(h->cfg.device);
+    return launch_roots_exchange(h, phases, S(stream));
+}
+
+RETH_EXPORT int reth_replay_all_roots_dev(reth_replay_t *h, double **all_roots_dev_out)
+{
+    if (!h || !all_roots_dev_out) return RETH_ERR_INVALID;
+    DeviceGuard guard(h->cfg.device);
+    int rc = board_alloc(h);
+    if (rc) return rc;
+    *all_roots_dev_out = h->all_roots;
+    return RETH_OK;
+}
+
 // ------------------------------------------------------------------ step loop --
 RETH_EXPORT int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, const float *prio_dev,
                                       const double *uniforms_dev, uint64_t seed, double alpha, double beta,
@@ -1778,9 +1896,12 @@ RETH_EXPORT int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, co
     const bool no_gather = flags & 1, serial = flags & 2, timed = flags & 4;
     const bool no_sample = flags & 8, no_update = flags & 16;   // kernel micro-timing only
     const bool one_gather_stream = flags & 32;
+    const bool global = flags & 64;                   // Mode G: roots exchange over NVLink + global stratified draw
     const int depth = (int)h->slots.size();
     int G = (flags >> 8) & 0xff;                      // batches per tree launch (prefetch group)
     if (G < 1) G = 1;
+    if (global && (G != 1 || h->board_shards < 1 || no_sample || no_update || uniforms_dev))
+        return fail(h, RETH_ERR_INVALID, "Mode G loop: connected roots board, group 1, device generator, sample and update on");
     if (G > 1 && (batch != h->cfg.max_batch || depth % G != 0 || depth < 2 * G || steps % G != 0 ||
                   (int64_t)G * batch > h->max_n))
         return fail(h, RETH_ERR_INVALID, "group %d needs batch == max_batch, ring_depth a multiple >= 2*group, steps %% group == 0", G);
@@ -1798,7 +1919,11 @@ RETH_EXPORT int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, co
         // the slots' index buffers are re-drawn: their previous gather must have consumed them
         if (!serial && !no_gather && k >= depth) CK(h, cudaStreamWaitEvent(st, h->ev_gathered[slot], 0));
         int rc = RETH_OK;
-        if (!no_sample || h->slots[slot].batch != batch)
+        if (global) {
+            rc = launch_roots_exchange(h, 3, st);
+            if (!rc) rc = do_sample(h, batch, nullptr, RETH_DEVICE, seed, beta, slot, h->all_roots,
+                                    h->board_shards, h->board_shard, st, 1);
+        } else if (!no_sample || h->slots[slot].batch != batch)
             rc = do_sample(h, batch, uniforms_dev ? uniforms_dev + (size_t)k * batch : nullptr, RETH_DEVICE,
                            seed, beta, slot, nullptr, 1, 0, st, G);
         if (rc) return rc;
@@ -1820,7 +1945,7 @@ RETH_EXPORT int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, co
                 }
                 CK(h, cudaEventRecord(h->ev_time[h->ev_time_used], sg));
             }
-            rc = do_gather(h, slot, false, sg, G);
+            rc = do_gather(h, slot, global, sg, G);
             if (rc) return rc;
             if (timed) h->ev_time_launches++;
             if (close_bracket) {
@@ -1834,6 +1959,7 @@ RETH_EXPORT int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, co
         a.n = (int64_t)batch * G; a.idx = h->slots[slot].idx; a.idx_kind = 0;
         a.prio = prio_dev + (size_t)k * batch; a.prio_kind = 0;
         a.alpha = alpha; a.transform = 1; a.dedupe = G == 1 ? 2 : 1;
+        if (global) a.n_dev = h->slots[slot].meta + 1;          // this shard's share of the global batch
         rc = launch_update(h, a, st);
         if (rc) return rc;
         h->st.updated_rows += (int64_t)batch * G;

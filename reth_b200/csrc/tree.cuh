@@ -664,6 +664,78 @@ __global__ void sampler_pick_kernel(const PickArgs a)
     if (a.idx_mirror) { a.idx_mirror[i] = v; a.w_mirror[i] = w; }
 }
 
+// ------------------------------------------------ shard roots over NVLink --
+// Mode G needs every shard's 16-byte root {total, min} on every rank before a global
+// stratified draw.  The message is pure latency, so instead of a host-driven collective each shard
+// owns a "roots board" in its HBM that every peer maps (CUDA IPC / peer access) and WRITES its root
+// into with plain stores over NVLink; the same kernel then waits on its OWN board (local L2 polls)
+// until the entries of the current exchange number arrived.  One launch per step on the sampling
+// stream, no host round trip: a device-side all-gather fused between the tree update and the draw.
+// Entries are double-buffered by the parity of the exchange number: a peer can publish exchange
+// k+1 only after its own wait for k, which needed MY publish of k, so nobody is ever two ahead.
+struct BoardEntry {
+    double sum, mn;
+    unsigned long long seq, pad;
+};
+constexpr int kMaxShards = 64;
+constexpr int kBoardEntries = 2 * kMaxShards;
+constexpr int kErrBoardTimeout = 0x100;
+
+struct RootsArgs {
+    const double2 *agg;                 // this shard's tree (root = agg[1])
+    BoardEntry *board[kMaxShards];      // board of shard s as mapped here (own board for s == shard)
+    double *all_roots;                  // out: double[2*n_shards] = {total_s, min_s} in rank order
+    int32_t n_shards, shard, phases;    // phases bit0: publish, bit1: wait + snapshot
+    unsigned long long seq;             // exchange number, >= 1
+    unsigned long long timeout_ns;
+    int32_t *err;
+};
+
+__device__ __forceinline__ void st_release_sys(unsigned long long *p, unsigned long long v)
+{
+    asm volatile("st.release.sys.global.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long *p)
+{
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned long long global_ns()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+// one thread per shard
+__global__ void __launch_bounds__(kMaxShards) roots_exchange_kernel(const RootsArgs a)
+{
+    const int s = threadIdx.x;
+    if (s >= a.n_shards) return;
+    const int par = (int)(a.seq & 1ull);
+    if (a.phases & 1) {
+        const double2 r = ldcg2(&a.agg[1]);
+        BoardEntry *e = a.board[s] + par * kMaxShards + a.shard;
+        volatile double *vs = &e->sum, *vm = &e->mn;
+        *vs = r.x;
+        *vm = r.y;
+        st_release_sys(&e->seq, a.seq);      // orders the two data stores before the flag, system scope
+    }
+    if (a.phases & 2) {
+        const BoardEntry *e = a.board[a.shard] + par * kMaxShards + s;
+        const unsigned long long t0 = global_ns();
+        bool ok = true;
+        while (ld_acquire_sys(&e->seq) != a.seq) {
+            if (global_ns() - t0 > a.timeout_ns) { ok = false; break; }
+        }
+        if (!ok) { atomicOr(a.err, kErrBoardTimeout); return; }
+        const volatile double *vs = &e->sum, *vm = &e->mn;
+        a.all_roots[2 * s] = *vs;
+        a.all_roots[2 * s + 1] = *vm;
+    }
+}
+
 // ---------------------------------------------------------------- readback --
 // Tiled -> heap order (the three arrays of NumbaSumTree, utils/sumtree.py:85-88).
 __global__ void tree_read_kernel(TreeGeom g, const double2 *desc, const double2 *agg,

@@ -535,6 +535,29 @@ class ReplayShard:
         self._ck(self._lib.reth_replay_ipc_export(self._h, C.byref(ex)))
         return bytes(ex)
 
+    # ---- shard roots over NVLink (Mode G without a host-driven collective)
+    def board_export(self):
+        """bytes descriptor of this shard's roots board, for board_connect() on every shard of the group."""
+        ex = _cabi.BoardExport()
+        self._ck(self._lib.reth_replay_board_export(self._h, C.byref(ex)))
+        return bytes(ex)
+
+    def board_connect(self, blobs, shard):
+        """blobs: board_export() of every shard in rank order (own entry included)."""
+        arr = (_cabi.BoardExport * len(blobs))(*[_cabi.BoardExport.from_buffer_copy(b) for b in blobs])
+        self._ck(self._lib.reth_replay_board_connect(self._h, arr, len(blobs), int(shard)))
+
+    def roots_exchange(self, phases=3, stream=None):
+        """ONE kernel on `stream`: store this shard's root {total, min} into every peer's board over NVLink
+        (phase 1) and wait until all roots of this exchange arrived in the own board (phase 2); the snapshot
+        is all_roots_dev().  Collective: every shard issues the same sequence."""
+        self._ck(self._lib.reth_replay_roots_exchange(self._h, int(phases), self._s(stream)))
+
+    def all_roots_dev(self, n_shards):
+        p = C.c_void_p()
+        self._ck(self._lib.reth_replay_all_roots_dev(self._h, C.byref(p)))
+        return _DevArray(p.value, (2 * int(n_shards),), np.float64, self)
+
     def gather_to(self, slot, ring, dst_slot, stream=None):
         """After sample_global(slot): gather this shard's rows, indices and weights straight into rows
         [first, first+count) of batch slot `dst_slot` of a peer's ring (NVLink stores from the kernel);
@@ -601,13 +624,13 @@ class ReplayShard:
 
     def step_loop(self, steps, batch, prio_dev, uniforms_dev=None, seed=0, alpha=0.6, beta=0.4,
                   gather=True, serial=False, time_gather=False, sample=True, update=True, group=1,
-                  one_gather_stream=False, stream=None):
+                  one_gather_stream=False, global_mode=False, stream=None):
         pp, ploc, pdt, pcnt, pk = _ptr_loc(prio_dev)
         assert ploc == DEVICE and pdt == np.dtype(np.float32) and pcnt >= steps * batch
         up, uloc, udt, ucnt, uk = _ptr_loc(uniforms_dev)
         if uniforms_dev is not None:
             assert uloc == DEVICE and udt == np.dtype(np.float64) and ucnt >= steps * batch
-        flags = (0 if gather else 1) | (2 if serial else 0) | (4 if time_gather else 0) | (0 if sample else 8) | (0 if update else 16) | (32 if one_gather_stream else 0) | ((int(group) & 0xff) << 8)
+        flags = (0 if gather else 1) | (2 if serial else 0) | (4 if time_gather else 0) | (0 if sample else 8) | (0 if update else 16) | (32 if one_gather_stream else 0) | (64 if global_mode else 0) | ((int(group) & 0xff) << 8)
         self._ck(self._lib.reth_replay_step_loop(self._h, int(steps), int(batch), pp, up,
                                                  int(seed) & (2**64 - 1), float(alpha), float(beta),
                                                  flags, self._s(stream)))

@@ -77,10 +77,27 @@ class ShardGroup:
         self.device = device if device is not None else torch.device("cuda", shard.device)
         self.all_roots = torch.zeros(2 * self.world, dtype=torch.float64, device=self.device)
         self._mine = torch.as_tensor(shard.root_dev(), device=self.device)   # zero-copy view of {total, min}
+        self.board = False
 
-    def exchange_roots(self, async_op=False):
-        """all-gather of the 16-byte shard roots (NCCL over NVLink); -> device float64[2*world]."""
+    def exchange_roots(self, async_op=False, stream=None):
+        """all-gather of the 16-byte shard roots -> device float64[2*world] (self.all_roots).
+        Default: torch.distributed (NCCL over NVLink).  After connect_board(): ONE kernel of this library on
+        `stream` (peer stores into every rank's roots board + a wait on the own board), no host round trip."""
+        if self.board:
+            self.shard.roots_exchange(3, stream=stream)
+            return None
         return self.dist.all_gather_into_tensor(self.all_roots, self._mine, group=self.group, async_op=async_op)
+
+    def connect_board(self):
+        """Map every rank's roots board into this process (CUDA IPC; peers are reached over NVLink) and
+        switch exchange_roots() to the device-side exchange.  Collective: every rank must call it."""
+        import torch
+        blobs = [None] * self.world
+        self.dist.all_gather_object(blobs, self.shard.board_export(), group=self.group)
+        self.shard.board_connect(blobs, self.rank)
+        self.all_roots = torch.as_tensor(self.shard.all_roots_dev(self.world), device=self.device)
+        self.dist.barrier(group=self.group)      # every board is mapped before anyone publishes
+        self.board = True
 
     def connect_learner(self, learner_rank):
         """Map the learner rank's batch ring into this process (CUDA IPC; a ring on another GPU is
