@@ -144,6 +144,7 @@ struct RowCol {
     int32_t units;        // 16 B units per chunk
     int32_t cast;         // gather only: 0 raw, 1 u8 -> f32, 2 u8 -> f32 / 255 (batch rows are 4*rb bytes)
     int64_t item_base;    // first work item of this column
+    int32_t chunk_base;   // chunks of the wide columns before this one (row-major item order, kDense)
 };
 
 struct RowArgs {
@@ -155,6 +156,8 @@ struct RowArgs {
     int32_t dst_row_from_meta; // batch row of local row i is meta[0] + i (cross-shard assembly into a peer's batch)
     int64_t wide_items;        // items over all wide columns (batch-relative layout)
     int32_t narrow_groups;     // ceil(batch / kCopyThreads) when narrow columns exist
+    int32_t chunks_per_row;    // chunks of one row over all wide columns
+    int32_t share_div;         // host-side launch hint: about batch / share_div rows are valid (Mode G: n_shards), 0 = all
     // scatter only: last-writer-wins arbitration (same stamps as the tree update)
     const uint32_t *stamp;
     int64_t capacity;
@@ -165,21 +168,38 @@ struct RowArgs {
 // kScatter=true : ring[idx[i]] <- batch[i]   (append to policy-chosen slots)
 // kWiden (gather only): some column is emitted as float32 (RowCol::cast); a separate instantiation so
 // that the plain byte mover keeps its register budget.
-template <bool kScatter, bool kWiden = false>
+// kDense (gather of a Mode G slot): the launch covers `batch` rows but only the first meta[1] belong to this
+// shard (1/n_shards of a global batch on average).  Items are then numbered row-major over the VALID rows only,
+// so surplus CTAs leave after one comparison -- with the column-major numbering every skipped item costs its
+// CTA a column search and a 64-bit division in all eight warps, which at 8 shards is more issue time than
+// the copy itself.
+template <bool kScatter, bool kWiden = false, bool kDense = false>
 __global__ void __launch_bounds__(kCopyThreads, kWiden ? 4 : 6) row_move_kernel(const RowArgs a)
 {
     const int rows = a.meta ? (int)a.meta[1] : a.batch;
     const int64_t row0 = (a.meta && a.dst_row_from_meta) ? a.meta[0] : 0;
-    const int64_t total = a.wide_items + a.narrow_groups;
+    const int64_t wide_items = kDense ? (int64_t)rows * a.chunks_per_row : a.wide_items;
+    const int64_t total = wide_items + (kDense ? (a.narrow_groups ? (rows + kCopyThreads - 1) / kCopyThreads : 0)
+                                               : a.narrow_groups);
     for (int64_t item = blockIdx.x; item < total; item += gridDim.x) {
-        if (item < a.wide_items) {
-            int c = 0;
+        if (item < wide_items) {
+            int c = 0, row, chunk;
+            if (kDense) {
+                row = (int)(item / a.chunks_per_row);
+                const int k = (int)(item - (int64_t)row * a.chunks_per_row);
 #pragma unroll 1
-            for (int k = 0; k < a.ncols; ++k)
-                if (a.col[k].chunks > 0 && item >= a.col[k].item_base) c = k;
+                for (int q = 0; q < a.ncols; ++q)
+                    if (a.col[q].chunks > 0 && k >= a.col[q].chunk_base) c = q;
+                chunk = k - a.col[c].chunk_base;
+            } else {
+#pragma unroll 1
+                for (int k = 0; k < a.ncols; ++k)
+                    if (a.col[k].chunks > 0 && item >= a.col[k].item_base) c = k;
+                const int64_t rel = item - a.col[c].item_base;
+                row = (int)(rel / a.col[c].chunks);
+                chunk = (int)(rel - (int64_t)row * a.col[c].chunks);
+            }
             const RowCol &col = a.col[c];
-            const int64_t rel = item - col.item_base;
-            const int row = (int)(rel / col.chunks), chunk = (int)(rel - (int64_t)row * col.chunks);
             if (row >= rows) continue;
             const int64_t slot = a.idx[row];
             if (slot < 0 || slot >= a.capacity) { if (threadIdx.x == 0) atomicOr(a.err, 1); continue; }
@@ -229,7 +249,7 @@ __global__ void __launch_bounds__(kCopyThreads, kWiden ? 4 : 6) row_move_kernel(
                 if (q < cnt) st_stream(d + j + q * kCopyThreads, v[q]);
         } else {
             // narrow / unaligned columns: one thread per row, all such columns
-            const int row = (int)(item - a.wide_items) * kCopyThreads + threadIdx.x;
+            const int row = (int)(item - wide_items) * kCopyThreads + threadIdx.x;
             if (row >= rows) continue;
             const int64_t slot = a.idx[row];
             if (slot < 0 || slot >= a.capacity) { atomicOr(a.err, 1); continue; }

@@ -32,6 +32,7 @@ struct BatchSlot {
     int64_t *meta = nullptr;   // {first, count}
     int32_t batch = 0;
     bool partial = false;      // Mode G draw: only meta[1] of the `batch` entries belong to this shard
+    int shards = 1;            // ... of a global batch drawn over this many shards (expected share batch / shards)
 };
 
 }  // namespace
@@ -744,6 +745,8 @@ void build_row_args(reth_replay *h, RowArgs &a, uint8_t *const *batch_cols, cons
             col.chunks = (int32_t)((upr + units_target - 1) / units_target);
             col.units = (int32_t)((upr + col.chunks - 1) / col.chunks);
             col.item_base = items;
+            col.chunk_base = a.chunks_per_row;
+            a.chunks_per_row += col.chunks;
             items += (int64_t)batch * col.chunks;
         } else {
             col.chunks = 0;
@@ -763,8 +766,16 @@ int launch_row_move(reth_replay *h, const RowArgs &a, cudaStream_t s)
     if (total <= 0) return RETH_OK;
     static const int waves = [] { const char *e = getenv("RETH_GATHER_WAVES"); int v = e ? atoi(e) : 64; return v < 1 ? 1 : v; }();
     const int64_t maxg = (int64_t)h->n_sms * 6 * waves;     // resident CTAs x waves; beyond that CTAs stride over the items
-    const unsigned grid = (unsigned)(total < maxg ? total : maxg);
+    unsigned grid = (unsigned)(total < maxg ? total : maxg);
+    if (!kScatter && !widen && a.meta && a.share_div > 1) {
+        // Mode G share: CTAs beyond the valid items leave at once, but 0.4 us per thousand of them adds up
+        // (48 k surplus CTAs = 22 us): size the grid for twice the expected share, a larger share strides
+        int64_t want = 2 * (total / a.share_div) + 64;
+        if (want < (int64_t)h->n_sms * 6 * 4) want = (int64_t)h->n_sms * 6 * 4;
+        if (want < (int64_t)grid) grid = (unsigned)want;
+    }
     if (!kScatter && widen) row_move_kernel<false, true><<<grid, kCopyThreads, 0, s>>>(a);
+    else if (!kScatter && a.meta) row_move_kernel<false, false, true><<<grid, kCopyThreads, 0, s>>>(a);   // row count on the device
     else row_move_kernel<kScatter><<<grid, kCopyThreads, 0, s>>>(a);
     CK(h, cudaGetLastError());
     h->st.kernel_launches++;
@@ -872,7 +883,11 @@ int do_sample(reth_replay *h, int batch, const double *uniforms, int uniforms_lo
     CK(h, cudaGetLastError());
     h->st.kernel_launches++;
     h->st.sampled_rows += (int64_t)batch * groups;
-    for (int g = 0; g < groups; ++g) { h->slots[slot + g].batch = batch; h->slots[slot + g].partial = n_shards > 1; }
+    for (int g = 0; g < groups; ++g) {
+        h->slots[slot + g].batch = batch;
+        h->slots[slot + g].partial = n_shards > 1;
+        h->slots[slot + g].shards = n_shards;
+    }
     return RETH_OK;
 }
 
@@ -890,6 +905,7 @@ int do_gather(reth_replay *h, int slot, bool use_meta, cudaStream_t s, int group
         RowArgs a;
         build_row_args(h, a, b.cols, b.idx, b.batch * groups, 0, true);
         a.meta = meta;
+        a.share_div = b.partial ? b.shards : 0;
         rc = launch_row_move<false>(h, a, s);
         if (!rc) rc = launch_frame_gather(h, b.cols, b.idx, b.batch * groups, meta, 0, s);
     }
@@ -1720,6 +1736,7 @@ RETH_EXPORT int reth_replay_gather_to(reth_replay_t *h, int slot, reth_ipc_view_
         build_row_args(h, a, cols, b.idx, b.batch, 0, true);
         a.meta = b.meta;
         a.dst_row_from_meta = 1;
+        a.share_div = b.partial ? b.shards : 0;
         int rc = launch_row_move<false>(h, a, s);
         if (!rc) rc = launch_frame_gather(h, cols, b.idx, b.batch, b.meta, 1, s);
         if (rc) return rc;
@@ -1753,6 +1770,7 @@ RETH_EXPORT int reth_replay_gather_from(reth_replay_t *h, int dst_slot, reth_rep
         build_row_args(h, a, d.cols, b.idx, b.batch, 0, true);
         a.meta = b.meta;
         a.dst_row_from_meta = 1;
+        a.share_div = b.partial ? b.shards : 0;
         int rc = launch_row_move<false>(h, a, s);
         if (!rc) rc = launch_frame_gather(h, d.cols, b.idx, b.batch, b.meta, 1, s);
         if (rc) return rc;
@@ -1763,6 +1781,7 @@ RETH_EXPORT int reth_replay_gather_from(reth_replay_t *h, int dst_slot, reth_rep
     h->st.kernel_launches++;
     d.batch = b.batch;
     d.partial = b.partial;
+    d.shards = b.shards;
     return RETH_OK;
 }
 

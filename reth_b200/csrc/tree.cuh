@@ -148,7 +148,7 @@ __global__ void __launch_bounds__(256) per_sample_kernel(const SampleArgs a)
     const int64_t cap = a.g.capacity;
 
     double total, pmin, prefix = 0.0;
-    int64_t first = 0, end = a.batch;
+    int64_t first = 0;
     if (a.n_shards > 1) {
         // global CDF over shard totals in rank order (Mode G)
         total = 0.0;
@@ -161,12 +161,19 @@ __global__ void __launch_bounds__(256) per_sample_kernel(const SampleArgs a)
         }
         pmin = (mn != 0.0) ? mn : 1.0;
         const double seg = total / (double)a.batch;
+        const bool last = a.shard == a.n_shards - 1;
+        if (i == 0) {                          // one warp reports the share {first, count}
+            const int64_t f = lower_bound_target(a, seg, prefix, lane);
+            int64_t e = last ? (int64_t)a.batch : lower_bound_target(a, seg, prefix + mine, lane);
+            if (e < f) e = f;
+            if (lane == 0) { a.meta[0] = f; a.meta[1] = e - f; }
+        }
+        // targets are monotone in i, so membership in [first, end) follows from the warp's own target:
+        // i >= first  <=>  target_i >= prefix,   i < end  <=>  not (target_i >= prefix + mine).
+        // Warps outside the share (all but 1/n_shards of a global batch) leave after one draw.
+        const double tgt = ((double)i + draw_u(a, W)) * seg;
+        if ((prefix > 0.0 && !(tgt >= prefix)) || (!last && tgt >= prefix + mine)) return;
         first = lower_bound_target(a, seg, prefix, lane);
-        end = (a.shard == a.n_shards - 1) ? (int64_t)a.batch
-                                          : lower_bound_target(a, seg, prefix + mine, lane);
-        if (end < first) end = first;
-        if (i == 0 && lane == 0) { a.meta[0] = first; a.meta[1] = end - first; }
-        if (i < first || i >= end) return;
     } else {
         const double2 root = ldcg2(&a.agg[1]);
         total = root.x;
@@ -428,6 +435,7 @@ __global__ void __launch_bounds__(kUpdateThreads) per_update_kernel(const Update
         const int64_t m = __ldcg(a.n_dev) - a.n_off;
         n = m < n ? (m < 0 ? 0 : m) : n;
     }
+    if (n <= 0) return;     // Mode G chunk beyond this shard's share: uniform over the cluster, nothing was touched
     const bool inrange = i < n;
     int64_t idx = 0, nxt = -1;
     double raw = 0.0;
