@@ -117,6 +117,7 @@ struct reth_replay {
     double *all_roots = nullptr;
     int board_shards = 0, board_shard = 0;
     unsigned long long board_seq = 0;
+    bool pdl = false;             // tree-chain launches carry the programmatic-dependent-launch attribute (set by step_loop)
     int pipe_reserved = 0;        // batch slots at the end of the ring that a pipe never uses (other sampler topics)
     // set by pipe_issue around its draw: the sampling kernel also writes into mapped pinned host memory
     int64_t *mirror_idx = nullptr;
@@ -433,13 +434,15 @@ int launch_update(reth_replay *h, UpdateArgs &a, cudaStream_t s)
         cfg.gridDim = dim3(h->update_cluster);
         cfg.blockDim = dim3(kUpdateThreads);
         cfg.stream = s;
-        cudaLaunchAttribute at[1];
+        cudaLaunchAttribute at[2];
         at[0].id = cudaLaunchAttributeClusterDimension;
         at[0].val.clusterDim.x = h->update_cluster;
         at[0].val.clusterDim.y = 1;
         at[0].val.clusterDim.z = 1;
+        at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[1].val.programmaticStreamSerializationAllowed = 1;
         cfg.attrs = at;
-        cfg.numAttrs = 1;
+        cfg.numAttrs = h->pdl ? 2 : 1;
         CK(h, cudaLaunchKernelEx(&cfg, per_update_kernel, (const UpdateArgs)a));
         h->st.kernel_launches++;
     }
@@ -879,7 +882,20 @@ int do_sample(reth_replay *h, int batch, const double *uniforms, int uniforms_lo
     a.idx_mirror = h->mirror_idx; a.w_mirror = h->mirror_w; a.err_mirror = h->mirror_err; a.err = h->err;
     a.all_roots = all_roots; a.n_shards = n_shards; a.shard = shard;
     const int wpb = 4;
-    per_sample_kernel<<<(batch * groups + wpb - 1) / wpb, wpb * 32, 0, s>>>(a);
+    if (h->pdl) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((batch * groups + wpb - 1) / wpb);
+        cfg.blockDim = dim3(wpb * 32);
+        cfg.stream = s;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at;
+        cfg.numAttrs = 1;
+        CK(h, cudaLaunchKernelEx(&cfg, per_sample_kernel, (const SampleArgs)a));
+    } else {
+        per_sample_kernel<<<(batch * groups + wpb - 1) / wpb, wpb * 32, 0, s>>>(a);
+    }
     CK(h, cudaGetLastError());
     h->st.kernel_launches++;
     h->st.sampled_rows += (int64_t)batch * groups;
@@ -1824,7 +1840,20 @@ int launch_roots_exchange(reth_replay *h, int phases, cudaStream_t s)
     a.seq = h->board_seq;
     a.timeout_ns = (unsigned long long)timeout_ms * 1000000ull;
     a.err = h->err;
-    roots_exchange_kernel<<<1, kMaxShards, 0, s>>>(a);
+    if (h->pdl) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(1);
+        cfg.blockDim = dim3(kMaxShards);
+        cfg.stream = s;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at;
+        cfg.numAttrs = 1;
+        CK(h, cudaLaunchKernelEx(&cfg, roots_exchange_kernel, (const RootsArgs)a));
+    } else {
+        roots_exchange_kernel<<<1, kMaxShards, 0, s>>>(a);
+    }
     CK(h, cudaGetLastError());
     h->st.kernel_launches++;
     return RETH_OK;
@@ -1925,6 +1954,13 @@ RETH_EXPORT int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, co
                   (int64_t)G * batch > h->max_n))
         return fail(h, RETH_ERR_INVALID, "group %d needs batch == max_batch, ring_depth a multiple >= 2*group, steps %% group == 0", G);
     cudaStream_t st = serial ? s : h->s_tree;
+    // the chain draw -> repair -> (exchange ->) draw is the critical path only without prefetch groups
+    static const int pdl_env = env_int("RETH_PDL", 1);
+    struct PdlScope { reth_replay *h; ~PdlScope() { h->pdl = false; } } pdl_scope{h};
+    // (measured: strict alternation 18.4 -> 20.4 M transitions/s; Mode G loop at 2 GPUs 34 -> 32 us per step when
+    // the share is small, but 50 -> 54 us when the step is gather-bound: grids resident ahead of their turn take
+    // CTA slots from the gather, so Mode G uses it only for shares of at most 512 rows)
+    h->pdl = pdl_env && G == 1 && !serial && (!global || batch / h->board_shards <= 512);
     if (!serial) {
         CK(h, cudaEventRecord(h->ev_fork, s));
         CK(h, cudaStreamWaitEvent(st, h->ev_fork, 0));

@@ -74,6 +74,16 @@ __device__ __forceinline__ NodeLoc locate(int64_t idx)
 
 __device__ __forceinline__ double2 ldcg2(const double2 *p) { return __ldcg(p); }
 
+// Programmatic dependent launch (a launch with cudaLaunchAttributeProgrammaticStreamSerialization): the next
+// kernel of the stream may be scheduled while this one still runs -- pdl_trigger() -- and blocks in
+// pdl_wait() until the kernel before it has completed and flushed.  Both are no-ops in an ordinary launch.
+// Every kernel waits FIRST and triggers after: at most one grid per stream is resident ahead of its turn
+// (triggering before the wait lets the whole queue of the stream cascade onto the device).
+// Used for the dependent chain draw -> repair -> draw of strict alternation and Mode G, where the launch
+// latency of every kernel is on the critical path.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // counter-based uniform in [0,1) with 53 random bits (splitmix64 finaliser);
 // the reference draws from numba's private generator (sumtree.py:75), so only
 // the distribution, not the stream, is part of the contract.
@@ -140,6 +150,8 @@ __device__ __forceinline__ int64_t lower_bound_target(const SampleArgs &a, doubl
 // fused (sampler/per_sampler.py:26).
 __global__ void __launch_bounds__(256) per_sample_kernel(const SampleArgs a)
 {
+    pdl_wait();
+    pdl_trigger();
     const int lane = threadIdx.x & 31;
     const int64_t W = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (W >= (int64_t)a.batch * a.groups) return;
@@ -427,6 +439,8 @@ __global__ void __launch_bounds__(kUpdateThreads) per_update_kernel(const Update
     constexpr int kWarps = kUpdateThreads / 32;
     const int NT = a.g.n_tile_levels;
 
+    pdl_wait();
+    pdl_trigger();
     RETH_STAMP(0);
     if (brank == 0 && threadIdx.x < kMaxTileLevels) a.counts_next[threadIdx.x] = 0;
     // every load that does not depend on another is issued up front
@@ -719,6 +733,8 @@ __device__ __forceinline__ unsigned long long global_ns()
 // one thread per shard
 __global__ void __launch_bounds__(kMaxShards) roots_exchange_kernel(const RootsArgs a)
 {
+    pdl_wait();
+    pdl_trigger();
     const int s = threadIdx.x;
     if (s >= a.n_shards) return;
     const int par = (int)(a.seq & 1ull);
