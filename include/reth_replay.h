@@ -328,6 +328,18 @@ int reth_ipc_close(reth_ipc_view_t *v);
  * reference has no counterpart (its learner polls whole batches shard by shard, trainer.py:33-36). */
 int reth_replay_gather_to(reth_replay_t *h, int slot, reth_ipc_view_t *dst, int dst_slot, void *stream);
 
+/* ---- Mode G with a prefetch group: n_slots (<= 32) independent GLOBAL stratified draws of global_batch from
+ *      the same tree state in one launch pair (share computation + descent), as sample_multi does for one
+ *      shard.  This shard's shares are PACKED back to back from batch slot first_slot on: the n_slots slots
+ *      then hold ONE batch of sum(count_g) rows (global_batch must equal max_batch), which gather_multi()
+ *      and update_slots() over the same slots handle as such (row count on the device).  slot_quota() reads
+ *      {first_g, count_g, offset_g, 0} per draw: rows offset_g .. offset_g+count_g of the packed batch are
+ *      positions first_g .. of global batch g.  uniforms_dev: device double[n_slots*global_batch] or NULL. */
+int reth_replay_sample_global_multi(reth_replay_t *h, int global_batch, const double *all_roots_dev,
+                                    int n_shards, int shard, int first_slot, int n_slots,
+                                    const double *uniforms_dev, uint64_t seed, double beta, void *stream);
+int reth_replay_slot_quota(reth_replay_t *h, int first_slot, int n_slots, int64_t *out /*[4*n_slots]*/, void *stream);
+
 /* ---- shard roots over NVLink (SURVEY.md 8e "read peers' totals via NVLink-mapped memory"; the
  *      reference has no counterpart: its shards never normalise against each other, trainer.py:33-36).
  *      Mode G needs every shard's root {total, min} on every rank before a global draw.  Instead of a
@@ -373,10 +385,10 @@ int reth_replay_gather_from(reth_replay_t *h, int dst_slot, reth_replay_t *src, 
  *      bit5: all gathers on ONE internal stream (default: consecutive gathers alternate between two
  *      streams so the tail of one overlaps the ramp-up of the next; bit2 timings are only per-kernel
  *      durations with bit5 set);
- *      bit6: Mode G (after reth_replay_board_connect; group 1): every iteration starts with
- *      roots_exchange(3) on the tree stream, draws this shard's share of a GLOBAL stratified batch of
- *      `batch`, gathers and writes back that share (prio_dev: the first share-count values of each
- *      step's `batch`); every shard of the group must run the same number of steps;
+ *      bit6: Mode G (after reth_replay_board_connect): every iteration starts with roots_exchange(3)
+ *      on the tree stream, draws this shard's share of G GLOBAL stratified batches of `batch` (packed,
+ *      see sample_global_multi), gathers and writes back that share (prio_dev: the first share-count
+ *      values of each iteration's G*batch); every shard of the group must run the same number of steps;
  *      bits 8..15: prefetch group G (0/1 = strict alternation): sample_multi / gather_multi /
  *      update_slots over G slots per iteration (steps must be a multiple of G). */
 int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, const float *prio_dev,

@@ -134,6 +134,8 @@ SIGNATURES = {
     "reth_ipc_slot_ptrs": [_vp, _i32, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp)],
     "reth_ipc_close": [_vp],
     "reth_replay_gather_to": [_vp, _i32, _vp, _i32, _vp],
+    "reth_replay_sample_global_multi": [_vp, _i32, _vp, _i32, _i32, _i32, _i32, _vp, _u64, _f64, _vp],
+    "reth_replay_slot_quota": [_vp, _i32, _i32, C.POINTER(_i64), _vp],
     "reth_replay_board_export": [_vp, C.POINTER(BoardExport)],
     "reth_replay_board_connect": [_vp, C.POINTER(BoardExport), _i32, _i32],
     "reth_replay_roots_exchange": [_vp, _i32, _vp],

@@ -33,6 +33,7 @@ struct BatchSlot {
     int32_t batch = 0;
     bool partial = false;      // Mode G draw: only meta[1] of the `batch` entries belong to this shard
     int shards = 1;            // ... of a global batch drawn over this many shards (expected share batch / shards)
+    int packed = 0;            // > 0: first slot of a packed Mode G group of this many draws (rows = meta[1] over all of them)
 };
 
 }  // namespace
@@ -117,6 +118,8 @@ struct reth_replay {
     double *all_roots = nullptr;
     int board_shards = 0, board_shard = 0;
     unsigned long long board_seq = 0;
+    int64_t *quota = nullptr;     // Mode G prefetch group: {first, count, offset, 0} per draw of the running launch
+    int64_t *slot_quota = nullptr; // the same per batch slot (kept for the consumer of the packed batch)
     bool pdl = false;             // tree-chain launches carry the programmatic-dependent-launch attribute (set by step_loop)
     int pipe_reserved = 0;        // batch slots at the end of the ring that a pipe never uses (other sampler topics)
     // set by pipe_issue around its draw: the sampling kernel also writes into mapped pinned host memory
@@ -174,7 +177,7 @@ void free_all(reth_replay *h)
     cudaFree(h->dbg);
     for (int i = 0; i < kMaxShards; ++i)
         if (h->peer_ipc[i] && h->peer_board[i]) cudaIpcCloseMemHandle(h->peer_board[i]);
-    cudaFree(h->board); cudaFree(h->all_roots);
+    cudaFree(h->board); cudaFree(h->all_roots); cudaFree(h->quota); cudaFree(h->slot_quota);
     cudaFree(h->stage_idx); cudaFree(h->stage_prio); cudaFree(h->stage_u);
     if (h->host_pin) cudaFreeHost(h->host_pin);
     for (int c = 0; c < kMaxCols; ++c) cudaFree(h->ring[c]);
@@ -863,14 +866,15 @@ int do_sample(reth_replay *h, int batch, const double *uniforms, int uniforms_lo
         return fail(h, RETH_ERR_INVALID, "batch %d outside [1, max_batch=%d]", batch, h->cfg.max_batch);
     if (groups < 1 || slot + groups > (int)h->slots.size())
         return fail(h, RETH_ERR_INVALID, "slots %d..%d outside the batch ring", slot, slot + groups - 1);
-    if (groups > 1 && (n_shards > 1 || batch != h->cfg.max_batch || (uniforms && uniforms_loc != RETH_DEVICE)))
-        return fail(h, RETH_ERR_INVALID, "multi-slot sampling: single shard, batch == max_batch, device uniforms");
+    if (groups > 1 && (batch != h->cfg.max_batch || (uniforms && uniforms_loc != RETH_DEVICE)))
+        return fail(h, RETH_ERR_INVALID, "multi-slot sampling: batch == max_batch, device uniforms");
+    if (groups > 32 && n_shards > 1) return fail(h, RETH_ERR_INVALID, "Mode G: at most 32 draws per launch");
     BatchSlot &b = h->slots[slot];
     SampleArgs a = {};
     a.g = h->geom; a.desc = h->desc; a.agg = h->agg; a.batch = batch;
     if (uniforms) {
         const void *u = nullptr;
-        int rc = to_device(h, uniforms, uniforms_loc, (size_t)batch * 8, h->stage_u, s, &u);
+        int rc = to_device(h, uniforms, uniforms_loc, (size_t)batch * groups * 8, h->stage_u, s, &u);
         if (rc) return rc;
         a.uniforms = (const double *)u;
     }
@@ -881,6 +885,17 @@ int do_sample(reth_replay *h, int batch, const double *uniforms, int uniforms_lo
     a.idx_out = b.idx; a.w_out = b.w; a.prio_out = b.prio; a.meta = b.meta;
     a.idx_mirror = h->mirror_idx; a.w_mirror = h->mirror_w; a.err_mirror = h->mirror_err; a.err = h->err;
     a.all_roots = all_roots; a.n_shards = n_shards; a.shard = shard;
+    if (n_shards > 1 && groups > 1) {
+        // the shares of the `groups` draws are packed back to back from slot `slot` on
+        if (!h->quota) {
+            CK(h, dalloc_zero(&h->quota, (size_t)4 * 32, &h->st.hbm_bytes));
+            CK(h, dalloc_zero(&h->slot_quota, (size_t)4 * h->slots.size(), &h->st.hbm_bytes));
+        }
+        global_quota_kernel<<<1, 32 * groups, 0, s>>>(a, h->quota, h->slot_quota + 4 * slot);
+        CK(h, cudaGetLastError());
+        h->st.kernel_launches++;
+        a.quota = h->quota;
+    }
     const int wpb = 4;
     if (h->pdl) {
         cudaLaunchConfig_t cfg = {};
@@ -903,6 +918,7 @@ int do_sample(reth_replay *h, int batch, const double *uniforms, int uniforms_lo
         h->slots[slot + g].batch = batch;
         h->slots[slot + g].partial = n_shards > 1;
         h->slots[slot + g].shards = n_shards;
+        h->slots[slot + g].packed = (n_shards > 1 && groups > 1 && g == 0) ? groups : 0;
     }
     return RETH_OK;
 }
@@ -913,7 +929,7 @@ int do_gather(reth_replay *h, int slot, bool use_meta, cudaStream_t s, int group
 {
     BatchSlot &b = h->slots[slot];
     if (!h->cfg.store_rows || h->cfg.n_columns == 0) return RETH_OK;
-    const int64_t *meta = (use_meta && groups == 1) ? b.meta : nullptr;
+    const int64_t *meta = (use_meta && (groups == 1 || b.packed == groups)) ? b.meta : nullptr;
     int rc;
     if (h->gather_bulk) {
         rc = launch_gather_bulk(h, b.cols, b.idx, b.batch * groups, meta, s);
@@ -966,6 +982,30 @@ RETH_EXPORT int reth_replay_sample_global(reth_replay_t *h, int global_batch, co
                      n_shards > 1 ? n_shards : 1, shard, S(stream));
 }
 
+RETH_EXPORT int reth_replay_sample_global_multi(reth_replay_t *h, int global_batch, const double *all_roots_dev,
+                                                int n_shards, int shard, int first_slot, int n_slots,
+                                                const double *uniforms_dev, uint64_t seed, double beta, void *stream)
+{
+    if (!h) return RETH_ERR_INVALID;
+    if (!all_roots_dev || n_shards < 2 || shard < 0 || shard >= n_shards || n_slots < 1)
+        return fail(h, RETH_ERR_INVALID, "bad shard arguments");
+    DeviceGuard guard(h->cfg.device);
+    return do_sample(h, global_batch, uniforms_dev, RETH_DEVICE, seed, beta, first_slot, all_roots_dev,
+                     n_shards, shard, S(stream), n_slots);
+}
+
+RETH_EXPORT int reth_replay_slot_quota(reth_replay_t *h, int first_slot, int n_slots, int64_t *out, void *stream)
+{
+    if (!h || !out) return RETH_ERR_INVALID;
+    if (n_slots < 1 || first_slot < 0 || first_slot + n_slots > (int)h->slots.size())
+        return fail(h, RETH_ERR_INVALID, "slots %d..%d outside the batch ring", first_slot, first_slot + n_slots - 1);
+    if (!h->slot_quota) return fail(h, RETH_ERR_STATE, "no packed Mode G draw has been made");
+    DeviceGuard guard(h->cfg.device);
+    CK(h, cudaMemcpyAsync(out, h->slot_quota + 4 * first_slot, (size_t)n_slots * 32, cudaMemcpyDeviceToHost, S(stream)));
+    CK(h, cudaStreamSynchronize(S(stream)));
+    return RETH_OK;
+}
+
 RETH_EXPORT int reth_replay_gather(reth_replay_t *h, int slot, void *stream)
 {
     if (!h) return RETH_ERR_INVALID;
@@ -1004,6 +1044,8 @@ RETH_EXPORT int reth_replay_update_slots(reth_replay_t *h, int first_slot, int n
     a.alpha = alpha; a.transform = transform;
     // one draw: duplicates adjacent; several draws: the same slot may recur anywhere -> stamps
     a.dedupe = n_slots == 1 ? 2 : 1;
+    if (h->slots[first_slot].packed == n_slots || (n_slots == 1 && h->slots[first_slot].partial))
+        a.n_dev = h->slots[first_slot].meta + 1;          // Mode G: the share count lives on the device
     int rc = set_prio(h, a, prio, prio_dtype, prio_loc, 0, n, S(stream));
     if (rc) return rc;
     rc = launch_update(h, a, S(stream));
@@ -1948,10 +1990,9 @@ RETH_EXPORT int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, co
     const int depth = (int)h->slots.size();
     int G = (flags >> 8) & 0xff;                      // batches per tree launch (prefetch group)
     if (G < 1) G = 1;
-    if (global && (G != 1 || h->board_shards < 1 || no_sample || no_update || uniforms_dev))
-        return fail(h, RETH_ERR_INVALID, "Mode G loop: connected roots board, group 1, device generator, sample and update on");
-    if (G > 1 && (batch != h->cfg.max_batch || depth % G != 0 || depth < 2 * G || steps % G != 0 ||
-                  (int64_t)G * batch > h->max_n))
+    if (global && (G > 32 || h->board_shards < 1 || no_sample || no_update || uniforms_dev))
+        return fail(h, RETH_ERR_INVALID, "Mode G loop: connected roots board, group <= 32, device generator, sample and update on");
+    if (G > 1 && (batch != h->cfg.max_batch || depth % G != 0 || depth < 2 * G || steps % G != 0))
         return fail(h, RETH_ERR_INVALID, "group %d needs batch == max_batch, ring_depth a multiple >= 2*group, steps %% group == 0", G);
     cudaStream_t st = serial ? s : h->s_tree;
     // the chain draw -> repair -> (exchange ->) draw is the critical path only without prefetch groups
@@ -1977,7 +2018,7 @@ RETH_EXPORT int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, co
         if (global) {
             rc = launch_roots_exchange(h, 3, st);
             if (!rc) rc = do_sample(h, batch, nullptr, RETH_DEVICE, seed, beta, slot, h->all_roots,
-                                    h->board_shards, h->board_shard, st, 1);
+                                    h->board_shards, h->board_shard, st, G);
         } else if (!no_sample || h->slots[slot].batch != batch)
             rc = do_sample(h, batch, uniforms_dev ? uniforms_dev + (size_t)k * batch : nullptr, RETH_DEVICE,
                            seed, beta, slot, nullptr, 1, 0, st, G);

@@ -111,6 +111,7 @@ struct SampleArgs {
     int64_t *meta;             // {first, count}
     const double *all_roots;   // global mode: double[2*n_shards]
     int32_t n_shards, shard;
+    const int64_t *quota;      // global mode with groups > 1: int64[4*groups] = {first, count, packed offset, -} per draw
     int32_t groups;            // independent stratified draws of `batch` in one launch (>= 1)
     int32_t out_stride;        // elements between the outputs of consecutive draws
     // loader pipeline: indices / weights are also written straight into pinned host memory mapped into
@@ -129,7 +130,7 @@ __device__ __forceinline__ double draw_u(const SampleArgs &a, int64_t i)
 // smallest i in [0,batch] with ((i + u_i) * segment) >= bound (targets are
 // monotone in i); evaluated with the exact target formula over a 32-wide window.
 __device__ __forceinline__ int64_t lower_bound_target(const SampleArgs &a, double segment,
-                                                      double bound, int lane)
+                                                      double bound, int lane, int64_t draw0 = 0)
 {
     if (!(bound > 0.0)) return 0;
     double q = bound / segment;
@@ -138,7 +139,7 @@ __device__ __forceinline__ int64_t lower_bound_target(const SampleArgs &a, doubl
     const int64_t j = i0 + lane;
     bool ge = true;
     if (j < 0) ge = false;
-    else if (j < a.batch) ge = (((double)j + draw_u(a, j)) * segment >= bound);
+    else if (j < a.batch) ge = (((double)j + draw_u(a, draw0 + j)) * segment >= bound);
     const unsigned b = __ballot_sync(0xffffffffu, ge);
     int64_t res = b ? i0 + (__ffs(b) - 1) : i0 + 32;
     if (res < 0) res = 0;
@@ -174,7 +175,7 @@ __global__ void __launch_bounds__(256) per_sample_kernel(const SampleArgs a)
         pmin = (mn != 0.0) ? mn : 1.0;
         const double seg = total / (double)a.batch;
         const bool last = a.shard == a.n_shards - 1;
-        if (i == 0) {                          // one warp reports the share {first, count}
+        if (i == 0 && !a.quota) {              // one warp reports the share {first, count}
             const int64_t f = lower_bound_target(a, seg, prefix, lane);
             int64_t e = last ? (int64_t)a.batch : lower_bound_target(a, seg, prefix + mine, lane);
             if (e < f) e = f;
@@ -185,7 +186,10 @@ __global__ void __launch_bounds__(256) per_sample_kernel(const SampleArgs a)
         // Warps outside the share (all but 1/n_shards of a global batch) leave after one draw.
         const double tgt = ((double)i + draw_u(a, W)) * seg;
         if ((prefix > 0.0 && !(tgt >= prefix)) || (!last && tgt >= prefix + mine)) return;
-        first = lower_bound_target(a, seg, prefix, lane);
+        // several draws in one launch: the shares are packed back to back, global_quota_kernel has
+        // published where each starts
+        if (a.quota) first = a.quota[4 * grp] - a.quota[4 * grp + 2];
+        else first = lower_bound_target(a, seg, prefix, lane);
     } else {
         const double2 root = ldcg2(&a.agg[1]);
         total = root.x;
@@ -225,12 +229,50 @@ __global__ void __launch_bounds__(256) per_sample_kernel(const SampleArgs a)
         tile = tile_base(T) + tile_rel;
     }
     if (lane == 0) {
-        const int64_t o = grp * a.out_stride + i - first;
+        const int64_t o = (a.quota ? 0 : grp * a.out_stride) + i - first;
         const double wt = pow(val / pmin, -a.beta);  // per_sampler.py:26
         a.idx_out[o] = idx;
         a.prio_out[o] = val;
         a.w_out[o] = wt;
         if (a.idx_mirror) { a.idx_mirror[o] = idx; a.w_mirror[o] = wt; }
+    }
+}
+
+// Mode G with a prefetch group: warp g computes the share {first, count} of draw g of this shard
+// (the range rule of per_sample_kernel); thread 0 then lays the shares out back to back -- the
+// slots of the group become ONE packed batch of sum(count) rows -- and writes
+//   quota[4g..] = {first_g, count_g, offset_g, 0},  meta = {0, sum(count)}.
+__global__ void __launch_bounds__(1024) global_quota_kernel(const SampleArgs a, int64_t *quota_out,
+                                                           int64_t *slot_quota /* per slot {first, count, offset, 0} */)
+{
+    pdl_wait();
+    pdl_trigger();
+    __shared__ int64_t sh_first[32], sh_count[32];
+    const int lane = threadIdx.x & 31, grp = threadIdx.x >> 5;
+    if (grp < a.groups) {
+        double total = 0.0, prefix = 0.0, mine = 0.0;
+        for (int s = 0; s < a.n_shards; ++s) {
+            const double t = a.all_roots[2 * s];
+            if (s == a.shard) { prefix = total; mine = t; }
+            total += t;
+        }
+        const double seg = total / (double)a.batch;
+        const int64_t d0 = (int64_t)grp * a.batch;
+        const int64_t f = lower_bound_target(a, seg, prefix, lane, d0);
+        int64_t e = (a.shard == a.n_shards - 1) ? (int64_t)a.batch : lower_bound_target(a, seg, prefix + mine, lane, d0);
+        if (e < f) e = f;
+        if (lane == 0) { sh_first[grp] = f; sh_count[grp] = e - f; }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int64_t off = 0;
+        for (int g = 0; g < a.groups; ++g) {
+            const int64_t q[4] = {sh_first[g], sh_count[g], off, 0};
+            for (int k = 0; k < 4; ++k) { quota_out[4 * g + k] = q[k]; slot_quota[4 * g + k] = q[k]; }
+            off += sh_count[g];
+        }
+        a.meta[0] = 0;
+        a.meta[1] = off;
     }
 }
 

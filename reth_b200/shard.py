@@ -399,6 +399,27 @@ class ReplayShard:
                                                      float(beta), int(slot), self._s(stream)))
         self._keep = (rkeep, ukeep)
 
+    def sample_global_multi(self, global_batch, all_roots, n_shards, shard, first_slot, n_slots, beta=0.4,
+                            uniforms_dev=None, seed=0, stream=None):
+        """Mode G prefetch group: n_slots global stratified draws in one launch; this shard's shares are packed
+        back to back from slot first_slot on (gather_multi / update_slots over the same slots handle the packed
+        batch; slot_quota gives the per-draw {first, count, offset})."""
+        rp, rloc, rdt, rcnt, rkeep = _ptr_loc(all_roots)
+        assert rloc == DEVICE and rdt == np.dtype(np.float64) and rcnt >= 2 * n_shards
+        up, uloc, udt, cnt, ukeep = _ptr_loc(uniforms_dev)
+        if uniforms_dev is not None:
+            assert uloc == DEVICE and udt == np.dtype(np.float64) and cnt >= global_batch * n_slots
+        self._ck(self._lib.reth_replay_sample_global_multi(self._h, int(global_batch), rp, int(n_shards), int(shard),
+                                                           int(first_slot), int(n_slots), up,
+                                                           int(seed) & (2**64 - 1), float(beta), self._s(stream)))
+        self._keep = (rkeep, ukeep)
+
+    def slot_quota(self, first_slot, n_slots, stream=None):
+        """-> int64[n_slots, 3]: {first, count, packed offset} of each draw of a packed Mode G group."""
+        out = (C.c_int64 * (4 * n_slots))()
+        self._ck(self._lib.reth_replay_slot_quota(self._h, int(first_slot), int(n_slots), out, self._s(stream)))
+        return np.array(out, dtype=np.int64).reshape(n_slots, 4)[:, :3]
+
     def sample_multi(self, batch, first_slot, n_slots, beta=0.4, uniforms_dev=None, seed=0, stream=None):
         """n_slots independent stratified draws in one launch (prefetch group)."""
         up, uloc, udt, cnt, ukeep = _ptr_loc(uniforms_dev)

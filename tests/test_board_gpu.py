@@ -126,7 +126,69 @@ def test_board_errors_and_timeout(Shard, monkeypatch):
     b.close()
 
 
-def _loop_body():
+def test_mode_g_prefetch_group_packed(Shard):
+    """sample_global_multi: G global stratified draws in one launch, this shard's shares packed back to back;
+    gather_multi / update_slots treat the slots as one batch of sum(count) rows.  Against n reference trees +
+    the range rule per draw, rows byte for byte, trees bit for bit after the write-back."""
+    import torch
+    cap, GB, n_shards, G = 3000, 128, 3, 4
+    struct = [(np.uint8, (48,)), (np.int64, ())]
+    rng = np.random.default_rng(11)
+    shards, trees, datas = [], [], []
+    for g in range(n_shards):
+        sh = Shard(cap, struct, max_batch=GB, ring_depth=2 * G)
+        cols = [rng.integers(0, 256, (cap, 48), dtype=np.uint8), np.arange(cap) + 100000 * g]
+        p = rng.random(cap) * (1 + 3 * g) + 0.01
+        sh.append(cols, None)
+        sh.update(np.arange(cap), p, transform=False)
+        t = po.OracleSumTree(cap)
+        t.update(np.arange(cap), p)
+        shards.append(sh); trees.append(t); datas.append(cols)
+    for step in range(3):
+        torch.cuda.synchronize()
+        roots = torch.cat([torch.as_tensor(sh.root_dev(), device="cuda").clone() for sh in shards])
+        u = rng.random(G * GB)
+        u_dev = torch.from_numpy(u).cuda()
+        first_slot = (step % 2) * G
+        newp = rng.random(G * GB) * 2 + 0.01
+        draws = [[po.global_sample(trees, g, GB, u[d * GB:(d + 1) * GB], 0.5) for d in range(G)] for g in range(n_shards)]
+        for d in range(G):                                   # the shares of every draw partition its global batch
+            assert sum(len(draws[g][d][1]) for g in range(n_shards)) == GB
+        for g, sh in enumerate(shards):
+            sh.sample_global_multi(GB, roots, n_shards, g, first_slot, G, beta=0.5, uniforms_dev=u_dev)
+            q = sh.slot_quota(first_slot, G)
+            oidx = np.concatenate([draws[g][d][1] for d in range(G)])
+            ow = np.concatenate([draws[g][d][2] for d in range(G)])
+            off = 0
+            for d in range(G):
+                n = len(draws[g][d][1])
+                assert q[d, 1] == n and q[d, 2] == off
+                if n:
+                    assert q[d, 0] == draws[g][d][0]
+                off += n
+            assert tuple(sh.slot_meta(first_slot)) == (0, off)
+            idx, w = sh.group_read(first_slot, G, with_weights=True)
+            assert np.array_equal(idx[:off], oidx)
+            assert np.allclose(w[:off], ow, rtol=RTOL, atol=0)
+            sh.gather_multi(first_slot, G)
+            torch.cuda.synchronize()
+            got = [torch.cat([sh.slot_tensors(first_slot + d)[0][c] for d in range(G)]).cpu().numpy() for c in range(2)]
+            for c in range(2):
+                assert np.array_equal(got[c][:off], datas[g][c][oidx]), (step, g, c)
+            mine = np.zeros(G * GB)
+            mine[:off] = newp[:off]
+            sh.update_slots(first_slot, G, mine, transform=False)
+        for g in range(n_shards):                            # oracle write-back after every shard has drawn
+            oidx = np.concatenate([draws[g][d][1] for d in range(G)])
+            trees[g].update(oidx, newp[:len(oidx)])
+        for g, sh in enumerate(shards):
+            for x, y in zip(sh.tree_arrays(), (trees[g]._sum, trees[g]._min, trees[g]._val)):
+                assert np.array_equal(x, y), (step, g)
+    for sh in shards:
+        sh.close()
+
+
+def _loop_body(G=1):
     import torch
     from reth_b200 import ReplayShard as Shard
     cap, GB, n_shards, steps, seed = 4096, 256, 2, 8, 1234
@@ -159,22 +221,27 @@ def _loop_body():
         t.update(np.arange(cap), v_)
         trees.append(t)
     views = [torch.as_tensor(sh.all_roots_dev(n_shards), device="cuda") for sh in step]
-    for k in range(steps):
+    for k in range(0, steps, G):
         _exchange_all(step)
-        u = device_uniforms(seed, k * GB, GB)
-        covered = 0
+        us = [device_uniforms(seed, (k + d) * GB, GB) for d in range(G)]
+        draws = [np.concatenate([po.global_sample(trees, g, GB, us[d], 0.4)[1] for d in range(G)]) for g in range(n_shards)]
+        assert sum(len(x) for x in draws) == G * GB
         for g, sh in enumerate(step):
-            sh.sample_global(GB, views[g], n_shards, g, beta=0.4, seed=seed, slot=k % 4)
-            first, count = sh.slot_meta(k % 4)
-            _, idx, w = sh.slot_read(k % 4)
-            ofirst, oidx, ow, _ = po.global_sample(trees, g, GB, u, 0.4)
-            assert (first, count) == (covered, len(oidx)), (k, g)
-            assert np.array_equal(idx[:count], oidx)
-            covered += count
-            sh.gather(k % 4)
-            sh.update_slot(k % 4, prio[g][k * GB:(k + 1) * GB], alpha=0.6)
-        assert covered == GB
-        draws = [po.global_sample(trees, g, GB, u, 0.4)[1] for g in range(n_shards)]
+            if G == 1:
+                sh.sample_global(GB, views[g], n_shards, g, beta=0.4, seed=seed, slot=k % 4)
+                first, count = sh.slot_meta(k % 4)
+                _, idx, w = sh.slot_read(k % 4)
+                assert first == (0 if g == 0 else len(draws[0])), (k, g)
+                sh.gather(k % 4)
+                sh.update_slot(k % 4, prio[g][k * GB:(k + 1) * GB], alpha=0.6)
+            else:
+                sh.sample_global_multi(GB, views[g], n_shards, g, k % 4, G, beta=0.4, seed=seed)
+                first, count = sh.slot_meta(k % 4)
+                idx, w = sh.group_read(k % 4, G, with_weights=True)
+                sh.gather_multi(k % 4, G)
+                sh.update_slots(k % 4, G, prio[g][k * GB:(k + G) * GB], alpha=0.6)
+            assert count == len(draws[g]), (k, g)
+            assert np.array_equal(idx[:count], draws[g])
         for g, sh in enumerate(step):                      # oracle leaves follow the engine's float32 pow
             _, _, v_ = sh.tree_arrays()
             trees[g].update(draws[g], v_[draws[g]])
@@ -186,7 +253,7 @@ def _loop_body():
 
     def run(g):
         try:
-            loop[g].step_loop(steps, GB, prio[g], seed=seed, alpha=0.6, beta=0.4, global_mode=True,
+            loop[g].step_loop(steps, GB, prio[g], seed=seed, alpha=0.6, beta=0.4, global_mode=True, group=G,
                               stream=streams[g])
         except Exception as e:                              # pragma: no cover
             errs.append(e)
@@ -199,11 +266,15 @@ def _loop_body():
     for g in range(n_shards):
         for x, y in zip(loop[g].tree_arrays(), step[g].tree_arrays()):
             assert np.array_equal(x, y), g
-        last = (steps - 1) % 4
+        last = (steps - G) % 4
         first, count = loop[g].slot_meta(last)
         assert (first, count) == tuple(step[g].slot_meta(last))
-        da, ia, wa, _ = loop[g].slot_tensors(last)
-        db, ib, wb, _ = step[g].slot_tensors(last)
+
+        def packed(sh):
+            parts = [sh.slot_tensors(last + d) for d in range(G)]
+            cols = [torch.cat([p[0][c] for p in parts]) for c in range(len(struct))]
+            return cols, torch.cat([p[1] for p in parts]), torch.cat([p[2] for p in parts])
+        (da, ia, wa), (db, ib, wb) = packed(loop[g]), packed(step[g])
         assert torch.equal(ia[:count], ib[:count]) and torch.equal(wa[:count], wb[:count])
         for x, y in zip(da, db):
             assert torch.equal(x[:count], y[:count])
@@ -214,7 +285,8 @@ def _loop_body():
 def _loop_worker(q):
     import traceback
     try:
-        _loop_body()
+        _loop_body(1)
+        _loop_body(2)                                       # prefetch group: two global draws per exchange, packed shares
         q.put("ok")
     except BaseException:                                   # report, never hang the parent
         q.put(traceback.format_exc())
