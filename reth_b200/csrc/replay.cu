@@ -1945,6 +1945,11 @@ RETH_EXPORT int reth_replay_board_connect(reth_replay_t *h, const reth_board_exp
             cudaError_t e = cudaIpcOpenMemHandle(&p, mh, cudaIpcMemLazyEnablePeerAccess);
             if (e != cudaSuccess) {
                 cudaGetLastError();
+                for (int k = 0; k < i; ++k) {               // undo the mappings made so far
+                    if (h->peer_ipc[k]) cudaIpcCloseMemHandle(h->peer_board[k]);
+                    h->peer_ipc[k] = false;
+                    h->peer_board[k] = nullptr;
+                }
                 return fail(h, RETH_ERR_CUDA, "cudaIpcOpenMemHandle (board of shard %d): %s", i, cudaGetErrorString(e));
             }
             h->peer_board[i] = (BoardEntry *)p;

@@ -63,6 +63,21 @@ def global_quota(all_roots, shard, batch, uniforms):
     return first, end - first, targets[first:end] - prefix[shard], pmin
 
 
+def global_quota_multi(all_roots, shard, batch, uniforms, groups):
+    """Host statement of the packed Mode-G prefetch group (reth_replay_sample_global_multi): `groups`
+    independent global draws of `batch` from the same roots, uniforms u[groups*batch].
+    -> (quota int64[groups, 3] = {first, count, packed offset}, local_targets float64[sum(count)], p_min)."""
+    u = np.asarray(uniforms, dtype=np.float64).reshape(groups, batch)
+    quota = np.zeros((groups, 3), np.int64)
+    targets, off, pmin = [], 0, 1.0
+    for g in range(groups):
+        first, count, t, pmin = global_quota(all_roots, shard, batch, u[g])
+        quota[g] = (first, count, off)
+        targets.append(t)
+        off += count
+    return quota, (np.concatenate(targets) if targets else np.empty(0)), pmin
+
+
 class ShardGroup:
     """This rank's shard inside a torch.distributed process group."""
 
@@ -116,9 +131,16 @@ class ShardGroup:
         the learner's reads after a collective on the same stream (e.g. exchange_roots())."""
         self.shard.gather_to(slot, self.learner_ring, dst_slot, stream=stream)
 
-    def sample_global(self, global_batch, beta=0.4, uniforms=None, seed=0, slot=0, stream=None):
+    def sample_global(self, global_batch, beta=0.4, uniforms=None, seed=0, slot=0, stream=None, groups=1):
         """Draw this rank's part of one global stratified batch into batch slot `slot`;
-        -> (first, count) of the global batch positions it serves."""
+        -> (first, count) of the global batch positions it serves.
+        groups > 1 (prefetch group; uniforms on the device or None): `groups` global batches from the same tree
+        state, this rank's shares packed back to back from `slot` on -> int64[groups, 3] = {first, count, offset}
+        per batch; gather_multi / update_slots over the same slots handle the packed batch."""
+        if groups > 1:
+            self.shard.sample_global_multi(global_batch, self.all_roots, self.world, self.rank, slot, groups,
+                                           beta=beta, uniforms_dev=uniforms, seed=seed, stream=stream)
+            return self.shard.slot_quota(slot, groups, stream=stream)
         self.shard.sample_global(global_batch, self.all_roots, self.world, self.rank, beta=beta,
                                  uniforms=uniforms, seed=seed, slot=slot, stream=stream)
         return self.shard.slot_meta(slot, stream=stream)

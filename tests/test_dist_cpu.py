@@ -107,3 +107,36 @@ def test_quota_edges():
     # all shards empty: total 0 -> every target is 0 and lands on the last shard's range rule
     z = np.zeros(4)
     assert sharded.combine_roots(z)[2] == 1.0
+
+
+def test_packed_quota_multi_matches_oracle():
+    """Host statement of the Mode-G prefetch group (sharded.global_quota_multi): G global draws from the same
+    roots, every shard's shares packed back to back -- against the n-tree oracle draw by draw."""
+    sys.path.insert(0, ROOT)
+    from oracle import per_oracle as po
+    from reth_b200 import sharded
+    cap, B, G, n = 2000, 48, 5, 3
+    rng = np.random.default_rng(9)
+    trees = []
+    for s in range(n):
+        t = po.OracleSumTree(cap)
+        m = cap if s != 1 else 300
+        t.update(np.arange(m), rng.random(m) * (1 + 4 * s) + 0.01)
+        trees.append(t)
+    roots = np.array([x for t in trees for x in (t.sum(), t._min[0])])
+    u = rng.random(G * B)
+    covered = np.zeros(G, np.int64)
+    for s in range(n):
+        quota, local, pmin = sharded.global_quota_multi(roots, s, B, u, G)
+        idx = np.array([trees[s].find_index(t) for t in local], np.int64)
+        off = 0
+        for g in range(G):
+            ofirst, oidx, ow, _ = po.global_sample(trees, s, B, u[g * B:(g + 1) * B], 0.4)
+            first, count, o = quota[g]
+            assert count == len(oidx) and o == off and first == covered[g]
+            assert np.array_equal(idx[off:off + count], oidx)
+            assert np.allclose(po.is_weights(trees[s]._val[oidx], pmin, 0.4), ow, rtol=1e-12)
+            off += count
+            covered[g] += count
+        assert off == len(local)
+    assert np.all(covered == B)
