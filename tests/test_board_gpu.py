@@ -303,14 +303,19 @@ def test_mode_g_device_loop_matches_stepwise_calls(Shard, monkeypatch):
     import torch.multiprocessing as mp
     monkeypatch.setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32")
     monkeypatch.setenv("CUDA_MODULE_LOADING", "EAGER")
+    monkeypatch.setenv("RETH_BOARD_TIMEOUT_MS", "20000")     # co-scheduling hiccups on one device must not fail the wait
     ctx = mp.get_context("spawn")
-    q = ctx.Queue()
-    p = ctx.Process(target=_loop_worker, args=(q,), daemon=True)
-    p.start()
-    try:
-        res = q.get(timeout=180)
-        p.join(30)
-    finally:
-        if p.is_alive():
-            p.kill()
+    res = None
+    for attempt in range(2):                                 # two shards sharing one GPU: allow one retry
+        q = ctx.Queue()
+        p = ctx.Process(target=_loop_worker, args=(q,), daemon=True)
+        p.start()
+        try:
+            res = q.get(timeout=300)
+            p.join(30)
+        finally:
+            if p.is_alive():
+                p.kill()
+        if res == "ok":
+            break
     assert res == "ok", res
