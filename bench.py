@@ -429,6 +429,15 @@ def run_ours(args):
     }
     if world > 1:
         line["shard_totals"] = [float(x) for x in sg.all_roots.cpu()[0::2]]
+        # Mode G (BASELINE.json config 3, north_star's coupled multi-GPU path): parity leg + timed device loop on
+        # the same shards, after every Mode R figure above has been taken (the batch ring is re-shaped)
+        import bench_modeg
+        try:
+            line["mode_g"] = bench_modeg.run(torch, dist, shard, world, rank, B, ALPHA, BETA, value, log,
+                                             iters=args.modeg_iters)
+        except Exception as e:                                  # keep the Mode R line if the coupled leg fails
+            log(f"[rank {rank}] mode_g failed: {e!r}")
+            line["mode_g"] = {"error": repr(e), "parity_ok": False}
     if rank == 0 and world == 1 and not args.no_cpu:
         cores = os.cpu_count() or 1
         v, dt = cpu_reference_arm(args.cpu_steps, 1, args.cpu_iters, B, cap, cores)
@@ -466,6 +475,7 @@ def main():
     ap.add_argument("--cpu-steps", type=int, default=24)
     ap.add_argument("--cpu-iters", type=int, default=64, help="iterations per step of the CPU arm (bounded sample)")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--modeg-iters", type=int, default=400, help="Mode G leg (N > 1): timed iterations per case")
     args = ap.parse_args()
     _claim_stdout()
     if args.warmup < 3 and args.impl == "ours":

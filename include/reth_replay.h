@@ -102,6 +102,12 @@ int reth_replay_abi_version(void);
  * + FIFO cursor reset (NumpyBuffer.clear, reth/reth/buffer/buffer.py:95-97) */
 int reth_replay_clear(reth_replay_t *h, void *stream);
 
+/* Re-shape the learner-batch ring: ring_depth slots of max_batch rows (TorchCudaLoader(buffer_size=...),
+ * client/torch_cuda_loader.py:70,114-135 allocates its ring per loader; here the ring belongs to the shard,
+ * so a shard that served batch-512 loaders can go on to serve Mode G global batches of n_shards x 512 beside
+ * the same row store).  Synchronises the device; every slot is empty afterwards; not while a pipe is open. */
+int reth_replay_batch_ring_resize(reth_replay_t *h, int max_batch, int ring_depth);
+
 /* ---- append: replaces Client.append -> append_loop -> FIFOPolicy.get_indices ->
  *      LMDB put -> PERSampler.update (client/client.py:21-35, server/main_loop.py:44-58,
  *      cache_policy/fifo_policy.py:11-18, sampler/per_sampler.py:34-35) and the in-process

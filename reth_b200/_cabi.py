@@ -86,6 +86,7 @@ SIGNATURES = {
     "reth_replay_destroy": [_vp],
     "reth_replay_abi_version": [],
     "reth_replay_clear": [_vp, _vp],
+    "reth_replay_batch_ring_resize": [_vp, _i32, _i32],
     "reth_replay_append": [_vp, _vp, _i32, _vp, _i32, _i32, _i64, _f64, _i32, C.POINTER(_i64), _vp],
     "reth_replay_append_at": [_vp, _vp, _i32, _vp, _i32, _vp, _i32, _i32, _i64, _f64, _i32, _vp],
     "reth_replay_update": [_vp, _vp, _i32, _i32, _vp, _i32, _i32, _i64, _f64, _i32, _vp],

@@ -71,7 +71,10 @@ struct reth_replay {
     cudaStream_t s_append = nullptr;          // large device-source appends: the row copy runs beside the tree update
     cudaEvent_t ev_app_fork = nullptr, ev_app_done = nullptr;
     cudaEvent_t last_gather_ev = nullptr;     // newest gather of the internal streams (appends wait for it: rows stay atomic)
-    int update_cluster = 8;
+    int update_cluster = 8;               // largest cluster the device hosts (16, else 8), or the caller's choice
+    int update_cluster_fixed = 0;         // the caller (config / RETH_UPDATE_CLUSTER) chose the cluster size
+    int update_threads = kUpdateThreads;  // threads per CTA of the repair kernel
+    int update_lean = -1;                 // repair-kernel build: 0 full registers, 1 lean (<= 64), -1 by launch size
     int64_t out_rb[kMaxCols] = {};      // bytes of one row of each BATCH column (4x row_bytes when the gather widens)
     int col_frames[kMaxCols] = {};      // K > 0: the column stores K int32 frame references per row
     int n_frame_cols = 0;
@@ -169,6 +172,9 @@ struct DeviceGuard {
 
 size_t dtype_size(int dt) { return (dt == RETH_F32 || dt == RETH_I32) ? 4 : 8; }
 
+void free_batch_ring(reth_replay *h);
+int alloc_batch_ring(reth_replay *h);
+
 void free_all(reth_replay *h)
 {
     cudaFree(h->desc); cudaFree(h->agg); cudaFree(h->stamp); cudaFree(h->mask);
@@ -177,15 +183,12 @@ void free_all(reth_replay *h)
     cudaFree(h->dbg);
     for (int i = 0; i < kMaxShards; ++i)
         if (h->peer_ipc[i] && h->peer_board[i]) cudaIpcCloseMemHandle(h->peer_board[i]);
-    cudaFree(h->board); cudaFree(h->all_roots); cudaFree(h->quota); cudaFree(h->slot_quota);
-    cudaFree(h->stage_idx); cudaFree(h->stage_prio); cudaFree(h->stage_u);
+    cudaFree(h->board); cudaFree(h->all_roots); cudaFree(h->quota);
+    cudaFree(h->stage_idx); cudaFree(h->stage_prio);
     if (h->host_pin) cudaFreeHost(h->host_pin);
     for (int c = 0; c < kMaxCols; ++c) cudaFree(h->ring[c]);
     cudaFree(h->frames);
-    for (int c = 0; c < kMaxCols; ++c) cudaFree(h->slot_cols[c]);
-    cudaFree(h->slot_idx); cudaFree(h->slot_w); cudaFree(h->slot_prio); cudaFree(h->slot_meta);
-    for (auto e : h->ev_sampled) cudaEventDestroy(e);
-    for (auto e : h->ev_gathered) cudaEventDestroy(e);
+    free_batch_ring(h);
     for (auto e : h->ev_time) cudaEventDestroy(e);
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
     if (h->ev_app_fork) cudaEventDestroy(h->ev_app_fork);
@@ -198,9 +201,92 @@ void free_all(reth_replay *h)
     if (h->s_gather2) cudaStreamDestroy(h->s_gather2);
 }
 
+
+// The learner-batch ring: ring_depth slots of max_batch rows, carved from one contiguous array per column
+// (so G consecutive slots form one G*max_batch batch), their per-slot events, and the uniform staging buffer.
+void free_batch_ring(reth_replay *h)
+{
+    for (int c = 0; c < kMaxCols; ++c) {
+        if (h->slot_cols[c]) h->st.hbm_bytes -= (int64_t)h->slots.size() * h->cfg.max_batch * h->out_rb[c];
+        cudaFree(h->slot_cols[c]);
+        h->slot_cols[c] = nullptr;
+    }
+    if (h->slot_idx) h->st.hbm_bytes -= (int64_t)h->slots.size() * ((int64_t)h->cfg.max_batch * 24 + 16);
+    cudaFree(h->slot_idx); cudaFree(h->slot_w); cudaFree(h->slot_prio); cudaFree(h->slot_meta);
+    cudaFree(h->slot_quota); cudaFree(h->stage_u);
+    h->slot_idx = nullptr; h->slot_w = nullptr; h->slot_prio = nullptr; h->slot_meta = nullptr;
+    h->slot_quota = nullptr; h->stage_u = nullptr;
+    for (auto e : h->ev_sampled) cudaEventDestroy(e);
+    for (auto e : h->ev_gathered) cudaEventDestroy(e);
+    h->ev_sampled.clear();
+    h->ev_gathered.clear();
+    h->slots.clear();
+    h->last_gather_ev = nullptr;
+}
+
+int alloc_batch_ring(reth_replay *h)
+{
+    int64_t *acct = &h->st.hbm_bytes;
+    const size_t depth = (size_t)h->cfg.ring_depth, mb = (size_t)h->cfg.max_batch;
+    h->slots.assign(depth, BatchSlot());
+    if (h->cfg.store_rows)
+        for (int c = 0; c < h->cfg.n_columns; ++c) {
+            CK(h, cudaMalloc((void **)&h->slot_cols[c], depth * mb * h->out_rb[c]));
+            *acct += (int64_t)(depth * mb * h->out_rb[c]);
+        }
+    CK(h, dalloc_zero(&h->slot_idx, depth * mb, acct));
+    CK(h, dalloc_zero(&h->slot_w, depth * mb, acct));
+    CK(h, dalloc_zero(&h->slot_prio, depth * mb, acct));
+    CK(h, dalloc_zero(&h->slot_meta, depth * 2, acct));
+    CK(h, cudaMalloc((void **)&h->stage_u, mb * 8));
+    for (size_t i = 0; i < depth; ++i) {
+        BatchSlot &s = h->slots[i];
+        for (int c = 0; c < h->cfg.n_columns; ++c)
+            s.cols[c] = h->slot_cols[c] ? h->slot_cols[c] + i * mb * h->out_rb[c] : nullptr;
+        s.idx = h->slot_idx + i * mb;
+        s.w = h->slot_w + i * mb;
+        s.prio = h->slot_prio + i * mb;
+        s.meta = h->slot_meta + i * 2;
+    }
+    h->ev_sampled.resize(depth);
+    h->ev_gathered.resize(depth);
+    for (size_t i = 0; i < depth; ++i) {
+        CK(h, cudaEventCreateWithFlags(&h->ev_sampled[i], cudaEventDisableTiming));
+        CK(h, cudaEventCreateWithFlags(&h->ev_gathered[i], cudaEventDisableTiming));
+    }
+    return RETH_OK;
+}
 }  // namespace
 
-RETH_EXPORT int reth_replay_abi_version(void) { return 2; }
+namespace {
+using UpdateKernel = void (*)(const UpdateArgs);
+// the instantiation of the repair kernel for this shard: 5 tile levels cover capacity <= 2^25
+UpdateKernel update_kernel_of(const reth_replay *h, bool lean)
+{
+    const bool small = h->geom.n_tile_levels <= 5;
+    if (lean) return small ? per_update_kernel<5, 2> : per_update_kernel<kMaxTileLevels, 2>;
+    return small ? per_update_kernel<5, 1> : per_update_kernel<kMaxTileLevels, 1>;
+}
+
+// Shape of one repair launch.  The kernel is latency-bound (3 cluster barriers, 5 dependent stages) and a
+// frame gather normally runs beside it, so what it costs the loop is the SM resources it HOLDS while it
+// waits (measured, profiles/r02_footprint_sweep.jsonl: prefetch-group loop 51.2 -> 52.8 M transitions/s).
+//   n <= 1024 (strict alternation, small batches: the repair is on the critical path): 16 CTAs, full
+//     register budget -- fastest single launch;
+//   n <= 4096 (one prefetch group): 8 CTAs x 512 threads of the lean build (<= 64 registers: half an SM's
+//     register file per CTA, so three gather CTAs stay resident on each of only 8 SMs);
+//   larger (appends): lean, 16 CTAs, 8192 entries per launch.
+struct UpdateShape { UpdateKernel fn; int cluster; };
+UpdateShape update_shape_of(const reth_replay *h, int64_t n)
+{
+    int cluster = h->update_cluster;
+    if (!h->update_cluster_fixed && n > 1024 && n <= (int64_t)8 * h->update_threads && cluster > 8) cluster = 8;
+    const bool lean = h->update_lean >= 0 ? h->update_lean != 0 : n > 1024;
+    return {update_kernel_of(h, lean), cluster};
+}
+}  // namespace
+
+RETH_EXPORT int reth_replay_abi_version(void) { return 3; }
 
 // lz4 frame codec (host code, lz4f.h)
 RETH_EXPORT int64_t reth_lz4f_content_size(const void *src, int64_t n)
@@ -262,7 +348,6 @@ RETH_EXPORT int reth_replay_create(const reth_replay_config *cfg, reth_replay_t 
             h->out_rb[c] = cfg->row_bytes[c] * (cast ? 4 : 1);
         }
     }
-    h->update_cluster = cfg->update_cluster > 0 ? cfg->update_cluster : 8;
     DeviceGuard guard(cfg->device);
     auto bail = [&](int code) { free_all(h); g_create_error = h->error; delete h; return code; };
 #define CKC(expr)                                                                          \
@@ -306,7 +391,6 @@ RETH_EXPORT int reth_replay_create(const reth_replay_config *cfg, reth_replay_t 
     CKC(dalloc_zero(&h->err, 4, acct));
     CKC(cudaMalloc(&h->stage_idx, h->max_n * 8));
     CKC(cudaMalloc(&h->stage_prio, h->max_n * 8));
-    CKC(cudaMalloc((void **)&h->stage_u, (size_t)cfg->max_batch * 8));
     CKC(cudaMallocHost((void **)&h->host_pin, 64 * sizeof(int64_t)));
     if (getenv("RETH_DEBUG_TIMING")) CKC(dalloc_zero(&h->dbg, 32, acct));
     if (cfg->store_rows)
@@ -318,25 +402,9 @@ RETH_EXPORT int reth_replay_create(const reth_replay_config *cfg, reth_replay_t 
         CKC(cudaMalloc((void **)&h->frames, (size_t)cfg->frame_capacity * cfg->frame_bytes));
         *acct += (int64_t)cfg->frame_capacity * cfg->frame_bytes;
     }
-    h->slots.resize(h->cfg.ring_depth);
-    const size_t depth = (size_t)h->cfg.ring_depth, mb = (size_t)cfg->max_batch;
-    if (cfg->store_rows)
-        for (int c = 0; c < cfg->n_columns; ++c) {
-            CKC(cudaMalloc((void **)&h->slot_cols[c], depth * mb * h->out_rb[c]));
-            *acct += (int64_t)(depth * mb * h->out_rb[c]);
-        }
-    CKC(dalloc_zero(&h->slot_idx, depth * mb, acct));
-    CKC(dalloc_zero(&h->slot_w, depth * mb, acct));
-    CKC(dalloc_zero(&h->slot_prio, depth * mb, acct));
-    CKC(dalloc_zero(&h->slot_meta, depth * 2, acct));
-    for (size_t i = 0; i < depth; ++i) {
-        BatchSlot &s = h->slots[i];
-        for (int c = 0; c < cfg->n_columns; ++c)
-            s.cols[c] = h->slot_cols[c] ? h->slot_cols[c] + i * mb * h->out_rb[c] : nullptr;
-        s.idx = h->slot_idx + i * mb;
-        s.w = h->slot_w + i * mb;
-        s.prio = h->slot_prio + i * mb;
-        s.meta = h->slot_meta + i * 2;
+    {
+        const int rc_ring = alloc_batch_ring(h);
+        if (rc_ring) return bail(rc_ring);
     }
     int lo = 0, hi = 0;
     CKC(cudaDeviceGetStreamPriorityRange(&lo, &hi));
@@ -344,38 +412,41 @@ RETH_EXPORT int reth_replay_create(const reth_replay_config *cfg, reth_replay_t 
     CKC(cudaStreamCreateWithPriority(&h->s_gather, cudaStreamNonBlocking, lo));
     CKC(cudaStreamCreateWithPriority(&h->s_gather2, cudaStreamNonBlocking, lo));
     if (const char *e = getenv("RETH_GATHER_STREAMS")) h->two_gather_streams = atoi(e) >= 2;
-    h->ev_sampled.resize(h->cfg.ring_depth);
-    h->ev_gathered.resize(h->cfg.ring_depth);
-    for (int i = 0; i < h->cfg.ring_depth; ++i) {
-        CKC(cudaEventCreateWithFlags(&h->ev_sampled[i], cudaEventDisableTiming));
-        CKC(cudaEventCreateWithFlags(&h->ev_gathered[i], cudaEventDisableTiming));
-    }
     CKC(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
     CKC(cudaEventCreateWithFlags(&h->ev_app_fork, cudaEventDisableTiming));
     CKC(cudaEventCreateWithFlags(&h->ev_app_done, cudaEventDisableTiming));
     CKC(cudaStreamCreateWithFlags(&h->s_append, cudaStreamNonBlocking));
     CKC(cudaEventCreateWithFlags(&h->ev_join_t, cudaEventDisableTiming));
     CKC(cudaEventCreateWithFlags(&h->ev_join_g, cudaEventDisableTiming));
-    if (h->update_cluster > 16) h->update_cluster = 16;
-    if (cfg->update_cluster <= 0) {
-        // default: a 16-CTA cluster (non-portable size, measured fastest) when the device can host one
-        CKC(cudaFuncSetAttribute(per_update_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    if (const char *e = getenv("RETH_UPDATE_LEAN")) h->update_lean = atoi(e);
+    if (const char *e = getenv("RETH_UPDATE_THREADS")) {
+        const int t = atoi(e);
+        if (t == 128 || t == 256 || t == 512) h->update_threads = t;
+    }
+    int want_cluster = cfg->update_cluster;
+    if (const char *e = getenv("RETH_UPDATE_CLUSTER")) want_cluster = atoi(e);
+    if (want_cluster > 16) want_cluster = 16;
+    for (int lean = 0; lean < 2; ++lean)
+        CKC(cudaFuncSetAttribute(update_kernel_of(h, lean != 0), cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    if (want_cluster <= 0) {
+        // default: up to a 16-CTA cluster (non-portable size) when the device can host one
         cudaLaunchConfig_t lc = {};
         lc.gridDim = dim3(16);
-        lc.blockDim = dim3(kUpdateThreads);
+        lc.blockDim = dim3(h->update_threads);
         cudaLaunchAttribute at[1];
         at[0].id = cudaLaunchAttributeClusterDimension;
         at[0].val.clusterDim.x = 16; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
         lc.attrs = at;
         lc.numAttrs = 1;
         int nclusters = 0;
-        if (cudaOccupancyMaxActiveClusters(&nclusters, per_update_kernel, &lc) == cudaSuccess && nclusters > 0)
+        if (cudaOccupancyMaxActiveClusters(&nclusters, update_kernel_of(h, false), &lc) == cudaSuccess && nclusters > 0)
             h->update_cluster = 16;
         else
             h->update_cluster = 8;
         cudaGetLastError();
-    } else if (h->update_cluster > 8) {
-        CKC(cudaFuncSetAttribute(per_update_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    } else {
+        h->update_cluster = want_cluster;
+        h->update_cluster_fixed = 1;
     }
     CKC(cudaDeviceSynchronize());
 #undef CKC
@@ -418,8 +489,10 @@ int launch_update(reth_replay *h, UpdateArgs &a, cudaStream_t s)
     if (a.n <= 0) return RETH_OK;
     a.g = h->geom; a.desc = h->desc; a.agg = h->agg; a.stamp = h->stamp; a.mask = h->mask;
     a.err = h->err; a.dbg = h->dbg;
-    const int64_t per = (int64_t)h->update_cluster * kUpdateThreads;
     const int64_t n = a.n;
+    const UpdateShape shape = update_shape_of(h, n);
+    const UpdateKernel uk = shape.fn;
+    const int64_t per = (int64_t)shape.cluster * h->update_threads;
     const uint8_t *idx0 = (const uint8_t *)a.idx, *prio0 = (const uint8_t *)a.prio;
     const int64_t iota0 = a.iota_base;
     const size_t is = a.idx_kind == 0 ? 8 : 4, ps = a.prio_kind == 0 ? 4 : 8;
@@ -434,19 +507,19 @@ int launch_update(reth_replay *h, UpdateArgs &a, cudaStream_t s)
         a.counts_next = h->counts + (h->counts_flip ^ 1) * kMaxTileLevels;
         h->counts_flip ^= 1;
         cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3(h->update_cluster);
-        cfg.blockDim = dim3(kUpdateThreads);
+        cfg.gridDim = dim3(shape.cluster);
+        cfg.blockDim = dim3(h->update_threads);
         cfg.stream = s;
         cudaLaunchAttribute at[2];
         at[0].id = cudaLaunchAttributeClusterDimension;
-        at[0].val.clusterDim.x = h->update_cluster;
+        at[0].val.clusterDim.x = shape.cluster;
         at[0].val.clusterDim.y = 1;
         at[0].val.clusterDim.z = 1;
         at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
         at[1].val.programmaticStreamSerializationAllowed = 1;
         cfg.attrs = at;
         cfg.numAttrs = h->pdl ? 2 : 1;
-        CK(h, cudaLaunchKernelEx(&cfg, per_update_kernel, (const UpdateArgs)a));
+        CK(h, cudaLaunchKernelEx(&cfg, uk, (const UpdateArgs)a));
         h->st.kernel_launches++;
     }
     a.n = n; a.idx = idx0; a.prio = prio0; a.iota_base = iota0;
@@ -501,6 +574,31 @@ RETH_EXPORT int reth_replay_clear(reth_replay_t *h, void *stream)
     h->tail = 0;
     h->size = 0;
     h->uni_tail = h->fifo_head = h->fifo_len = 0;   // UniformSampler.clear / FIFOSampler.clear
+    return RETH_OK;
+}
+
+RETH_EXPORT int reth_replay_batch_ring_resize(reth_replay_t *h, int max_batch, int ring_depth)
+{
+    if (!h) return RETH_ERR_INVALID;
+    if (max_batch < 1 || ring_depth < 1) return fail(h, RETH_ERR_INVALID, "batch ring: max_batch and ring_depth must be >= 1");
+    if (h->pipe.open) return fail(h, RETH_ERR_STATE, "batch ring: close the loader pipe first");
+    DeviceGuard guard(h->cfg.device);
+    CK(h, cudaDeviceSynchronize());                       // nothing may still read or fill a slot
+    free_batch_ring(h);
+    h->cfg.max_batch = max_batch;
+    h->cfg.ring_depth = ring_depth;
+    h->pipe_reserved = 0;
+    const int64_t want = max_batch > 16384 ? max_batch : 16384;
+    if (want > h->max_n) {                                // staging of host-resident index / priority arguments
+        cudaFree(h->stage_idx); cudaFree(h->stage_prio);
+        h->stage_idx = h->stage_prio = nullptr;
+        h->max_n = want;
+        CK(h, cudaMalloc(&h->stage_idx, h->max_n * 8));
+        CK(h, cudaMalloc(&h->stage_prio, h->max_n * 8));
+    }
+    int rc = alloc_batch_ring(h);
+    if (rc) return rc;
+    CK(h, cudaDeviceSynchronize());
     return RETH_OK;
 }
 
@@ -887,10 +985,8 @@ int do_sample(reth_replay *h, int batch, const double *uniforms, int uniforms_lo
     a.all_roots = all_roots; a.n_shards = n_shards; a.shard = shard;
     if (n_shards > 1 && groups > 1) {
         // the shares of the `groups` draws are packed back to back from slot `slot` on
-        if (!h->quota) {
-            CK(h, dalloc_zero(&h->quota, (size_t)4 * 32, &h->st.hbm_bytes));
-            CK(h, dalloc_zero(&h->slot_quota, (size_t)4 * h->slots.size(), &h->st.hbm_bytes));
-        }
+        if (!h->quota) CK(h, dalloc_zero(&h->quota, (size_t)4 * 32, &h->st.hbm_bytes));
+        if (!h->slot_quota) CK(h, dalloc_zero(&h->slot_quota, (size_t)4 * h->slots.size(), &h->st.hbm_bytes));
         global_quota_kernel<<<1, 32 * groups, 0, s>>>(a, h->quota, h->slot_quota + 4 * slot);
         CK(h, cudaGetLastError());
         h->st.kernel_launches++;

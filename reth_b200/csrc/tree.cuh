@@ -470,7 +470,12 @@ __device__ __forceinline__ void repair_tiles_warp(const UpdateArgs &a, const int
 //   ROOT     : tile 0 by one warp of CTA 0 (derived rule)
 // The result equals the reference's sequential loop because sum/min are pure functions of
 // the final leaves on the union of touched paths.
-__global__ void __launch_bounds__(kUpdateThreads) per_update_kernel(const UpdateArgs a)
+// kLv: tile levels compiled in (5 covers capacity <= 2^25 and keeps the per-level bookkeeping of the two
+// deepest levels out of the register file; 7 covers the ABI's 2^31); kRegCtas: CTAs of this kernel that
+// must fit one SM's register file (2 -> <= 64 registers at 512 threads): the repair is latency-bound
+// and waits most of its life, so what matters is how many gather CTAs stay resident beside it.
+template <int kLv, int kRegCtas>
+__global__ void __launch_bounds__(kUpdateThreads, kRegCtas) per_update_kernel(const UpdateArgs a)
 {
     cg::cluster_group cluster = cg::this_cluster();
     const int nblk = (int)cluster.num_blocks(), brank = (int)cluster.block_rank();
@@ -478,13 +483,13 @@ __global__ void __launch_bounds__(kUpdateThreads) per_update_kernel(const Update
     const int64_t i = (int64_t)threadIdx.x * nblk + brank;
     const int64_t cap = a.g.capacity;
     const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
-    constexpr int kWarps = kUpdateThreads / 32;
+    const int kWarps = (int)(blockDim.x >> 5);          // block size is a launch parameter (<= kUpdateThreads)
     const int NT = a.g.n_tile_levels;
 
     pdl_wait();
     pdl_trigger();
     RETH_STAMP(0);
-    if (brank == 0 && threadIdx.x < kMaxTileLevels) a.counts_next[threadIdx.x] = 0;
+    if (brank == 0 && threadIdx.x < kMaxTileLevels /* array size */) a.counts_next[threadIdx.x] = 0;
     // every load that does not depend on another is issued up front
     int64_t n = a.n;
     if (a.n_dev) {
@@ -518,22 +523,22 @@ __global__ void __launch_bounds__(kUpdateThreads) per_update_kernel(const Update
         if (st != my_stamp) active = false;
         else if (!a.keep_stamps) __stcg(&a.stamp[idx], 0u);       // stamps are zero between launches
     }
-    int32_t own_tile[kMaxTileLevels];                             // tile this thread owns at level T (>= 3), else -1
+    int32_t own_tile[kLv];                             // tile this thread owns at level T (>= 3), else -1
 #pragma unroll
-    for (int T = 0; T < kMaxTileLevels; ++T) own_tile[T] = -1;
+    for (int T = 0; T < kLv; ++T) own_tile[T] = -1;
     if (active) {
         const NodeLoc n = locate(idx);
         __stcg(&a.desc[n.tile * 32 + n.local].y, leaf);
         if (n.T <= 1) {
             atomicOr(&a.mask[n.tile], 1u << n.local);             // own bit; ancestors are derived
         } else {
-            int64_t tiles[kMaxTileLevels];
-            uint32_t bits[kMaxTileLevels], old[kMaxTileLevels];
+            int64_t tiles[kLv];
+            uint32_t bits[kLv], old[kLv];
             int64_t tile = n.tile;
             int local = n.local, r = n.r;
             uint64_t kroot = ((uint64_t)idx + 1ull) >> n.r;       // heap k of the tile root
 #pragma unroll
-            for (int T = kMaxTileLevels - 1; T >= 2; --T) {
+            for (int T = kLv - 1; T >= 2; --T) {
                 if (T > n.T) continue;
                 uint32_t b = 0;
                 for (int j = 0; j <= r; ++j) b |= 1u << (local >> (r - j));
@@ -547,16 +552,16 @@ __global__ void __launch_bounds__(kUpdateThreads) per_update_kernel(const Update
                 tile = tile_base(T - 1) + (int64_t)(kroot - (1ull << (5 * (T - 1))));
             }
 #pragma unroll
-            for (int T = kMaxTileLevels - 1; T >= 3; --T)
+            for (int T = kLv - 1; T >= 3; --T)
                 if (T <= n.T) old[T] = atomicOr(&a.mask[tiles[T]], bits[T]);
             atomicOr(&a.mask[tiles[2]], bits[2]);                 // level 2 is swept densely: no owner
 #pragma unroll
-            for (int T = kMaxTileLevels - 1; T >= 3; --T)
+            for (int T = kLv - 1; T >= 3; --T)
                 if (T <= n.T && old[T] == 0u) own_tile[T] = (int32_t)tiles[T];
         }
     }
 #pragma unroll
-    for (int T = kMaxTileLevels - 1; T >= 3; --T) {
+    for (int T = kLv - 1; T >= 3; --T) {
         if (T >= NT) continue;                                    // uniform
         const unsigned bal = __ballot_sync(0xffffffffu, own_tile[T] >= 0);
         if (bal != 0u && lane == __ffs(bal) - 1) atomicOr(&a.counts[0], 1 << T);   // level has work
@@ -569,7 +574,7 @@ __global__ void __launch_bounds__(kUpdateThreads) per_update_kernel(const Update
     if (NT > 3) {
         const int flags = __ldcg(&a.counts[0]);                   // bit T: somebody owns a tile at level T
 #pragma unroll
-        for (int T = kMaxTileLevels - 1; T >= 3; --T) {
+        for (int T = kLv - 1; T >= 3; --T) {
             if (T >= NT || !((flags >> T) & 1)) continue;         // uniform over the cluster
             const int32_t t = own_tile[T];
             uint32_t m = 0;
@@ -611,18 +616,21 @@ __global__ void __launch_bounds__(kUpdateThreads) per_update_kernel(const Update
                 if (rel < n2) { tile = 33 + rel; m = __ldcg(&a.mask[tile]); }
             }
             unsigned todo = __ballot_sync(0xffffffffu, m != 0u);
+            constexpr int kK2 = kRegCtas > 1 ? 2 : 4;             // tiles per round trip (register budget)
             while (todo) {
-                int64_t t4[4] = {0, 0, 0, 0};
+                int64_t tk[kK2];
                 int cnt = 0;
 #pragma unroll
-                for (int q = 0; q < 4; ++q)
+                for (int q = 0; q < kK2; ++q) {
+                    tk[q] = 0;
                     if (todo) {
                         const int src = __ffs(todo) - 1;
                         todo &= todo - 1;
-                        t4[q] = __shfl_sync(0xffffffffu, tile, src);
+                        tk[q] = __shfl_sync(0xffffffffu, tile, src);
                         ++cnt;
                     }
-                repair_tiles_warp<4>(a, t4, cnt, 2, lane, false);
+                }
+                repair_tiles_warp<kK2>(a, tk, cnt, 2, lane, false);
             }
         }
         RETH_STAMP(20);

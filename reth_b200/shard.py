@@ -245,7 +245,7 @@ class ReplayShard:
         # what a batch slot holds (struct is what the ring stores)
         self.out_struct = [((np.dtype(np.float32) if code else dt), sh)
                            for (dt, sh), code in zip(logical, self.out_cast)]
-        cfg.gather_mode = int(gather_mode)      # 0 auto (TMA bulk when a column is wide), 1 LDG/STG, 2 TMA bulk
+        cfg.gather_mode = int(gather_mode)      # 0 auto (= 1: LDG/STG.128, the faster one on B200), 1 LDG/STG, 2 TMA bulk
         h = C.c_void_p()
         rc = self._lib.reth_replay_create(C.byref(cfg), C.byref(h))
         if rc != 0:
@@ -308,6 +308,11 @@ class ReplayShard:
     # -- write side -------------------------------------------------------
     def clear(self, stream=None):
         self._ck(self._lib.reth_replay_clear(self._h, self._s(stream)))
+
+    def resize_batch_ring(self, max_batch, ring_depth):
+        """Re-shape the learner-batch ring (reth_replay_batch_ring_resize); all slots are emptied."""
+        self._ck(self._lib.reth_replay_batch_ring_resize(self._h, int(max_batch), int(ring_depth)))
+        self.max_batch, self.ring_depth = int(max_batch), int(ring_depth)
 
     def append(self, cols, prio=None, alpha=0.6, transform=True, stream=None):
         """Client.append / PrioritizedBuffer.append_batch; returns the first FIFO slot."""

@@ -30,7 +30,7 @@ def test_header_symbols_exported_and_bound():
         assert re.search(rf"\bT {n}\b", syms), f"{n} not exported"
         assert hasattr(L, n)
         assert n in _cabi.SIGNATURES or n in _cabi.LZ4F_SIGNATURES or n == "reth_replay_last_error", f"{n} has no ctypes signature"
-    assert L.reth_replay_abi_version() == 2
+    assert L.reth_replay_abi_version() == 3
 
 
 def test_library_is_sm100a_with_lineinfo():
