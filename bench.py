@@ -158,6 +158,78 @@ def cpu_reference_arm(steps, warmup, iters, batch, cap, threads, ring_rows=1 << 
     return threads * steps * iters * batch / dt, dt
 
 
+# ---- the reference's OWN code (SURVEY.md 8d Tier A), from oracle/_ref (oracle/make_ref.py places it there at build time)
+def ref_path():
+    p = os.path.join(ROOT, "oracle", "_ref")
+    return p if os.path.exists(os.path.join(p, "reth_ref", "utils", "sumtree.py")) else None
+
+
+def _ref_numba_worker(a):
+    """One replica = one process (the njit tree holds the GIL; the reference scales by processes too):
+    FIFOPolicy.get_indices + NumpyBuffer.append_batch + PERSampler.update for the fill, then per iteration
+    PERSampler.sample -> NumpyBuffer.select -> PERSampler.update, all the reference's own code."""
+    path, cap, batch, warm, iters, ring_rows, seed, barrier = a
+    sys.path.insert(0, path)
+    from reth_ref.buffer import NumpyBuffer
+    from reth_ref.cache_policy import FIFOPolicy
+    from reth_ref.sampler import PERSampler
+    rng = np.random.default_rng(seed)
+    sampler, policy = PERSampler(cap, ALPHA, BETA), FIFOPolicy(cap)
+    buf = NumpyBuffer(ring_rows, struct=[(np.dtype(dt).name, sh) for dt, sh in ATARI])
+    blk = [rng.integers(0, 256, (64, 4, 84, 84), dtype=np.uint8), rng.integers(0, 18, 64), np.zeros(64, np.float32),
+           rng.integers(0, 256, (64, 4, 84, 84), dtype=np.uint8), np.zeros(64, np.float32)]
+    for _ in range(0, ring_rows, 64):                     # rows arrive 64 at a time (test/apex-dqn/config.yaml:3)
+        buf.append_batch(blk)
+    for st in range(0, cap, 1 << 14):
+        n = min(1 << 14, cap - st)
+        w = (np.abs(rng.standard_normal(n)) * (1 + 9 * (rng.random(n) < 0.05))).astype(np.float32)
+        sampler.update(policy.get_indices(n), w)
+    newp = np.abs(rng.standard_normal((64, batch))).astype(np.float32)
+    mask = ring_rows - 1
+
+    def loop(n):
+        rows = None
+        for i in range(n):
+            idx, w = sampler.sample(batch)
+            rows = buf.select(idx & mask)                 # bounded frame ring: slot & mask (the tree has full capacity)
+            sampler.update(idx, newp[i & 63])
+        return rows
+    loop(warm)                                            # absorbs the numba JIT
+    barrier.wait()
+    t0 = time.perf_counter()
+    loop(iters)
+    return time.perf_counter() - t0
+
+
+def reference_numba_arm(iters, batch, cap, procs, ring_rows=1 << 12, warm=3):
+    """-> (transitions/s over all replicas, slowest replica's seconds) or None when numba / oracle/_ref is missing."""
+    path = ref_path()
+    if path is None:
+        return None
+    try:
+        import numba  # noqa: F401
+    except Exception:
+        return None
+    import multiprocessing as mp
+    ctx = mp.get_context("spawn")                          # the parent may hold a CUDA context
+    with ctx.Manager() as mgr:
+        barrier = mgr.Barrier(procs)
+        with ctx.Pool(procs) as pool:
+            dts = pool.map(_ref_numba_worker, [(path, cap, batch, warm, iters, ring_rows, 100 + k, barrier) for k in range(procs)])
+    return procs * iters * batch / max(dts), max(dts)
+
+
+def service_tier_b():
+    """BASELINE.md 3 Tier B: the reference's real multi-process service needs lmdb, portpicker, netifaces."""
+    missing = []
+    for m in ("lmdb", "portpicker", "netifaces", "lz4"):
+        try:
+            __import__(m)
+        except Exception:
+            missing.append(m)
+    return ("service end-to-end: unavailable on this box (missing " + ", ".join(missing) + ")") if missing else "importable"
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -168,16 +240,35 @@ def run_reference(args):
     del entry
     cores = os.cpu_count() or 1
     iters = args.cpu_iters
-    value, dt = cpu_reference_arm(args.steps, args.warmup, iters, args.batch, args.capacity, cores)
-    sample = (f"{cores} replicas x {args.steps} steps x {iters} iterations of batch {args.batch}; tree capacity "
-              f"{args.capacity}, frame ring bounded to 16384 rows (slot & mask)")
+    pvalue, pdt = cpu_reference_arm(args.steps, args.warmup, iters, args.batch, args.capacity, cores)
+    psample = (f"{cores} replicas x {args.steps} steps x {iters} iterations of batch {args.batch}; tree capacity "
+               f"{args.capacity}, frame ring bounded to 16384 rows (slot & mask)")
+    port = {"value": pvalue, "unit": "transitions/s", "cores": cores, "kind": "port", "sample": psample}
+    ref = None
+    try:
+        ref = reference_numba_arm(args.steps * iters, args.batch, args.capacity, cores, warm=max(3, args.warmup))
+    except Exception as e:
+        log(f"reference numba arm failed: {e!r}")
+    if ref is not None:
+        # the reference's own njit tree + NumPy ring (oracle/_ref) is the baseline of record; the C port beside it
+        value, dt = ref
+        dt = dt / max(1, args.steps)
+        base = {"value": value, "unit": "transitions/s", "cores": cores, "kind": "reference",
+                "sample": f"{cores} processes x {args.steps * iters} iterations of batch {args.batch}: the reference's own "
+                          f"PERSampler (njit sum tree) + NumpyBuffer.select + PERSampler.update; tree capacity "
+                          f"{args.capacity}, frame ring bounded to 4096 rows per process (slot & mask)",
+                "port": port}
+    else:
+        value, dt = pvalue, pdt / max(1, args.steps)
+        base = dict(port, note="numba or oracle/_ref unavailable on this box: C port of the reference's tree + memcpy ring")
+    base["service_e2e"] = service_tier_b()
     line = {
         "impl": "reference", "metric": "sampled transitions/sec (sample+gather+priority update)",
         "value": value, "unit": "transitions/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": dt * 1e3 / max(1, args.steps), "higher_is_better": True, "scaling": "weak",
+        "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8 rows / f64 tree", "data": "synthetic",
         "config": workload_config(args), "iterations_per_step": iters,
-        "cpu_baseline": {"value": value, "unit": "transitions/s", "cores": cores, "kind": "port", "sample": sample},
+        "cpu_baseline": base,
         "e2e": {"value": value, "unit": "transitions/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -446,6 +537,18 @@ def run_ours(args):
             "value": v, "unit": "transitions/s", "cores": cores, "kind": "port", "one_core": v1,
             "sample": f"{cores} replicas x {args.cpu_steps} steps x {args.cpu_iters} iterations of batch {B} "
                       f"({dt:.1f} s); tree capacity {cap}, frame ring bounded to 16384 rows (slot & mask)"}
+        try:                                            # the reference's own code on the same cores (oracle/_ref)
+            rn = reference_numba_arm(max(64, args.cpu_steps * args.cpu_iters // 4), B, cap, cores)
+            rn1 = reference_numba_arm(max(64, args.cpu_steps * args.cpu_iters // 4), B, cap, 1, ring_rows=1 << 16)
+        except Exception as e:
+            log(f"reference numba arm failed: {e!r}")
+            rn = rn1 = None
+        line["cpu_baseline"]["reference_numba"] = None if rn is None else {
+            "value": rn[0], "unit": "transitions/s", "cores": cores, "one_core_ring_65536": rn1[0] if rn1 else None,
+            "sample": f"{cores} processes: reference PERSampler (njit tree, capacity {cap}) + NumpyBuffer.select "
+                      f"(ring bounded to 4096 rows per process; one-core figure with a 65536-row = 3.7 GB ring) + "
+                      f"PERSampler.update, {rn[1]:.1f} s"}
+        line["cpu_baseline"]["service_e2e"] = service_tier_b()
     if rank == 0:
         emit(line)
     proc.terminate()

@@ -174,7 +174,7 @@ def parity_leg(torch, dist, shard, sg, world, rank, GB, alpha, beta, log):
 
 def timed_case(torch, dist, shard, GB, G, iters, alpha, beta, seed):
     """Mode G device loop: `iters` iterations of G global batches each -> us per global batch (max over ranks)."""
-    depth = max(4, 2 * G)
+    depth = max(4, 3 * G)                                         # the tree chain may run two groups ahead of the gather
     if shard.max_batch != GB or shard.ring_depth != depth:
         shard.resize_batch_ring(GB, depth)
     steps = iters * G

@@ -125,11 +125,38 @@ int reth_replay_append(reth_replay_t *h, const void *const *cols, int cols_loc,
 /* Frame ring of a shard with RETH_COL_FRAMES columns: n frames of frame_bytes, stored at frame slots
  * tail, tail+1, ... mod frame_capacity; first_frame_out (host, may be NULL) gets `tail`.  The caller writes
  * those slots into the frame-reference columns of the transitions it appends afterwards.  A frame slot is
- * reused after frame_capacity later frames: size the ring for the frames `capacity` transitions span. */
+ * reused after frame_capacity later frames: size the ring for the frames `capacity` transitions span
+ * (one frame per step plus one per episode reset, times the environments that interleave).  Liveness is
+ * tracked: every stored row remembers the oldest frame it refers to, and a gather that meets a transition
+ * which has outlived one of its frames reports RETH_ERR_STATE at the next synchronising call instead of
+ * handing the learner a stack rebuilt from another time or environment. */
 int reth_replay_append_frames(reth_replay_t *h, const void *frames, int frames_loc, int64_t n,
                               int64_t *first_frame_out, void *stream);
 /* parity / debug: frames [first_frame, first_frame + n) of the ring -> host */
 int reth_replay_frame_read(reth_replay_t *h, int64_t first_frame, int64_t n, void *out_host, void *stream);
+
+/* ---- n-step assembly at append time: replaces NStepAdder.push on the actor (reth/reth/utils/nstep_adder.py:11-28,
+ *      driven per environment by test/apex-dqn/worker.py:35,53).  The actor sends its RAW 1-step rows; the shard
+ *      keeps, per environment stream, the rows that have not left the adder yet and writes every finished n-step
+ *      transition straight into its FIFO slot: reward = r_t + g r_{t+1} + ... (the reference's running product
+ *      t_gamma *= gamma and its operation order; float32 rewards accumulate in float32 like numpy does on the
+ *      worker's 0-d float32 array, float64 in float64), s1 = the s1 of the last row folded in, folding stops
+ *      behind a row whose done flag is set, every other column is the row's own (its own done flag included).
+ *      Works on full rows and on frame-reference columns alike (s1 is then k frame slots).
+ *  nstep_open: n_streams environment streams, `step` = n, reward / s1 / done column indices of the row struct;
+ *      max_rows = most rows of one append_nstep call that are staged at once (host-resident input).
+ *  append_nstep: n raw rows of stream `stream_id` in step order.  The row that push p of this call sends out
+ *      of the adder takes prio[p] (pushes that emit nothing ignore theirs; NULL = raw 1.0), as the worker
+ *      computes its loss on the rows the adder returned (worker.py:53-60).  *emitted_out = rows stored
+ *      (= pushes so far - step, clipped at 0, minus what earlier calls stored).  Rows still buffered when a
+ *      stream ends are never stored (nstep_adder.py has no flush); nstep_reset(stream) = a fresh adder
+ *      (stream_id -1: all streams). */
+int reth_replay_nstep_open(reth_replay_t *h, int n_streams, int step, double gamma, int r_col, int s1_col,
+                           int done_col, int64_t max_rows);
+int reth_replay_nstep_reset(reth_replay_t *h, int stream_id);
+int reth_replay_append_nstep(reth_replay_t *h, int stream_id, const void *const *cols, int cols_loc,
+                             const void *prio, int prio_dtype, int prio_loc, int64_t n, double alpha,
+                             int transform, int64_t *first_slot_out, int64_t *emitted_out, void *stream);
 
 /* Plugin cache policies (cache_policy/base_policy.py:4-7): rows go to caller-chosen slots.
  * slots: int64[n] on slots_loc; duplicates resolve to the last row in batch order. */

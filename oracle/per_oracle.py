@@ -324,3 +324,38 @@ class OracleFIFOSampler:
 
     def clear(self):
         self.buffer.clear()
+
+
+def nstep_fold(cols, step, gamma, r_col=2, s1_col=3, done_col=4):
+    """Closed form of what NStepAdder.push emits over one environment stream
+    (reth/reth/utils/nstep_adder.py:11-28, fed as in test/apex-dqn/worker.py:35,53).
+
+    cols: the stream's raw 1-step rows, one array per column.  Row t leaves the adder at push t+step
+    (:13-14) after the pushes t+1 .. t+step-1 have touched it (:16-24): push t+j adds gamma^j * r_{t+j} to
+    its reward and replaces its s1, unless one of the rows t .. t+j-1 has its done flag set (the scan runs
+    from the newest row and stops at the first done row, :18-19).  gamma^j is the running product
+    t_gamma *= gamma (:22); a float32 reward column accumulates in float32 with the factor rounded to
+    float32 (numpy on the 0-d float32 array of worker.py:49), a float64 one in float64.
+    -> (emitted columns for rows 0 .. L-step-1, push index that emits each row = t + step)."""
+    L = len(cols[r_col])
+    E = max(0, L - step)
+    out = [np.array(c[:E], copy=True) for c in cols]
+    r = np.asarray(cols[r_col])
+    done = np.asarray(cols[done_col]).reshape(L, -1).any(axis=1) if L else np.zeros(0, bool)
+    f32 = r.dtype == np.float32
+    for t in range(E):
+        acc = r[t]
+        g = float(gamma)
+        last = t
+        for j in range(1, step):
+            if done[t + j - 1]:
+                break
+            if f32:
+                acc = np.float32(acc + np.float32(np.float32(g) * r[t + j]))
+            else:
+                acc = acc + g * r[t + j]
+            g *= float(gamma)
+            last = t + j
+        out[r_col][t] = acc
+        out[s1_col][t] = cols[s1_col][last]
+    return out, np.arange(E) + step

@@ -88,6 +88,10 @@ SIGNATURES = {
     "reth_replay_clear": [_vp, _vp],
     "reth_replay_batch_ring_resize": [_vp, _i32, _i32],
     "reth_replay_append": [_vp, _vp, _i32, _vp, _i32, _i32, _i64, _f64, _i32, C.POINTER(_i64), _vp],
+    "reth_replay_nstep_open": [_vp, _i32, _i32, _f64, _i32, _i32, _i32, _i64],
+    "reth_replay_nstep_reset": [_vp, _i32],
+    "reth_replay_append_nstep": [_vp, _i32, _vp, _i32, _vp, _i32, _i32, _i64, _f64, _i32, C.POINTER(_i64),
+                                 C.POINTER(_i64), _vp],
     "reth_replay_append_at": [_vp, _vp, _i32, _vp, _i32, _vp, _i32, _i32, _i64, _f64, _i32, _vp],
     "reth_replay_update": [_vp, _vp, _i32, _i32, _vp, _i32, _i32, _i64, _f64, _i32, _vp],
     "reth_replay_update_slot": [_vp, _i32, _vp, _i32, _i32, _f64, _i32, _vp],

@@ -300,7 +300,49 @@ struct FrameArgs {
     int32_t dst_row_from_meta;
     int64_t capacity;
     int32_t *err;
+    // liveness of frame references: row_oldest[slot] = sequence number of the oldest frame the stored row refers
+    // to (frame_mark_kernel); a frame is overwritten once frame_capacity later frames arrived
+    const int64_t *row_oldest;
+    int64_t frames_appended, frame_capacity;
 };
+constexpr int kErrStaleFrame = 0x200;
+
+// After rows were stored at `n` slots (FIFO: (first + i) % capacity, or an explicit list): record for each the
+// sequence number of the OLDEST frame its frame-reference columns point at.  Frames are numbered in arrival order
+// (frame `seq` lives in ring slot seq % frame_capacity), so a reference r made when `frames_appended` frames had
+// arrived names frame  frames_appended - 1 - ((frame_tail - 1 - r) mod frame_capacity).  The gather compares this
+// against the frames appended since: a transition that outlived one of its frames is reported, never handed out.
+struct MarkArgs {
+    const uint8_t *refs[kMaxCols];   // ring columns holding int32[K] references
+    int64_t rb[kMaxCols];
+    int32_t K[kMaxCols];
+    int32_t ncols;
+    const int64_t *slots;            // explicit slots, or nullptr: (first + i) % capacity
+    int64_t first, n, capacity;
+    int64_t frame_tail, frames_appended, frame_capacity;
+    int64_t *row_oldest;
+    int32_t *err;
+};
+
+__global__ void frame_mark_kernel(const MarkArgs a)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.n) return;
+    const int64_t slot = a.slots ? a.slots[i] : (a.first + i) % a.capacity;
+    if (slot < 0 || slot >= a.capacity) return;          // reported by the row mover
+    int64_t max_age = 0;
+    for (int c = 0; c < a.ncols; ++c) {
+        const int32_t *r = (const int32_t *)(a.refs[c] + slot * a.rb[c]);
+        for (int k = 0; k < a.K[c]; ++k) {
+            const int64_t ref = r[k];
+            if (ref < 0 || ref >= a.frame_capacity) { atomicOr(a.err, 1); continue; }
+            int64_t age = (a.frame_tail - 1 - ref) % a.frame_capacity;
+            if (age < 0) age += a.frame_capacity;
+            max_age = age > max_age ? age : max_age;
+        }
+    }
+    a.row_oldest[slot] = a.frames_appended - 1 - max_age;
+}
 
 // Also the widening gather of stored wide columns (direct = 1): the same warp-per-part streaming, which
 // keeps 6 CTAs per SM resident where the general row mover's widening path manages 4.
@@ -323,6 +365,10 @@ __global__ void __launch_bounds__(kCopyThreads, 6) frame_gather_kernel(const Fra
         if (slot < 0 || slot >= a.capacity) { if (threadIdx.x == 0) atomicOr(a.err, 1); continue; }
         const int32_t *refs = (const int32_t *)(col.refs + slot * col.rb);
         const int64_t out_row = (int64_t)row + row0;
+        if (!col.direct && a.row_oldest && a.frames_appended - a.row_oldest[slot] > a.frame_capacity) {
+            if (threadIdx.x == 0) atomicOr(a.err, kErrStaleFrame);      // a referenced frame has been overwritten
+            continue;
+        }
         const int pieces = col.K * col.split;
         const int upf = (int)(col.fb >> 4);
         for (int p = warp; p < pieces; p += kWarps) {

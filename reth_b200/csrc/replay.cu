@@ -14,6 +14,7 @@
 #include "../../include/reth_replay.h"
 #include "copy.cuh"
 #include "lz4f.h"
+#include "nstep.cuh"
 #include "tree.cuh"
 
 using namespace reth;
@@ -70,7 +71,20 @@ struct reth_replay {
     cudaEvent_t ev_fork = nullptr, ev_join_t = nullptr, ev_join_g = nullptr;
     cudaStream_t s_append = nullptr;          // large device-source appends: the row copy runs beside the tree update
     cudaEvent_t ev_app_fork = nullptr, ev_app_done = nullptr;
-    cudaEvent_t last_gather_ev = nullptr;     // newest gather of the internal streams (appends wait for it: rows stay atomic)
+    cudaEvent_t last_gather_ev = nullptr;     // newest gather of the internal streams
+    cudaEvent_t last_gather_on[2] = {nullptr, nullptr};   // ... per gather stream (s_gather, s_gather2): a writer of ring
+                                              // rows waits for BOTH, the other stream's previous gather may still run
+    // n-step assembly at append time (reth_replay_nstep_*): per environment stream, the raw rows that have not
+    // left the adder yet (double-buffered), and a staging area for host-resident rows
+    struct NStep {
+        bool open = false;
+        int n_streams = 0, step = 0, r_col = 0, s1_col = 0, done_col = 0;
+        double gamma = 0.0;
+        int64_t max_rows = 0;
+        uint8_t *carry[2][kMaxCols] = {};
+        uint8_t *stage[kMaxCols] = {};
+        std::vector<int> count, cur;
+    } nstep;
     int update_cluster = 8;               // largest cluster the device hosts (16, else 8), or the caller's choice
     int update_cluster_fixed = 0;         // the caller (config / RETH_UPDATE_CLUSTER) chose the cluster size
     int update_threads = kUpdateThreads;  // threads per CTA of the repair kernel
@@ -80,6 +94,7 @@ struct reth_replay {
     int n_frame_cols = 0;
     uint8_t *frames = nullptr;          // frame ring: frame_capacity x frame_bytes
     int64_t frame_tail = 0, frames_appended = 0;
+    int64_t *row_oldest = nullptr;      // [capacity] oldest frame (sequence number) each stored row refers to
     int max_dyn_smem = 0;               // opt-in shared memory per block
     bool gather_bulk = false;           // gather through row_gather_bulk_kernel (TMA bulk copies)
     int bulk_grid_cap = 0;              // RETH_BULK_GRID at create time: cap on the persistent grid (tests)
@@ -121,6 +136,9 @@ struct reth_replay {
     double *all_roots = nullptr;
     int board_shards = 0, board_shard = 0;
     unsigned long long board_seq = 0;
+    BoardEntry **board_ptrs_dev = nullptr;   // peer_board[] on the device (the repair kernel publishes through it)
+    unsigned long long wait_seq = 0;         // set around a draw: take the roots of this exchange from the board
+    int modeg_fused = 1;                     // Mode G loop: publish folded into the repair kernel, wait into the draw
     int64_t *quota = nullptr;     // Mode G prefetch group: {first, count, offset, 0} per draw of the running launch
     int64_t *slot_quota = nullptr; // the same per batch slot (kept for the consumer of the packed batch)
     bool pdl = false;             // tree-chain launches carry the programmatic-dependent-launch attribute (set by step_loop)
@@ -172,6 +190,28 @@ struct DeviceGuard {
 
 size_t dtype_size(int dt) { return (dt == RETH_F32 || dt == RETH_I32) ? 4 : 8; }
 
+// A gather was enqueued on one of the internal gather streams and `ev` recorded behind it.
+void note_gather(reth_replay *h, cudaEvent_t ev, cudaStream_t sg)
+{
+    h->last_gather_ev = ev;
+    h->last_gather_on[sg == h->s_gather2 ? 1 : 0] = ev;
+}
+void forget_gathers(reth_replay *h)
+{
+    h->last_gather_ev = nullptr;
+    h->last_gather_on[0] = h->last_gather_on[1] = nullptr;
+}
+// Writers of ring rows (append, append_at, append_frames, n-step append) wait for every gather still in flight:
+// a gathered row is never half old, half new (the reference's LMDB rows are replaced atomically,
+// server/main_loop.py:55-57).  Consecutive gathers alternate between two streams, so the newest event of EACH
+// stream is waited for -- the newest gather overall says nothing about the one before it on the other stream.
+int wait_gathers(reth_replay *h, cudaStream_t s)
+{
+    for (int k = 0; k < 2; ++k)
+        if (h->last_gather_on[k]) CK(h, cudaStreamWaitEvent(s, h->last_gather_on[k], 0));
+    return RETH_OK;
+}
+
 void free_batch_ring(reth_replay *h);
 int alloc_batch_ring(reth_replay *h);
 
@@ -183,12 +223,13 @@ void free_all(reth_replay *h)
     cudaFree(h->dbg);
     for (int i = 0; i < kMaxShards; ++i)
         if (h->peer_ipc[i] && h->peer_board[i]) cudaIpcCloseMemHandle(h->peer_board[i]);
-    cudaFree(h->board); cudaFree(h->all_roots); cudaFree(h->quota);
+    cudaFree(h->board); cudaFree(h->all_roots); cudaFree(h->quota); cudaFree(h->board_ptrs_dev);
     cudaFree(h->stage_idx); cudaFree(h->stage_prio);
     if (h->host_pin) cudaFreeHost(h->host_pin);
     for (int c = 0; c < kMaxCols; ++c) cudaFree(h->ring[c]);
-    cudaFree(h->frames);
+    cudaFree(h->frames); cudaFree(h->row_oldest);
     free_batch_ring(h);
+    for (int c = 0; c < kMaxCols; ++c) { cudaFree(h->nstep.carry[0][c]); cudaFree(h->nstep.carry[1][c]); cudaFree(h->nstep.stage[c]); }
     for (auto e : h->ev_time) cudaEventDestroy(e);
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
     if (h->ev_app_fork) cudaEventDestroy(h->ev_app_fork);
@@ -211,7 +252,7 @@ void free_batch_ring(reth_replay *h)
         cudaFree(h->slot_cols[c]);
         h->slot_cols[c] = nullptr;
     }
-    if (h->slot_idx) h->st.hbm_bytes -= (int64_t)h->slots.size() * ((int64_t)h->cfg.max_batch * 24 + 16);
+    if (h->slot_idx) h->st.hbm_bytes -= (int64_t)h->slots.size() * ((int64_t)h->cfg.max_batch * 24 + 16 + 32);
     cudaFree(h->slot_idx); cudaFree(h->slot_w); cudaFree(h->slot_prio); cudaFree(h->slot_meta);
     cudaFree(h->slot_quota); cudaFree(h->stage_u);
     h->slot_idx = nullptr; h->slot_w = nullptr; h->slot_prio = nullptr; h->slot_meta = nullptr;
@@ -221,7 +262,7 @@ void free_batch_ring(reth_replay *h)
     h->ev_sampled.clear();
     h->ev_gathered.clear();
     h->slots.clear();
-    h->last_gather_ev = nullptr;
+    forget_gathers(h);
 }
 
 int alloc_batch_ring(reth_replay *h)
@@ -238,6 +279,8 @@ int alloc_batch_ring(reth_replay *h)
     CK(h, dalloc_zero(&h->slot_w, depth * mb, acct));
     CK(h, dalloc_zero(&h->slot_prio, depth * mb, acct));
     CK(h, dalloc_zero(&h->slot_meta, depth * 2, acct));
+    CK(h, dalloc_zero(&h->slot_quota, depth * 4, acct));
+    if (!h->quota) CK(h, dalloc_zero(&h->quota, (size_t)4 * 32, acct));
     CK(h, cudaMalloc((void **)&h->stage_u, mb * 8));
     for (size_t i = 0; i < depth; ++i) {
         BatchSlot &s = h->slots[i];
@@ -401,6 +444,7 @@ RETH_EXPORT int reth_replay_create(const reth_replay_config *cfg, reth_replay_t 
     if (h->n_frame_cols) {
         CKC(cudaMalloc((void **)&h->frames, (size_t)cfg->frame_capacity * cfg->frame_bytes));
         *acct += (int64_t)cfg->frame_capacity * cfg->frame_bytes;
+        CKC(dalloc_zero(&h->row_oldest, (size_t)cfg->capacity, acct));
     }
     {
         const int rc_ring = alloc_batch_ring(h);
@@ -490,6 +534,8 @@ int launch_update(reth_replay *h, UpdateArgs &a, cudaStream_t s)
     a.g = h->geom; a.desc = h->desc; a.agg = h->agg; a.stamp = h->stamp; a.mask = h->mask;
     a.err = h->err; a.dbg = h->dbg;
     const int64_t n = a.n;
+    const unsigned long long pub_seq = a.pub_seq;
+    if (pub_seq) { a.pub_boards = h->board_ptrs_dev; a.pub_shards = h->board_shards; a.pub_shard = h->board_shard; }
     const UpdateShape shape = update_shape_of(h, n);
     const UpdateKernel uk = shape.fn;
     const int64_t per = (int64_t)shape.cluster * h->update_threads;
@@ -499,6 +545,7 @@ int launch_update(reth_replay *h, UpdateArgs &a, cudaStream_t s)
     for (int64_t off = 0; off < n; off += per) {
         a.n = n - off < per ? n - off : per;
         a.n_off = off;
+        a.pub_seq = (off + per >= n) ? pub_seq : 0ull;       // the launch that completes the write-back publishes
         a.stamp_base = (uint32_t)off;
         if (a.idx_kind != 2) a.idx = idx0 + off * is;
         if (a.prio_kind != 2) a.prio = prio0 + off * ps;
@@ -522,7 +569,7 @@ int launch_update(reth_replay *h, UpdateArgs &a, cudaStream_t s)
         CK(h, cudaLaunchKernelEx(&cfg, uk, (const UpdateArgs)a));
         h->st.kernel_launches++;
     }
-    a.n = n; a.idx = idx0; a.prio = prio0; a.iota_base = iota0;
+    a.n = n; a.idx = idx0; a.prio = prio0; a.iota_base = iota0; a.pub_seq = pub_seq;
     return RETH_OK;
 }
 
@@ -537,6 +584,17 @@ int set_prio(reth_replay *h, UpdateArgs &a, const void *prio, int prio_dtype, in
     return to_device(h, (const uint8_t *)prio + off * es, prio_loc, n * es, h->stage_prio, s, &a.prio);
 }
 
+// What a non-zero device-side error flag means.
+int device_err(reth_replay *h, int32_t flag)
+{
+    if (flag & kErrBoardTimeout)
+        return fail(h, RETH_ERR_STATE, "roots exchange timed out: a peer shard did not publish its root");
+    if (flag & kErrStaleFrame)
+        return fail(h, RETH_ERR_STATE, "a sampled transition refers to a frame that has been overwritten: the frame "
+                                       "ring (frame_capacity) is too small for the transitions it must outlive");
+    return fail(h, RETH_ERR_RANGE, "an index outside [0, capacity) was passed to the shard");
+}
+
 // Device-side error flag (index out of range seen by a kernel); checked at sync points.
 int check_device_err(reth_replay *h, cudaStream_t s)
 {
@@ -545,9 +603,7 @@ int check_device_err(reth_replay *h, cudaStream_t s)
     CK(h, cudaStreamSynchronize(s));
     if (*flag) {
         cudaMemsetAsync(h->err, 0, sizeof(int32_t), s);
-        if (*flag & kErrBoardTimeout)
-            return fail(h, RETH_ERR_STATE, "roots exchange timed out: a peer shard did not publish its root");
-        return fail(h, RETH_ERR_RANGE, "an index outside [0, capacity) was passed to the shard");
+        return device_err(h, *flag);
     }
     return RETH_OK;
 }
@@ -576,6 +632,27 @@ RETH_EXPORT int reth_replay_clear(reth_replay_t *h, void *stream)
     h->uni_tail = h->fifo_head = h->fifo_len = 0;   // UniformSampler.clear / FIFOSampler.clear
     return RETH_OK;
 }
+
+namespace {
+// Record the oldest referenced frame of the rows just stored at n slots (see frame_mark_kernel).
+int mark_frame_refs(reth_replay *h, const int64_t *slots_dev, int64_t first, int64_t n, cudaStream_t s)
+{
+    if (!h->n_frame_cols || n <= 0) return RETH_OK;
+    MarkArgs a = {};
+    for (int c = 0; c < h->cfg.n_columns; ++c)
+        if (h->col_frames[c]) {
+            a.refs[a.ncols] = h->ring[c]; a.rb[a.ncols] = h->cfg.row_bytes[c]; a.K[a.ncols] = h->col_frames[c];
+            a.ncols++;
+        }
+    a.slots = slots_dev; a.first = first; a.n = n; a.capacity = h->cfg.capacity;
+    a.frame_tail = h->frame_tail; a.frames_appended = h->frames_appended; a.frame_capacity = h->cfg.frame_capacity;
+    a.row_oldest = h->row_oldest; a.err = h->err;
+    frame_mark_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(a);
+    CK(h, cudaGetLastError());
+    h->st.kernel_launches++;
+    return RETH_OK;
+}
+}  // namespace
 
 RETH_EXPORT int reth_replay_batch_ring_resize(reth_replay_t *h, int max_batch, int ring_depth)
 {
@@ -614,7 +691,7 @@ RETH_EXPORT int reth_replay_append_frames(reth_replay_t *h, const void *frames, 
     if (n == 0) return RETH_OK;
     DeviceGuard guard(h->cfg.device);
     cudaStream_t s = S(stream);
-    if (h->last_gather_ev) CK(h, cudaStreamWaitEvent(s, h->last_gather_ev, 0));   // a running gather may still read the slots
+    { const int rcw = wait_gathers(h, s); if (rcw) return rcw; }   // a running gather may still read the slots
     const cudaMemcpyKind kind = frames_loc == RETH_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
     const int64_t len1 = n < cap - h->frame_tail ? n : cap - h->frame_tail, len2 = n - len1;
     CK(h, cudaMemcpyAsync(h->frames + h->frame_tail * fb, frames, (size_t)(len1 * fb), kind, s));
@@ -648,10 +725,11 @@ RETH_EXPORT int reth_replay_append(reth_replay_t *h, const void *const *cols, in
     DeviceGuard guard(h->cfg.device);
     cudaStream_t s = S(stream);
     const int64_t cap = h->cfg.capacity;
+    const int64_t first_slot = h->tail;
     if (first_slot_out) *first_slot_out = h->tail;
     // a gather still running on the internal streams must not see half-written rows (the reference's
     // LMDB rows are replaced atomically, main_loop.py:55-57)
-    if (h->last_gather_ev && h->cfg.store_rows && n > 0) CK(h, cudaStreamWaitEvent(s, h->last_gather_ev, 0));
+    if (h->cfg.store_rows && n > 0) { const int rcw = wait_gathers(h, s); if (rcw) return rcw; }
     bool forked = false;
     for (int64_t off = 0; off < n; off += h->max_n) {
         const int64_t m = (n - off < h->max_n) ? n - off : h->max_n;
@@ -745,7 +823,144 @@ RETH_EXPORT int reth_replay_append(reth_replay_t *h, const void *const *cols, in
         CK(h, cudaEventRecord(h->ev_app_done, h->s_append));
         CK(h, cudaStreamWaitEvent(s, h->ev_app_done, 0));
     }
+    if (h->cfg.store_rows && n > 0) {
+        const int rcm = mark_frame_refs(h, nullptr, first_slot, n, s);
+        if (rcm) return rcm;
+    }
     h->st.tail = h->tail; h->st.size = h->size;
+    return RETH_OK;
+}
+
+// ------------------------------------------------------------ n-step assembly --
+RETH_EXPORT int reth_replay_nstep_open(reth_replay_t *h, int n_streams, int step, double gamma, int r_col, int s1_col,
+                                       int done_col, int64_t max_rows)
+{
+    if (!h) return RETH_ERR_INVALID;
+    auto &ns = h->nstep;
+    if (ns.open) return fail(h, RETH_ERR_STATE, "n-step assembly is already open");
+    const int nc = h->cfg.n_columns;
+    if (!h->cfg.store_rows || nc < 1) return fail(h, RETH_ERR_STATE, "n-step assembly needs a shard that stores rows");
+    if (n_streams < 1 || step < 1 || max_rows < 1) return fail(h, RETH_ERR_INVALID, "n_streams, step and max_rows must be >= 1");
+    if (r_col < 0 || r_col >= nc || s1_col < 0 || s1_col >= nc || done_col < 0 || done_col >= nc || r_col == s1_col ||
+        r_col == done_col || s1_col == done_col)
+        return fail(h, RETH_ERR_INVALID, "reward / s1 / done columns must be three different columns of the row struct");
+    if (h->cfg.row_bytes[r_col] != 4 && h->cfg.row_bytes[r_col] != 8)
+        return fail(h, RETH_ERR_INVALID, "the reward column must be one float32 or float64 per row");
+    DeviceGuard guard(h->cfg.device);
+    for (int c = 0; c < nc; ++c) {
+        const size_t rb = (size_t)h->cfg.row_bytes[c];
+        for (int b = 0; b < 2; ++b) {
+            CK(h, cudaMalloc((void **)&ns.carry[b][c], (size_t)n_streams * step * rb));
+            h->st.hbm_bytes += (int64_t)((size_t)n_streams * step * rb);
+        }
+        CK(h, cudaMalloc((void **)&ns.stage[c], (size_t)max_rows * rb));
+        h->st.hbm_bytes += (int64_t)((size_t)max_rows * rb);
+    }
+    ns.n_streams = n_streams; ns.step = step; ns.gamma = gamma; ns.r_col = r_col; ns.s1_col = s1_col;
+    ns.done_col = done_col; ns.max_rows = max_rows;
+    ns.count.assign(n_streams, 0);
+    ns.cur.assign(n_streams, 0);
+    ns.open = true;
+    return RETH_OK;
+}
+
+RETH_EXPORT int reth_replay_nstep_reset(reth_replay_t *h, int stream_id)
+{
+    if (!h) return RETH_ERR_INVALID;
+    auto &ns = h->nstep;
+    if (!ns.open) return fail(h, RETH_ERR_STATE, "n-step assembly is not open");
+    if (stream_id < -1 || stream_id >= ns.n_streams) return fail(h, RETH_ERR_INVALID, "bad stream id %d", stream_id);
+    for (int k = 0; k < ns.n_streams; ++k)
+        if (stream_id < 0 || k == stream_id) ns.count[k] = 0;      // a fresh NStepAdder: buffered rows are dropped
+    return RETH_OK;
+}
+
+RETH_EXPORT int reth_replay_append_nstep(reth_replay_t *h, int stream_id, const void *const *cols, int cols_loc,
+                                         const void *prio, int prio_dtype, int prio_loc, int64_t n, double alpha,
+                                         int transform, int64_t *first_slot_out, int64_t *emitted_out, void *stream)
+{
+    if (!h) return RETH_ERR_INVALID;
+    auto &ns = h->nstep;
+    if (!ns.open) return fail(h, RETH_ERR_STATE, "n-step assembly is not open");
+    if (stream_id < 0 || stream_id >= ns.n_streams) return fail(h, RETH_ERR_INVALID, "bad stream id %d", stream_id);
+    if (n < 0 || (n > 0 && !cols)) return fail(h, RETH_ERR_INVALID, "bad rows");
+    if (prio && prio_dtype != RETH_F32 && prio_dtype != RETH_F64) return fail(h, RETH_ERR_INVALID, "priorities must be float32 or float64");
+    DeviceGuard guard(h->cfg.device);
+    cudaStream_t s = S(stream);
+    const int nc = h->cfg.n_columns;
+    const int64_t cap = h->cfg.capacity;
+    if (first_slot_out) *first_slot_out = h->tail;
+    int64_t emitted = 0;
+    if (n > 0) { const int rcw = wait_gathers(h, s); if (rcw) return rcw; }
+    const size_t ps = prio ? dtype_size(prio_dtype) : 0;
+    for (int64_t off = 0; off < n; off += ns.max_rows) {
+        const int64_t m = (n - off < ns.max_rows) ? n - off : ns.max_rows;
+        NStepArgs a = {};
+        a.ncols = nc; a.step = ns.step; a.r_col = ns.r_col; a.s1_col = ns.s1_col; a.done_col = ns.done_col;
+        a.r_f64 = h->cfg.row_bytes[ns.r_col] == 8;
+        a.carry_count = ns.count[stream_id];
+        a.n = m; a.tail = h->tail; a.capacity = cap; a.gamma = ns.gamma;
+        const int64_t L = a.carry_count + m;
+        a.E = L > ns.step ? L - ns.step : 0;
+        if (a.E > cap) return fail(h, RETH_ERR_INVALID, "n-step append of %lld rows exceeds capacity", (long long)a.E);
+        const int cur = ns.cur[stream_id];
+        for (int c = 0; c < nc; ++c) {
+            NStepCol &col = a.col[c];
+            const int64_t rb = h->cfg.row_bytes[c];
+            col.rb = rb;
+            col.carry = ns.carry[cur][c] + (size_t)stream_id * ns.step * rb;
+            col.carry_next = ns.carry[cur ^ 1][c] + (size_t)stream_id * ns.step * rb;
+            col.ring = h->ring[c];
+            const uint8_t *src = (const uint8_t *)cols[c] + off * rb;
+            if (cols_loc == RETH_DEVICE) col.fresh = src;
+            else {
+                CK(h, cudaMemcpyAsync(ns.stage[c], src, (size_t)(m * rb), cudaMemcpyHostToDevice, s));
+                col.fresh = ns.stage[c];
+            }
+            col.part_bytes = 8192;
+            col.parts = rb > 8192 ? (int32_t)((rb + 8191) / 8192) : 1;
+            col.part_base = a.parts_per_row;
+            a.parts_per_row += col.parts;
+        }
+        const int64_t maxg = (int64_t)h->n_sms * 8 * 16;
+        if (a.E > 0) {
+            const int64_t items = a.E * a.parts_per_row;
+            nstep_emit_kernel<<<(unsigned)(items < maxg ? items : maxg), kCopyThreads, 0, s>>>(a);
+            CK(h, cudaGetLastError());
+            h->st.kernel_launches++;
+        }
+        if (a.E > 0) { const int rcm = mark_frame_refs(h, nullptr, h->tail, a.E, s); if (rcm) return rcm; }
+        const int keep = (int)(L < ns.step ? L : ns.step);
+        {
+            const int64_t items = (int64_t)keep * a.parts_per_row;
+            nstep_carry_kernel<<<(unsigned)(items < maxg ? items : maxg), kCopyThreads, 0, s>>>(a, keep);
+            CK(h, cudaGetLastError());
+            h->st.kernel_launches++;
+        }
+        if (a.E > 0) {
+            // the row that push p of this call sends out of the adder carries prio[p]: emitted row e left at push
+            // e + step - carry_count, so the emitted rows' priorities are one contiguous slice
+            const int64_t p0 = off + (ns.step - a.carry_count);
+            for (int64_t uo = 0; uo < a.E; uo += h->max_n) {
+                const int64_t um = a.E - uo < h->max_n ? a.E - uo : h->max_n;
+                UpdateArgs u = {};
+                u.n = um; u.idx = nullptr; u.idx_kind = 2; u.iota_base = h->tail + uo;
+                u.alpha = alpha; u.transform = transform; u.dedupe = 0;
+                int rc = set_prio(h, u, prio ? (const uint8_t *)prio + (p0 + uo) * ps : nullptr, prio_dtype, prio_loc, 0, um, s);
+                if (rc) return rc;
+                rc = launch_update(h, u, s);
+                if (rc) return rc;
+            }
+            h->tail = (h->tail + a.E) % cap;
+            h->size = (h->size + a.E < cap) ? h->size + a.E : cap;
+            h->st.appended_rows += a.E;
+            emitted += a.E;
+        }
+        ns.count[stream_id] = keep;
+        ns.cur[stream_id] = cur ^ 1;
+    }
+    h->st.tail = h->tail; h->st.size = h->size;
+    if (emitted_out) *emitted_out = emitted;
     return RETH_OK;
 }
 
@@ -874,7 +1089,10 @@ int launch_row_move(reth_replay *h, const RowArgs &a, cudaStream_t s)
     if (!kScatter && !widen && a.meta && a.share_div > 1) {
         // Mode G share: CTAs beyond the valid items leave at once, but 0.4 us per thousand of them adds up
         // (48 k surplus CTAs = 22 us): size the grid for twice the expected share, a larger share strides
-        int64_t want = 2 * (total / a.share_div) + 64;
+        // (stratified targets: a shard's share is its fraction of the global total +- 1 row per draw, so the
+        // slack only has to cover unequal shard totals; a larger share strides)
+        static const double slack = [] { const char *e = getenv("RETH_SHARE_GRID"); return e ? atof(e) : 1.25; }();
+        int64_t want = (int64_t)(slack * (double)(total / a.share_div)) + 64;
         if (want < (int64_t)h->n_sms * 6 * 4) want = (int64_t)h->n_sms * 6 * 4;
         if (want < (int64_t)grid) grid = (unsigned)want;
     }
@@ -907,6 +1125,7 @@ int launch_frame_gather(reth_replay *h, uint8_t *const *batch_cols, const int64_
         }
         col.split = col.K >= 8 ? 1 : (8 + col.K - 1) / col.K;      // K * split >= the 8 warps of a CTA
     }
+    a.row_oldest = h->row_oldest; a.frames_appended = h->frames_appended; a.frame_capacity = h->cfg.frame_capacity;
     const int64_t items = (int64_t)batch * a.ncols;
     if (items <= 0) return RETH_OK;
     const int64_t maxg = (int64_t)h->n_sms * 6 * 64;
@@ -983,10 +1202,14 @@ int do_sample(reth_replay *h, int batch, const double *uniforms, int uniforms_lo
     a.idx_out = b.idx; a.w_out = b.w; a.prio_out = b.prio; a.meta = b.meta;
     a.idx_mirror = h->mirror_idx; a.w_mirror = h->mirror_w; a.err_mirror = h->mirror_err; a.err = h->err;
     a.all_roots = all_roots; a.n_shards = n_shards; a.shard = shard;
+    if (h->wait_seq && n_shards > 1) {
+        a.wait_board = h->board; a.wait_seq = h->wait_seq; a.roots_out = h->all_roots; a.err_rw = h->err;
+        a.wait_timeout_ns = (unsigned long long)env_int("RETH_BOARD_TIMEOUT_MS", 2000) * 1000000ull;
+    }
     if (n_shards > 1 && groups > 1) {
         // the shares of the `groups` draws are packed back to back from slot `slot` on
-        if (!h->quota) CK(h, dalloc_zero(&h->quota, (size_t)4 * 32, &h->st.hbm_bytes));
-        if (!h->slot_quota) CK(h, dalloc_zero(&h->slot_quota, (size_t)4 * h->slots.size(), &h->st.hbm_bytes));
+        // (both buffers exist since create / the last ring resize: no allocation -- and no legacy-stream memset,
+        // which would wait for every blocking stream of the process -- on the sampling path)
         global_quota_kernel<<<1, 32 * groups, 0, s>>>(a, h->quota, h->slot_quota + 4 * slot);
         CK(h, cudaGetLastError());
         h->st.kernel_launches++;
@@ -1095,7 +1318,6 @@ RETH_EXPORT int reth_replay_slot_quota(reth_replay_t *h, int first_slot, int n_s
     if (!h || !out) return RETH_ERR_INVALID;
     if (n_slots < 1 || first_slot < 0 || first_slot + n_slots > (int)h->slots.size())
         return fail(h, RETH_ERR_INVALID, "slots %d..%d outside the batch ring", first_slot, first_slot + n_slots - 1);
-    if (!h->slot_quota) return fail(h, RETH_ERR_STATE, "no packed Mode G draw has been made");
     DeviceGuard guard(h->cfg.device);
     CK(h, cudaMemcpyAsync(out, h->slot_quota + 4 * first_slot, (size_t)n_slots * 32, cudaMemcpyDeviceToHost, S(stream)));
     CK(h, cudaStreamSynchronize(S(stream)));
@@ -1176,10 +1398,13 @@ RETH_EXPORT int reth_replay_append_at(reth_replay_t *h, const int64_t *slots, in
             return fail(h, RETH_ERR_INVALID, "append_at needs device-resident rows (stage them first)");
         uint8_t *src[kMaxCols];
         for (int c = 0; c < h->cfg.n_columns; ++c) src[c] = (uint8_t *)cols[c];
+        { const int rcw = wait_gathers(h, s); if (rcw) return rcw; }   // no gather may read a slot while it is rewritten
         RowArgs r;
         build_row_args(h, r, src, (const int64_t *)a.idx, (int)n);
         r.stamp = h->stamp;
         rc = launch_row_move<true>(h, r, s);
+        if (rc) return rc;
+        rc = mark_frame_refs(h, (const int64_t *)a.idx, 0, n, s);
         if (rc) return rc;
     }
     stamp_clear_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(h->stamp, (const int64_t *)a.idx, n,
@@ -1497,7 +1722,7 @@ void pipe_free(reth_replay *h)
         v->clear();
     }
     if (p.s_copy) cudaStreamDestroy(p.s_copy);
-    h->last_gather_ev = nullptr;
+    forget_gathers(h);
     p = reth_replay::Pipe();
 }
 
@@ -1532,7 +1757,7 @@ int pipe_issue(reth_replay *h, double beta, bool give_up_lent = false)
     rc = do_gather(h, slot, false, sg, p.G);
     if (rc) return rc;
     CK(h, cudaEventRecord(p.ev_gat[g], sg));
-    h->last_gather_ev = p.ev_gat[g];
+    note_gather(h, p.ev_gat[g], sg);
     if (!p.zero_copy) {
         CK(h, cudaStreamWaitEvent(p.s_copy, p.ev_gat[g], 0));
         CK(h, cudaEventRecord(p.ev_done[g], p.s_copy));
@@ -1553,7 +1778,7 @@ int pipe_wait(reth_replay *h, int32_t *group_out)
     if (group_out) *group_out = g;
     if (p.err_host[g]) {
         cudaMemsetAsync(h->err, 0, sizeof(int32_t), h->s_tree);
-        return fail(h, RETH_ERR_RANGE, "an index outside [0, capacity) was passed to the shard");
+        return device_err(h, p.err_host[g]);
     }
     return RETH_OK;
 }
@@ -2052,6 +2277,9 @@ RETH_EXPORT int reth_replay_board_connect(reth_replay_t *h, const reth_board_exp
             h->peer_ipc[i] = true;
         }
     }
+    if (!h->board_ptrs_dev) CK(h, cudaMalloc((void **)&h->board_ptrs_dev, sizeof(BoardEntry *) * kMaxShards));
+    CK(h, cudaMemcpy(h->board_ptrs_dev, h->peer_board, sizeof(BoardEntry *) * kMaxShards, cudaMemcpyHostToDevice));
+    if (const char *e = getenv("RETH_MODEG_FUSED")) h->modeg_fused = atoi(e);
     h->board_shards = n_shards;
     h->board_shard = shard;
     return RETH_OK;
@@ -2117,9 +2345,18 @@ RETH_EXPORT int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, co
         if (!serial && !no_gather && k >= depth) CK(h, cudaStreamWaitEvent(st, h->ev_gathered[slot], 0));
         int rc = RETH_OK;
         if (global) {
-            rc = launch_roots_exchange(h, 3, st);
+            // the first exchange of the call is its own kernel; after that the repair kernel of iteration k has
+            // published exchange board_seq and the draw of iteration k+1 waits for it on the board itself
+            // (prefetch groups only: there the single-CTA share kernel does the waiting.  With G = 1 every warp of
+            // the draw kernel would poll the board -- a launch saved, 30.8 -> 29.1 us per step on 2 GPUs, but when
+            // several shards share ONE device those spinning CTAs keep a peer's repair cluster off the SMs until
+            // the timeout; RETH_MODEG_FUSED=2 opts in for one shard per GPU)
+            const bool fused = k > 0 && (h->modeg_fused >= 2 || (h->modeg_fused == 1 && G > 1));
+            if (!fused) rc = launch_roots_exchange(h, 3, st);
+            h->wait_seq = fused ? h->board_seq : 0ull;
             if (!rc) rc = do_sample(h, batch, nullptr, RETH_DEVICE, seed, beta, slot, h->all_roots,
                                     h->board_shards, h->board_shard, st, G);
+            h->wait_seq = 0ull;
         } else if (!no_sample || h->slots[slot].batch != batch)
             rc = do_sample(h, batch, uniforms_dev ? uniforms_dev + (size_t)k * batch : nullptr, RETH_DEVICE,
                            seed, beta, slot, nullptr, 1, 0, st, G);
@@ -2149,14 +2386,17 @@ RETH_EXPORT int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, co
                 CK(h, cudaEventRecord(h->ev_time[h->ev_time_used + 1], sg));
                 h->ev_time_used += 2;
             }
-            if (!serial) { CK(h, cudaEventRecord(h->ev_gathered[slot], sg)); h->last_gather_ev = h->ev_gathered[slot]; }
+            if (!serial) { CK(h, cudaEventRecord(h->ev_gathered[slot], sg)); note_gather(h, h->ev_gathered[slot], sg); }
         }
         if (no_update) continue;
         UpdateArgs a = {};
         a.n = (int64_t)batch * G; a.idx = h->slots[slot].idx; a.idx_kind = 0;
         a.prio = prio_dev + (size_t)k * batch; a.prio_kind = 0;
         a.alpha = alpha; a.transform = 1; a.dedupe = G == 1 ? 2 : 1;
-        if (global) a.n_dev = h->slots[slot].meta + 1;          // this shard's share of the global batch
+        if (global) {
+            a.n_dev = h->slots[slot].meta + 1;                  // this shard's share of the global batch
+            if ((h->modeg_fused >= 2 || (h->modeg_fused == 1 && G > 1)) && k + G < steps) a.pub_seq = ++h->board_seq;
+        }
         rc = launch_update(h, a, st);
         if (rc) return rc;
         h->st.updated_rows += (int64_t)batch * G;

@@ -84,6 +84,59 @@ __device__ __forceinline__ double2 ldcg2(const double2 *p) { return __ldcg(p); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
+// ---- shard roots board (Mode G, see roots_exchange_kernel below)
+struct BoardEntry {
+    double sum, mn;
+    unsigned long long seq, pad;
+};
+constexpr int kMaxShards = 64;
+constexpr int kBoardEntries = 2 * kMaxShards;
+constexpr int kErrBoardTimeout = 0x100;
+
+__device__ __forceinline__ void st_release_sys(unsigned long long *p, unsigned long long v)
+{
+    asm volatile("st.release.sys.global.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long *p)
+{
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned long long global_ns()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+
+// Publish this shard's root {total, min} with exchange number `seq` into every shard's roots board (plain
+// stores over NVLink, the flag with release semantics at system scope); lanes stride over the shards.
+__device__ __forceinline__ void board_publish(BoardEntry *const *boards, int n_shards, int shard,
+                                              unsigned long long seq, const double2 *agg, int lane)
+{
+    const double2 r = ldcg2(&agg[1]);
+    for (int s = lane; s < n_shards; s += 32) {
+        BoardEntry *e = boards[s] + (int)(seq & 1ull) * kMaxShards + shard;
+        volatile double *vs = &e->sum, *vm = &e->mn;
+        *vs = r.x;
+        *vm = r.y;
+        st_release_sys(&e->seq, seq);
+    }
+}
+// Wait until shard s's entry of exchange `seq` has arrived in the OWN board (local L2 polls); false on timeout.
+__device__ __forceinline__ bool board_wait(const BoardEntry *own, int s, unsigned long long seq,
+                                           unsigned long long timeout_ns)
+{
+    const BoardEntry *e = own + (int)(seq & 1ull) * kMaxShards + s;
+    if (ld_acquire_sys(&e->seq) == seq) return true;
+    const unsigned long long t0 = global_ns();
+    while (ld_acquire_sys(&e->seq) != seq)
+        if (global_ns() - t0 > timeout_ns) return false;
+    return true;
+}
+
 // counter-based uniform in [0,1) with 53 random bits (splitmix64 finaliser);
 // the reference draws from numba's private generator (sumtree.py:75), so only
 // the distribution, not the stream, is part of the contract.
@@ -120,7 +173,30 @@ struct SampleArgs {
     double *w_mirror;
     int32_t *err_mirror;
     const int32_t *err;
+    // Mode G with the exchange folded into the chain: the shard roots of exchange `wait_seq` are taken from
+    // this shard's roots board (published by the peers' repair kernels) instead of a snapshot made by
+    // roots_exchange_kernel; the first kernel of the draw waits for them and writes the snapshot roots_out.
+    const BoardEntry *wait_board;
+    unsigned long long wait_seq, wait_timeout_ns;
+    double *roots_out;
+    int32_t *err_rw;
 };
+
+// Wait for every shard's root of exchange a.wait_seq on the own board and return shard s's {total, min}
+// through `roots_out` (snapshot) -- one call per launch by a single warp / block; false on timeout.
+__device__ __forceinline__ bool board_collect(const SampleArgs &a, int tid, int nthr)
+{
+    bool ok = true;
+    for (int s = tid; s < a.n_shards; s += nthr) {
+        if (!board_wait(a.wait_board, s, a.wait_seq, a.wait_timeout_ns)) { ok = false; continue; }
+        const BoardEntry *e = a.wait_board + (int)(a.wait_seq & 1ull) * kMaxShards + s;
+        const volatile double *vs = &e->sum, *vm = &e->mn;
+        a.roots_out[2 * s] = *vs;
+        a.roots_out[2 * s + 1] = *vm;
+    }
+    if (!ok) atomicOr(a.err_rw, kErrBoardTimeout);
+    return ok;
+}
 
 __device__ __forceinline__ double draw_u(const SampleArgs &a, int64_t i)
 {
@@ -166,8 +242,21 @@ __global__ void __launch_bounds__(256) per_sample_kernel(const SampleArgs a)
         // global CDF over shard totals in rank order (Mode G)
         total = 0.0;
         double mn = 0.0, mine = 0.0;
+        const bool from_board = a.wait_seq != 0ull && !a.quota;    // with a quota kernel, that one waited and snapshot
+        const BoardEntry *brd = a.wait_board + (int)(a.wait_seq & 1ull) * kMaxShards;
+        if (from_board) {
+            // every warp waits on the own board (local L2); warp 0 also leaves the snapshot for the host side
+            bool ok = true;
+            for (int s = lane; s < a.n_shards; s += 32) ok = board_wait(a.wait_board, s, a.wait_seq, a.wait_timeout_ns) && ok;
+            if (!__all_sync(0xffffffffu, ok)) { if (lane == 0) atomicOr(a.err_rw, kErrBoardTimeout); return; }
+        }
         for (int s = 0; s < a.n_shards; ++s) {
-            const double t = a.all_roots[2 * s], m = a.all_roots[2 * s + 1];
+            double t, m;
+            if (from_board) {
+                const volatile double *vs = &brd[s].sum, *vm = &brd[s].mn;
+                t = *vs; m = *vm;
+                if (W == 0 && lane == 0) { a.roots_out[2 * s] = t; a.roots_out[2 * s + 1] = m; }
+            } else { t = a.all_roots[2 * s]; m = a.all_roots[2 * s + 1]; }
             if (s == a.shard) { prefix = total; mine = t; }
             total += t;
             if (t != 0.0 && m != 0.0) mn = (mn == 0.0 || m < mn) ? m : mn;
@@ -249,6 +338,10 @@ __global__ void __launch_bounds__(1024) global_quota_kernel(const SampleArgs a, 
     pdl_trigger();
     __shared__ int64_t sh_first[32], sh_count[32];
     const int lane = threadIdx.x & 31, grp = threadIdx.x >> 5;
+    if (a.wait_seq != 0ull) {          // exchange folded into the chain: wait for the peers' roots, snapshot them
+        board_collect(a, threadIdx.x, blockDim.x);
+        __syncthreads();               // the snapshot (a.all_roots == a.roots_out) is read below by this block
+    }
     if (grp < a.groups) {
         double total = 0.0, prefix = 0.0, mine = 0.0;
         for (int s = 0; s < a.n_shards; ++s) {
@@ -300,6 +393,11 @@ struct UpdateArgs {
     int32_t keep_stamps;  // leave the winners' stamps in place (policy-slot scatter reads them)
     int32_t dedupe;       // 0 none (distinct slots), 1 stamps (arbitrary order), 2 adjacent runs
     long long *dbg;       // optional: SM-clock stamps of stage boundaries (CTA 0, thread 0)
+    // Mode G: the launch that completes a write-back also publishes the new root to every shard's roots
+    // board (exchange number pub_seq != 0), so the next global draw needs no exchange kernel before it
+    BoardEntry *const *pub_boards;
+    int32_t pub_shards, pub_shard;
+    unsigned long long pub_seq;
 };
 
 #define RETH_STAMP(k) do { if (a.dbg && brank == 0 && threadIdx.x == 0) a.dbg[k] = clock64(); } while (0)
@@ -474,8 +572,13 @@ __device__ __forceinline__ void repair_tiles_warp(const UpdateArgs &a, const int
 // deepest levels out of the register file; 7 covers the ABI's 2^31); kRegCtas: CTAs of this kernel that
 // must fit one SM's register file (2 -> <= 64 registers at 512 threads): the repair is latency-bound
 // and waits most of its life, so what matters is how many gather CTAs stay resident beside it.
+// kRegCtas == 1 is capped at 104 registers, not the 128 the block size would allow: a 512-thread CTA then
+// leaves 12 K registers on its SM, room for the CTAs of a draw kernel that programmatic dependent launch made
+// resident ahead of its turn.  At 114 registers an SM holding ONE such waiting CTA could no longer host a
+// repair CTA, and with the draw kernel's CTAs spread over every GPC no GPC had 16 free SMs for the cluster:
+// two shards on one device then waited for each other until the exchange timed out.
 template <int kLv, int kRegCtas>
-__global__ void __launch_bounds__(kUpdateThreads, kRegCtas) per_update_kernel(const UpdateArgs a)
+__global__ void __maxnreg__(kRegCtas == 1 ? 104 : 64) per_update_kernel(const UpdateArgs a)
 {
     cg::cluster_group cluster = cg::this_cluster();
     const int nblk = (int)cluster.num_blocks(), brank = (int)cluster.block_rank();
@@ -496,7 +599,10 @@ __global__ void __launch_bounds__(kUpdateThreads, kRegCtas) per_update_kernel(co
         const int64_t m = __ldcg(a.n_dev) - a.n_off;
         n = m < n ? (m < 0 ? 0 : m) : n;
     }
-    if (n <= 0) return;     // Mode G chunk beyond this shard's share: uniform over the cluster, nothing was touched
+    if (n <= 0) {           // Mode G chunk beyond this shard's share: uniform over the cluster, nothing was touched
+        if (a.pub_seq && brank == 0 && wic == 0) board_publish(a.pub_boards, a.pub_shards, a.pub_shard, a.pub_seq, a.agg, lane);
+        return;
+    }
     const bool inrange = i < n;
     int64_t idx = 0, nxt = -1;
     double raw = 0.0;
@@ -648,6 +754,10 @@ __global__ void __launch_bounds__(kUpdateThreads, kRegCtas) per_update_kernel(co
     if (brank == 0 && wic == 0) {
         const int64_t t0[1] = {0};
         repair_tiles_warp<1>(a, t0, 1, 0, lane, true);
+        if (a.pub_seq) {
+            __syncwarp();              // lane 1 stored the root; order it before the other lanes' loads
+            board_publish(a.pub_boards, a.pub_shards, a.pub_shard, a.pub_seq, a.agg, lane);
+        }
     }
     RETH_STAMP(22);
 }
@@ -745,14 +855,6 @@ __global__ void sampler_pick_kernel(const PickArgs a)
 // stream, no host round trip: a device-side all-gather fused between the tree update and the draw.
 // Entries are double-buffered by the parity of the exchange number: a peer can publish exchange
 // k+1 only after its own wait for k, which needed MY publish of k, so nobody is ever two ahead.
-struct BoardEntry {
-    double sum, mn;
-    unsigned long long seq, pad;
-};
-constexpr int kMaxShards = 64;
-constexpr int kBoardEntries = 2 * kMaxShards;
-constexpr int kErrBoardTimeout = 0x100;
-
 struct RootsArgs {
     const double2 *agg;                 // this shard's tree (root = agg[1])
     BoardEntry *board[kMaxShards];      // board of shard s as mapped here (own board for s == shard)
@@ -762,23 +864,6 @@ struct RootsArgs {
     unsigned long long timeout_ns;
     int32_t *err;
 };
-
-__device__ __forceinline__ void st_release_sys(unsigned long long *p, unsigned long long v)
-{
-    asm volatile("st.release.sys.global.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
-}
-__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long *p)
-{
-    unsigned long long v;
-    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ unsigned long long global_ns()
-{
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    return t;
-}
 
 // one thread per shard
 __global__ void __launch_bounds__(kMaxShards) roots_exchange_kernel(const RootsArgs a)

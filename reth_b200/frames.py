@@ -8,37 +8,12 @@ Here a shard built with `frames=` keeps single frames once in a frame ring and a
 k int32 frame slots for s0 and for s1; the gather rebuilds the stacks on the device.
 
 FrameRefWriter turns per-environment step streams into batched `append_frames` + `append` calls
-with exactly FrameStack's stacking rule.  NStepAdder restates reth/reth/utils/nstep_adder.py:5-28;
-with frame references its s1 is just another set of k slots."""
+with exactly FrameStack's stacking rule.  n-step returns are assembled on the device at append time
+(reth_replay_append_nstep, csrc/nstep.cuh: with frame references the n-step s1 is just the k slots of a
+later row); an actor that still folds them itself uses the reference's own NStepAdder unchanged."""
 from collections import deque
 
 import numpy as np
-
-
-class NStepAdder:
-    """reth/reth/utils/nstep_adder.py:5-28, behaviour kept as is: rows are [s0, a, r, s1, done, *extra];
-    push() returns the row that is `step` pushes old (its r accumulated with gamma, its s1 replaced by
-    the newest s1) or None; accumulation into a row stops at the first row -- scanning from the
-    newest -- whose done flag is set; rows still buffered when the stream ends are not emitted."""
-
-    def __init__(self, gamma, step=3):
-        self.step = step
-        self.gamma = gamma
-        self._buffer = deque(maxlen=step)
-
-    def push(self, s0, a, r, s1, done, *extra_args):
-        res = None
-        if self._buffer.maxlen == len(self._buffer):           # :13-14
-            res = self._buffer.pop()
-        t_gamma = self.gamma
-        for item in self._buffer:                               # newest first (:16-24)
-            if item[4]:
-                break
-            item[2] += t_gamma * r
-            t_gamma *= self.gamma
-            item[3] = s1
-        self._buffer.appendleft([s0, a, r, s1, done, *extra_args])
-        return res
 
 
 class FrameRefWriter:

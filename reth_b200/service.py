@@ -213,6 +213,7 @@ class _Engine:
                         o = np.asarray(next(it))
                         struct.append((o.dtype, tuple(o.shape[1:])))
                 self._ensure_shard(None, struct=struct)
+            self.flush()                                      # staged write-backs first (call order, as in append)
             if self._writer is None:
                 self._writer = FrameRefWriter(self.shard, k=k, frame_cols=cols)
             w = self._writer
@@ -237,6 +238,7 @@ class _Engine:
     def append(self, data, weights):
         with self.lock:
             self._ensure_shard(data)
+            self.flush()                                      # staged write-backs land before the rows that may recycle their slots
             alpha = self.sampler["alpha"].value()
             if self.cache_policy is None:
                 first = self.shard.append(list(data), weights, alpha=alpha, transform=True, stream=self.stream)
@@ -252,6 +254,11 @@ class _Engine:
                        for c, (dt, _) in zip(data, self.struct)]
                 torch.cuda.current_stream(self.device).synchronize()
                 self.shard.append_at(slots, dev, weights, alpha=alpha, transform=True, stream=self.stream)
+                # the scatter reads `dev` on the engine's stream (not a torch stream): tell the caching allocator,
+                # or the blocks could be handed to the next .cuda() copy while the kernel still reads them
+                ext = torch.cuda.ExternalStream(self.stream, device=self.device)
+                for t in dev:
+                    t.record_stream(ext)
                 if self.kind == "uniform":
                     self.shard.uniform_note(slots, stream=self.stream)
                 elif self.kind == "fifo":
@@ -378,7 +385,9 @@ class _Engine:
         host memory and enqueued behind everything issued so far; `group` consecutive messages of
         batch_size share one staging entry = one host->device copy + one tree-update launch (the
         frames the reference keeps in its PUSH/SUB pipes).  Order and last-writer-wins are those of
-        the message sequence; alpha is read when the entry is committed."""
+        the message sequence; alpha is read when the entry is committed (with a scheduled alpha the up to
+        `group` coalesced messages share the value at commit time: a deviation of at most group - 1 schedule
+        steps from the reference's per-message read, per_sampler.py:34-35)."""
         with self.lock:
             if self.shard is None:
                 return                                        # nothing stored yet: the reference updates an empty tree

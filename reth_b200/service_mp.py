@@ -93,6 +93,7 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
     seen = {}                    # client id -> [last append message, last update frame] taken in
     segments = {}                # shared-memory ingest rings of same-host clients: name -> _ShmSegment
     pending = []                 # (cuda event, segment, seq): H2D copies out of a ring still in flight
+    dropped = {"append": 0, "update": 0, "late": 0}   # malformed messages dropped / requests that went ahead of late writes
     ready_evt.set()
 
     def append_from_ring(head, weights):
@@ -157,24 +158,33 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
                 frame = app.recv(zmq.NOBLOCK, copy=False)
             except zmq.Again:
                 break
-            kind, payload, weights, src = pack.open_append(frame.buffer)
-            if kind == "steps":
-                head, frames, others = payload
-                reset = head.get("reset")
-                eng.append_steps((src[0] if src else "", head[pack.KEY_STEPS]), frames, others, weights,
-                                 None if reset is None else np.asarray(reset))
-            elif kind == "shm":
-                try:
-                    append_from_ring(payload, weights)
-                except FileNotFoundError:              # the producer vanished with its ring: the rows are lost
-                    print(f"reth_b200 server: ingest ring {payload[pack.KEY_SHM]} is gone, message dropped",
-                          file=sys.stderr, flush=True)
-            else:
-                eng.append(payload, weights)
+            src = None
+            try:
+                src = take_append(frame)
+            except Exception as e:                     # one bad message from one actor must not stop the server
+                dropped["append"] += 1
+                print(f"reth_b200 server: append message dropped ({type(e).__name__}: {e})", file=sys.stderr, flush=True)
             if src:
                 seen.setdefault(src[0], [0, 0])[0] = int(src[1])
             retire_ring_copies()
         retire_ring_copies()
+
+    def take_append(frame):
+        kind, payload, weights, src = pack.open_append(frame.buffer)
+        if kind == "steps":
+            head, frames, others = payload
+            reset = head.get("reset")
+            eng.append_steps((src[0] if src else "", head[pack.KEY_STEPS]), frames, others, weights,
+                             None if reset is None else np.asarray(reset))
+        elif kind == "shm":
+            try:
+                append_from_ring(payload, weights)
+            except FileNotFoundError:              # the producer vanished with its ring: the rows are lost
+                print(f"reth_b200 server: ingest ring {payload[pack.KEY_SHM]} is gone, message dropped",
+                      file=sys.stderr, flush=True)
+        else:
+            eng.append(payload, weights)
+        return src
 
     def drain_updates():
         while True:
@@ -182,7 +192,11 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
                 frame = upd.recv(zmq.NOBLOCK, copy=False)
             except zmq.Again:
                 break
-            apply_updates(frame.buffer)
+            try:
+                apply_updates(frame.buffer)
+            except Exception as e:
+                dropped["update"] += 1
+                print(f"reth_b200 server: update message dropped ({type(e).__name__}: {e})", file=sys.stderr, flush=True)
 
     def await_writes(after, timeout=2.0):
         """A loader's request names the appends / write-backs its own process sent before it (they
@@ -197,6 +211,10 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
             poller.poll(1)
             drain_appends()
             drain_updates()
+        if behind():                                   # a write named by the request never arrived (dropped / lost)
+            dropped["late"] += 1
+            print(f"reth_b200 server: a loader request went ahead without writes sent before it ({timeout:.1f} s "
+                  "wait): ordering against those writes is not guaranteed", file=sys.stderr, flush=True)
 
     def handle_loader(ident, req):
         op = req.get("op")
@@ -246,7 +264,7 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
             reply(ident, {"ok": True, "op": "close"})
         elif op == "drain":
             eng.drain()
-            reply(ident, {"ok": True, "op": "drain", "cnt": eng.cnt})
+            reply(ident, {"ok": True, "op": "drain", "cnt": eng.cnt, "dropped": dropped})
         else:
             reply(ident, {"ok": False, "op": op, "error": f"unknown op {op!r}"})
 

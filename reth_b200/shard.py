@@ -53,6 +53,27 @@ def _ptr_loc(x):
     return a.ctypes.data, HOST, a.dtype, a.size, a
 
 
+def _record_streams(keep, stream_handle, device):
+    """Device tensors handed to a call that runs on a raw (non-torch) stream: register that stream with torch's
+    caching allocator, so the memory is not reused while the library's kernels still read it."""
+    if not stream_handle:
+        return
+    ext = None
+    stack = [keep]
+    while stack:
+        x = stack.pop()
+        if isinstance(x, (list, tuple)):
+            stack.extend(x)
+        elif x is not None and _is_torch(x) and x.is_cuda:
+            if ext is None:
+                import torch
+                cur = torch.cuda.current_stream(device)
+                if int(cur.cuda_stream) == int(stream_handle):
+                    return
+                ext = torch.cuda.ExternalStream(int(stream_handle), device=device)
+            x.record_stream(ext)
+
+
 def _stream_handle(stream, device):
     if stream is None:
         import sys
@@ -323,7 +344,28 @@ class ReplayShard:
         self._ck(self._lib.reth_replay_append(self._h, ptrs, cloc, p, pdt, ploc, n, float(alpha),
                                               int(bool(transform)), C.byref(first), self._s(stream)))
         self._keep = (keep, pkeep)
+        _record_streams(self._keep, _stream_handle(stream, self.device), self.device)
         return first.value
+
+    def nstep_open(self, n_streams, step, gamma, r_col=2, s1_col=3, done_col=4, max_rows=4096):
+        """n-step assembly at append time (reth_replay_nstep_open): replaces NStepAdder on the actor."""
+        self._ck(self._lib.reth_replay_nstep_open(self._h, int(n_streams), int(step), float(gamma), int(r_col),
+                                                  int(s1_col), int(done_col), int(max_rows)))
+
+    def nstep_reset(self, stream_id=-1):
+        self._ck(self._lib.reth_replay_nstep_reset(self._h, int(stream_id)))
+
+    def append_nstep(self, stream_id, cols, prio=None, alpha=0.6, transform=True, stream=None):
+        """Raw 1-step rows of one environment stream -> finished n-step transitions in the ring.
+        prio[p] belongs to the row that push p sends out of the adder.  -> (first slot, rows stored)."""
+        n = len(prio) if prio is not None else len(cols[0])
+        ptrs, cloc, keep = self._cols(cols, n)
+        p, pdt, ploc, pkeep = self._prio(prio, n)
+        first, emitted = C.c_int64(-1), C.c_int64(0)
+        self._ck(self._lib.reth_replay_append_nstep(self._h, int(stream_id), ptrs, cloc, p, pdt, ploc, n, float(alpha),
+                                                    int(bool(transform)), C.byref(first), C.byref(emitted), self._s(stream)))
+        self._keep = (keep, pkeep)
+        return first.value, emitted.value
 
     def append_frames(self, frames, stream=None):
         """n frames -> the frame ring; returns the first frame slot (slots are first, first+1, ... mod
@@ -354,6 +396,7 @@ class ReplayShard:
         self._ck(self._lib.reth_replay_append_at(self._h, sp, sloc, ptrs, cloc, p, pdt, ploc, n,
                                                  float(alpha), int(bool(transform)), self._s(stream)))
         self._keep = (skeep, keep, pkeep)
+        _record_streams(self._keep, _stream_handle(stream, self.device), self.device)
 
     def update(self, indices, prio, alpha=0.6, transform=True, stream=None):
         """Client.update_priorities -> PERSampler.update."""
@@ -370,6 +413,7 @@ class ReplayShard:
                                               p, pdt, ploc, n, float(alpha), int(bool(transform)),
                                               self._s(stream)))
         self._keep = (ikeep, pkeep)
+        _record_streams(self._keep, _stream_handle(stream, self.device), self.device)
 
     def update_slot(self, slot, prio, alpha=0.6, transform=True, stream=None):
         p, pdt, ploc, pkeep = self._prio(prio, self.slot_batch(slot))

@@ -16,7 +16,7 @@ dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 cap = int(os.environ.get("CAP", 1 << 18)); iters = int(os.environ.get("ITERS", 200))
 CASES = [tuple(int(x) for x in c.split(":")) for c in os.environ.get("CASES", "4096:1,4096:8").split(",")]
 for GB, G in CASES:
-    sh = ReplayShard(cap, ATARI, max_batch=GB, ring_depth=max(4, 2 * G), device=local)
+    sh = ReplayShard(cap, ATARI, max_batch=GB, ring_depth=max(4, int(os.environ.get('DEPTH', 2)) * G), device=local)
     g = torch.Generator(device="cuda").manual_seed(rank)
     for st in range(0, cap, 1 << 14):
         n = min(1 << 14, cap - st)

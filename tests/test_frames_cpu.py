@@ -1,5 +1,5 @@
-"""Host logic of the frame-de-duplicated layout: NStepAdder against a tape recorded from the
-reference's own class (tests/golden/make_nstep_golden.py), FrameRefWriter's stacking rule against
+"""Host logic of the frame-de-duplicated layout and the n-step oracle: the closed form of NStepAdder against
+tapes recorded from the reference's own class (tests/golden/make_nstep_golden.py), FrameRefWriter's stacking rule against
 FrameStack's (reth/reth/env/util.py:179-209) with a stand-in shard."""
 import os
 from collections import deque
@@ -7,25 +7,34 @@ from collections import deque
 import numpy as np
 import pytest
 
-from reth_b200.frames import FrameRefWriter, NStepAdder
+from oracle import per_oracle as po
+from reth_b200.frames import FrameRefWriter
 
 GOLD = np.load(os.path.join(os.path.dirname(__file__), "golden", "nstep_adder.npz"))
+TAPES = ["g99_s3", "g9_s5", "g1_s1", "f32_g99_s3", "f32_g97_s4"]
 
 
-@pytest.mark.parametrize("name", ["g99_s3", "g9_s5", "g1_s1"])
-def test_nstep_adder_matches_reference_tape(name):
+def tape_columns(name):
+    """Raw rows of a recorded tape as columns [s0, a, r, s1, done] and what the reference emitted per push."""
     gamma, step, n = GOLD[name + "_cfg"]
-    adder = NStepAdder(float(gamma), int(step))
-    cols, r, want = GOLD[name + "_in"], GOLD[name + "_r"], GOLD[name + "_out"]
-    for i in range(int(n)):
-        s0, a, s1, done = (int(x) for x in cols[i])
-        res = adder.push(s0, a, float(r[i]), s1, bool(done))
-        if want[i][1] < 0:
-            assert res is None
-        else:
-            assert res is not None
-            assert [res[0], res[1], res[3], int(res[4])] == [int(want[i][1]), int(want[i][2]), int(want[i][4]), int(want[i][5])]
-            assert res[2] == want[i][3]                      # same float operations in the same order
+    cin, r, want = GOLD[name + "_in"], GOLD[name + "_r"], GOLD[name + "_out"]
+    done = cin[:, 3].astype(np.float32) if r.dtype == np.float32 else cin[:, 3].astype(np.int64)
+    return float(gamma), int(step), int(n), [cin[:, 0].copy(), cin[:, 1].copy(), r.copy(), cin[:, 2].copy(), done], want
+
+
+@pytest.mark.parametrize("name", TAPES)
+def test_nstep_closed_form_matches_reference_tape(name):
+    """oracle.nstep_fold (the closed form the device kernel implements) against tapes recorded from the
+    reference's own NStepAdder: float64 rewards, and float32 0-d arrays as worker.py feeds it."""
+    gamma, step, n, cols, want = tape_columns(name)
+    out, push = po.nstep_fold(cols, step, gamma)
+    assert (want[:step, 1] < 0).all() and (want[step:, 1] >= 0).all()       # push i emits row i - step
+    w = want[step:]
+    assert np.array_equal(push, w[:, 0].astype(np.int64))
+    assert np.array_equal(out[0], w[:, 1].astype(np.int64)) and np.array_equal(out[1], w[:, 2].astype(np.int64))
+    assert np.array_equal(out[3], w[:, 4].astype(np.int64))
+    assert np.array_equal(out[4].astype(np.int64), w[:, 5].astype(np.int64))
+    assert np.array_equal(out[2].astype(np.float64), w[:, 3])               # same float operations in the same order
 
 
 class _FakeShard:

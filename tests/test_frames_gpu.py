@@ -102,6 +102,38 @@ def test_frame_ring_wraps_and_group_gather(mods):
     sh.close()
 
 
+def test_frame_ring_wraps_before_row_ring_is_reported(mods):
+    """the frame ring advances one frame per step plus one per reset, so with frame_capacity close to
+    capacity old but still sampleable transitions can outlive their frames.  The gather must say so (RETH_ERR_STATE)
+    instead of rebuilding stacks from overwritten slots; a big enough ring over the same steps stays clean."""
+    ReplayShard, FrameRefWriter = mods
+    from reth_b200 import ReplayError
+    cap, B, n = 512, 64, 500
+    for fcap, stale in ((300, True), (600, False)):
+        rng = np.random.default_rng(21)
+        sh = ReplayShard(cap, STRUCT, max_batch=B, ring_depth=2, frames={"shape": FRAME, "capacity": fcap, "columns": [0, 3]})
+        full = _episodes(rng, FrameRefWriter(sh, k=K, frame_cols=(0, 3)), n, p_done=0.0)
+        assert sh.size == n                                           # the ROW ring has not wrapped: all 500 rows are alive
+        # stratified draw over all rows: the oldest ones refer to frames 500 + 3 - 300 steps behind the frame cursor
+        sh.sample(B, uniforms=rng.random(B), slot=0)
+        sh.gather(0)
+        if stale:
+            with pytest.raises(ReplayError) as ei:
+                sh.slot_read(0, with_rows=True)
+            assert ei.value.code == -5 and "overwritten" in str(ei.value)
+            # nearly all priority on the newest rows: the same shard keeps serving the rows whose frames are alive
+            sh.update(np.arange(n - 150), np.full(n - 150, 1e-12), transform=False)
+            sh.sample(B, uniforms=rng.random(B), slot=1)
+            sh.gather(1)
+            data, idx, _ = sh.slot_read(1, with_rows=True)
+            assert idx.min() >= n - 150
+        else:
+            data, idx, _ = sh.slot_read(0, with_rows=True)
+        assert np.array_equal(data[0], np.stack([full[i][0] for i in idx]))
+        assert np.array_equal(data[3], np.stack([full[i][3] for i in idx]))
+        sh.close()
+
+
 def test_frame_column_errors(mods):
     ReplayShard, _ = mods
     with pytest.raises(ValueError):
