@@ -334,7 +334,7 @@ def timed_loop(torch, dist, shard, steps, warmup, iters, batch, prio, group, wor
     return ms, launches, shard.gather_time()
 
 
-def e2e_loop(torch, dist, service, addr, iters_total, warm, batch, world, group, ahead):
+def e2e_loop(torch, dist, service, addr, iters_total, warm, batch, world, group, ahead, reference_call=None):
     """Public reth_buffer-style API with HOST buffers, per learner iteration:
         data, indices, weights = loader.sample()       # TorchCudaLoader: batch lent as CUDA tensors,
                                                        # indices = host int64 array (D2H inside)
@@ -344,7 +344,10 @@ def e2e_loop(torch, dist, service, addr, iters_total, warm, batch, world, group,
     rng = np.random.default_rng(3)
     newp = np.abs(rng.standard_normal((64, batch))).astype(np.float32)
     client = service.Client(addr)
-    loader = service.TorchCudaLoader(addr, buffer_size=(ahead + 1) * group, prefetch=group, ahead=ahead)
+    if reference_call:      # exactly as the reference's Ape-X trainer builds it (test/apex-dqn/trainer.py:22-24)
+        loader = service.TorchCudaLoader(addr, **reference_call)
+    else:
+        loader = service.TorchCudaLoader(addr, buffer_size=(ahead + 1) * group, prefetch=group, ahead=ahead)
     eng = service._ENGINES[addr]
 
     def it(i):
@@ -370,7 +373,10 @@ def e2e_loop(torch, dist, service, addr, iters_total, warm, batch, world, group,
         t = torch.tensor([ms], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
+    geom = (loader.prefetch, loader.ahead)
     loader.close()
+    if reference_call:
+        return world * iters_total * batch / (ms / 1e3), geom
     return world * iters_total * batch / (ms / 1e3), batch * (8 + 4), batch * (8 + 8)
 
 
@@ -474,6 +480,8 @@ def run_ours(args):
     e2e_iters -= e2e_iters % G
     e2e, h2d, d2h = e2e_loop(torch, dist, service, addr, e2e_iters, 64, B, world, G, args.ahead)
     e2e_strict, _, _ = e2e_loop(torch, dist, service, addr, min(4000, e2e_iters), 16, B, world, 1, 0)
+    ref_call = {"buffer_size": 4, "num_procs": 2}
+    e2e_ref, ref_geom = e2e_loop(torch, dist, service, addr, min(8192, e2e_iters), 64, B, world, 0, 0, reference_call=ref_call)
     app_rows, app_gbs = append_rate(torch, shard) if rank == 0 or world == 1 else (None, None)
     apph_rows, apph_gbs = append_rate_host(torch, shard) if rank == 0 and world == 1 else (None, None)
 
@@ -498,6 +506,11 @@ def run_ours(args):
         "clocks": clk, "gpu_launches": int(launches),
         "e2e": {"value": e2e, "unit": "transitions/s", "h2d_bytes_per_step": h2d * iters, "d2h_bytes_per_step": d2h * iters,
                 "strict_alternation": e2e_strict,
+                "e2e_ref_geometry": {"value": e2e_ref, "call": "TorchCudaLoader(addr, buffer_size=4, num_procs=2)",
+                                     "prefetch_group": ref_geom[0], "groups_ahead": ref_geom[1],
+                                     "batches_in_flight": ref_geom[0] * (ref_geom[1] + 1),
+                                     "note": "the loader exactly as test/apex-dqn/trainer.py:22-24 builds it: the reference keeps "
+                                             "buffer_size + num_procs + 2 = 8 batches between draw and consumption"},
                 "loader": {"prefetch_group": G, "groups_ahead": args.ahead, "buffer_size": (args.ahead + 1) * G},
                 "note": "reth_buffer-style public API per iteration: TorchCudaLoader.sample() (batch lent as CUDA "
                         "tensors; indices + weights D2H into pinned host rings, indices returned as a host int64 "

@@ -216,7 +216,8 @@ def run(torch, dist, shard, world, rank, batch, alpha, beta, mode_r_value, log, 
     cases = []
     for gb, G, it in ((GB, 8, iters), (GB, 1, iters), (4 * GB, 8, max(50, iters // 4)), (4 * GB, 1, max(50, iters // 4))):
         cases.append(timed_case(torch, dist, shard, gb, G, it, alpha, beta, seed=300 + rank))
-        log(f"[mode_g] global batch {gb} group {G}: {cases[-1]['us_per_batch']:.1f} us / batch")
+        if rank == 0:
+            log(f"[mode_g] global batch {gb} group {G}: {cases[-1]['us_per_batch']:.1f} us / batch")
     head = cases[0]
     return {"value": head["value"], "unit": "transitions/s", "us_per_batch": head["us_per_batch"],
             "global_batch": head["global_batch"], "prefetch_group": head["prefetch_group"], "exchange": "board",

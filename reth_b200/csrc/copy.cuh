@@ -173,6 +173,10 @@ struct RowArgs {
 // so surplus CTAs leave after one comparison -- with the column-major numbering every skipped item costs its
 // CTA a column search and a 64-bit division in all eight warps, which at 8 shards is more issue time than
 // the copy itself.
+// (Tried and rejected, profiles/r02_lean_gather.jsonl: a <= 32-register build capped at 6 CTAs per SM through a
+// dynamic shared-memory request, to keep 16 K registers of every SM free for the tree kernels.  The request alone
+// costs the gather a quarter of its rate -- 41 vs 54 M rows/s gather-only -- and uncapped the 32-register build
+// is 5 % slower than this one.)
 template <bool kScatter, bool kWiden = false, bool kDense = false>
 __global__ void __launch_bounds__(kCopyThreads, kWiden ? 4 : 6) row_move_kernel(const RowArgs a)
 {

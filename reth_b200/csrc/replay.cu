@@ -139,6 +139,7 @@ struct reth_replay {
     BoardEntry **board_ptrs_dev = nullptr;   // peer_board[] on the device (the repair kernel publishes through it)
     unsigned long long wait_seq = 0;         // set around a draw: take the roots of this exchange from the board
     int modeg_fused = 1;                     // Mode G loop: publish folded into the repair kernel, wait into the draw
+    bool quota_first = false;                // set by the Mode G loop: the share kernel runs before single draws too
     int64_t *quota = nullptr;     // Mode G prefetch group: {first, count, offset, 0} per draw of the running launch
     int64_t *slot_quota = nullptr; // the same per batch slot (kept for the consumer of the packed batch)
     bool pdl = false;             // tree-chain launches carry the programmatic-dependent-launch attribute (set by step_loop)
@@ -304,27 +305,30 @@ int alloc_batch_ring(reth_replay *h)
 namespace {
 using UpdateKernel = void (*)(const UpdateArgs);
 // the instantiation of the repair kernel for this shard: 5 tile levels cover capacity <= 2^25
-UpdateKernel update_kernel_of(const reth_replay *h, bool lean)
+UpdateKernel update_kernel_of(const reth_replay *h, bool lean, bool rounds = false)
 {
     const bool small = h->geom.n_tile_levels <= 5;
-    if (lean) return small ? per_update_kernel<5, 2> : per_update_kernel<kMaxTileLevels, 2>;
-    return small ? per_update_kernel<5, 1> : per_update_kernel<kMaxTileLevels, 1>;
+    if (rounds) return small ? per_update_kernel<5, 2, true> : per_update_kernel<kMaxTileLevels, 2, true>;
+    if (lean) return small ? per_update_kernel<5, 2, false> : per_update_kernel<kMaxTileLevels, 2, false>;
+    return small ? per_update_kernel<5, 1, false> : per_update_kernel<kMaxTileLevels, 1, false>;
 }
 
 // Shape of one repair launch.  The kernel is latency-bound (3 cluster barriers, 5 dependent stages) and a
 // frame gather normally runs beside it, so what it costs the loop is the SM resources it HOLDS while it
 // waits (measured, profiles/r02_footprint_sweep.jsonl: prefetch-group loop 51.2 -> 52.8 M transitions/s).
-//   n <= 1024 (strict alternation, small batches: the repair is on the critical path): 16 CTAs, full
-//     register budget -- fastest single launch;
+//   n <= 2048 (strict alternation, prefetch groups of <= 4 batches: the repair is on the critical path, the
+//     gather of so few rows is shorter than the tree chain): 16 CTAs, full register budget -- fastest launch;
 //   n <= 4096 (one prefetch group): 8 CTAs x 512 threads of the lean build (<= 64 registers: half an SM's
 //     register file per CTA, so three gather CTAs stay resident on each of only 8 SMs);
 //   larger (appends): lean, 16 CTAs, 8192 entries per launch.
+int env_int(const char *name, int dflt);
 struct UpdateShape { UpdateKernel fn; int cluster; };
 UpdateShape update_shape_of(const reth_replay *h, int64_t n)
 {
+    static const int fast_n = env_int("RETH_UPDATE_FAST_N", 2048);
     int cluster = h->update_cluster;
-    if (!h->update_cluster_fixed && n > 1024 && n <= (int64_t)8 * h->update_threads && cluster > 8) cluster = 8;
-    const bool lean = h->update_lean >= 0 ? h->update_lean != 0 : n > 1024;
+    if (!h->update_cluster_fixed && n > fast_n && n <= (int64_t)8 * h->update_threads && cluster > 8) cluster = 8;
+    const bool lean = h->update_lean >= 0 ? h->update_lean != 0 : n > fast_n;
     return {update_kernel_of(h, lean), cluster};
 }
 }  // namespace
@@ -472,6 +476,7 @@ RETH_EXPORT int reth_replay_create(const reth_replay_config *cfg, reth_replay_t 
     if (want_cluster > 16) want_cluster = 16;
     for (int lean = 0; lean < 2; ++lean)
         CKC(cudaFuncSetAttribute(update_kernel_of(h, lean != 0), cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    CKC(cudaFuncSetAttribute(update_kernel_of(h, true, true), cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
     if (want_cluster <= 0) {
         // default: up to a 16-CTA cluster (non-portable size) when the device can host one
         cudaLaunchConfig_t lc = {};
@@ -526,9 +531,12 @@ int to_device(reth_replay *h, const void *p, int loc, size_t bytes, void *stagin
     return RETH_OK;
 }
 
-// Tree update of n <= max_n entries: one launch of the cluster kernel per (cluster size x 512)
-// entries, in batch order on one stream, so last-writer-wins holds across the launches too.
-int launch_update(reth_replay *h, UpdateArgs &a, cudaStream_t s)
+// Tree update of n entries: one launch of the cluster kernel per (cluster size x block size) entries, in batch
+// order on one stream, so last-writer-wins holds across the launches too.
+// n_expected > 0 (Mode G: only the first *a.n_dev of the n entries are valid, about n_expected of them): ordinary
+// launches cover 1.25 x n_expected + 64 entries and ONE catch-all launch (the build with rounds) takes whatever lies
+// beyond -- normally nothing.  A write-back padded to 8 x the share then costs 2 launches on the chain, not 8..16.
+int launch_update(reth_replay *h, UpdateArgs &a, cudaStream_t s, int64_t n_expected = 0)
 {
     if (a.n <= 0) return RETH_OK;
     a.g = h->geom; a.desc = h->desc; a.agg = h->agg; a.stamp = h->stamp; a.mask = h->mask;
@@ -536,16 +544,28 @@ int launch_update(reth_replay *h, UpdateArgs &a, cudaStream_t s)
     const int64_t n = a.n;
     const unsigned long long pub_seq = a.pub_seq;
     if (pub_seq) { a.pub_boards = h->board_ptrs_dev; a.pub_shards = h->board_shards; a.pub_shard = h->board_shard; }
-    const UpdateShape shape = update_shape_of(h, n);
-    const UpdateKernel uk = shape.fn;
+    const bool spec = a.n_dev != nullptr && n_expected > 0;
+    const UpdateShape shape = update_shape_of(h, spec ? n_expected : n);
     const int64_t per = (int64_t)shape.cluster * h->update_threads;
+    int64_t covered = n;                 // entries [0, covered) go through ordinary launches
+    if (spec) {
+        covered = (int64_t)(1.25 * (double)n_expected) + 64;
+        covered = (covered + per - 1) / per * per;
+        if (covered > n) covered = n;
+    }
     const uint8_t *idx0 = (const uint8_t *)a.idx, *prio0 = (const uint8_t *)a.prio;
     const int64_t iota0 = a.iota_base;
     const size_t is = a.idx_kind == 0 ? 8 : 4, ps = a.prio_kind == 0 ? 4 : 8;
-    for (int64_t off = 0; off < n; off += per) {
-        a.n = n - off < per ? n - off : per;
+    for (int64_t off = 0; off < n;) {
+        const bool rest = off >= covered;                    // the catch-all launch: everything that is left
+        const int64_t m = rest ? n - off : (covered - off < per ? covered - off : per);
+        a.n = m;
         a.n_off = off;
-        a.pub_seq = (off + per >= n) ? pub_seq : 0ull;       // the launch that completes the write-back publishes
+        // the launch that completes the write-back publishes the new root: with a catch-all, the last ordinary
+        // launch when the share ends inside it (the normal case: the publish does not wait for an empty launch),
+        // else the catch-all
+        a.pub_seq = (off + m >= n || (spec && off + m >= covered)) ? pub_seq : 0ull;
+        a.pub_when = !spec || covered >= n ? 0 : (rest ? 2 : 1);
         a.stamp_base = (uint32_t)off;
         if (a.idx_kind != 2) a.idx = idx0 + off * is;
         if (a.prio_kind != 2) a.prio = prio0 + off * ps;
@@ -566,8 +586,9 @@ int launch_update(reth_replay *h, UpdateArgs &a, cudaStream_t s)
         at[1].val.programmaticStreamSerializationAllowed = 1;
         cfg.attrs = at;
         cfg.numAttrs = h->pdl ? 2 : 1;
-        CK(h, cudaLaunchKernelEx(&cfg, uk, (const UpdateArgs)a));
+        CK(h, cudaLaunchKernelEx(&cfg, rest ? update_kernel_of(h, true, true) : shape.fn, (const UpdateArgs)a));
         h->st.kernel_launches++;
+        off += m;
     }
     a.n = n; a.idx = idx0; a.prio = prio0; a.iota_base = iota0; a.pub_seq = pub_seq;
     return RETH_OK;
@@ -1007,7 +1028,7 @@ RETH_EXPORT int reth_replay_update_slot(reth_replay_t *h, int slot, const void *
     a.alpha = alpha; a.transform = transform; a.dedupe = 2;   // own stratified draw: duplicates are adjacent
     int rc = set_prio(h, a, prio, prio_dtype, prio_loc, 0, b.batch, S(stream));
     if (rc) return rc;
-    rc = launch_update(h, a, S(stream));
+    rc = launch_update(h, a, S(stream), b.partial ? b.batch / b.shards + 1 : 0);
     if (rc) return rc;
     h->st.updated_rows += b.batch;
     return RETH_OK;
@@ -1015,6 +1036,12 @@ RETH_EXPORT int reth_replay_update_slot(reth_replay_t *h, int slot, const void *
 
 // ------------------------------------------------------------ sample / gather --
 namespace {
+
+int env_int(const char *name, int dflt)
+{
+    const char *e = getenv(name);
+    return e ? atoi(e) : dflt;
+}
 
 int gather_units_target()
 {
@@ -1135,11 +1162,6 @@ int launch_frame_gather(reth_replay *h, uint8_t *const *batch_cols, const int64_
     return RETH_OK;
 }
 
-int env_int(const char *name, int dflt)
-{
-    const char *e = getenv(name);
-    return e ? atoi(e) : dflt;
-}
 
 // TMA bulk-copy gather (row_gather_bulk_kernel): persistent, one CTA per SM.
 int launch_gather_bulk(reth_replay *h, uint8_t *const *batch_cols, const int64_t *idx, int batch,
@@ -1206,8 +1228,10 @@ int do_sample(reth_replay *h, int batch, const double *uniforms, int uniforms_lo
         a.wait_board = h->board; a.wait_seq = h->wait_seq; a.roots_out = h->all_roots; a.err_rw = h->err;
         a.wait_timeout_ns = (unsigned long long)env_int("RETH_BOARD_TIMEOUT_MS", 2000) * 1000000ull;
     }
-    if (n_shards > 1 && groups > 1) {
-        // the shares of the `groups` draws are packed back to back from slot `slot` on
+    const bool with_quota = n_shards > 1 && (groups > 1 || h->quota_first);
+    if (with_quota) {
+        // the shares of the `groups` draws are computed first (and packed back to back from slot `slot` on): the
+        // draw kernel is then launched for about this shard's share instead of the whole global batch
         // (both buffers exist since create / the last ring resize: no allocation -- and no legacy-stream memset,
         // which would wait for every blocking stream of the process -- on the sampling path)
         global_quota_kernel<<<1, 32 * groups, 0, s>>>(a, h->quota, h->slot_quota + 4 * slot);
@@ -1216,9 +1240,18 @@ int do_sample(reth_replay *h, int batch, const double *uniforms, int uniforms_lo
         a.quota = h->quota;
     }
     const int wpb = 4;
+    int64_t warps = (int64_t)batch * groups;
+    if (with_quota) {
+        // stratified targets: the share is this shard's fraction of the global total +- 1; slack for unequal
+        // shards, beyond which the warps stride
+        int64_t wpd = (int64_t)(1.25 * (double)batch / n_shards) + 32;
+        if (wpd > batch) wpd = batch;
+        a.warps_per_draw = (int32_t)wpd;
+        warps = wpd * groups;
+    }
     if (h->pdl) {
         cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3((batch * groups + wpb - 1) / wpb);
+        cfg.gridDim = dim3((unsigned)((warps + wpb - 1) / wpb));
         cfg.blockDim = dim3(wpb * 32);
         cfg.stream = s;
         cudaLaunchAttribute at[1];
@@ -1228,7 +1261,7 @@ int do_sample(reth_replay *h, int batch, const double *uniforms, int uniforms_lo
         cfg.numAttrs = 1;
         CK(h, cudaLaunchKernelEx(&cfg, per_sample_kernel, (const SampleArgs)a));
     } else {
-        per_sample_kernel<<<(batch * groups + wpb - 1) / wpb, wpb * 32, 0, s>>>(a);
+        per_sample_kernel<<<(unsigned)((warps + wpb - 1) / wpb), wpb * 32, 0, s>>>(a);
     }
     CK(h, cudaGetLastError());
     h->st.kernel_launches++;
@@ -1356,7 +1389,8 @@ RETH_EXPORT int reth_replay_update_slots(reth_replay_t *h, int first_slot, int n
     if (group_ok(h, first_slot, n_slots)) return h->error.find("holds no") != std::string::npos ? RETH_ERR_STATE : RETH_ERR_INVALID;
     DeviceGuard guard(h->cfg.device);
     const int64_t n = (int64_t)h->slots[first_slot].batch * n_slots;
-    if (n > h->max_n) return fail(h, RETH_ERR_INVALID, "group of %lld rows exceeds %lld", (long long)n, (long long)h->max_n);
+    if (n > h->max_n && prio && prio_loc != RETH_DEVICE)       // host priorities pass through the staging buffer
+        return fail(h, RETH_ERR_INVALID, "group of %lld rows with host priorities exceeds %lld", (long long)n, (long long)h->max_n);
     UpdateArgs a = {};
     a.n = n; a.idx = h->slots[first_slot].idx; a.idx_kind = 0;
     a.alpha = alpha; a.transform = transform;
@@ -1366,7 +1400,7 @@ RETH_EXPORT int reth_replay_update_slots(reth_replay_t *h, int first_slot, int n
         a.n_dev = h->slots[first_slot].meta + 1;          // Mode G: the share count lives on the device
     int rc = set_prio(h, a, prio, prio_dtype, prio_loc, 0, n, S(stream));
     if (rc) return rc;
-    rc = launch_update(h, a, S(stream));
+    rc = launch_update(h, a, S(stream), a.n_dev ? n / h->slots[first_slot].shards + 1 : 0);
     if (rc) return rc;
     h->st.updated_rows += n;
     return RETH_OK;
@@ -2347,16 +2381,17 @@ RETH_EXPORT int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, co
         if (global) {
             // the first exchange of the call is its own kernel; after that the repair kernel of iteration k has
             // published exchange board_seq and the draw of iteration k+1 waits for it on the board itself
-            // (prefetch groups only: there the single-CTA share kernel does the waiting.  With G = 1 every warp of
-            // the draw kernel would poll the board -- a launch saved, 30.8 -> 29.1 us per step on 2 GPUs, but when
-            // several shards share ONE device those spinning CTAs keep a peer's repair cluster off the SMs until
-            // the timeout; RETH_MODEG_FUSED=2 opts in for one shard per GPU)
-            const bool fused = k > 0 && (h->modeg_fused >= 2 || (h->modeg_fused == 1 && G > 1));
+            // (the waiting is done by the single-CTA share kernel that precedes every draw of the loop: letting all
+            // warps of the draw kernel poll the board deadlocks several shards sharing one device -- the spinning
+            // CTAs keep a peer's repair cluster off the SMs -- and wins nothing on one shard per GPU)
+            const bool fused = k > 0 && h->modeg_fused;
             if (!fused) rc = launch_roots_exchange(h, 3, st);
             h->wait_seq = fused ? h->board_seq : 0ull;
+            h->quota_first = true;
             if (!rc) rc = do_sample(h, batch, nullptr, RETH_DEVICE, seed, beta, slot, h->all_roots,
                                     h->board_shards, h->board_shard, st, G);
             h->wait_seq = 0ull;
+            h->quota_first = false;
         } else if (!no_sample || h->slots[slot].batch != batch)
             rc = do_sample(h, batch, uniforms_dev ? uniforms_dev + (size_t)k * batch : nullptr, RETH_DEVICE,
                            seed, beta, slot, nullptr, 1, 0, st, G);
@@ -2395,9 +2430,9 @@ RETH_EXPORT int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, co
         a.alpha = alpha; a.transform = 1; a.dedupe = G == 1 ? 2 : 1;
         if (global) {
             a.n_dev = h->slots[slot].meta + 1;                  // this shard's share of the global batch
-            if ((h->modeg_fused >= 2 || (h->modeg_fused == 1 && G > 1)) && k + G < steps) a.pub_seq = ++h->board_seq;
+            if (h->modeg_fused && k + G < steps) a.pub_seq = ++h->board_seq;
         }
-        rc = launch_update(h, a, st);
+        rc = launch_update(h, a, st, global ? (a.n / h->board_shards > 0 ? a.n / h->board_shards : 1) : 0);
         if (rc) return rc;
         h->st.updated_rows += (int64_t)batch * G;
     }

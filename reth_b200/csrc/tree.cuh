@@ -166,6 +166,7 @@ struct SampleArgs {
     int32_t n_shards, shard;
     const int64_t *quota;      // global mode with groups > 1: int64[4*groups] = {first, count, packed offset, -} per draw
     int32_t groups;            // independent stratified draws of `batch` in one launch (>= 1)
+    int32_t warps_per_draw;    // with quota: warps the launch provides per draw (they stride over the share)
     int32_t out_stride;        // elements between the outputs of consecutive draws
     // loader pipeline: indices / weights are also written straight into pinned host memory mapped into
     // the device address space (no device->host copy operation), and the error flag is mirrored
@@ -223,73 +224,12 @@ __device__ __forceinline__ int64_t lower_bound_target(const SampleArgs &a, doubl
     return res;
 }
 
-// One warp per stratified sample (utils/sumtree.py:70-79 + :34-58), IS weight
-// fused (sampler/per_sampler.py:26).
-__global__ void __launch_bounds__(256) per_sample_kernel(const SampleArgs a)
+// _numba_find_index (utils/sumtree.py:34-58) on the tiled layout, by one warp: a coalesced 512-byte tile load,
+// five levels walked with shuffles, next tile.  The comparisons and subtractions are the reference's, in the
+// reference's order.  Returns the leaf's value.
+__device__ __forceinline__ double descend(const SampleArgs &a, double w, int lane, int64_t &idx_out)
 {
-    pdl_wait();
-    pdl_trigger();
-    const int lane = threadIdx.x & 31;
-    const int64_t W = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (W >= (int64_t)a.batch * a.groups) return;
-    if (a.err_mirror && W == 0 && lane == 0) *a.err_mirror = *a.err;   // set by earlier launches of the stream
-    const int64_t grp = W / a.batch, i = W - grp * a.batch;   // draw `grp`, stratum i
     const int64_t cap = a.g.capacity;
-
-    double total, pmin, prefix = 0.0;
-    int64_t first = 0;
-    if (a.n_shards > 1) {
-        // global CDF over shard totals in rank order (Mode G)
-        total = 0.0;
-        double mn = 0.0, mine = 0.0;
-        const bool from_board = a.wait_seq != 0ull && !a.quota;    // with a quota kernel, that one waited and snapshot
-        const BoardEntry *brd = a.wait_board + (int)(a.wait_seq & 1ull) * kMaxShards;
-        if (from_board) {
-            // every warp waits on the own board (local L2); warp 0 also leaves the snapshot for the host side
-            bool ok = true;
-            for (int s = lane; s < a.n_shards; s += 32) ok = board_wait(a.wait_board, s, a.wait_seq, a.wait_timeout_ns) && ok;
-            if (!__all_sync(0xffffffffu, ok)) { if (lane == 0) atomicOr(a.err_rw, kErrBoardTimeout); return; }
-        }
-        for (int s = 0; s < a.n_shards; ++s) {
-            double t, m;
-            if (from_board) {
-                const volatile double *vs = &brd[s].sum, *vm = &brd[s].mn;
-                t = *vs; m = *vm;
-                if (W == 0 && lane == 0) { a.roots_out[2 * s] = t; a.roots_out[2 * s + 1] = m; }
-            } else { t = a.all_roots[2 * s]; m = a.all_roots[2 * s + 1]; }
-            if (s == a.shard) { prefix = total; mine = t; }
-            total += t;
-            if (t != 0.0 && m != 0.0) mn = (mn == 0.0 || m < mn) ? m : mn;
-        }
-        pmin = (mn != 0.0) ? mn : 1.0;
-        const double seg = total / (double)a.batch;
-        const bool last = a.shard == a.n_shards - 1;
-        if (i == 0 && !a.quota) {              // one warp reports the share {first, count}
-            const int64_t f = lower_bound_target(a, seg, prefix, lane);
-            int64_t e = last ? (int64_t)a.batch : lower_bound_target(a, seg, prefix + mine, lane);
-            if (e < f) e = f;
-            if (lane == 0) { a.meta[0] = f; a.meta[1] = e - f; }
-        }
-        // targets are monotone in i, so membership in [first, end) follows from the warp's own target:
-        // i >= first  <=>  target_i >= prefix,   i < end  <=>  not (target_i >= prefix + mine).
-        // Warps outside the share (all but 1/n_shards of a global batch) leave after one draw.
-        const double tgt = ((double)i + draw_u(a, W)) * seg;
-        if ((prefix > 0.0 && !(tgt >= prefix)) || (!last && tgt >= prefix + mine)) return;
-        // several draws in one launch: the shares are packed back to back, global_quota_kernel has
-        // published where each starts
-        if (a.quota) first = a.quota[4 * grp] - a.quota[4 * grp + 2];
-        else first = lower_bound_target(a, seg, prefix, lane);
-    } else {
-        const double2 root = ldcg2(&a.agg[1]);
-        total = root.x;
-        if (a.min_mode == 0) pmin = (root.x != 0.0) ? root.y : 1.0;   // utils/sumtree.py:109-110
-        else pmin = (root.y != 0.0) ? root.y : 1.0;                   // reth/buffer/sumtree.py:112-113
-        if (i == 0 && lane == 0) { a.meta[2 * grp] = 0; a.meta[2 * grp + 1] = a.batch; }
-    }
-    const double segment = total / (double)a.batch;                  // sumtree.py:73
-    double w = ((double)i + draw_u(a, W)) * segment;                 // sumtree.py:74
-    w -= prefix;                                                      // 0.0 for a single shard
-
     int64_t idx = 0, tile = 0, tile_rel = 0;
     int T = 0;
     double val = 0.0;
@@ -317,8 +257,110 @@ __global__ void __launch_bounds__(256) per_sample_kernel(const SampleArgs a)
         ++T;
         tile = tile_base(T) + tile_rel;
     }
+    idx_out = idx;
+    return val;
+}
+
+// One warp per stratified sample (utils/sumtree.py:70-79 + :34-58), IS weight
+// fused (sampler/per_sampler.py:26).
+__global__ void __launch_bounds__(256) per_sample_kernel(const SampleArgs a)
+{
+    pdl_wait();
+    pdl_trigger();
+    const int lane = threadIdx.x & 31;
+    const int64_t W = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (a.err_mirror && W == 0 && lane == 0) *a.err_mirror = *a.err;   // set by earlier launches of the stream
+
+    if (a.quota) {
+        // Mode G with the shares already known (global_quota_kernel ran just before: {first, count, packed
+        // offset} per draw): the launch covers warps_per_draw warps per draw -- about this shard's share, not
+        // the global batch -- and warp j of draw g takes positions first_g + j, + warps_per_draw, ... of it.
+        const int64_t grp = W / a.warps_per_draw;
+        if (grp >= a.groups) return;
+        const int64_t first = a.quota[4 * grp], count = a.quota[4 * grp + 1], off = a.quota[4 * grp + 2];
+        double total = 0.0, prefix = 0.0, mn = 0.0;
+        for (int s = 0; s < a.n_shards; ++s) {          // global CDF over shard totals in rank order
+            const double t = a.all_roots[2 * s], m = a.all_roots[2 * s + 1];
+            if (s == a.shard) prefix = total;
+            total += t;
+            if (t != 0.0 && m != 0.0) mn = (mn == 0.0 || m < mn) ? m : mn;
+        }
+        const double pmin = (mn != 0.0) ? mn : 1.0;
+        const double segment = total / (double)a.batch;
+        for (int64_t j = W - grp * a.warps_per_draw; j < count; j += a.warps_per_draw) {
+            const int64_t i = first + j;
+            double w = ((double)i + draw_u(a, grp * a.batch + i)) * segment;
+            w -= prefix;
+            int64_t idx;
+            const double val = descend(a, w, lane, idx);
+            if (lane == 0) {
+                const int64_t o = off + j;
+                const double wt = pow(val / pmin, -a.beta);
+                a.idx_out[o] = idx;
+                a.prio_out[o] = val;
+                a.w_out[o] = wt;
+                if (a.idx_mirror) { a.idx_mirror[o] = idx; a.w_mirror[o] = wt; }
+            }
+        }
+        return;
+    }
+
+    if (W >= (int64_t)a.batch * a.groups) return;
+    const int64_t grp = W / a.batch, i = W - grp * a.batch;   // draw `grp`, stratum i
+    double total, pmin, prefix = 0.0;
+    int64_t first = 0;
+    if (a.n_shards > 1) {
+        // global CDF over shard totals in rank order (Mode G), one draw, share not known yet
+        total = 0.0;
+        double mn = 0.0, mine = 0.0;
+        const bool from_board = a.wait_seq != 0ull;
+        const BoardEntry *brd = a.wait_board + (int)(a.wait_seq & 1ull) * kMaxShards;
+        if (from_board) {
+            // every warp waits on the own board (local L2); warp 0 also leaves the snapshot for the host side
+            bool ok = true;
+            for (int s = lane; s < a.n_shards; s += 32) ok = board_wait(a.wait_board, s, a.wait_seq, a.wait_timeout_ns) && ok;
+            if (!__all_sync(0xffffffffu, ok)) { if (lane == 0) atomicOr(a.err_rw, kErrBoardTimeout); return; }
+        }
+        for (int s = 0; s < a.n_shards; ++s) {
+            double t, m;
+            if (from_board) {
+                const volatile double *vs = &brd[s].sum, *vm = &brd[s].mn;
+                t = *vs; m = *vm;
+                if (W == 0 && lane == 0) { a.roots_out[2 * s] = t; a.roots_out[2 * s + 1] = m; }
+            } else { t = a.all_roots[2 * s]; m = a.all_roots[2 * s + 1]; }
+            if (s == a.shard) { prefix = total; mine = t; }
+            total += t;
+            if (t != 0.0 && m != 0.0) mn = (mn == 0.0 || m < mn) ? m : mn;
+        }
+        pmin = (mn != 0.0) ? mn : 1.0;
+        const double seg = total / (double)a.batch;
+        const bool last = a.shard == a.n_shards - 1;
+        if (i == 0) {                          // one warp reports the share {first, count}
+            const int64_t f = lower_bound_target(a, seg, prefix, lane);
+            int64_t e = last ? (int64_t)a.batch : lower_bound_target(a, seg, prefix + mine, lane);
+            if (e < f) e = f;
+            if (lane == 0) { a.meta[0] = f; a.meta[1] = e - f; }
+        }
+        // targets are monotone in i, so membership in [first, end) follows from the warp's own target:
+        // i >= first  <=>  target_i >= prefix,   i < end  <=>  not (target_i >= prefix + mine).
+        // Warps outside the share (all but 1/n_shards of a global batch) leave after one draw.
+        const double tgt = ((double)i + draw_u(a, W)) * seg;
+        if ((prefix > 0.0 && !(tgt >= prefix)) || (!last && tgt >= prefix + mine)) return;
+        first = lower_bound_target(a, seg, prefix, lane);
+    } else {
+        const double2 root = ldcg2(&a.agg[1]);
+        total = root.x;
+        if (a.min_mode == 0) pmin = (root.x != 0.0) ? root.y : 1.0;   // utils/sumtree.py:109-110
+        else pmin = (root.y != 0.0) ? root.y : 1.0;                   // reth/buffer/sumtree.py:112-113
+        if (i == 0 && lane == 0) { a.meta[2 * grp] = 0; a.meta[2 * grp + 1] = a.batch; }
+    }
+    const double segment = total / (double)a.batch;                  // sumtree.py:73
+    double w = ((double)i + draw_u(a, W)) * segment;                 // sumtree.py:74
+    w -= prefix;                                                      // 0.0 for a single shard
+    int64_t idx;
+    const double val = descend(a, w, lane, idx);
     if (lane == 0) {
-        const int64_t o = (a.quota ? 0 : grp * a.out_stride) + i - first;
+        const int64_t o = grp * a.out_stride + i - first;
         const double wt = pow(val / pmin, -a.beta);  // per_sampler.py:26
         a.idx_out[o] = idx;
         a.prio_out[o] = val;
@@ -364,7 +406,8 @@ __global__ void __launch_bounds__(1024) global_quota_kernel(const SampleArgs a, 
             for (int k = 0; k < 4; ++k) { quota_out[4 * g + k] = q[k]; slot_quota[4 * g + k] = q[k]; }
             off += sh_count[g];
         }
-        a.meta[0] = 0;
+        // one draw: the slot is an ordinary Mode G slot {first, count}; several: ONE packed batch of `off` rows
+        a.meta[0] = a.groups == 1 ? sh_first[0] : 0;
         a.meta[1] = off;
     }
 }
@@ -398,6 +441,8 @@ struct UpdateArgs {
     BoardEntry *const *pub_boards;
     int32_t pub_shards, pub_shard;
     unsigned long long pub_seq;
+    int32_t pub_when;     // 0 always; 1 only if the device-side entry count ends inside this launch (or before it);
+                          // 2 only if this launch has entries (the catch-all behind launches sized for the expected share)
 };
 
 #define RETH_STAMP(k) do { if (a.dbg && brank == 0 && threadIdx.x == 0) a.dbg[k] = clock64(); } while (0)
@@ -577,32 +622,19 @@ __device__ __forceinline__ void repair_tiles_warp(const UpdateArgs &a, const int
 // resident ahead of its turn.  At 114 registers an SM holding ONE such waiting CTA could no longer host a
 // repair CTA, and with the draw kernel's CTAs spread over every GPC no GPC had 16 free SMs for the cluster:
 // two shards on one device then waited for each other until the exchange timed out.
+// One round of the repair: entries [base, min(n, base + cluster size x block size)) of the launch.
 template <int kLv, int kRegCtas>
-__global__ void __maxnreg__(kRegCtas == 1 ? 104 : 64) per_update_kernel(const UpdateArgs a)
+__device__ __forceinline__ void update_round(const UpdateArgs &a, const int64_t base, const int64_t n, const bool publish)
 {
     cg::cluster_group cluster = cg::this_cluster();
     const int nblk = (int)cluster.num_blocks(), brank = (int)cluster.block_rank();
-    // consecutive entries are spread over the CTAs of the cluster
-    const int64_t i = (int64_t)threadIdx.x * nblk + brank;
     const int64_t cap = a.g.capacity;
     const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
     const int kWarps = (int)(blockDim.x >> 5);          // block size is a launch parameter (<= kUpdateThreads)
     const int NT = a.g.n_tile_levels;
-
-    pdl_wait();
-    pdl_trigger();
-    RETH_STAMP(0);
-    if (brank == 0 && threadIdx.x < kMaxTileLevels /* array size */) a.counts_next[threadIdx.x] = 0;
-    // every load that does not depend on another is issued up front
-    int64_t n = a.n;
-    if (a.n_dev) {
-        const int64_t m = __ldcg(a.n_dev) - a.n_off;
-        n = m < n ? (m < 0 ? 0 : m) : n;
-    }
-    if (n <= 0) {           // Mode G chunk beyond this shard's share: uniform over the cluster, nothing was touched
-        if (a.pub_seq && brank == 0 && wic == 0) board_publish(a.pub_boards, a.pub_shards, a.pub_shard, a.pub_seq, a.agg, lane);
-        return;
-    }
+    const int64_t per = (int64_t)nblk * blockDim.x;
+    // consecutive entries are spread over the CTAs of the cluster
+    const int64_t i = base + (int64_t)threadIdx.x * nblk + brank;
     const bool inrange = i < n;
     int64_t idx = 0, nxt = -1;
     double raw = 0.0;
@@ -754,12 +786,55 @@ __global__ void __maxnreg__(kRegCtas == 1 ? 104 : 64) per_update_kernel(const Up
     if (brank == 0 && wic == 0) {
         const int64_t t0[1] = {0};
         repair_tiles_warp<1>(a, t0, 1, 0, lane, true);
-        if (a.pub_seq) {
+        if (publish && base + per >= n) {
             __syncwarp();              // lane 1 stored the root; order it before the other lanes' loads
             board_publish(a.pub_boards, a.pub_shards, a.pub_shard, a.pub_seq, a.agg, lane);
         }
     }
     RETH_STAMP(22);
+}
+
+// kRounds == false: one round, n <= cluster size x block size (the host cuts larger batches into launches).
+// kRounds == true: the launch takes its n entries in rounds of (cluster size x block size), each a complete repair
+// (batch order, hence last-writer-wins, is kept across rounds as across launches); how many rounds run is decided
+// on the device.  The loop costs this build registers (spills), so it only serves as the CATCH-ALL behind a Mode G
+// write-back: the host sizes the ordinary launches for the share it expects of a batch whose real share count
+// lives on the device, and this one launch takes whatever lies beyond -- normally nothing, then it returns at once.
+template <int kLv, int kRegCtas, bool kRounds>
+__global__ void __maxnreg__(kRegCtas == 1 ? 104 : 64) per_update_kernel(const UpdateArgs a)
+{
+    cg::cluster_group cluster = cg::this_cluster();
+    const int nblk = (int)cluster.num_blocks(), brank = (int)cluster.block_rank();
+    const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
+
+    pdl_wait();
+    pdl_trigger();
+    RETH_STAMP(0);
+    if (brank == 0 && threadIdx.x < kMaxTileLevels /* array size */) a.counts_next[threadIdx.x] = 0;
+    int64_t n = a.n;
+    bool publish = a.pub_seq != 0ull;
+    if (a.n_dev) {
+        const int64_t m = __ldcg(a.n_dev) - a.n_off;
+        if (a.pub_when == 1) publish = publish && m <= a.n;      // the share ends here: nothing is left for the catch-all
+        if (a.pub_when == 2) publish = publish && m > 0;
+        n = m < n ? (m < 0 ? 0 : m) : n;
+    }
+    if (n <= 0) {           // Mode G: nothing of the share falls into this launch: uniform over the cluster
+        if (publish && brank == 0 && wic == 0) board_publish(a.pub_boards, a.pub_shards, a.pub_shard, a.pub_seq, a.agg, lane);
+        return;
+    }
+    if (!kRounds) {
+        update_round<kLv, kRegCtas>(a, 0, n, publish);
+    } else {
+        const int64_t per = (int64_t)nblk * blockDim.x;
+        for (int64_t base = 0; base < n; base += per) {
+            update_round<kLv, kRegCtas>(a, base, n, publish);
+            if (base + per < n) {      // another round: its level flags start clear, this round's stores are visible
+                if (brank == 0 && threadIdx.x == 0) __stcg(&a.counts[0], 0);
+                cluster.sync();
+            }
+        }
+    }
 }
 
 // Zero the arbitration stamps of `n` slots (after a policy-slot scatter that needed them).

@@ -665,12 +665,25 @@ class NumpyLoader(_LoaderBase):
             return data, idx, w
 
 
+def loader_geometry(buffer_size, num_procs, max_ring):
+    """(prefetch group, groups ahead) for a reference-style TorchCudaLoader(buffer_size, num_procs).
+    The reference keeps up to buffer_size + num_procs + 2 pre-sampled batches between a draw and its
+    consumption: `buffer_size` ring slots (torch_cuda_loader.py:70,114-135), one batch in each of the
+    `num_procs` worker processes (:20-66), one in the sampler's HWM-1 PUSH socket and one being drawn
+    (server/sampler_loop.py:14,37-39) -- 16 at its defaults (8, 6), 8 as the Ape-X trainer calls it
+    (trainer.py:22-24: 4, 2).  The same budget here: half of it is the group being consumed, the other
+    half is drawn + gathered ahead."""
+    budget = max(2, min(int(buffer_size) + max(0, int(num_procs)) + 2, int(max_ring)))
+    prefetch = max(1, budget // 2)
+    return prefetch, (1 if budget >= 2 else 0)
+
+
 class TorchCudaLoader(_LoaderBase):
     """client/torch_cuda_loader.py:69-163: data = list of CUDA tensors lent until the next
     sample() (:152-163), indices on the host (np.int64), weights a CUDA float64 tensor.
-    buffer_size = batches resident in the lending ring, as in the reference; by default half of
-    them form the group being consumed and the other half is drawn + gathered ahead
-    (prefetch = buffer_size // 2, ahead = 1).  prefetch=1, ahead=0 is strict alternation."""
+    buffer_size / num_procs set the staleness budget as in the reference (loader_geometry): by default
+    half of the batches it allows in flight form the group being consumed and the other half is drawn +
+    gathered ahead.  prefetch=1, ahead=0 is strict alternation."""
 
     def __new__(cls, meta_addr, *args, **kwargs):
         if cls is TorchCudaLoader and _remote(meta_addr):
@@ -681,6 +694,8 @@ class TorchCudaLoader(_LoaderBase):
     def __init__(self, meta_addr, topic="default", buffer_size=8, num_procs=6, prefetch=None, ahead=None):
         eng = _engine(meta_addr)
         buffer_size = max(1, min(int(buffer_size), eng.max_ring))
+        if prefetch is None and ahead is None:
+            prefetch, ahead = loader_geometry(buffer_size, num_procs, eng.max_ring)
         if prefetch is None:
             prefetch = max(1, buffer_size // 2)
         if ahead is None:
@@ -688,7 +703,7 @@ class TorchCudaLoader(_LoaderBase):
         ahead = min(int(ahead), max(0, eng.max_ring // int(prefetch) - 1))
         super().__init__(meta_addr, topic, prefetch, ahead)
         self.buffer_size = buffer_size
-        self.num_procs = num_procs                            # accepted, unused: no gather processes are needed
+        self.num_procs = num_procs                            # no gather processes are needed; counts towards the staleness budget
         self._views = {}                                      # slot -> cached zero-copy torch views
 
     def sample(self):

@@ -126,19 +126,22 @@ def test_board_errors_and_timeout(Shard, monkeypatch):
     b.close()
 
 
-def test_mode_g_prefetch_group_packed(Shard):
+@pytest.mark.parametrize("cap,GB,n_shards,G,heavy", [(3000, 128, 3, 4, 1.0), (20000, 8192, 4, 4, 40.0)])
+def test_mode_g_prefetch_group_packed(Shard, cap, GB, n_shards, G, heavy):
     """sample_global_multi: G global stratified draws in one launch, this shard's shares packed back to back;
     gather_multi / update_slots treat the slots as one batch of sum(count) rows.  Against n reference trees +
-    the range rule per draw, rows byte for byte, trees bit for bit after the write-back."""
+    the range rule per draw, rows byte for byte, trees bit for bit after the write-back.
+    Second case: shard 0 holds most of the priority mass, so its share (about 0.8 x 32768 entries) is far beyond what
+    the write-back's ordinary launches are sized for (1.25 x an equal share) and the catch-all launch runs two rounds;
+    the draw kernel's warps stride over a share three times their number."""
     import torch
-    cap, GB, n_shards, G = 3000, 128, 3, 4
     struct = [(np.uint8, (48,)), (np.int64, ())]
     rng = np.random.default_rng(11)
     shards, trees, datas = [], [], []
     for g in range(n_shards):
         sh = Shard(cap, struct, max_batch=GB, ring_depth=2 * G)
         cols = [rng.integers(0, 256, (cap, 48), dtype=np.uint8), np.arange(cap) + 100000 * g]
-        p = rng.random(cap) * (1 + 3 * g) + 0.01
+        p = (rng.random(cap) * (1 + 3 * g) + 0.01) * (heavy if g == 0 else 1.0)
         sh.append(cols, None)
         sh.update(np.arange(cap), p, transform=False)
         t = po.OracleSumTree(cap)
@@ -177,7 +180,7 @@ def test_mode_g_prefetch_group_packed(Shard):
                 assert np.array_equal(got[c][:off], datas[g][c][oidx]), (step, g, c)
             mine = np.zeros(G * GB)
             mine[:off] = newp[:off]
-            sh.update_slots(first_slot, G, mine, transform=False)
+            sh.update_slots(first_slot, G, torch.from_numpy(mine).cuda() if G * GB > 16384 else mine, transform=False)
         for g in range(n_shards):                            # oracle write-back after every shard has drawn
             oidx = np.concatenate([draws[g][d][1] for d in range(G)])
             trees[g].update(oidx, newp[:len(oidx)])
