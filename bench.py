@@ -417,6 +417,36 @@ def append_rate_host(torch, shard, n=4096, reps=5):
     return n / (ms / 1e3), n * ROW_BYTES / (ms / 1e3) / 1e9
 
 
+def config4_loop(torch, shard, batch, group, rows_per_step, groups):
+    """BASELINE.json config 4, device-resident producer: per group of `group` learner steps the pending actor rows
+    (rows_per_step per step) are appended, then `group` batches are drawn, gathered and written back.
+    alpha 0.5, beta 0.4 (test/apex-dqn/config.yaml:26-27).  -> (sampled transitions/s, appended rows/s, HBM GB/s)."""
+    n = rows_per_step * group
+    g = torch.Generator(device="cuda").manual_seed(5)
+    s0 = torch.randint(0, 256, (n, 4, 84, 84), dtype=torch.uint8, device="cuda", generator=g)
+    z = torch.zeros(n, device="cuda")
+    cols, w = [s0, z.long(), z, s0, z], torch.rand(n, device="cuda", generator=g)
+    prio = torch.rand(group * batch, device="cuda", generator=g) + 0.01
+
+    chunk = 8                                     # groups per call of the device loop (prio covers one group, reused)
+    prio = prio.repeat(chunk)
+
+    def loop(k):
+        for _ in range(0, k, chunk):
+            # reth_replay_step_loop_ingest: after every group the actor rows are appended without draining the loop
+            shard.step_loop(group * chunk, batch, prio, alpha=0.5, beta=0.4, group=group, ingest=(cols, w))
+    groups -= groups % chunk
+    loop(chunk)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    loop(groups)
+    e1.record()
+    torch.cuda.synchronize()
+    us = e0.elapsed_time(e1) * 1e3 / (groups * group)
+    return batch / us * 1e6, rows_per_step / us * 1e6, 2 * ROW_BYTES * (batch + rows_per_step) / us / 1e3
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -484,6 +514,17 @@ def run_ours(args):
     e2e_ref, ref_geom = e2e_loop(torch, dist, service, addr, min(8192, e2e_iters), 64, B, world, 0, 0, reference_call=ref_call)
     app_rows, app_gbs = append_rate(torch, shard) if rank == 0 or world == 1 else (None, None)
     apph_rows, apph_gbs = append_rate_host(torch, shard) if rank == 0 and world == 1 else (None, None)
+    config4 = None
+    if world == 1:
+        c4a = config4_loop(torch, shard, B, G, 64, 150)
+        c4s = config4_loop(torch, shard, B, G, 256 * 64, 30)
+        config4 = {"apex_like": {"value": c4a[0], "appended_rows_per_s": c4a[1], "hbm_gbs": c4a[2], "rows_appended_per_learner_step": 64},
+                   "stress": {"value": c4s[0], "appended_rows_per_s": c4s[1], "hbm_gbs": c4s[2], "rows_appended_per_learner_step": 256 * 64},
+                   "unit": "sampled transitions/s", "prefetch_group": G,
+                   "note": "learner loop with actor ingest on one shard, device-resident producer (reth_replay_step_loop_ingest): "
+                           "per group G x (sample 512 + gather + update), then the rows that arrived are appended -- leaves on the "
+                           "tree stream at once, the row copy behind the gathers in flight, later gathers behind the copy; alpha 0.5 "
+                           "beta 0.4 (config.yaml:26-27); 256 actor connections over ZeroMQ: see ingest_256"}
 
     peak, peak_src = measured_peak()
     rows_per_launch = G * B
@@ -529,6 +570,7 @@ def run_ours(args):
         "strict_alternation": {"value": strict, "unit": "transitions/s", "prefetch_group": 1},
         "append": {"rows_per_s": app_rows, "gbs": app_gbs, "rows_per_call": 16384, "source": "device"},
         "append_host": {"rows_per_s": apph_rows, "pcie_gbs": apph_gbs, "rows_per_call": 4096, "source": "pinned host"},
+        "config4": config4,
         "shard_mode": "one shard per GPU, no data-path collective; NCCL all-gather of the 16-byte shard roots {total,min} once per bench step inside the timed region" if world > 1 else "single shard",
     }
     if world > 1:
@@ -562,9 +604,17 @@ def run_ours(args):
                       f"(ring bounded to 4096 rows per process; one-core figure with a 65536-row = 3.7 GB ring) + "
                       f"PERSampler.update, {rn[1]:.1f} s"}
         line["cpu_baseline"]["service_e2e"] = service_tier_b()
+    proc.terminate()
+    if rank == 0 and world == 1 and not args.no_process:
+        import bench_process
+        try:
+            line["e2e_process"] = bench_process.e2e_process(batch=B)
+        except Exception as e:
+            log(f"e2e_process failed: {e!r}")
+            line["e2e_process"] = {"error": repr(e)}
+        line["ingest_256"] = bench_process.ingest_256(log)
     if rank == 0:
         emit(line)
-    proc.terminate()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -591,6 +641,7 @@ def main():
     ap.add_argument("--cpu-steps", type=int, default=24)
     ap.add_argument("--cpu-iters", type=int, default=64, help="iterations per step of the CPU arm (bounded sample)")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-process", action="store_true", help="skip the server-process legs (e2e_process, ingest_256)")
     ap.add_argument("--modeg-iters", type=int, default=400, help="Mode G leg (N > 1): timed iterations per case")
     args = ap.parse_args()
     _claim_stdout()

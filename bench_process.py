@@ -1,0 +1,85 @@
+"""Process-layout legs of `bench.py` (N = 1, rank 0): the path the `reth_buffer` import shim defaults to.
+
+The reference runs its replay as a server process reached by address (test/apex-dqn/trainer.py:49-66); the
+shim's default (`RETH_B200_SERVER=process`, reth_b200/service_mp.py) does the same: ZeroMQ for append / update /
+loader requests in the reference wire format, CUDA IPC for the batch ring.  Measured here, beside the in-process
+engine the headline `e2e` uses:
+
+  e2e_process   TorchCudaLoader(addr).sample() + Client.update_priorities() against a spawned server, loader
+                built with the DEFAULT arguments a caller of the reference API passes; capacity bounded to
+                2^16 Atari rows (3.7 GB: the rows travel to the server to get in)
+  ingest        rows/s taken in by the server: same-host shared-memory ring (this build's Client default), and
+                BASELINE.json config 4 as worded -- 256 concurrent PUSH connections x 64-row messages in the
+                reference's ROW wire format (client/client.py:26-35), plain and lz4-framed (worker.py:60)
+"""
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+
+
+def e2e_process(batch=512, capacity=1 << 16, iters=4000, warm=128):
+    from reth_b200 import service_mp
+    proc, addr = service_mp.start_per(capacity, batch, alpha=0.6, beta=0.4, sample_start=batch)
+    try:
+        client = service_mp.Client(addr)                      # wire "auto": shared-memory ring on the server's host
+        rng = np.random.default_rng(0)
+        n = 2048
+        s0 = rng.integers(0, 256, (n, 4, 84, 84), dtype=np.uint8)
+        cols = [s0, rng.integers(0, 18, n), np.zeros(n, np.float32), s0, np.zeros(n, np.float32)]
+        wts = np.abs(rng.standard_normal(n)).astype(np.float32)
+        loader = service_mp.TorchCudaLoader(addr)             # the reference's defaults: buffer_size=8, num_procs=6
+        client.append(cols, wts)
+        loader.drain()
+        t0 = time.perf_counter()
+        for _ in range(n, capacity, n):
+            client.append(cols, wts)
+        loader.drain()
+        t_fill = time.perf_counter() - t0
+        newp = np.abs(rng.standard_normal((64, batch))).astype(np.float32)
+        for i in range(warm):
+            data, idx, w = loader.sample()
+            client.update_priorities(idx, newp[i % 64])
+        loader.drain()
+        t0 = time.perf_counter()
+        for i in range(iters):
+            data, idx, w = loader.sample()
+            client.update_priorities(idx, newp[i % 64])
+        loader.drain()
+        dt = time.perf_counter() - t0
+        out = {"value": iters * batch / dt, "unit": "transitions/s", "us_per_iteration": dt / iters * 1e6,
+               "call": "reth_buffer.start_per(...) in its own process; TorchCudaLoader(addr) [defaults]; Client(addr)",
+               "prefetch_group": loader.group, "groups_ahead": loader.ahead, "capacity": capacity,
+               "ingest_shm_rows_per_s": (capacity - n) / t_fill, "ingest_shm_GBps": (capacity - n) * 56464 / t_fill / 1e9,
+               "h2d_bytes_per_iteration": batch * 12, "d2h_bytes_per_iteration": batch * 16}
+        loader.close()
+        client.close()
+        return out
+    finally:
+        proc.terminate()
+        proc.join()
+
+
+def ingest_256(log=None):
+    """256 connections x 64-row messages, reference row format (scripts/ingest_rate.py)."""
+    sys.path.insert(0, os.path.join(ROOT, "scripts"))
+    import ingest_rate
+    out = {}
+    for name, comp, msgs in (("rows", False, 6), ("rows_lz4", True, 6)):
+        try:
+            r = ingest_rate.run(256, msgs, compress=comp, wire="rows")
+            out[name] = {k: r[k] for k in ("rows_per_s", "wire_GBps", "messages", "message_bytes", "dropped")}
+        except Exception as e:                                  # keep the bench line
+            out[name] = {"error": repr(e)}
+            if log:
+                log(f"ingest_256 {name} failed: {e!r}")
+    out["connections"], out["rows_per_message"] = 256, 64
+    out["ingest_threads"] = int(os.environ.get("RETH_B200_INGEST_THREADS", "4"))
+    out["note"] = ("256 concurrent ZeroMQ PUSH connections (one per actor) x 64-row messages in the reference's row wire "
+                   "format into the server process: ZeroMQ I/O threads -> decode threads (header, lz4, row->column "
+                   "transpose in one library call) -> pinned staging -> asynchronous H2D -> ring append + tree update; "
+                   "messages are encoded once and re-sent (the per-row Python encode is the actor's cost)")
+    return out

@@ -427,6 +427,18 @@ int reth_replay_gather_from(reth_replay_t *h, int dst_slot, reth_replay_t *src, 
 int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, const float *prio_dev,
                           const double *uniforms_dev, uint64_t seed, double alpha, double beta,
                           int flags, void *stream);
+/* The same loop with actor ingest (BASELINE.json config 4: learner loop + actor append streams; reference: appends
+ * and draws are serialised by the one append process and the sampler's SUB socket, server/main_loop.py:44-58,
+ * server/sampler_loop.py:29-39).  After every group of G learner steps, rows_per_group device-resident rows
+ * (ingest_cols_dev[c]: rows_per_group rows of column c; ingest_prio_dev: their float32 |TD|) are appended:
+ * their leaves go onto the tree stream at once, in order behind the write-back, so the chain draw -> repair -> draw
+ * never waits for a gather; the row copy runs on the ingest stream behind every gather enqueued so far (those may
+ * still read the slots being recycled) and every later gather waits for it.  Same order of tree mutations as
+ * step_loop(G) followed by append(), repeated.  Not with flags bit1 (serial) / bit6 (Mode G). */
+int reth_replay_step_loop_ingest(reth_replay_t *h, int steps, int batch, const float *prio_dev,
+                                 const double *uniforms_dev, uint64_t seed, double alpha, double beta, int flags,
+                                 const void *const *ingest_cols_dev, const float *ingest_prio_dev,
+                                 int64_t rows_per_group, void *stream);
 /* Sum of the event-bracketed gather launch durations recorded since the last call
  * (step_loop flag bit2), and how many launches that covers.  Synchronises the device. */
 int reth_replay_gather_time(reth_replay_t *h, double *total_ms, int64_t *launches);
@@ -447,6 +459,15 @@ int64_t reth_lz4f_content_size(const void *src, int64_t n);   /* -1: the frame d
 int64_t reth_lz4f_decompress(const void *src, int64_t n, void *dst, int64_t cap);
 int64_t reth_lz4f_compress_bound(int64_t n);
 int64_t reth_lz4f_compress(const void *src, int64_t n, void *dst, int64_t cap);
+
+/* ---- row messages -> columns (host code, no handle).  The reference's Client.append serializes every transition
+ *      on its own (client/client.py:26-35) and the server / loaders undo that row by row in Python
+ *      (client/numpy_loader.py:35-50).  Rows of one append share a struct, so they form an (n, L) byte matrix:
+ *      this copies column c of every row (bytes [lo[c], lo[c]+len[c]) of each row) to the C-contiguous array
+ *      dst[c] -- typically pinned staging memory the host->device copy then reads -- in one call without the
+ *      interpreter (several ingest threads call it concurrently).  Returns the bytes copied, -1 on bad arguments. */
+int64_t reth_pack_scatter_rows(const void *mat, int64_t n, int64_t L, int32_t ncols, const int64_t *lo,
+                               const int64_t *len, void *const *dst);
 
 #ifdef __cplusplus
 }

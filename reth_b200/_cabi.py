@@ -146,6 +146,7 @@ SIGNATURES = {
     "reth_replay_roots_exchange": [_vp, _i32, _vp],
     "reth_replay_all_roots_dev": [_vp, C.POINTER(_vp)],
     "reth_replay_step_loop": [_vp, _i32, _i32, _vp, _vp, _u64, _f64, _f64, _i32, _vp],
+    "reth_replay_step_loop_ingest": [_vp, _i32, _i32, _vp, _vp, _u64, _f64, _f64, _i32, _vp, _vp, _i64, _vp],
     "reth_replay_gather_time": [_vp, C.POINTER(_f64), C.POINTER(_i64)],
     "reth_replay_debug_stamps": [_vp, C.POINTER(_i64)],
 }
@@ -158,6 +159,7 @@ LZ4F_SIGNATURES = {                      # return a byte count (int64) or a nega
     "reth_lz4f_decompress": [_vp, _i64, _vp, _i64],
     "reth_lz4f_compress_bound": [_i64],
     "reth_lz4f_compress": [_vp, _i64, _vp, _i64],
+    "reth_pack_scatter_rows": [_vp, _i64, _i64, _i32, _vp, _vp, _vp],
 }
 
 

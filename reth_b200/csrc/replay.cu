@@ -70,7 +70,7 @@ struct reth_replay {
     std::vector<cudaEvent_t> ev_sampled, ev_gathered;
     cudaEvent_t ev_fork = nullptr, ev_join_t = nullptr, ev_join_g = nullptr;
     cudaStream_t s_append = nullptr;          // large device-source appends: the row copy runs beside the tree update
-    cudaEvent_t ev_app_fork = nullptr, ev_app_done = nullptr;
+    cudaEvent_t ev_app_fork = nullptr, ev_app_done = nullptr, ev_ingest = nullptr;
     cudaEvent_t last_gather_ev = nullptr;     // newest gather of the internal streams
     cudaEvent_t last_gather_on[2] = {nullptr, nullptr};   // ... per gather stream (s_gather, s_gather2): a writer of ring
                                               // rows waits for BOTH, the other stream's previous gather may still run
@@ -235,6 +235,7 @@ void free_all(reth_replay *h)
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
     if (h->ev_app_fork) cudaEventDestroy(h->ev_app_fork);
     if (h->ev_app_done) cudaEventDestroy(h->ev_app_done);
+    if (h->ev_ingest) cudaEventDestroy(h->ev_ingest);
     if (h->s_append) cudaStreamDestroy(h->s_append);
     if (h->ev_join_t) cudaEventDestroy(h->ev_join_t);
     if (h->ev_join_g) cudaEventDestroy(h->ev_join_g);
@@ -323,8 +324,11 @@ UpdateKernel update_kernel_of(const reth_replay *h, bool lean, bool rounds = fal
 //   larger (appends): lean, 16 CTAs, 8192 entries per launch.
 int env_int(const char *name, int dflt);
 struct UpdateShape { UpdateKernel fn; int cluster; };
-UpdateShape update_shape_of(const reth_replay *h, int64_t n)
+UpdateShape update_shape_of(const reth_replay *h, int64_t n, bool critical = false)
 {
+    // critical: the repair is on a cross-GPU dependent chain (Mode G: every shard's next draw waits for every
+    // shard's root), so its latency counts, not the SM resources it holds: widest cluster, full register budget
+    if (critical && h->update_lean < 0 && !h->update_cluster_fixed) return {update_kernel_of(h, false), h->update_cluster};
     static const int fast_n = env_int("RETH_UPDATE_FAST_N", 2048);
     int cluster = h->update_cluster;
     if (!h->update_cluster_fixed && n > fast_n && n <= (int64_t)8 * h->update_threads && cluster > 8) cluster = 8;
@@ -351,6 +355,29 @@ RETH_EXPORT int64_t reth_lz4f_compress(const void *src, int64_t n, void *dst, in
 {
     if (n < 0 || (!src && n > 0) || !dst) return lz4f::kErrFormat;
     return lz4f::compress((const uint8_t *)src, n, (uint8_t *)dst, cap);
+}
+
+// Row messages -> columns (host code, no handle): the n row messages of one reference-format append
+// (client/client.py:26-35: every row is its own serialize()d message, same struct, hence same length L and the
+// same column offsets) form an (n, L) byte matrix `mat`; column c of row i sits at mat[i*L + lo[c] .. + len[c]).
+// One call copies every column of every row to dst[c] + i*len[c] -- C-contiguous columns, e.g. in pinned
+// staging memory -- with no interpreter in the loop (ctypes drops the GIL for the duration: several ingest
+// threads run this concurrently).  Replaces the per-row deserialize loop of client/numpy_loader.py:35-50 on the
+// ingest side.
+RETH_EXPORT int64_t reth_pack_scatter_rows(const void *mat, int64_t n, int64_t L, int32_t ncols, const int64_t *lo,
+                                          const int64_t *len, void *const *dst)
+{
+    if (!mat || n < 0 || L < 0 || ncols < 0 || (ncols > 0 && (!lo || !len || !dst))) return -1;
+    for (int c = 0; c < ncols; ++c)
+        if (lo[c] < 0 || len[c] < 0 || lo[c] + len[c] > L || !dst[c]) return -1;
+    const uint8_t *m = (const uint8_t *)mat;
+    int64_t bytes = 0;
+    for (int64_t i = 0; i < n; ++i)
+        for (int c = 0; c < ncols; ++c) {
+            memcpy((uint8_t *)dst[c] + i * len[c], m + i * L + lo[c], (size_t)len[c]);
+            bytes += len[c];
+        }
+    return bytes;
 }
 
 RETH_EXPORT const char *reth_replay_last_error(const reth_replay_t *h)
@@ -463,6 +490,7 @@ RETH_EXPORT int reth_replay_create(const reth_replay_config *cfg, reth_replay_t 
     CKC(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
     CKC(cudaEventCreateWithFlags(&h->ev_app_fork, cudaEventDisableTiming));
     CKC(cudaEventCreateWithFlags(&h->ev_app_done, cudaEventDisableTiming));
+    CKC(cudaEventCreateWithFlags(&h->ev_ingest, cudaEventDisableTiming));
     CKC(cudaStreamCreateWithFlags(&h->s_append, cudaStreamNonBlocking));
     CKC(cudaEventCreateWithFlags(&h->ev_join_t, cudaEventDisableTiming));
     CKC(cudaEventCreateWithFlags(&h->ev_join_g, cudaEventDisableTiming));
@@ -536,7 +564,7 @@ int to_device(reth_replay *h, const void *p, int loc, size_t bytes, void *stagin
 // n_expected > 0 (Mode G: only the first *a.n_dev of the n entries are valid, about n_expected of them): ordinary
 // launches cover 1.25 x n_expected + 64 entries and ONE catch-all launch (the build with rounds) takes whatever lies
 // beyond -- normally nothing.  A write-back padded to 8 x the share then costs 2 launches on the chain, not 8..16.
-int launch_update(reth_replay *h, UpdateArgs &a, cudaStream_t s, int64_t n_expected = 0)
+int launch_update(reth_replay *h, UpdateArgs &a, cudaStream_t s, int64_t n_expected = 0, bool critical = false)
 {
     if (a.n <= 0) return RETH_OK;
     a.g = h->geom; a.desc = h->desc; a.agg = h->agg; a.stamp = h->stamp; a.mask = h->mask;
@@ -545,7 +573,7 @@ int launch_update(reth_replay *h, UpdateArgs &a, cudaStream_t s, int64_t n_expec
     const unsigned long long pub_seq = a.pub_seq;
     if (pub_seq) { a.pub_boards = h->board_ptrs_dev; a.pub_shards = h->board_shards; a.pub_shard = h->board_shard; }
     const bool spec = a.n_dev != nullptr && n_expected > 0;
-    const UpdateShape shape = update_shape_of(h, spec ? n_expected : n);
+    const UpdateShape shape = update_shape_of(h, spec ? n_expected : n, critical);
     const int64_t per = (int64_t)shape.cluster * h->update_threads;
     int64_t covered = n;                 // entries [0, covered) go through ordinary launches
     if (spec) {
@@ -2338,9 +2366,87 @@ RETH_EXPORT int reth_replay_all_roots_dev(reth_replay_t *h, double **all_roots_d
 }
 
 // ------------------------------------------------------------------ step loop --
+namespace {
+
+// Device-resident rows -> FIFO slots start, start+1, ... of the ring (at most two spans per column), on stream sc.
+int launch_ring_copy(reth_replay *h, const void *const *cols, int64_t start, int64_t m, cudaStream_t sc)
+{
+    const int64_t cap = h->cfg.capacity;
+    const int64_t len1 = (m < cap - start) ? m : cap - start, len2 = m - len1;
+    AppendTiledArgs t = {};
+    AppendArgs a = {};
+    a.ncols = h->cfg.n_columns; a.start = start; a.n = m; a.capacity = cap;
+    bool aligned = true;
+    int64_t bytes = 0;
+    for (int c = 0; c < a.ncols; ++c) {
+        const int64_t rb = h->cfg.row_bytes[c];
+        a.rb[c] = rb; a.src[c] = (const uint8_t *)cols[c]; a.ring[c] = h->ring[c];
+        bytes += m * rb;
+        uint8_t *d1 = h->ring[c] + start * rb;
+        const uint8_t *s1 = a.src[c], *s2 = a.src[c] + len1 * rb;
+        if ((((uintptr_t)d1 | (uintptr_t)s1 | (uint64_t)(len1 * rb)) & 15) ||
+            (len2 > 0 && (((uintptr_t)h->ring[c] | (uintptr_t)s2 | (uint64_t)(len2 * rb)) & 15))) aligned = false;
+        if (!aligned) continue;
+        if (len1 > 0) {
+            AppendSeg &g = t.seg[t.nseg++];
+            g.dst = d1; g.src = s1; g.units = len1 * rb / 16; g.tile_base = t.tiles;
+            t.tiles += (g.units + kAppendTileUnits - 1) / kAppendTileUnits;
+        }
+        if (len2 > 0) {
+            AppendSeg &g = t.seg[t.nseg++];
+            g.dst = h->ring[c]; g.src = s2; g.units = len2 * rb / 16; g.tile_base = t.tiles;
+            t.tiles += (g.units + kAppendTileUnits - 1) / kAppendTileUnits;
+        }
+    }
+    if (aligned && t.tiles > 0) {
+        const int64_t maxg = (int64_t)h->n_sms * 8 * 64;
+        ring_append_tiled_kernel<<<(unsigned)(t.tiles < maxg ? t.tiles : maxg), kCopyThreads, 0, sc>>>(t);
+    } else {
+        int64_t blocks = (bytes / 16 + kCopyThreads * 4 - 1) / (kCopyThreads * 4);
+        const int64_t cap_blocks = (int64_t)h->n_sms * 8;
+        blocks = blocks > cap_blocks ? cap_blocks : (blocks < 1 ? 1 : blocks);
+        ring_append_kernel<<<(unsigned)blocks, kCopyThreads, 0, sc>>>(a);
+    }
+    CK(h, cudaGetLastError());
+    h->st.kernel_launches++;
+    return RETH_OK;
+}
+
+struct LoopIngest {
+    const void *const *cols;      // device-resident rows of the producer: rows_per_group rows per column
+    const float *prio;            // their |TD| priorities (device float32)
+    int64_t rows_per_group;
+};
+
+int step_loop_impl(reth_replay_t *h, int steps, int batch, const float *prio_dev, const double *uniforms_dev,
+                   uint64_t seed, double alpha, double beta, int flags, const LoopIngest *ing, void *stream);
+
+}  // namespace
+
 RETH_EXPORT int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, const float *prio_dev,
                                       const double *uniforms_dev, uint64_t seed, double alpha, double beta,
                                       int flags, void *stream)
+{
+    return step_loop_impl(h, steps, batch, prio_dev, uniforms_dev, seed, alpha, beta, flags, nullptr, stream);
+}
+
+RETH_EXPORT int reth_replay_step_loop_ingest(reth_replay_t *h, int steps, int batch, const float *prio_dev,
+                                             const double *uniforms_dev, uint64_t seed, double alpha, double beta,
+                                             int flags, const void *const *ingest_cols_dev, const float *ingest_prio_dev,
+                                             int64_t rows_per_group, void *stream)
+{
+    if (!h) return RETH_ERR_INVALID;
+    if (rows_per_group < 0 || rows_per_group > h->cfg.capacity || (rows_per_group > 0 && (!ingest_cols_dev || !ingest_prio_dev)))
+        return fail(h, RETH_ERR_INVALID, "bad ingest arguments");
+    if ((flags & (2 | 64)) || !h->cfg.store_rows)
+        return fail(h, RETH_ERR_INVALID, "the ingest loop needs row storage and runs neither serial nor in Mode G");
+    LoopIngest ing = {ingest_cols_dev, ingest_prio_dev, rows_per_group};
+    return step_loop_impl(h, steps, batch, prio_dev, uniforms_dev, seed, alpha, beta, flags, rows_per_group > 0 ? &ing : nullptr, stream);
+}
+
+namespace {
+int step_loop_impl(reth_replay_t *h, int steps, int batch, const float *prio_dev, const double *uniforms_dev,
+                   uint64_t seed, double alpha, double beta, int flags, const LoopIngest *ing, void *stream)
 {
     if (!h) return RETH_ERR_INVALID;
     if (steps < 0 || !prio_dev) return fail(h, RETH_ERR_INVALID, "bad step_loop arguments");
@@ -2370,7 +2476,9 @@ RETH_EXPORT int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, co
         CK(h, cudaStreamWaitEvent(st, h->ev_fork, 0));
         CK(h, cudaStreamWaitEvent(h->s_gather, h->ev_fork, 0));
         CK(h, cudaStreamWaitEvent(h->s_gather2, h->ev_fork, 0));
+        if (ing) CK(h, cudaStreamWaitEvent(h->s_append, h->ev_fork, 0));
     }
+    bool copy_pending = false;            // an ingest copy is in flight on s_append: the next gather waits for it
     for (int k = 0; k < steps; k += G) {
         const int slot = k % depth;
         // consecutive gathers alternate streams: the tail of one overlaps the ramp-up of the next
@@ -2414,6 +2522,7 @@ RETH_EXPORT int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, co
                 }
                 CK(h, cudaEventRecord(h->ev_time[h->ev_time_used], sg));
             }
+            if (copy_pending) CK(h, cudaStreamWaitEvent(sg, h->ev_ingest, 0));   // rows the draw may have picked are in place
             rc = do_gather(h, slot, global, sg, G);
             if (rc) return rc;
             if (timed) h->ev_time_launches++;
@@ -2432,9 +2541,37 @@ RETH_EXPORT int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, co
             a.n_dev = h->slots[slot].meta + 1;                  // this shard's share of the global batch
             if (h->modeg_fused && k + G < steps) a.pub_seq = ++h->board_seq;
         }
-        rc = launch_update(h, a, st, global ? (a.n / h->board_shards > 0 ? a.n / h->board_shards : 1) : 0);
+        static const int modeg_critical = env_int("RETH_MODEG_CRITICAL", 1);
+        rc = launch_update(h, a, st, global ? (a.n / h->board_shards > 0 ? a.n / h->board_shards : 1) : 0,
+                           global && modeg_critical);
         if (rc) return rc;
         h->st.updated_rows += (int64_t)batch * G;
+        if (ing) {
+            // Actor rows that arrived during this group (config 4): their LEAVES go onto the tree stream at once, in
+            // order behind the write-back -- the chain draw -> repair -> draw never waits for a gather -- while the ROW
+            // copy runs on the ingest stream behind every gather enqueued so far (those may still read the slots being
+            // recycled), and every later gather waits for the copy (a later draw may pick the new slots).
+            const int64_t n = ing->rows_per_group, cap = h->cfg.capacity, start = h->tail;
+            rc = wait_gathers(h, h->s_append);
+            if (!rc) rc = launch_ring_copy(h, ing->cols, start, n, h->s_append);
+            if (!rc) rc = mark_frame_refs(h, nullptr, start, n, h->s_append);
+            if (rc) return rc;
+            CK(h, cudaEventRecord(h->ev_ingest, h->s_append));
+            copy_pending = true;
+            UpdateArgs u = {};
+            u.n = n; u.idx = nullptr; u.idx_kind = 2; u.iota_base = start;
+            u.prio = ing->prio; u.prio_kind = 0;
+            u.alpha = alpha; u.transform = 1; u.dedupe = 0;
+            rc = launch_update(h, u, st);
+            if (rc) return rc;
+            h->tail = (start + n) % cap;
+            h->size = (h->size + n < cap) ? h->size + n : cap;
+            h->st.appended_rows += n;
+        }
+    }
+    if (ing && !serial) {
+        CK(h, cudaEventRecord(h->ev_app_done, h->s_append));
+        CK(h, cudaStreamWaitEvent(s, h->ev_app_done, 0));
     }
     if (!serial) {
         CK(h, cudaEventRecord(h->ev_join_t, st));
@@ -2446,6 +2583,8 @@ RETH_EXPORT int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, co
     }
     return RETH_OK;
 }
+
+}  // namespace
 
 RETH_EXPORT int reth_replay_gather_time(reth_replay_t *h, double *total_ms, int64_t *launches)
 {

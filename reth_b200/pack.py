@@ -223,11 +223,13 @@ def is_shm(buf):
     return isinstance(meta, list) and len(meta) == 2 and isinstance(meta[0], dict) and KEY_SHM in meta[0]
 
 
-def open_append(buf):
+def open_append(buf, alloc=None):
     """An append message, header parsed once -> (kind, payload, weights, src):
     kind "shm": payload = descriptor of columns in a shared-memory ring (service_mp._ShmRing);
     kind "columns": payload = list of C-contiguous (n, ...) arrays (row or columnar wire format);
-    src = the sender's [client id, message number] or None (a reference client)."""
+    src = the sender's [client id, message number] or None (a reference client).
+    alloc(nbytes) -> writable uint8 buffer: where the columns of a "columns" message are put (pinned staging
+    memory on the server's ingest threads); default: fresh arrays."""
     header, body, _ = _split(buf)
     meta = header["meta"]
     src = header.get(KEY_SRC)
@@ -237,7 +239,7 @@ def open_append(buf):
     if isinstance(meta, list) and len(meta) == 4 and isinstance(meta[0], dict) and KEY_STEPS in meta[0]:
         head, frames, others, weights = _rebuild(meta, body)
         return "steps", (head, frames, others), np.asarray(weights), src
-    cols, weights = _decode_append(header, body)
+    cols, weights = _decode_append(header, body, alloc)
     return "columns", cols, weights, src
 
 
@@ -252,11 +254,25 @@ def decode_append(buf):
     return _decode_append(header, body)
 
 
-def _decode_append(header, body):
+def _place(arrays, alloc):
+    """Copy arrays into one buffer obtained from alloc (columns back to back, 256-byte aligned)."""
+    sizes = [(a.nbytes + 255) & ~255 for a in arrays]
+    slab = np.frombuffer(alloc(sum(sizes)), np.uint8)
+    out, at = [], 0
+    for a, sz in zip(arrays, sizes):
+        dst = slab[at:at + a.nbytes].view(a.dtype).reshape(a.shape)
+        np.copyto(dst, a)
+        out.append(dst)
+        at += sz
+    return out
+
+
+def _decode_append(header, body, alloc=None):
     meta = header["meta"]
     if header.get(KEY_COLUMNAR):
         cols, weights = _rebuild(meta, body)
-        return [np.ascontiguousarray(c) for c in cols], np.asarray(weights)
+        cols = [np.ascontiguousarray(c) for c in cols]
+        return (_place(cols, alloc) if alloc else cols), np.array(weights)
     rows, wnode = meta
     weights = _rebuild(wnode, body)
     n = len(rows)
@@ -268,23 +284,36 @@ def _decode_append(header, body):
         mat = np.frombuffer(body[first:first + n * L], np.uint8).reshape(n, L)
         h0, _, skip = _split(mat[0])
         hl = mat[:, :4]
-        if np.all(hl == hl[0]) and all(isinstance(x, dict) and KEY_NUMPY in x for x in h0["meta"]):
-            cols = []
-            for node in h0["meta"]:
+        if np.all(hl == hl[0]) and all(isinstance(x, dict) and KEY_NUMPY in x for x in h0["meta"]) and not any(
+                x["header"]["fortran_order"] and len(x["header"]["shape"]) > 1 for x in h0["meta"]):
+            # every column of every row in ONE call of the library (reth_pack_scatter_rows, no interpreter in the
+            # loop, GIL released), straight into the destination buffer (pinned staging on the ingest threads)
+            nodes = h0["meta"]
+            ncol = len(nodes)
+            lens = np.array([x["length"] for x in nodes], np.int64)
+            los = np.array([skip + x["offset"] for x in nodes], np.int64)
+            sizes = [(int(n * ln) + 255) & ~255 for ln in lens]
+            total = sum(sizes)
+            slab = np.frombuffer(alloc(total), np.uint8) if alloc else np.empty(total, np.uint8)
+            import ctypes as C
+            dst = (C.c_void_p * max(1, ncol))()
+            cols, at = [], 0
+            for c, node in enumerate(nodes):
                 hd = node["header"]
                 dt = np.lib.format.descr_to_dtype(hd["descr"])
-                if hd["fortran_order"] and len(hd["shape"]) > 1:
-                    break
-                lo = skip + node["offset"]
-                raw = np.ascontiguousarray(mat[:, lo:lo + node["length"]])
-                cols.append(raw.view(dt).reshape((n,) + tuple(hd["shape"])))
-            else:
-                return cols, np.asarray(weights)
+                view = slab[at:at + n * int(lens[c])]
+                dst[c] = view.ctypes.data
+                cols.append(view.view(dt).reshape((n,) + tuple(hd["shape"])))
+                at += sizes[c]
+            got = _native().reth_pack_scatter_rows(mat.ctypes.data, n, L, ncol, los.ctypes.data, lens.ctypes.data, dst)
+            if got != int((lens * n).sum()):
+                raise ValueError("row message: a column lies outside its row")
+            return cols, np.array(weights)
     # general path: decode row by row
     per_row = [decode(body[r["offset"]:r["offset"] + r["length"]]) for r in rows]
     ncol = len(per_row[0])
     cols = [np.stack([np.asarray(per_row[i][c]) for i in range(n)]) for c in range(ncol)]
-    return cols, np.asarray(weights)
+    return (_place(cols, alloc) if alloc else cols), np.array(weights)
 
 
 def encode_append_rows(columns, weights, compress=False, now=None, extra=None):

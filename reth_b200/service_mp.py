@@ -56,6 +56,125 @@ def _pick_port(host):
 
 
 # ------------------------------------------------------------------ server --
+class _Ingest:
+    """Decode threads of the server's ingest (replaces the single append_loop process,
+    server/main_loop.py:21-61, as the ceiling of the service's append rate).
+
+    The poll loop only RECEIVES append frames (zero-copy ZeroMQ frames) and numbers them; `n_threads` workers
+    undo the wire format -- header, lz4 body, and for the reference's row format the row -> column transpose
+    (reth_pack_scatter_rows, one library call per message, GIL released) -- writing the columns straight into
+    a slab of PINNED host memory; the poll loop then commits finished messages strictly in arrival order
+    (slot = arrival order, cache_policy/fifo_policy.py:11-18) with an asynchronous host->device copy out of the
+    slab, which is recycled once a CUDA event behind the copy has fired."""
+
+    def __init__(self, n_threads, device, max_slabs=24):
+        import queue
+        self.device = device
+        self.q = queue.Queue()
+        self.lock = threading.Lock()
+        self.cv = threading.Condition(self.lock)
+        self.done = {}                 # message number -> result tuple or exception
+        self.submitted = self.committed = 0
+        self.free = []                 # pinned slabs (torch uint8 tensors), largest first
+        self.slabs = 0
+        self.max_slabs = max_slabs
+        self.window = max(1, max_slabs // 2)
+        self.busy = []                 # (cuda event, slab): copies still reading a slab
+        self.stop = False
+        self.threads = [threading.Thread(target=self._work, daemon=True) for _ in range(max(1, n_threads))]
+        for t in self.threads:
+            t.start()
+
+    def _slab(self, nbytes, seq):
+        import torch
+        with self.cv:
+            while True:
+                # slabs go to the messages that commit next: a message more than `window` ahead of the commit point
+                # waits, so the decoded-but-uncommitted messages can never hold every slab while the message the commit
+                # point waits for has none (slabs come back only through commits)
+                if seq - self.committed >= self.window:
+                    self.cv.wait(0.01)
+                    continue
+                for k, t in enumerate(self.free):
+                    if t.numel() >= nbytes:
+                        return self.free.pop(k)
+                if self.slabs < self.max_slabs:
+                    self.slabs += 1
+                    break
+                if self.free:                     # every free slab is too small: replace the smallest
+                    self.free.pop()
+                    break
+                self.cv.wait(0.01)                # back-pressure: every slab is being filled or copied from
+        size = max(1 << 20, 1 << int(np.ceil(np.log2(max(1, nbytes)))))
+        return torch.empty(size, dtype=torch.uint8).pin_memory()
+
+    def _work(self):
+        while True:
+            item = self.q.get()
+            if item is None:
+                return
+            seq, frame = item
+            slab = []
+
+            def alloc(nbytes):
+                t = self._slab(nbytes, seq)
+                slab.append(t)
+                return t.numpy()[:nbytes]
+            try:
+                res = pack.open_append(frame.buffer, alloc) + (slab[0] if slab else None,)
+            except Exception as e:                 # reported and dropped at commit time, in order
+                res = e
+                for t in slab:
+                    self.release(t)
+            with self.cv:
+                self.done[seq] = res
+                self.cv.notify_all()
+
+    def submit(self, frame):
+        self.q.put((self.submitted, frame))
+        self.submitted += 1
+
+    def pop_ready(self):
+        """The next message in arrival order if its decode has finished, else None."""
+        with self.lock:
+            if self.committed in self.done:
+                res = self.done.pop(self.committed)
+                self.committed += 1
+                self.cv.notify_all()
+                return res
+        return None
+
+    @property
+    def backlog(self):
+        return self.submitted - self.committed
+
+    def wait_next(self, timeout):
+        with self.cv:
+            if self.committed not in self.done and self.backlog:
+                self.cv.wait(timeout)
+
+    def hold(self, slab, stream):
+        """The host->device copy out of `slab` was just enqueued on `stream`: recycle it once that has run."""
+        import torch
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.ExternalStream(stream, device=self.device))
+        self.busy.append((ev, slab))
+
+    def release(self, slab):
+        with self.cv:
+            self.free.append(slab)
+            self.free.sort(key=lambda t: -t.numel())
+            self.cv.notify_all()
+
+    def retire(self):
+        while self.busy and self.busy[0][0].query():
+            self.release(self.busy.pop(0)[1])
+
+    def close(self):
+        for _ in self.threads:
+            self.q.put(None)
+
+
 def server_main(capacity, batch_size, host, ports, samplers, cache_policy, device, max_ring, ready_evt, frames=None, float_frames=None):
     """Body of the server process (main_loop.py:110-216 + append_loop + sampler_loop in one loop)."""
     import zmq
@@ -63,10 +182,23 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
 
     signal.signal(signal.SIGINT, signal.SIG_IGN)
     stop = {"flag": False}
-    signal.signal(signal.SIGTERM, lambda *_: stop.__setitem__("flag", True))
+
+    def on_term(*_):
+        # leave the loop; if that has not happened 10 s later, say where every thread stands and exit anyway:
+        # proc.terminate() + proc.join() (trainer.py:72-74) must never hang its caller
+        import faulthandler
+        stop["flag"] = True
+        faulthandler.dump_traceback_later(10, exit=True)
+        if os.environ.get("RETH_B200_DEBUG") and "ingest" in stop:
+            g = stop["ingest"]
+            print(f"reth_b200 server: ingest submitted {g.submitted} committed {g.committed} decoded-waiting {sorted(g.done)[:8]} "
+                  f"slabs {g.slabs} free {len(g.free)} busy {len(g.busy)} "
+                  f"busy[0] done {g.busy[0][0].query() if g.busy else None}", file=sys.stderr, flush=True)
+    signal.signal(signal.SIGTERM, on_term)
 
     eng = service._Engine(capacity, batch_size, samplers, cache_policy, device, max_ring, float_frames=float_frames, frames=frames)
     ctx = zmq.Context.instance()
+    ctx.set(zmq.IO_THREADS, int(os.environ.get("RETH_B200_IO_THREADS", "4")))   # many actor connections (worker.py:22,57-61)
     ctx.setsockopt(zmq.LINGER, 0)
     addrs = {k: f"tcp://{host}:{p}" for k, p in ports.items()}
     meta = ctx.socket(zmq.REP)
@@ -88,6 +220,8 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
     poller = zmq.Poller()
     for s in (meta, app, upd, ldr):
         poller.register(s, zmq.POLLIN)
+    ingest = _Ingest(int(os.environ.get("RETH_B200_INGEST_THREADS", "4")), device)
+    stop["ingest"] = ingest
     waiting = []                 # loader requests parked until the buffer is ready (sampler_loop.py:25-28)
     owed = []                    # loaders that asked for a group which is still being drawn / gathered
     seen = {}                    # client id -> [last append message, last update frame] taken in
@@ -152,25 +286,40 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
         eng.update_block(idx, w, sizes, steps)
         seen.setdefault(cid.hex(), [0, 0])[1] = seq
 
-    def drain_appends():
+    def drain_appends(wait=False):
+        """Receive every pending append frame (decoded by the ingest threads), then commit what has been decoded,
+        strictly in arrival order.  wait: block until everything received so far is committed (a loader's request
+        named these writes, or updates that must stay behind them are about to be applied)."""
         while True:
             try:
-                frame = app.recv(zmq.NOBLOCK, copy=False)
+                ingest.submit(app.recv(zmq.NOBLOCK, copy=False))
             except zmq.Again:
+                break
+        while True:
+            res = ingest.pop_ready()
+            if res is None:
+                if wait and ingest.backlog:
+                    retire_ring_copies()
+                    ingest.retire()                    # the decode threads may be waiting for a staging slab
+                    ingest.wait_next(0.002)
+                    continue
                 break
             src = None
             try:
-                src = take_append(frame)
+                if isinstance(res, Exception):
+                    raise res
+                src = take_append(*res)
             except Exception as e:                     # one bad message from one actor must not stop the server
                 dropped["append"] += 1
                 print(f"reth_b200 server: append message dropped ({type(e).__name__}: {e})", file=sys.stderr, flush=True)
             if src:
                 seen.setdefault(src[0], [0, 0])[0] = int(src[1])
             retire_ring_copies()
+            ingest.retire()
         retire_ring_copies()
+        ingest.retire()
 
-    def take_append(frame):
-        kind, payload, weights, src = pack.open_append(frame.buffer)
+    def take_append(kind, payload, weights, src, slab):
         if kind == "steps":
             head, frames, others = payload
             reset = head.get("reset")
@@ -184,6 +333,11 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
                       file=sys.stderr, flush=True)
         else:
             eng.append(payload, weights)
+        if slab is not None:                       # the columns sit in pinned staging: the copy is asynchronous
+            if eng.stream is not None:
+                ingest.hold(slab, eng.stream)
+            else:
+                ingest.release(slab)
         return src
 
     def drain_updates():
@@ -192,6 +346,8 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
                 frame = upd.recv(zmq.NOBLOCK, copy=False)
             except zmq.Again:
                 break
+            if ingest.backlog:                         # appends received earlier are applied first (one total order)
+                drain_appends(wait=True)
             try:
                 apply_updates(frame.buffer)
             except Exception as e:
@@ -209,7 +365,7 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
         t0 = time.time()
         while behind() and time.time() - t0 < timeout:
             poller.poll(1)
-            drain_appends()
+            drain_appends(wait=True)
             drain_updates()
         if behind():                                   # a write named by the request never arrived (dropped / lost)
             dropped["late"] += 1
@@ -218,6 +374,8 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
 
     def handle_loader(ident, req):
         op = req.get("op")
+        if ingest.backlog:
+            drain_appends(wait=True)                   # drain every pending write before serving a draw (sampler_loop.py:29-36)
         await_writes(req.get("after"))
         if op == "open":
             if eng.shard is None:                      # row struct unknown until the first append
@@ -257,6 +415,9 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
         elif op == "rows":                             # NumpyLoader: rows of a lent slot, device -> host
             data, _, _ = eng.shard.slot_read(int(req["slot"]), with_rows=True, stream=eng.stream)
             reply(ident, {"ok": True, "op": "rows"}, *[np.ascontiguousarray(c).tobytes() for c in data])
+        elif op == "ring":                             # parity / debug: rows [first, first + n) of a ring column
+            col = eng.shard.ring_read(int(req["column"]), int(req["first"]), int(req["n"]), stream=eng.stream)
+            reply(ident, {"ok": True, "op": "ring", "dtype": col.dtype.str, "shape": list(col.shape)}, col.tobytes())
         elif op == "close":
             owed[:] = [i for i in owed if i != ident]
             if req.get("topic", eng.topic) == eng.topic:
@@ -273,7 +434,7 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
         while not stop["flag"]:
             # a delivery is owed, or traffic within the last 2 ms: spin (a blocking poll costs a scheduler
             # wake-up per message; the reference's sampler loop spins in zmq.select too, sampler_loop.py:22-24)
-            busy = owed or (eng.loaders > 0 and time.perf_counter() - last_traffic < 0.002)
+            busy = owed or ingest.backlog or (eng.loaders > 0 and time.perf_counter() - last_traffic < 0.002)
             events = dict(poller.poll(0 if busy else (1 if pending else 50)))
             if events:
                 last_traffic = time.perf_counter()
@@ -300,6 +461,7 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
                     reply(ident, {"ok": False, "op": req.get("op"), "error": f"{type(e).__name__}: {e}"})
             deliver()
     finally:
+        ingest.close()
         eng.close()
         for seg in segments.values():
             seg.close()
@@ -785,6 +947,11 @@ class _RemoteLoader:
         rc = self._lib.reth_ipc_slot_ptrs(self._view, int(slot), cols, C.byref(ip), C.byref(wp))
         assert rc == 0
         return [cols[c] for c in range(self._ncols)], ip.value, wp.value
+
+    def ring_read(self, column, first, n):
+        """Parity / debug (reth_replay_ring_read): rows [first, first + n) of ring column `column` as stored."""
+        head, blobs = self._call({"op": "ring", "column": int(column), "first": int(first), "n": int(n)})
+        return np.frombuffer(blobs[0], np.dtype(head["dtype"])).reshape(head["shape"])
 
     def drain(self):
         """Block until the server has executed everything it has received so far; -> {"cnt": ...}."""

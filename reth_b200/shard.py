@@ -694,13 +694,26 @@ class ReplayShard:
 
     def step_loop(self, steps, batch, prio_dev, uniforms_dev=None, seed=0, alpha=0.6, beta=0.4,
                   gather=True, serial=False, time_gather=False, sample=True, update=True, group=1,
-                  one_gather_stream=False, global_mode=False, stream=None):
+                  one_gather_stream=False, global_mode=False, stream=None, ingest=None):
+        """ingest = (device columns, device float32 priorities): after every group of `group` learner steps those
+        rows are appended without draining the loop (reth_replay_step_loop_ingest, BASELINE config 4)."""
         pp, ploc, pdt, pcnt, pk = _ptr_loc(prio_dev)
         assert ploc == DEVICE and pdt == np.dtype(np.float32) and pcnt >= steps * batch
         up, uloc, udt, ucnt, uk = _ptr_loc(uniforms_dev)
         if uniforms_dev is not None:
             assert uloc == DEVICE and udt == np.dtype(np.float64) and ucnt >= steps * batch
         flags = (0 if gather else 1) | (2 if serial else 0) | (4 if time_gather else 0) | (0 if sample else 8) | (0 if update else 16) | (32 if one_gather_stream else 0) | (64 if global_mode else 0) | ((int(group) & 0xff) << 8)
+        if ingest is not None:
+            icols, iprio = ingest
+            ip, iloc, idt, n, ik = _ptr_loc(iprio)
+            assert iloc == DEVICE and idt == np.dtype(np.float32)
+            ptrs, cloc, ckeep = self._cols(icols, n)
+            assert cloc == DEVICE
+            self._ck(self._lib.reth_replay_step_loop_ingest(self._h, int(steps), int(batch), pp, up,
+                                                            int(seed) & (2**64 - 1), float(alpha), float(beta), flags,
+                                                            ptrs, ip, n, self._s(stream)))
+            self._keep = (pk, uk, ik, ckeep)
+            return
         self._ck(self._lib.reth_replay_step_loop(self._h, int(steps), int(batch), pp, up,
                                                  int(seed) & (2**64 - 1), float(alpha), float(beta),
                                                  flags, self._s(stream)))

@@ -452,3 +452,48 @@ def test_capacity_2p24_tree_only(Shard):
     s, m, v = sh.tree_arrays()
     assert np.array_equal(s, ref._sum) and np.array_equal(m, ref._min)
     sh.close()
+
+
+def test_step_loop_ingest_matches_call_by_call(Shard):
+    """reth_replay_step_loop_ingest (config 4 without draining the loop: leaves on the tree stream, row copy behind the
+    gathers in flight, later gathers behind the copy) against the same operations issued one by one on a twin shard:
+    per group  sample_multi -> gather_multi -> update_slots -> append.  Trees and rings bit-identical, the batches of
+    the last group row for row; the ring (which wraps three times) against the oracle's."""
+    import torch
+    cap, B, G, groups, rows = 3000, 64, 4, 10, 1000
+    struct = [(np.uint8, (4, 84, 84)), (np.int64, ()), (np.float32, ())]
+    rng = np.random.default_rng(61)
+    fill = [rng.integers(0, 256, (cap, 4, 84, 84), dtype=np.uint8), np.arange(cap), rng.standard_normal(cap).astype(np.float32)]
+    fill_w = (rng.random(cap) + 0.05).astype(np.float32)
+    new = [rng.integers(0, 256, (rows, 4, 84, 84), dtype=np.uint8), 10 ** 6 + np.arange(rows), rng.standard_normal(rows).astype(np.float32)]
+    new_w = (rng.random(rows) + 0.05).astype(np.float32)
+    a, b = (Shard(cap, struct, max_batch=B, ring_depth=2 * G) for _ in range(2))
+    ring = po.OracleRing(cap, struct)
+    ring.append_batch(fill)
+    for sh in (a, b):
+        sh.append(fill, fill_w, alpha=0.5)
+    prio = torch.rand(groups * G * B, device="cuda", generator=torch.Generator(device="cuda").manual_seed(3)) + 0.01
+    dev_new = [torch.from_numpy(c).cuda() for c in new]
+    dev_w = torch.from_numpy(new_w).cuda()
+    a.step_loop(groups * G, B, prio, seed=77, alpha=0.5, beta=0.4, group=G, ingest=(dev_new, dev_w))
+    for k in range(groups):
+        first = (k % 2) * G
+        b.sample_multi(B, first, G, beta=0.4, seed=77)
+        b.gather_multi(first, G)
+        b.update_slots(first, G, prio[k * G * B:(k + 1) * G * B], alpha=0.5)
+        b.append(dev_new, dev_w, alpha=0.5)
+        ring.append_batch(new)
+    torch.cuda.synchronize()
+    for x, y in zip(a.tree_arrays(), b.tree_arrays()):
+        assert np.array_equal(x, y)
+    assert a.stats()["tail"] == b.stats()["tail"] == ring.tail and a.stats()["appended_rows"] == cap + groups * rows
+    for c in range(3):
+        got = a.ring_read(c, 0, cap)
+        assert np.array_equal(got, b.ring_read(c, 0, cap)) and np.array_equal(got, ring.column(c)), c
+    last = ((groups - 1) % 2) * G
+    for g in range(G):
+        da, ia, wa = a.slot_read(last + g, with_rows=True)
+        db, ib, wb = b.slot_read(last + g, with_rows=True)
+        assert np.array_equal(ia, ib) and np.array_equal(wa, wb)
+        for x, y in zip(da, db):
+            assert np.array_equal(x, y)

@@ -190,3 +190,61 @@ def test_mp_producers(reth_buffer):
     finally:
         proc.terminate()
         proc.join()
+
+
+@pytest.mark.timeout(240)
+def test_256_actor_connections_row_format(reth_buffer):
+    """BASELINE.json config 4 as worded -- 256 actor append streams: 256 concurrent PUSH connections
+    (worker.py:22,57-61) send 64-row messages in the reference's row wire format, half of them lz4-framed,
+    through the server's ingest threads.  Every row must land exactly once and self-consistent, the messages of
+    one connection in the order they were sent (slot = arrival order, fifo_policy.py:11-18); a malformed
+    message in between is dropped without stopping the server."""
+    import time
+    import zmq
+    from reth_b200 import pack, service_mp
+    n_conn, per_conn, rows, B = 256, 3, 64, 64
+    total = n_conn * per_conn * rows
+    proc, addr = reth_buffer.start_per(total, B, sample_start=B)
+    ctx = zmq.Context(2)
+    socks = []
+    try:
+        meta = service_mp.get_meta(addr)
+        for k in range(n_conn):
+            s = ctx.socket(zmq.PUSH)
+            s.connect(meta["append_addr"])
+            socks.append(s)
+        for m in range(per_conn):
+            for k, s in enumerate(socks):
+                ids = (k * per_conn + m) * rows + np.arange(rows)
+                cols = [ids, np.repeat(ids[:, None], 24, 1).astype(np.float32), np.full(rows, m, np.int32)]
+                s.send(pack.encode_append_rows(cols, np.ones(rows, np.float32), compress=bool(k & 1)), copy=False)
+            if m == 1:
+                socks[0].send(b"\x00\x00\x00\x02garbage")     # not a message: dropped, the server keeps going
+        loader = reth_buffer.NumpyLoader(addr)
+        t0 = time.time()
+        while True:
+            st = loader.drain()
+            if st["cnt"] >= total or time.time() - t0 > 90:
+                break
+            time.sleep(0.01)
+        assert st["cnt"] == total and st["dropped"]["append"] == 1
+        ids = loader.ring_read(0, 0, total)
+        feat = loader.ring_read(1, 0, total)
+        mcol = loader.ring_read(2, 0, total)
+        assert np.array_equal(np.sort(ids), np.arange(total))                     # every row exactly once
+        assert np.array_equal(feat, np.repeat(ids[:, None], 24, 1).astype(np.float32))
+        msg = ids // rows
+        assert np.array_equal(ids.reshape(-1, rows), (msg.reshape(-1, rows)[:, :1] * rows + np.arange(rows)))  # messages stay whole
+        assert np.array_equal(mcol, msg % per_conn)
+        conn, m = msg[::rows] // per_conn, msg[::rows] % per_conn
+        for k in range(n_conn):                                                    # per connection: arrival order = send order
+            assert np.array_equal(m[conn == k], np.arange(per_conn)), k
+        data, indices, weights = loader.sample()
+        assert np.array_equal(data[0], ids[indices])
+        loader.close()
+    finally:
+        for s in socks:
+            s.close(0)
+        ctx.term()
+        proc.terminate()
+        proc.join()
