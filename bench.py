@@ -435,7 +435,7 @@ def config4_loop(torch, shard, batch, group, rows_per_step, groups):
         for _ in range(0, k, chunk):
             # reth_replay_step_loop_ingest: after every group the actor rows are appended without draining the loop
             shard.step_loop(group * chunk, batch, prio, alpha=0.5, beta=0.4, group=group, ingest=(cols, w))
-    groups -= groups % chunk
+    groups = max(chunk, groups // chunk * chunk)
     loop(chunk)
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -535,7 +535,8 @@ def run_ours(args):
     if os.path.exists(tpath):
         try:
             tj = json.load(open(tpath))
-            if int(tj.get("rows_per_launch", -1)) == rows_per_launch:
+            # only a capture of THIS configuration counts (capacity, rows per launch); anything else stays null
+            if int(tj.get("rows_per_launch", -1)) == rows_per_launch and int(tj.get("capacity", -1)) == cap:
                 traffic = tj["dram_bytes_per_launch"]
         except Exception:
             pass

@@ -11,6 +11,8 @@
 
 #include <unistd.h>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "../../include/reth_replay.h"
 #include "copy.cuh"
 #include "lz4f.h"
@@ -182,6 +184,20 @@ cudaError_t dalloc_zero(T **p, size_t count, int64_t *acct)
 }
 
 inline cudaStream_t S(void *s) { return (cudaStream_t)s; }
+
+// NVTX ranges around the four stages of the path (append / draw / gather / repair), SURVEY.md 5 "Tracing": on with
+// RETH_NVTX=1 in the environment (a profiler attaches to them; without one the calls are no-ops of the header-only
+// NVTX v3 loader), off by default so that the enqueue path stays free of them.
+struct NvtxRange {
+    bool on;
+    explicit NvtxRange(const char *name)
+    {
+        static const bool enabled = [] { const char *e = getenv("RETH_NVTX"); return e && atoi(e) != 0; }();
+        on = enabled;
+        if (on) nvtxRangePushA(name);
+    }
+    ~NvtxRange() { if (on) nvtxRangePop(); }
+};
 
 struct DeviceGuard {
     int prev = -1;
@@ -566,6 +582,7 @@ int to_device(reth_replay *h, const void *p, int loc, size_t bytes, void *stagin
 // beyond -- normally nothing.  A write-back padded to 8 x the share then costs 2 launches on the chain, not 8..16.
 int launch_update(reth_replay *h, UpdateArgs &a, cudaStream_t s, int64_t n_expected = 0, bool critical = false)
 {
+    NvtxRange nvtx("reth:repair");
     if (a.n <= 0) return RETH_OK;
     a.g = h->geom; a.desc = h->desc; a.agg = h->agg; a.stamp = h->stamp; a.mask = h->mask;
     a.err = h->err; a.dbg = h->dbg;
@@ -767,6 +784,7 @@ RETH_EXPORT int reth_replay_append(reth_replay_t *h, const void *const *cols, in
                                    const void *prio, int prio_dtype, int prio_loc, int64_t n,
                                    double alpha, int transform, int64_t *first_slot_out, void *stream)
 {
+    NvtxRange nvtx("reth:append");
     if (!h) return RETH_ERR_INVALID;
     if (n < 0 || n > h->cfg.capacity)   // fifo_policy.py:12
         return fail(h, RETH_ERR_INVALID, "append of %lld rows exceeds capacity", (long long)n);
@@ -928,6 +946,7 @@ RETH_EXPORT int reth_replay_append_nstep(reth_replay_t *h, int stream_id, const 
                                          const void *prio, int prio_dtype, int prio_loc, int64_t n, double alpha,
                                          int transform, int64_t *first_slot_out, int64_t *emitted_out, void *stream)
 {
+    NvtxRange nvtx("reth:append_nstep");
     if (!h) return RETH_ERR_INVALID;
     auto &ns = h->nstep;
     if (!ns.open) return fail(h, RETH_ERR_STATE, "n-step assembly is not open");
@@ -1228,6 +1247,7 @@ int do_sample(reth_replay *h, int batch, const double *uniforms, int uniforms_lo
               double beta, int slot, const double *all_roots, int n_shards, int shard, cudaStream_t s,
               int groups = 1)
 {
+    NvtxRange nvtx("reth:draw");
     if (slot_ok(h, slot)) return RETH_ERR_INVALID;
     if (batch < 1 || batch > h->cfg.max_batch)
         return fail(h, RETH_ERR_INVALID, "batch %d outside [1, max_batch=%d]", batch, h->cfg.max_batch);
@@ -1307,6 +1327,7 @@ int do_sample(reth_replay *h, int batch, const double *uniforms, int uniforms_lo
 // contiguous groups*batch index array and one contiguous output per column
 int do_gather(reth_replay *h, int slot, bool use_meta, cudaStream_t s, int groups = 1)
 {
+    NvtxRange nvtx("reth:gather");
     BatchSlot &b = h->slots[slot];
     if (!h->cfg.store_rows || h->cfg.n_columns == 0) return RETH_OK;
     const int64_t *meta = (use_meta && (groups == 1 || b.packed == groups)) ? b.meta : nullptr;
