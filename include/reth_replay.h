@@ -225,6 +225,16 @@ int reth_replay_slot_read(reth_replay_t *h, int slot, int64_t *indices, double *
 /* ---- parity / debug: the three arrays of NumbaSumTree in heap order (utils/sumtree.py:85-88).
  *      host double[capacity] each; any may be NULL.  Synchronises. */
 int reth_replay_tree_read(reth_replay_t *h, double *sum, double *min, double *val, void *stream);
+/* The same readback without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  tree_read() takes its device scratch from cudaMalloc on every call; this variant runs the same
+ * kernel into a static device array of 3 x RETH_NOALLOC_MAX_CAPACITY doubles (1.5 MB held by every GPU that loads the
+ * library, until exit) and calls no cudaMalloc / cudaFree / allocating library routine.  Shards with capacity >
+ * RETH_NOALLOC_MAX_CAPACITY are rejected with RETH_ERR_INVALID.  Every call on a GPU shares the array, which keeps
+ * the last call's contents (the kernel overwrites all it reads back, nothing needs clearing): calls that overlap on
+ * the same GPU race -- serialise them.  Same outputs as tree_read(), bit for bit.  Synchronises. */
+#define RETH_NOALLOC_MAX_CAPACITY 65536
+int reth_replay_tree_read_noalloc(reth_replay_t *h, double *sum, double *min, double *val, void *stream);
 /* root: sum() and min() as the reference defines them (utils/sumtree.py:106-110) */
 int reth_replay_tree_root(reth_replay_t *h, double *total, double *minimum, void *stream);
 /* Read rows straight from the ring (host out), for storage parity tests. */

@@ -105,6 +105,7 @@ SIGNATURES = {
     "reth_replay_slot_read": [_vp, _i32, _vp, _vp, _vp, _vp],
     "reth_replay_group_read": [_vp, _i32, _i32, _vp, _vp, _vp],
     "reth_replay_tree_read": [_vp, _vp, _vp, _vp, _vp],
+    "reth_replay_tree_read_noalloc": [_vp, _vp, _vp, _vp, _vp],
     "reth_replay_tree_root": [_vp, C.POINTER(_f64), C.POINTER(_f64), _vp],
     "reth_replay_ring_read": [_vp, _i32, _i64, _i64, _vp, _vp],
     "reth_replay_stats_get": [_vp, C.POINTER(Stats)],

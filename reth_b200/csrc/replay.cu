@@ -1579,6 +1579,57 @@ RETH_EXPORT int reth_replay_tree_read(reth_replay_t *h, double *sum, double *mn,
     return check_device_err(h, s);
 }
 
+// ---- tree_read without allocation (no counterpart in the reference).
+// reth_replay_tree_read() above takes its device scratch (three capacity-sized arrays in heap order) from cudaMalloc
+// on every call; callers that must not allocate (CUDA graph capture, tight serving loops, harnesses that forbid it)
+// get the same kernel writing into a file-scope device array instead.  The array is shared by every call on a GPU and
+// keeps the last call's contents: tree_read_kernel writes every element [0, capacity) of each requested array, so
+// nothing has to start at zero; two calls that overlap on the same GPU race on it.
+constexpr int64_t kNoAllocMaxCapacity = RETH_NOALLOC_MAX_CAPACITY;
+static __device__ __align__(256) double g_tree_scratch[3 * kNoAllocMaxCapacity];     // 1.5 MB on every GPU that loads the library
+
+namespace {
+// The array's name is a host-side stand-in in host code, not a device address: resolve it once per device, with that
+// device current, and hand the kernel the resolved pointer.
+int tree_scratch_ptr(reth_replay *h, double **out)
+{
+    static double *ptr[64] = {};
+    const int dev = h->cfg.device;
+    if (dev < 0 || dev >= 64) return fail(h, RETH_ERR_INVALID, "device ordinal %d out of range", dev);
+    if (!ptr[dev]) {
+        void *p = nullptr;
+        CK(h, cudaGetSymbolAddress(&p, g_tree_scratch));      // the caller holds a DeviceGuard for h->cfg.device
+        if (!p) return fail(h, RETH_ERR_CUDA, "cudaGetSymbolAddress returned a null scratch address");
+        ptr[dev] = (double *)p;
+    }
+    *out = ptr[dev];
+    return RETH_OK;
+}
+}  // namespace
+
+RETH_EXPORT int reth_replay_tree_read_noalloc(reth_replay_t *h, double *sum, double *mn, double *val, void *stream)
+{
+    if (!h) return RETH_ERR_INVALID;
+    const int64_t cap = h->cfg.capacity;
+    if (cap > kNoAllocMaxCapacity)
+        return fail(h, RETH_ERR_INVALID, "tree_read_noalloc: capacity %lld exceeds the static scratch (at most %lld nodes); "
+                                         "use reth_replay_tree_read", (long long)cap, (long long)kNoAllocMaxCapacity);
+    DeviceGuard guard(h->cfg.device);
+    cudaStream_t s = S(stream);
+    double *base = nullptr;
+    int rc = tree_scratch_ptr(h, &base);
+    if (rc) return rc;
+    double *host[3] = {sum, mn, val};
+    double *d[3] = {nullptr, nullptr, nullptr};
+    for (int k = 0; k < 3; ++k)
+        if (host[k]) d[k] = base + k * kNoAllocMaxCapacity;
+    tree_read_kernel<<<(unsigned)((cap + 255) / 256), 256, 0, s>>>(h->geom, h->desc, h->agg, d[0], d[1], d[2]);
+    CK(h, cudaGetLastError());
+    for (int k = 0; k < 3; ++k)
+        if (host[k]) CK(h, cudaMemcpyAsync(host[k], d[k], (size_t)cap * 8, cudaMemcpyDeviceToHost, s));
+    return check_device_err(h, s);                             // synchronises the stream
+}
+
 RETH_EXPORT int reth_replay_tree_root(reth_replay_t *h, double *total, double *minimum, void *stream)
 {
     if (!h) return RETH_ERR_INVALID;
