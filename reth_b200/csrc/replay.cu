@@ -1111,7 +1111,14 @@ int gather_warp_mode()
 void build_row_args(reth_replay *h, RowArgs &a, uint8_t *const *batch_cols, const int64_t *idx, int batch,
                     int units_target = 0, bool widen = false)
 {
-    if (units_target <= 0) units_target = gather_units_target();
+    if (units_target <= 0) {
+        units_target = gather_units_target();
+        // small launches (strict alternation, a Mode G share): the tree chain is what is critical there, and its
+        // cluster launch waits for gather CTAs to retire -- shorter-lived gather CTAs (8 KB items) cost the chain less
+        // (strict loop 25.1 -> 23.4 us per iteration, scripts/strict_probe.py)
+        static const bool fixed = getenv("RETH_GATHER_UNITS") != nullptr;
+        if (!fixed && batch <= 1024 && units_target > 512) units_target = 512;
+    }
     a = RowArgs{};
     a.ncols = h->cfg.n_columns;
     a.idx = idx;

@@ -2,6 +2,7 @@
 client.update_priorities(), split into calls that cross a group boundary (pipe_next / commit)
 and calls that do not.  Run on the GPU box:  python scripts/e2e_profile.py [group] [ahead]"""
 import json
+import os
 import sys
 import time
 
@@ -50,6 +51,10 @@ out = {"group": G, "ahead": A, "rate_M": N * B / tot / 1e6, "us_per_batch": tot 
        "update_inner_us": float(np.median(u[k != G - 1])), "update_commit_us": float(np.median(u[k == G - 1])),
        "sum_us_per_group": float(np.median(s[k != 0]) * (G - 1) + np.median(s[k == 0]) + np.median(u[k != G - 1]) * (G - 1)
                                  + np.median(u[k == G - 1]))}
+b = s[k == 0]
+out.update({"boundary_mean_us": float(b.mean()), "boundary_max_us": float(b.max()), "boundary_p99_us": float(np.percentile(b, 99)),
+            "boundary_over_100us": int((b > 100).sum()), "sample_inner_mean_us": float(s[k != 0].mean()), "sample_inner_max_us": float(s[k != 0].max()),
+            "update_mean_us": float(u.mean()), "update_max_us": float(u.max()), "n_groups": int(len(b))})
 print(json.dumps(out))
 loader.close()
 proc.terminate()
