@@ -647,6 +647,7 @@ def main():
     args = ap.parse_args()
     _claim_stdout()
     if args.warmup < 3 and args.impl == "ours":
+        log(f"--warmup {args.warmup} raised to 3 (timing rule: at least three untimed warm-up steps)")
         args.warmup = 3
     if args.impl == "reference":
         run_reference(args)

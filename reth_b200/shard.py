@@ -53,25 +53,15 @@ def _ptr_loc(x):
     return a.ctypes.data, HOST, a.dtype, a.size, a
 
 
-def _record_streams(keep, stream_handle, device):
-    """Device tensors handed to a call that runs on a raw (non-torch) stream: register that stream with torch's
-    caching allocator, so the memory is not reused while the library's kernels still read it."""
-    if not stream_handle:
-        return
-    ext = None
+def _has_cuda_tensor(keep):
     stack = [keep]
     while stack:
         x = stack.pop()
         if isinstance(x, (list, tuple)):
             stack.extend(x)
         elif x is not None and _is_torch(x) and x.is_cuda:
-            if ext is None:
-                import torch
-                cur = torch.cuda.current_stream(device)
-                if int(cur.cuda_stream) == int(stream_handle):
-                    return
-                ext = torch.cuda.ExternalStream(int(stream_handle), device=device)
-            x.record_stream(ext)
+            return True
+    return False
 
 
 def _stream_handle(stream, device):
@@ -276,8 +266,9 @@ class ReplayShard:
     # -- lifetime ---------------------------------------------------------
     def close(self):
         if self._h is not None:
-            self._lib.reth_replay_destroy(self._h)
+            self._lib.reth_replay_destroy(self._h)            # synchronises the device first
             self._h = None
+            self.__dict__.pop("_held", None)
 
     def __del__(self):
         try:
@@ -288,6 +279,25 @@ class ReplayShard:
     def _ck(self, rc):
         if rc != 0:
             _cabi.check(self._h, rc)
+
+    def _hold(self, keep, stream):
+        """Device tensors handed to a call that runs on a raw (non-torch) stream: keep them referenced until an event
+        recorded behind the call on that stream has completed, so torch's caching allocator cannot hand their memory
+        to somebody else while the library's kernels still read it.  (tensor.record_stream() would do the same, but
+        it makes the allocator record an event on OUR stream when the tensor is freed -- after close() has destroyed
+        the stream that aborts the process.)"""
+        h = _stream_handle(stream, self.device)
+        if not h or not _has_cuda_tensor(keep):
+            return
+        import torch
+        if int(torch.cuda.current_stream(self.device).cuda_stream) == int(h):
+            return                                            # the caller's own stream: torch orders the reuse itself
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.ExternalStream(int(h), device=self.device))
+        held = self.__dict__.setdefault("_held", [])
+        held.append((ev, keep))
+        while held and held[0][0].query():
+            held.pop(0)
 
     def _s(self, stream):
         return C.c_void_p(_stream_handle(stream, self.device))
@@ -344,7 +354,7 @@ class ReplayShard:
         self._ck(self._lib.reth_replay_append(self._h, ptrs, cloc, p, pdt, ploc, n, float(alpha),
                                               int(bool(transform)), C.byref(first), self._s(stream)))
         self._keep = (keep, pkeep)
-        _record_streams(self._keep, _stream_handle(stream, self.device), self.device)
+        self._hold(self._keep, stream)
         return first.value
 
     def nstep_open(self, n_streams, step, gamma, r_col=2, s1_col=3, done_col=4, max_rows=4096):
@@ -396,7 +406,7 @@ class ReplayShard:
         self._ck(self._lib.reth_replay_append_at(self._h, sp, sloc, ptrs, cloc, p, pdt, ploc, n,
                                                  float(alpha), int(bool(transform)), self._s(stream)))
         self._keep = (skeep, keep, pkeep)
-        _record_streams(self._keep, _stream_handle(stream, self.device), self.device)
+        self._hold(self._keep, stream)
 
     def update(self, indices, prio, alpha=0.6, transform=True, stream=None):
         """Client.update_priorities -> PERSampler.update."""
@@ -413,7 +423,7 @@ class ReplayShard:
                                               p, pdt, ploc, n, float(alpha), int(bool(transform)),
                                               self._s(stream)))
         self._keep = (ikeep, pkeep)
-        _record_streams(self._keep, _stream_handle(stream, self.device), self.device)
+        self._hold(self._keep, stream)
 
     def update_slot(self, slot, prio, alpha=0.6, transform=True, stream=None):
         p, pdt, ploc, pkeep = self._prio(prio, self.slot_batch(slot))

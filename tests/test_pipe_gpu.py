@@ -183,3 +183,45 @@ def test_service_pipeline_final_tree(mods, prefetch, ahead):
         l2.close()
     finally:
         proc.terminate()
+
+
+def test_appends_never_tear_rows_of_groups_in_flight(mods):
+    """gathers alternate between two streams and several groups are in flight; an append that recycles
+    sampled slots must wait for ALL of them (reth_replay_append waits for the newest gather of each gather stream), so
+    a gathered row is entirely old or entirely new -- across its bytes and across its columns -- never half and half
+    (the reference's LMDB rows are replaced atomically, server/main_loop.py:55-57).  Every row carries its version
+    in every byte of the frame column and in the scalar column."""
+    ReplayShard, _ = mods
+    import torch
+    cap, B, G, ahead = 2048, 256, 2, 2
+    struct = [(np.uint8, (4, 84, 84)), (np.int64, ())]
+    sh = ReplayShard(cap, struct, max_batch=B, ring_depth=(ahead + 2) * G)
+    stream = sh.pipe_stream
+
+    def rows(n, first_slot, version):
+        frames = torch.full((n, 4, 84, 84), version % 251, dtype=torch.uint8, device="cuda")
+        tag = (torch.arange(first_slot, first_slot + n, device="cuda") % cap) + version * cap
+        torch.cuda.current_stream().synchronize()      # the append runs on the shard's own stream, not on torch's
+        return [frames, tag]
+    sh.append(rows(cap, 0, 0), torch.ones(cap, device="cuda"), alpha=1.0, transform=False, stream=stream)
+    pipe = sh.open_pipe(B, G, seed=3)
+    for _ in range(ahead + 1):
+        pipe.issue(0.4)
+    version, tail = 0, 0
+    for it in range(40):
+        g = pipe.wait()
+        for k in range(G):
+            data, idx, _, _ = sh.slot_tensors(g * G + k)
+            frames, tag = data[0].reshape(B, -1), data[1]
+            v = tag // cap
+            assert torch.equal(tag % cap, idx), it                                 # the scalar column is the sampled slot's
+            assert bool((frames == (v % 251).to(torch.uint8)[:, None]).all()), it   # and the frames are the same version's
+        # recycle 768 slots (more than a third of the ring: in-flight groups have sampled many of them)
+        version += 1
+        n = 768
+        sh.append(rows(n, tail, version), torch.ones(n, device="cuda"), alpha=1.0, transform=False, stream=stream)
+        tail = (tail + n) % cap
+        pipe.issue(0.4)
+    pipe.drain()
+    pipe.close()
+    sh.close()
