@@ -57,11 +57,14 @@ def np_find_index(s_sum, s_val, targets):
 
 
 def np_tree_recompute(val):
-    """_sum / _min of a FULLY maintained tree from its leaves (_numba_maintain_node, utils/sumtree.py:5-21):
-    sum = (val + sum_l) + sum_r;  min = val (1 when 0), then the children's non-zero minima."""
+    """_sum / _min of a tree from its leaves (_numba_maintain_node, utils/sumtree.py:5-21):
+    sum = (val + sum_l) + sum_r;  min = val (1 when 0), then the children's non-zero minima.  A node has been
+    maintained -- and carries a non-zero min -- iff it or a descendant was ever written (written values are
+    positive: (w + 1e-6) ** alpha); never-maintained nodes keep sum = min = 0 as in the reference."""
     cap = len(val)
     s = np.zeros(cap + 2)
     m = np.zeros(cap + 2)
+    live = np.zeros(cap + 2, bool)
     d = int(np.floor(np.log2(cap)))
     while d >= 0:
         lo, hi = (1 << d) - 1, min((2 << d) - 1, cap)
@@ -72,7 +75,8 @@ def np_tree_recompute(val):
         ml, mr = m[l], m[r]
         mn = np.where((ml != 0.0) & (ml < mn), ml, mn)
         mn = np.where((mr != 0.0) & (mr < mn), mr, mn)
-        m[i] = mn
+        live[i] = (val[i] != 0.0) | live[l] | live[r]
+        m[i] = np.where(live[i], mn, 0.0)
         d -= 1
     return s[:cap], m[:cap]
 
