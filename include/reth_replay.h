@@ -266,7 +266,9 @@ int reth_replay_slot_meta(reth_replay_t *h, int slot, int64_t *first_count, void
  *  UniformSampler (sampler/uniform_sampler.py:6-25): uniform_note() is its update(): the first
  *  `capacity` notified indices are logged in arrival order (appends AND priority updates notify, as
  *  in the reference where both travel the update channel, main_loop.py:58); the reference raises
- *  IndexError when a message crosses the capacity of the log, here the excess is dropped.
+ *  IndexError when a message crosses the capacity of the log; the C ABI drops the excess (the server keeps running,
+ *  where the reference's sampler process would die) and the plugin class reth_b200.sampler.UniformSampler raises
+ *  IndexError after the log has been filled, like the reference.
  *  append_note != 0 on reth_replay_append-style FIFO slots: idx == NULL, slots first_slot.. mod capacity.
  *  sample_uniform(): positions = draws[n] in [0, tail) (parity: the reference uses
  *  np.random.choice(tail, batch)) or NULL = device generator; weights are 1.

@@ -150,7 +150,12 @@ class UniformSampler(BaseSampler):
         return indices, np.ones(batch_size, dtype="i8")
 
     def update(self, indices, weights):
-        self.shard.uniform_note(indices)
+        tail = self.tail
+        self.shard.uniform_note(indices)                 # logs up to capacity, a full log ignores the message (:18-19)
+        if tail < self.capacity < tail + len(indices):
+            # the reference writes element by element and runs off the end of its log when a message CROSSES the
+            # capacity (uniform_sampler.py:20-22: indices[capacity] = idx): same state (log filled), same exception
+            raise IndexError(f"index {self.capacity} is out of bounds for axis 0 with size {self.capacity}")
 
     def clear(self):
         self.shard.clear()

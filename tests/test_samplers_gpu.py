@@ -38,6 +38,13 @@ def test_plugins_golden(mods, golden):
         sampler.FIFOSampler(10, max_batch=8).sample(4)             # nothing queued: ready_sample is False
     us.clear()
     assert us.tail == 0
+    # a message that crosses the capacity fills the log and raises like the reference (uniform_sampler.py:20-22)
+    us.update(np.arange(290), np.ones(290))
+    with pytest.raises(IndexError):
+        us.update(np.arange(20), np.ones(20))
+    assert us.tail == 300
+    us.update(np.arange(5), np.ones(5))                            # a full log ignores further messages (:18-19)
+    assert us.tail == 300
 
 
 def test_plugins_with_rows_and_pipe(mods):
