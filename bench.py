@@ -608,12 +608,11 @@ def run_ours(args):
     proc.terminate()
     if rank == 0 and world == 1 and not args.no_process:
         import bench_process
-        try:
-            line["e2e_process"] = bench_process.e2e_process(batch=B)
-        except Exception as e:
-            log(f"e2e_process failed: {e!r}")
-            line["e2e_process"] = {"error": repr(e)}
-        line["ingest_256"] = bench_process.ingest_256(log)
+        line["e2e_process"] = bench_process.run_leg("e2e_process", 180, batch=B)
+        line["ingest_256"] = bench_process.run_leg("ingest_256", 240)
+        for k in ("e2e_process", "ingest_256"):
+            if "error" in line[k]:
+                log(f"{k} failed: {line[k]['error']}")
     if rank == 0:
         emit(line)
     if world > 1:

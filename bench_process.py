@@ -83,3 +83,36 @@ def ingest_256(log=None):
                    "transpose in one library call) -> pinned staging -> asynchronous H2D -> ring append + tree update; "
                    "messages are encoded once and re-sent (the per-row Python encode is the actor's cost)")
     return out
+
+
+# ---- isolation: each leg runs in a child process (own session) under a deadline, so that a hung server or a lost
+# message can cost the bench line one key, never the line
+def _leg_main(name, kwargs, q):
+    os.setsid()
+    sys.path.insert(0, ROOT)
+    try:
+        q.put(("ok", globals()[name](**kwargs)))
+    except BaseException as e:                                  # noqa: BLE001 -- reported to the parent
+        q.put(("error", repr(e)))
+
+
+def run_leg(name, timeout_s=180, **kwargs):
+    """-> the leg's dict, or {"error": ...}.  name: "e2e_process" | "ingest_256"."""
+    import multiprocessing as mp
+    import signal
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    p = ctx.Process(target=_leg_main, args=(name, kwargs, q))
+    p.start()
+    try:
+        kind, val = q.get(timeout=timeout_s)
+    except Exception:
+        kind, val = "error", f"no result within {timeout_s} s"
+    p.join(10)
+    if p.is_alive() or kind == "error":
+        try:
+            os.killpg(p.pid, signal.SIGKILL)                    # the leg and whatever it spawned
+        except Exception:
+            pass
+        p.join(5)
+    return val if kind == "ok" else {"error": val}

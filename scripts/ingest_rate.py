@@ -38,7 +38,10 @@ def run(n_conn=256, msgs_per_conn=8, rows=64, compress=False, sender_threads=8, 
         for s in socks:
             s.send(msg, copy=False)
         total = n_conn * (msgs_per_conn + 1) * rows
+        deadline = time.time() + 60
         while loader.drain()["cnt"] < n_conn * rows:
+            if time.time() > deadline:
+                raise TimeoutError("ingest warm-up: the server did not take in one message per connection within 60 s")
             time.sleep(0.01)
 
         def sender(k):
@@ -51,10 +54,13 @@ def run(n_conn=256, msgs_per_conn=8, rows=64, compress=False, sender_threads=8, 
         [t.start() for t in th]
         [t.join() for t in th]
         t_sent = time.perf_counter() - t0
+        deadline = time.time() + 120
         while True:
             st = loader.drain()
             if st["cnt"] >= total:
                 break
+            if time.time() > deadline or st.get("dropped", {}).get("append"):
+                raise TimeoutError(f"ingest: {st['cnt']} of {total} rows taken in (dropped: {st.get('dropped')})")
             time.sleep(0.002)
         dt = time.perf_counter() - t0
         n = n_conn * msgs_per_conn * rows
