@@ -77,7 +77,7 @@ def ingest_256(log=None):
             if log:
                 log(f"ingest_256 {name} failed: {e!r}")
     out["connections"], out["rows_per_message"] = 256, 64
-    out["ingest_threads"] = int(os.environ.get("RETH_B200_INGEST_THREADS", "4"))
+    out["ingest_threads"] = int(os.environ.get("RETH_B200_INGEST_THREADS", 0)) or max(2, min(8, (os.cpu_count() or 4) // 2))
     out["note"] = ("256 concurrent ZeroMQ PUSH connections (one per actor) x 64-row messages in the reference's row wire "
                    "format into the server process: ZeroMQ I/O threads -> decode threads (header, lz4, row->column "
                    "transpose in one library call) -> pinned staging -> asynchronous H2D -> ring append + tree update; "

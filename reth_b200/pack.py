@@ -19,6 +19,7 @@ with one strided copy per column instead of the reference's per-row Python loop
 (client/numpy_loader.py:35-50).  This build's own clients send the columns directly
 (`encode([columns, weights])` with COLUMNAR set in the header), which skips the row split.
 """
+import threading
 import time
 
 import msgpack
@@ -41,11 +42,15 @@ def _native():
 
 def lz4_compress(buf):
     """lz4.frame.compress(buf) (utils/pack.py:69) -> uint8 array holding one LZ4 frame."""
-    try:
-        import lz4.frame
-        return np.frombuffer(lz4.frame.compress(buf, return_bytearray=True), np.uint8)
-    except ImportError:
-        pass
+    global _LZ4_PKG
+    if _LZ4_PKG is None:
+        try:
+            import lz4.frame
+            _LZ4_PKG = lz4.frame
+        except ImportError:
+            _LZ4_PKG = False
+    if _LZ4_PKG:
+        return np.frombuffer(_LZ4_PKG.compress(buf, return_bytearray=True), np.uint8)
     src = np.ascontiguousarray(np.frombuffer(buf, np.uint8))
     L = _native()
     out = np.empty(L.reth_lz4f_compress_bound(src.size), np.uint8)
@@ -59,13 +64,31 @@ _LZ4F_ERR = {-1: "truncated frame", -2: "malformed frame", -3: "checksum mismatc
              -5: "frames with a dictionary id are not supported"}
 
 
-def lz4_decompress(buf):
-    """lz4.frame.decompress(buf) (utils/pack.py:155) -> uint8 array."""
-    try:
-        import lz4.frame
-        return np.frombuffer(lz4.frame.decompress(buf, return_bytearray=True), np.uint8)
-    except ImportError:
-        pass
+_LZ4_PKG = None          # the `lz4` package: None = not probed yet, False = absent (a failed import is not cached by Python)
+_SCRATCH = threading.local()
+
+
+def _scratch(nbytes):
+    """A per-thread buffer that is reused from call to call (warm pages: a fresh 3.6 MB array per message costs
+    more in page faults than the decode itself)."""
+    buf = getattr(_SCRATCH, "buf", None)
+    if buf is None or buf.size < nbytes:
+        buf = _SCRATCH.buf = np.empty(max(nbytes, 1 << 20), np.uint8)
+    return buf[:nbytes]
+
+
+def lz4_decompress(buf, reuse=False):
+    """lz4.frame.decompress(buf) (utils/pack.py:155) -> uint8 array.  reuse: the result may live in this thread's
+    scratch buffer, i.e. it is only valid until the thread's next call (callers that copy everything out at once)."""
+    global _LZ4_PKG
+    if _LZ4_PKG is None:
+        try:
+            import lz4.frame
+            _LZ4_PKG = lz4.frame
+        except ImportError:
+            _LZ4_PKG = False
+    if _LZ4_PKG:
+        return np.frombuffer(_LZ4_PKG.decompress(buf, return_bytearray=True), np.uint8)
     src = np.ascontiguousarray(np.frombuffer(buf, np.uint8))
     L = _native()
     size = L.reth_lz4f_content_size(src.ctypes.data, src.size)
@@ -75,7 +98,7 @@ def lz4_decompress(buf):
         raise ValueError("lz4 frame: the stored content size is not credible")
     cap = size if size >= 0 else max(4 * src.size, 1 << 16)
     while True:
-        out = np.empty(cap, np.uint8)
+        out = _scratch(cap) if reuse else np.empty(cap, np.uint8)
         n = L.reth_lz4f_decompress(src.ctypes.data, src.size, out.ctypes.data, cap)
         if n == -4 and cap < (1 << 40):                       # size not stored / concatenated frames: grow
             cap = max(4 * cap, 1 << 16)
@@ -161,7 +184,8 @@ def encode(obj, compress=False, columnar=False, now=None, extra=None):
     return out.data
 
 
-def _split(buf):
+def _split(buf, reuse=None):
+    """reuse(header) -> bool: the decompressed body may live in the thread's scratch buffer (see lz4_decompress)."""
     mv = memoryview(buf).cast("B")
     hl = int.from_bytes(mv[:4], "big")
     header = msgpack.unpackb(mv[4:4 + hl])
@@ -169,7 +193,7 @@ def _split(buf):
     if body.nbytes != header["body_len"]:
         raise ValueError("truncated message: body_len does not match")
     if header.get(KEY_COMPRESS):
-        body = memoryview(lz4_decompress(body))
+        body = memoryview(lz4_decompress(body, reuse=bool(reuse and reuse(header))))
     return header, body, 4 + hl
 
 
@@ -230,7 +254,13 @@ def open_append(buf, alloc=None):
     src = the sender's [client id, message number] or None (a reference client).
     alloc(nbytes) -> writable uint8 buffer: where the columns of a "columns" message are put (pinned staging
     memory on the server's ingest threads); default: fresh arrays."""
-    header, body, _ = _split(buf)
+    def plain_columns(header):
+        # row / columnar appends with a destination allocator copy every byte out of the body before they return
+        # (scatter / _place / np.array(weights)): the decompressed body can live in the thread's scratch buffer
+        m = header["meta"]
+        special = isinstance(m, list) and m and isinstance(m[0], dict) and (KEY_SHM in m[0] or KEY_STEPS in m[0])
+        return alloc is not None and not special
+    header, body, _ = _split(buf, plain_columns)
     meta = header["meta"]
     src = header.get(KEY_SRC)
     if isinstance(meta, list) and len(meta) == 2 and isinstance(meta[0], dict) and KEY_SHM in meta[0]:

@@ -56,6 +56,12 @@ def _pick_port(host):
 
 
 # ------------------------------------------------------------------ server --
+def _default_ingest_threads():
+    """Decode threads of the ingest: half the host's cores, between 2 and 8 (the decode -- lz4 frame, row scatter --
+    runs in the library with the GIL released)."""
+    return max(2, min(8, (os.cpu_count() or 4) // 2))
+
+
 class _Ingest:
     """Decode threads of the server's ingest (replaces the single append_loop process,
     server/main_loop.py:21-61, as the ceiling of the service's append rate).
@@ -220,7 +226,7 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
     poller = zmq.Poller()
     for s in (meta, app, upd, ldr):
         poller.register(s, zmq.POLLIN)
-    ingest = _Ingest(int(os.environ.get("RETH_B200_INGEST_THREADS", "4")), device)
+    ingest = _Ingest(int(os.environ.get("RETH_B200_INGEST_THREADS", str(_default_ingest_threads()))), device)
     stop["ingest"] = ingest
     waiting = []                 # loader requests parked until the buffer is ready (sampler_loop.py:25-28)
     owed = []                    # loaders that asked for a group which is still being drawn / gathered

@@ -67,7 +67,7 @@ def run(n_conn=256, msgs_per_conn=8, rows=64, compress=False, sender_threads=8, 
         out = {"connections": n_conn, "rows_per_message": rows, "messages": n_conn * msgs_per_conn, "wire": wire,
                "compress": bool(compress), "message_bytes": len(msg), "rows_per_s": n / dt, "wire_GBps": n_conn * msgs_per_conn * len(msg) / dt / 1e9,
                "seconds": dt, "send_seconds": t_sent, "dropped": st.get("dropped"),
-               "ingest_threads": int(os.environ.get("RETH_B200_INGEST_THREADS", "4"))}
+               "ingest_threads": int(os.environ.get("RETH_B200_INGEST_THREADS", 0)) or max(2, min(8, (os.cpu_count() or 4) // 2))}
         loader.close()
         for s in socks:
             s.close(0)
