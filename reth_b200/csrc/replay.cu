@@ -2651,6 +2651,9 @@ int step_loop_impl(reth_replay_t *h, int steps, int batch, const float *prio_dev
     if (ing && !serial) {
         CK(h, cudaEventRecord(h->ev_app_done, h->s_append));
         CK(h, cudaStreamWaitEvent(s, h->ev_app_done, 0));
+        // whoever gathers next (another call of the loop, a loader pipe) may have drawn the rows of the last copy
+        CK(h, cudaStreamWaitEvent(h->s_gather, h->ev_app_done, 0));
+        CK(h, cudaStreamWaitEvent(h->s_gather2, h->ev_app_done, 0));
     }
     if (!serial) {
         CK(h, cudaEventRecord(h->ev_join_t, st));
