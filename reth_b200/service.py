@@ -44,7 +44,13 @@ class _Engine:
     of a pre-sampled group (ShardPipe.wait)."""
 
     def __init__(self, capacity, batch_size, samplers=None, cache_policy=None, device=0, max_ring=16,
-                 float_frames=None, frames=None):
+                 float_frames=None, frames=None, nstep=None):
+        # nstep = {"step": n, "gamma": g, "streams": 256, "r_col": 2, "s1_col": 3, "done_col": 4}: producers send their
+        # RAW 1-step rows and the shard assembles the n-step transitions while it appends (reth_replay_append_nstep;
+        # replaces NStepAdder on the actor, reth/reth/utils/nstep_adder.py:11-28, test/apex-dqn/worker.py:35,53).
+        # Every Client is one environment stream, as every reference worker owns one adder.
+        self.nstep = dict(nstep) if nstep else None
+        self._nstep_streams = {}
         self.float_frames = float_frames                      # None | "f32" | "f32/255": see ReplayShard(out_cast=)
         # frames = {"k": stack depth, "shape": frame shape, "capacity": frames in the frame ring,
         #           "columns": (0, 3)}: frame-de-duplicated rows, fed through append_steps()
@@ -235,11 +241,28 @@ class _Engine:
                 self._notify_append(first, None, wts)
                 self.cnt += n
 
-    def append(self, data, weights):
+    def append(self, data, weights, stream_key=None):
         with self.lock:
             self._ensure_shard(data)
             self.flush()                                      # staged write-backs land before the rows that may recycle their slots
             alpha = self.sampler["alpha"].value()
+            if self.nstep is not None:
+                if self.cache_policy is not None or self.secondary or self.kind != "per":
+                    raise ValueError("n-step assembly serves one PER topic with the FIFO policy")
+                ns = self.nstep
+                if stream_key is None:
+                    raise ValueError("n-step assembly needs messages that name their producer (this build's Client does; "
+                                     "an unmodified reference actor keeps folding with its own NStepAdder)")
+                if not self._nstep_streams:
+                    self.shard.nstep_open(int(ns.get("streams", 256)), int(ns["step"]), float(ns["gamma"]),
+                                          r_col=int(ns.get("r_col", 2)), s1_col=int(ns.get("s1_col", 3)),
+                                          done_col=int(ns.get("done_col", 4)), max_rows=int(ns.get("max_rows", 4096)))
+                sid = self._nstep_streams.setdefault(stream_key, len(self._nstep_streams))
+                if sid >= int(ns.get("streams", 256)):
+                    raise ValueError(f"more than {ns.get('streams', 256)} producer streams: raise nstep['streams']")
+                _, emitted = self.shard.append_nstep(sid, list(data), weights, alpha=alpha, transform=True, stream=self.stream)
+                self.cnt += emitted                           # rows that left the adder, as the reference counts stored rows
+                return
             if self.cache_policy is None:
                 first = self.shard.append(list(data), weights, alpha=alpha, transform=True, stream=self.stream)
                 if self.kind == "uniform":                    # the append notice every sampler receives (main_loop.py:58)
@@ -539,20 +562,20 @@ class _ServerHandle:
 
 
 def start_server(capacity, batch_size, host=None, port=None, samplers=None, cache_policy=None, device=0,
-                 max_ring=16, float_frames=None, frames=None):
+                 max_ring=16, float_frames=None, frames=None, nstep=None):
     """reth_buffer.start_server (__init__.py:11-27).  host/port are accepted for signature
     compatibility; the engine is reached through the returned in-process address."""
     addr = f"{_SCHEME}{next(_COUNTER)}"
-    _ENGINES[addr] = _Engine(capacity, batch_size, samplers, cache_policy, device, max_ring, float_frames, frames)
+    _ENGINES[addr] = _Engine(capacity, batch_size, samplers, cache_policy, device, max_ring, float_frames, frames, nstep)
     return _ServerHandle(addr), addr
 
 
 def start_per(capacity, batch_size, alpha=0.6, beta=0.4, sample_start=1000, num_sampler_procs=1,
-              host=None, port=None, cache_policy=None, device=0, max_ring=16, float_frames=None, frames=None):
+              host=None, port=None, cache_policy=None, device=0, max_ring=16, float_frames=None, frames=None, nstep=None):
     """reth_buffer.start_per (__init__.py:30-49)."""
     samplers = [{"sampler_cls": PERSampler, "num_procs": num_sampler_procs, "sample_start": sample_start,
                  "kwargs": {"alpha": alpha, "beta": beta}}]
-    return start_server(capacity, batch_size, host, port, samplers, cache_policy, device, max_ring, float_frames, frames)
+    return start_server(capacity, batch_size, host, port, samplers, cache_policy, device, max_ring, float_frames, frames, nstep)
 
 
 def _engine(meta_addr):
@@ -585,7 +608,7 @@ class Client:
         for col in data:
             assert isinstance(col, np.ndarray)                # :24
             assert len(col) == len(weights)                   # :25
-        self._eng.append(data, np.asarray(weights))
+        self._eng.append(data, np.asarray(weights), stream_key=id(self))
 
     def append_steps(self, env, frames, others, weights, reset=None):
         """Frame-de-duplicated ingest for a buffer started with frames=...: see _Engine.append_steps."""

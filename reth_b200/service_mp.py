@@ -181,7 +181,8 @@ class _Ingest:
             self.q.put(None)
 
 
-def server_main(capacity, batch_size, host, ports, samplers, cache_policy, device, max_ring, ready_evt, frames=None, float_frames=None):
+def server_main(capacity, batch_size, host, ports, samplers, cache_policy, device, max_ring, ready_evt, frames=None, float_frames=None,
+                nstep=None):
     """Body of the server process (main_loop.py:110-216 + append_loop + sampler_loop in one loop)."""
     import zmq
     from . import _cabi, service
@@ -202,7 +203,8 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
                   f"busy[0] done {g.busy[0][0].query() if g.busy else None}", file=sys.stderr, flush=True)
     signal.signal(signal.SIGTERM, on_term)
 
-    eng = service._Engine(capacity, batch_size, samplers, cache_policy, device, max_ring, float_frames=float_frames, frames=frames)
+    eng = service._Engine(capacity, batch_size, samplers, cache_policy, device, max_ring, float_frames=float_frames, frames=frames,
+                          nstep=nstep)
     ctx = zmq.Context.instance()
     ctx.set(zmq.IO_THREADS, int(os.environ.get("RETH_B200_IO_THREADS", "4")))   # many actor connections (worker.py:22,57-61)
     ctx.setsockopt(zmq.LINGER, 0)
@@ -236,13 +238,13 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
     dropped = {"append": 0, "update": 0, "late": 0}   # malformed messages dropped / requests that went ahead of late writes
     ready_evt.set()
 
-    def append_from_ring(head, weights):
+    def append_from_ring(head, weights, key=None):
         import torch
         seg = segments.get(head[pack.KEY_SHM])
         if seg is None:
             seg = segments[head[pack.KEY_SHM]] = _ShmSegment(head[pack.KEY_SHM], head["size"], device)
         cols = [seg.buf[at:at + nb].view(np.dtype(dt)).reshape(sh) for dt, sh, at, nb in head["cols"]]
-        eng.append(cols, weights)
+        eng.append(cols, weights, stream_key=key)
         if seg.pinned:                                  # the copies run asynchronously out of the ring
             ev = torch.cuda.Event()
             ev.record(torch.cuda.ExternalStream(eng.stream, device=device))
@@ -333,12 +335,12 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
                              None if reset is None else np.asarray(reset))
         elif kind == "shm":
             try:
-                append_from_ring(payload, weights)
+                append_from_ring(payload, weights, src[0] if src else None)
             except FileNotFoundError:              # the producer vanished with its ring: the rows are lost
                 print(f"reth_b200 server: ingest ring {payload[pack.KEY_SHM]} is gone, message dropped",
                       file=sys.stderr, flush=True)
         else:
-            eng.append(payload, weights)
+            eng.append(payload, weights, stream_key=src[0] if src else None)
         if slab is not None:                       # the columns sit in pinned staging: the copy is asynchronous
             if eng.stream is not None:
                 ingest.hold(slab, eng.stream)
@@ -510,7 +512,7 @@ class _ShmSegment:
 
 # ------------------------------------------------------------ public surface --
 def start_server(capacity, batch_size, host=None, port=None, samplers=None, cache_policy=None, device=0,
-                 max_ring=32, frames=None, float_frames=None):
+                 max_ring=32, frames=None, float_frames=None, nstep=None):
     """reth_buffer.start_server (__init__.py:11-27): spawn the server process, return
     (proc, meta_addr).  `proc` supports terminate()/join() as callers expect (trainer.py:72-74)."""
     host = host or "127.0.0.1"
@@ -522,7 +524,7 @@ def start_server(capacity, batch_size, host=None, port=None, samplers=None, cach
     ctx = mp.get_context("spawn")
     ready = ctx.Event()
     proc = ctx.Process(target=_server_entry, args=(capacity, batch_size, host, ports, samplers, cache_policy, device,
-                                                   max_ring, ready, frames, float_frames), daemon=True)
+                                                   max_ring, ready, frames, float_frames, nstep), daemon=True)
     proc.start()
     if not ready.wait(120):
         proc.terminate()
@@ -531,14 +533,14 @@ def start_server(capacity, batch_size, host=None, port=None, samplers=None, cach
 
 
 def _server_entry(capacity, batch_size, host, ports, samplers, cache_policy, device, max_ring, ready, frames=None,
-                  float_frames=None):
+                  float_frames=None, nstep=None):
     from .sampler import PERSampler
     if samplers is not None:
         for s in samplers:
             pass                                       # class names are resolved by service._Engine
     prof_path = os.environ.get("RETH_B200_SERVER_PROFILE")      # diagnostic: cProfile of the server loop
     if not prof_path:
-        server_main(capacity, batch_size, host, ports, samplers, cache_policy, device, max_ring, ready, frames, float_frames)
+        server_main(capacity, batch_size, host, ports, samplers, cache_policy, device, max_ring, ready, frames, float_frames, nstep)
         return
     import cProfile
     import io
@@ -546,7 +548,7 @@ def _server_entry(capacity, batch_size, host, ports, samplers, cache_policy, dev
     pr = cProfile.Profile()
     try:
         pr.runcall(server_main, capacity, batch_size, host, ports, samplers, cache_policy, device, max_ring, ready, frames,
-                   float_frames)
+                   float_frames, nstep)
     finally:
         out = io.StringIO()
         pstats.Stats(pr, stream=out).sort_stats("tottime").print_stats(25)
@@ -556,12 +558,12 @@ def _server_entry(capacity, batch_size, host, ports, samplers, cache_policy, dev
 
 
 def start_per(capacity, batch_size, alpha=0.6, beta=0.4, sample_start=1000, num_sampler_procs=1,
-              host=None, port=None, cache_policy=None, device=0, max_ring=32, frames=None, float_frames=None):
+              host=None, port=None, cache_policy=None, device=0, max_ring=32, frames=None, float_frames=None, nstep=None):
     """reth_buffer.start_per (__init__.py:30-49)."""
     from .sampler import PERSampler
     samplers = [{"sampler_cls": PERSampler, "num_procs": num_sampler_procs, "sample_start": sample_start,
                  "kwargs": {"alpha": alpha, "beta": beta}}]
-    return start_server(capacity, batch_size, host, port, samplers, cache_policy, device, max_ring, frames, float_frames)
+    return start_server(capacity, batch_size, host, port, samplers, cache_policy, device, max_ring, frames, float_frames, nstep)
 
 
 _META_CACHE = {}

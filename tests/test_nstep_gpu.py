@@ -139,3 +139,62 @@ def test_nstep_argument_errors(Shard):
     with pytest.raises(ReplayError):
         sh.append_nstep(2, [np.zeros(2, np.int64), np.zeros(2, np.int64), np.zeros(2, np.float32), np.zeros(2, np.int64),
                             np.zeros(2, np.float32)], None)
+
+
+@pytest.mark.parametrize("layout", ["inproc", "process"])
+def test_nstep_through_the_service_surface(layout):
+    """start_per(..., nstep={"step", "gamma"}): producers send RAW 1-step rows through Client.append, every Client is
+    one environment stream (as every reference worker owns one NStepAdder, test/apex-dqn/worker.py:35,53), and what the
+    loaders sample are the n-step transitions the reference's adder would have emitted, in arrival order."""
+    import __graft_entry__ as entry
+    entry.build()
+    from reth_b200 import service, service_mp
+    mod = service if layout == "inproc" else service_mp
+    step, gamma, n, B, cap = 3, 0.99, 120, 16, 1024
+    rng = np.random.default_rng(31)
+    streams = []
+    for s in range(2):
+        ids = 1000 * s + np.arange(n)
+        streams.append([np.repeat(ids[:, None], 8, 1).astype(np.float32), rng.integers(0, 6, n), rng.standard_normal(n).astype(np.float32),
+                        np.repeat((ids + 1)[:, None], 8, 1).astype(np.float32), (rng.random(n) < 0.1).astype(np.float32)])
+    folded = [po.nstep_fold(cols, step, gamma)[0] for cols in streams]
+    proc, addr = mod.start_per(cap, B, sample_start=B, nstep={"step": step, "gamma": gamma, "streams": 4})
+    try:
+        clients = [mod.Client(addr), mod.Client(addr)]
+        loader = mod.NumpyLoader(addr)
+        want = [[] for _ in range(5)]
+        sent, out = [0, 0], [0, 0]
+        while min(sent) < n:
+            s = int(rng.integers(0, 2))
+            if sent[s] >= n:
+                continue
+            m = int(min(n - sent[s], rng.integers(1, 20)))
+            lo, hi = sent[s], sent[s] + m
+            clients[s].append([c[lo:hi] for c in streams[s]], np.ones(m, np.float32))
+            if layout == "process":
+                loader.drain()                         # two connections: arrival order = send order only when serialised
+            emitted = max(0, hi - step) - max(0, lo - step)
+            for c in range(5):
+                want[c].append(folded[s][c][out[s]:out[s] + emitted])
+            out[s] += emitted
+            sent[s] = hi
+        want = [np.concatenate(w) for w in want]
+        total = len(want[0])
+        assert total == 2 * (n - step)
+        if layout == "process":
+            assert loader.drain()["cnt"] == total
+            got = [loader.ring_read(c, 0, total) for c in range(5)]
+        else:
+            eng = service._ENGINES[addr]
+            eng.drain()
+            assert eng.cnt == total
+            got = [eng.shard.ring_read(c, 0, total) for c in range(5)]
+        for c in range(5):
+            assert np.array_equal(got[c], want[c]), c
+        data, indices, weights = loader.sample()
+        assert np.array_equal(data[0], want[0][indices]) and np.array_equal(data[2], want[2][indices])
+        assert np.array_equal(data[3], want[3][indices])
+        loader.close()
+    finally:
+        proc.terminate()
+        proc.join()
