@@ -482,14 +482,20 @@ class _ShmSegment:
     host->device copies of the rows are true asynchronous DMA out of the ring."""
 
     def __init__(self, name, size, device):
-        from multiprocessing import resource_tracker, shared_memory
-        self.shm = shared_memory.SharedMemory(name=name)
-        try:                                            # the client owns (and unlinks) the segment
-            resource_tracker.unregister(self.shm._name, "shared_memory")
-        except Exception:
-            pass
-        self.buf = np.frombuffer(self.shm.buf, np.uint8)
-        self.consumed = np.frombuffer(self.shm.buf, np.uint64, count=1)
+        # mapped directly: SharedMemory(name=...) would register the segment with this process's resource tracker,
+        # which a spawned server SHARES with the client that owns (and unlinks) it -- the tracker then complains
+        # about the second unregister at exit
+        import _posixshmem
+        import mmap
+        fd = _posixshmem.shm_open("/" + name.lstrip("/"), os.O_RDWR, mode=0o600)
+        try:
+            self.shm = mmap.mmap(fd, os.fstat(fd).st_size)
+        finally:
+            os.close(fd)
+        if len(self.shm) < int(size):
+            raise ValueError(f"ingest ring {name}: {len(self.shm)} bytes mapped, the message says {size}")
+        self.buf = np.frombuffer(self.shm, np.uint8)
+        self.consumed = np.frombuffer(self.shm, np.uint64, count=1)
         self.pinned = False
         try:
             import torch

@@ -55,3 +55,29 @@ def test_make_ref_places_the_reference_modules_unchanged():
         assert a == b, dst                                           # byte for byte: the reference itself is what gets timed
     # oracle/_ref never enters the history
     assert "oracle/_ref/" in open(os.path.join(ROOT, ".gitignore")).read()
+
+
+def test_shared_memory_ingest_ring_is_mapped_without_the_resource_tracker():
+    """The server side of the same-host ingest ring (service_mp._ShmSegment) maps the client's segment directly: the
+    producer's bump allocator, the consumed counter the server writes back, and a segment that is gone."""
+    from reth_b200 import service_mp as m
+    ring = m._ShmRing(1 << 16)
+    a = ring.reserve(1000)
+    b = ring.reserve(3000)
+    assert a == 64 and b == 64 + 1024 and ring.seq == 2                   # 64-byte header, 64-byte granules
+    ring.buf[a:a + 1000] = 7
+    name = ring.shm.name
+    seg = m._ShmSegment(name, ring.size, 0)
+    assert not seg.pinned or seg.pinned is True
+    assert len(seg.buf) >= ring.size and int(seg.buf[a:a + 1000].sum()) == 7000
+    seg.consumed[0] = 1                                                    # the server has copied message 1 out
+    ring._retire()
+    assert [s for s, _, _ in ring.inflight] == [2]
+    assert ring.reserve(1 << 17) is None                                   # larger than the ring: the caller falls back
+    with pytest.raises(ValueError):
+        m._ShmSegment(name, ring.size * 2, 0)                              # the descriptor disagrees with the mapping
+    seg.consumed[0] = 2
+    seg.close()
+    ring.close(timeout=1.0)
+    with pytest.raises(FileNotFoundError):
+        m._ShmSegment(name, 64, 0)
