@@ -600,6 +600,11 @@ int launch_update(reth_replay *h, UpdateArgs &a, cudaStream_t s, int64_t n_expec
     }
     const uint8_t *idx0 = (const uint8_t *)a.idx, *prio0 = (const uint8_t *)a.prio;
     const int64_t iota0 = a.iota_base;
+    // appended rows riding behind a write-back: entries [n - tail, n) of the batch
+    const int64_t tail = a.tail_n, tail_base0 = a.tail_base, n_main = n - tail;
+    const float *tail_prio0 = a.tail_prio;
+    if (tail < 0 || tail > n || (tail > 0 && (a.n_dev || a.prio_kind != 0 || a.dedupe != 1 || !tail_prio0)))
+        return fail(h, RETH_ERR_INVALID, "update: bad tail entries");
     const size_t is = a.idx_kind == 0 ? 8 : 4, ps = a.prio_kind == 0 ? 4 : 8;
     for (int64_t off = 0; off < n;) {
         const bool rest = off >= covered;                    // the catch-all launch: everything that is left
@@ -615,6 +620,12 @@ int launch_update(reth_replay *h, UpdateArgs &a, cudaStream_t s, int64_t n_expec
         if (a.idx_kind != 2) a.idx = idx0 + off * is;
         if (a.prio_kind != 2) a.prio = prio0 + off * ps;
         a.iota_base = iota0 + off;
+        if (tail > 0) {
+            const int64_t skip = off > n_main ? off - n_main : 0;       // tail entries taken by earlier launches
+            a.tail_n = off + m > n_main ? off + m - n_main - skip : 0;
+            a.tail_base = tail_base0 + skip;
+            a.tail_prio = tail_prio0 + skip;
+        }
         a.counts = h->counts + h->counts_flip * kMaxTileLevels;
         a.counts_next = h->counts + (h->counts_flip ^ 1) * kMaxTileLevels;
         h->counts_flip ^= 1;
@@ -636,6 +647,7 @@ int launch_update(reth_replay *h, UpdateArgs &a, cudaStream_t s, int64_t n_expec
         off += m;
     }
     a.n = n; a.idx = idx0; a.prio = prio0; a.iota_base = iota0; a.pub_seq = pub_seq;
+    a.tail_n = tail; a.tail_base = tail_base0; a.tail_prio = tail_prio0;
     return RETH_OK;
 }
 
@@ -2558,6 +2570,11 @@ int step_loop_impl(reth_replay_t *h, int steps, int batch, const float *prio_dev
         if (ing) CK(h, cudaStreamWaitEvent(h->s_append, h->ev_fork, 0));
     }
     bool copy_pending = false;            // an ingest copy is in flight on s_append: the next gather waits for it
+    // timing diagnosis only (scripts/c4_probe.py): bit 0 the copy does not wait for gathers, bit 1 gathers do not wait for
+    // the copy (both UNSAFE: rows may tear), bit 2 no leaf update for the new rows, bit 3 no row copy, bit 4 the leaves in
+    // a launch of their own (as before they rode in the write-back's)
+    const char *probe_env = ing ? getenv("RETH_C4_PROBE") : nullptr;
+    const int probe = probe_env ? atoi(probe_env) : 0;
     for (int k = 0; k < steps; k += G) {
         const int slot = k % depth;
         // consecutive gathers alternate streams: the tail of one overlaps the ramp-up of the next
@@ -2601,7 +2618,7 @@ int step_loop_impl(reth_replay_t *h, int steps, int batch, const float *prio_dev
                 }
                 CK(h, cudaEventRecord(h->ev_time[h->ev_time_used], sg));
             }
-            if (copy_pending) CK(h, cudaStreamWaitEvent(sg, h->ev_ingest, 0));   // rows the draw may have picked are in place
+            if (copy_pending && !(probe & 2)) CK(h, cudaStreamWaitEvent(sg, h->ev_ingest, 0));   // rows the draw may have picked are in place
             rc = do_gather(h, slot, global, sg, G);
             if (rc) return rc;
             if (timed) h->ev_time_launches++;
@@ -2616,6 +2633,12 @@ int step_loop_impl(reth_replay_t *h, int steps, int batch, const float *prio_dev
         a.n = (int64_t)batch * G; a.idx = h->slots[slot].idx; a.idx_kind = 0;
         a.prio = prio_dev + (size_t)k * batch; a.prio_kind = 0;
         a.alpha = alpha; a.transform = 1; a.dedupe = G == 1 ? 2 : 1;
+        // config 4: the LEAVES of the actor rows that arrived during this group ride in the write-back's launch, as its
+        // last entries (batch order: a sampled slot that is being recycled ends up with the new row's priority, as in
+        // the call-by-call order write-back, then append).  A launch of their own cost 33 us of the tree stream per
+        // group against 42 us for the draw and the write-back together (profiles/r02_c4_probe.jsonl).
+        const bool fold = ing && !(probe & 4) && !(probe & 16);
+        if (fold) { a.n += ing->rows_per_group; a.tail_n = ing->rows_per_group; a.tail_base = h->tail; a.tail_prio = ing->prio; a.dedupe = 1; }
         if (global) {
             a.n_dev = h->slots[slot].meta + 1;                  // this shard's share of the global batch
             if (h->modeg_fused && k + G < steps) a.pub_seq = ++h->board_seq;
@@ -2626,13 +2649,13 @@ int step_loop_impl(reth_replay_t *h, int steps, int batch, const float *prio_dev
         if (rc) return rc;
         h->st.updated_rows += (int64_t)batch * G;
         if (ing) {
-            // Actor rows that arrived during this group (config 4): their LEAVES go onto the tree stream at once, in
-            // order behind the write-back -- the chain draw -> repair -> draw never waits for a gather -- while the ROW
-            // copy runs on the ingest stream behind every gather enqueued so far (those may still read the slots being
-            // recycled), and every later gather waits for the copy (a later draw may pick the new slots).
+            // Actor rows that arrived during this group (config 4): their LEAVES are on the tree stream already (last
+            // entries of the write-back's launch) -- the chain draw -> repair -> draw never waits for a gather -- while
+            // the ROW copy runs on the ingest stream behind every gather enqueued so far (those may still read the slots
+            // being recycled), and every later gather waits for the copy (a later draw may pick the new slots).
             const int64_t n = ing->rows_per_group, cap = h->cfg.capacity, start = h->tail;
-            rc = wait_gathers(h, h->s_append);
-            if (!rc) rc = launch_ring_copy(h, ing->cols, start, n, h->s_append);
+            rc = (probe & 1) ? RETH_OK : wait_gathers(h, h->s_append);
+            if (!rc && !(probe & 8)) rc = launch_ring_copy(h, ing->cols, start, n, h->s_append);
             if (!rc) rc = mark_frame_refs(h, nullptr, start, n, h->s_append);
             if (rc) return rc;
             CK(h, cudaEventRecord(h->ev_ingest, h->s_append));
@@ -2641,7 +2664,7 @@ int step_loop_impl(reth_replay_t *h, int steps, int batch, const float *prio_dev
             u.n = n; u.idx = nullptr; u.idx_kind = 2; u.iota_base = start;
             u.prio = ing->prio; u.prio_kind = 0;
             u.alpha = alpha; u.transform = 1; u.dedupe = 0;
-            rc = launch_update(h, u, st);
+            if (!(probe & 4) && !fold) rc = launch_update(h, u, st);
             if (rc) return rc;
             h->tail = (start + n) % cap;
             h->size = (h->size + n < cap) ? h->size + n : cap;

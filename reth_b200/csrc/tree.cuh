@@ -443,12 +443,18 @@ struct UpdateArgs {
     unsigned long long pub_seq;
     int32_t pub_when;     // 0 always; 1 only if the device-side entry count ends inside this launch (or before it);
                           // 2 only if this launch has entries (the catch-all behind launches sized for the expected share)
+    // Rows appended right behind a write-back ride in its launch (config 4: a launch of their own costs the repair's
+    // fixed ~30 us again): the last tail_n entries of the launch are the slots (tail_base + t) % capacity with float32
+    // priorities tail_prio[t].  Needs prio_kind 0 and dedupe 1 (a sampled slot that is being recycled: the row wins).
+    int64_t tail_n, tail_base;
+    const float *tail_prio;
 };
 
 #define RETH_STAMP(k) do { if (a.dbg && brank == 0 && threadIdx.x == 0) a.dbg[k] = clock64(); } while (0)
 
 __device__ __forceinline__ int64_t upd_index(const UpdateArgs &a, int64_t i)
 {
+    if (a.tail_n > 0 && i >= a.n - a.tail_n) return (a.tail_base + (i - (a.n - a.tail_n))) % a.g.capacity;
     if (a.idx_kind == 0) return ((const int64_t *)a.idx)[i];
     if (a.idx_kind == 1) return (int64_t)((const int32_t *)a.idx)[i];
     return (a.iota_base + i) % a.g.capacity;
@@ -459,6 +465,7 @@ __device__ __forceinline__ int64_t upd_index(const UpdateArgs &a, int64_t i)
 __device__ __forceinline__ double upd_prio_load(const UpdateArgs &a, int64_t i)
 {
     if (a.prio_kind == 2) return 1.0;                    // prioritized_buffer.py:36-37
+    if (a.tail_n > 0 && i >= a.n - a.tail_n) return (double)a.tail_prio[i - (a.n - a.tail_n)];
     if (a.prio_kind == 0) return (double)((const float *)a.prio)[i];   // exact widening
     return ((const double *)a.prio)[i];
 }

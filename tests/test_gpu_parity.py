@@ -454,18 +454,22 @@ def test_capacity_2p24_tree_only(Shard):
     sh.close()
 
 
-def test_step_loop_ingest_matches_call_by_call(Shard):
-    """reth_replay_step_loop_ingest (config 4 without draining the loop: leaves on the tree stream, row copy behind the
-    gathers in flight, later gathers behind the copy) against the same operations issued one by one on a twin shard:
-    per group  sample_multi -> gather_multi -> update_slots -> append.  Trees and rings bit-identical, the batches of
-    the last group row for row; the ring (which wraps three times) against the oracle's."""
+@pytest.mark.parametrize("cap,B,G,groups,rows,frame", [
+    (3000, 64, 4, 10, 1000, (4, 84, 84)),     # a third of the ring recycled per group: sampled slots collide with new rows
+    (20000, 64, 4, 6, 9000, (64,)),           # write-back + new leaves exceed one repair launch: the cut falls among the new rows
+    (20000, 1100, 8, 4, 500, (64,)),          # ... and among the write-back entries
+])
+def test_step_loop_ingest_matches_call_by_call(Shard, cap, B, G, groups, rows, frame):
+    """reth_replay_step_loop_ingest (config 4 without draining the loop: the new rows' leaves ride in the write-back's
+    repair launch, row copy behind the gathers in flight, later gathers behind the copy) against the same operations
+    issued one by one on a twin shard: per group  sample_multi -> gather_multi -> update_slots -> append.  Trees and
+    rings bit-identical, the batches of the last group row for row; the ring (which wraps) against the oracle's."""
     import torch
-    cap, B, G, groups, rows = 3000, 64, 4, 10, 1000
-    struct = [(np.uint8, (4, 84, 84)), (np.int64, ()), (np.float32, ())]
+    struct = [(np.uint8, frame), (np.int64, ()), (np.float32, ())]
     rng = np.random.default_rng(61)
-    fill = [rng.integers(0, 256, (cap, 4, 84, 84), dtype=np.uint8), np.arange(cap), rng.standard_normal(cap).astype(np.float32)]
+    fill = [rng.integers(0, 256, (cap,) + frame, dtype=np.uint8), np.arange(cap), rng.standard_normal(cap).astype(np.float32)]
     fill_w = (rng.random(cap) + 0.05).astype(np.float32)
-    new = [rng.integers(0, 256, (rows, 4, 84, 84), dtype=np.uint8), 10 ** 6 + np.arange(rows), rng.standard_normal(rows).astype(np.float32)]
+    new = [rng.integers(0, 256, (rows,) + frame, dtype=np.uint8), 10 ** 6 + np.arange(rows), rng.standard_normal(rows).astype(np.float32)]
     new_w = (rng.random(rows) + 0.05).astype(np.float32)
     a, b = (Shard(cap, struct, max_batch=B, ring_depth=2 * G) for _ in range(2))
     ring = po.OracleRing(cap, struct)
