@@ -443,8 +443,8 @@ int reth_replay_step_loop(reth_replay_t *h, int steps, int batch, const float *p
  * and draws are serialised by the one append process and the sampler's SUB socket, server/main_loop.py:44-58,
  * server/sampler_loop.py:29-39).  After every group of G learner steps, rows_per_group device-resident rows
  * (ingest_cols_dev[c]: rows_per_group rows of column c; ingest_prio_dev: their float32 |TD|) are appended:
- * their leaves go onto the tree stream at once, in order behind the write-back, so the chain draw -> repair -> draw
- * never waits for a gather; the row copy runs on the ingest stream behind every gather enqueued so far (those may
+ * their leaves ride in the write-back's repair launch, as its last entries (batch order: behind the write-back), so
+ * the chain draw -> repair -> draw never waits for a gather and pays the repair's fixed cost once per group; the row copy runs on the ingest stream behind every gather enqueued so far (those may
  * still read the slots being recycled) and every later gather waits for it.  Same order of tree mutations as
  * step_loop(G) followed by append(), repeated.  Not with flags bit1 (serial) / bit6 (Mode G). */
 int reth_replay_step_loop_ingest(reth_replay_t *h, int steps, int batch, const float *prio_dev,

@@ -47,6 +47,11 @@ def timed(label, probe=None, ingest=True, groups=400, **kw):
                       "sampled_M_per_s": round(G * B / us, 2)}), flush=True)
 
 
+if os.environ.get("C4_ONLY"):                 # shape sweeps (RETH_UPDATE_CLUSTER=...): the two lines that matter
+    timed("plain loop, no ingest", ingest=False)
+    timed("ingest (product path)")
+    timed("tree stream alone with ingest leaves folded (no gathers, no copy)", probe=8, gather=False)
+    sys.exit(0)
 timed("plain loop, no ingest", ingest=False)
 timed("ingest (product path: leaves in the write-back's launch)")
 timed("ingest, leaves in a launch of their own", probe=16)
