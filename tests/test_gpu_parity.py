@@ -458,6 +458,7 @@ def test_capacity_2p24_tree_only(Shard):
     (3000, 64, 4, 10, 1000, (4, 84, 84)),     # a third of the ring recycled per group: sampled slots collide with new rows
     (20000, 64, 4, 6, 9000, (64,)),           # write-back + new leaves exceed one repair launch: the cut falls among the new rows
     (20000, 1100, 8, 4, 500, (64,)),          # ... and among the write-back entries
+    (3000, 64, 1, 12, 300, (64,)),            # strict alternation (programmatic dependent launches on the tree stream)
 ])
 def test_step_loop_ingest_matches_call_by_call(Shard, cap, B, G, groups, rows, frame):
     """reth_replay_step_loop_ingest (config 4 without draining the loop: the new rows' leaves ride in the write-back's
