@@ -50,7 +50,8 @@ class _Engine:
         # replaces NStepAdder on the actor, reth/reth/utils/nstep_adder.py:11-28, test/apex-dqn/worker.py:35,53).
         # Every Client is one environment stream, as every reference worker owns one adder.
         self.nstep = dict(nstep) if nstep else None
-        self._nstep_streams = {}
+        self._nstep_streams = {}                              # producer id -> stream id, least recently used first
+        self._nstep_open = False
         self.float_frames = float_frames                      # None | "f32" | "f32/255": see ReplayShard(out_cast=)
         # frames = {"k": stack depth, "shape": frame shape, "capacity": frames in the frame ring,
         #           "columns": (0, 3)}: frame-de-duplicated rows, fed through append_steps()
@@ -253,13 +254,20 @@ class _Engine:
                 if stream_key is None:
                     raise ValueError("n-step assembly needs messages that name their producer (this build's Client does; "
                                      "an unmodified reference actor keeps folding with its own NStepAdder)")
-                if not self._nstep_streams:
+                if not self._nstep_open:
+                    self._nstep_open = True
                     self.shard.nstep_open(int(ns.get("streams", 256)), int(ns["step"]), float(ns["gamma"]),
                                           r_col=int(ns.get("r_col", 2)), s1_col=int(ns.get("s1_col", 3)),
                                           done_col=int(ns.get("done_col", 4)), max_rows=int(ns.get("max_rows", 4096)))
-                sid = self._nstep_streams.setdefault(stream_key, len(self._nstep_streams))
-                if sid >= int(ns.get("streams", 256)):
-                    raise ValueError(f"more than {ns.get('streams', 256)} producer streams: raise nstep['streams']")
+                sid = self._nstep_streams.pop(stream_key, None)
+                if sid is None:
+                    if len(self._nstep_streams) < int(ns.get("streams", 256)):
+                        sid = len(self._nstep_streams)
+                    else:                                     # producers come and go (a restarted actor has a new id): the
+                        oldest = next(iter(self._nstep_streams))   # least recently used stream starts over for the new one,
+                        sid = self._nstep_streams.pop(oldest)      # its unfinished rows are dropped like a dead actor's
+                        self.shard.nstep_reset(sid)
+                self._nstep_streams[stream_key] = sid         # most recently used last
                 _, emitted = self.shard.append_nstep(sid, list(data), weights, alpha=alpha, transform=True, stream=self.stream)
                 self.cnt += emitted                           # rows that left the adder, as the reference counts stored rows
                 return
@@ -602,18 +610,19 @@ class Client:
     def __init__(self, meta_addr):
         self._eng = _engine(meta_addr)
         self.meta = {"capacity": self._eng.capacity, "batch_size": self._eng.batch_size, "meta_addr": meta_addr}
+        self._id = next(_COUNTER)                             # producer id (n-step stream key); id(self) could be reused
 
     def append(self, data, weights, compress=False):
         assert isinstance(data, (list, tuple))                # client.py:22
         for col in data:
             assert isinstance(col, np.ndarray)                # :24
             assert len(col) == len(weights)                   # :25
-        self._eng.append(data, np.asarray(weights), stream_key=id(self))
+        self._eng.append(data, np.asarray(weights), stream_key=self._id)
 
     def append_steps(self, env, frames, others, weights, reset=None):
         """Frame-de-duplicated ingest for a buffer started with frames=...: see _Engine.append_steps."""
         assert len(frames) == len(weights) and all(len(o) == len(weights) for o in others)
-        self._eng.append_steps((id(self), env), frames, others, np.asarray(weights), reset)
+        self._eng.append_steps((self._id, env), frames, others, np.asarray(weights), reset)
 
     def update_priorities(self, indices, weights, step=True):
         assert len(indices) == len(weights)                   # :38

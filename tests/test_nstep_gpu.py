@@ -198,3 +198,30 @@ def test_nstep_through_the_service_surface(layout):
     finally:
         proc.terminate()
         proc.join()
+
+
+def test_nstep_service_streams_are_recycled():
+    """More producers over time than n-step streams: the least recently used stream starts over for the newcomer (a
+    restarted actor connects with a new id), its unfinished rows are dropped."""
+    import __graft_entry__ as entry
+    entry.build()
+    from reth_b200 import service
+    step, gamma, n = 3, 0.9, 10
+    rng = np.random.default_rng(2)
+    proc, addr = service.start_per(256, 8, sample_start=8, nstep={"step": step, "gamma": gamma, "streams": 2})
+    try:
+        eng = service._ENGINES[addr]
+        want = [[] for _ in range(5)]
+        for who in range(4):                                  # four producers, two streams
+            ids = 100 * who + np.arange(n)
+            cols = [ids.astype(np.float32), rng.integers(0, 4, n), rng.standard_normal(n).astype(np.float32),
+                    (ids + 1).astype(np.float32), np.zeros(n, np.float32)]
+            service.Client(addr).append(cols, np.ones(n, np.float32))
+            for c, col in enumerate(po.nstep_fold(cols, step, gamma)[0]):
+                want[c].append(col[:n - step])
+        eng.drain()
+        assert eng.cnt == 4 * (n - step) and len(eng._nstep_streams) == 2
+        for c in range(5):
+            assert np.array_equal(eng.shard.ring_read(c, 0, eng.cnt), np.concatenate(want[c])), c
+    finally:
+        proc.terminate()
