@@ -522,8 +522,8 @@ def run_ours(args):
                    "stress": {"value": c4s[0], "appended_rows_per_s": c4s[1], "hbm_gbs": c4s[2], "rows_appended_per_learner_step": 256 * 64},
                    "unit": "sampled transitions/s", "prefetch_group": G,
                    "note": "learner loop with actor ingest on one shard, device-resident producer (reth_replay_step_loop_ingest): "
-                           "per group G x (sample 512 + gather + update), then the rows that arrived are appended -- leaves on the "
-                           "tree stream at once, the row copy behind the gathers in flight, later gathers behind the copy; alpha 0.5 "
+                           "per group G x (sample 512 + gather + update), then the rows that arrived are appended -- their leaves in "
+                           "the write-back's repair launch, the row copy behind the gathers in flight, later gathers behind the copy; alpha 0.5 "
                            "beta 0.4 (config.yaml:26-27); 256 actor connections over ZeroMQ: see ingest_256"}
 
     peak, peak_src = measured_peak()
