@@ -610,7 +610,8 @@ def run_ours(args):
         import bench_process
         line["e2e_process"] = bench_process.run_leg("e2e_process", 180, batch=B)
         line["ingest_256"] = bench_process.run_leg("ingest_256", 240)
-        for k in ("e2e_process", "ingest_256"):
+        line["apex_process"] = bench_process.run_leg("apex_process", 150)      # both at once: config 4 over the wire
+        for k in ("e2e_process", "ingest_256", "apex_process"):
             if "error" in line[k]:
                 log(f"{k} failed: {line[k]['error']}")
     if rank == 0:

@@ -85,6 +85,117 @@ def ingest_256(log=None):
     return out
 
 
+def _apex_sender(meta_addr, append_addr, n_conn, rows, pace_rows_per_s, stop, sent, window=512):
+    """Actor side of apex_process, in a process of its own: n_conn PUSH connections, one pre-encoded `rows`-row message
+    in the reference's row format re-sent round robin, paced to pace_rows_per_s (None: as fast as the server takes
+    them).  At most `window` messages are outstanding (the server's row counter is read every 32 sends): 256
+    connections x HWM 10 on both ends would otherwise park up to 19 GB of messages in host memory."""
+    import zmq
+    from reth_b200 import pack, service_mp
+    ctl = service_mp.NumpyLoader(meta_addr)
+    cnt0 = ctl.stat()["appended_rows"]
+    taken = 0
+    rng = np.random.default_rng(1)
+    cols = [rng.integers(0, 256, (rows, 4, 84, 84), dtype=np.uint8), rng.integers(0, 18, rows),
+            rng.standard_normal(rows).astype(np.float32), rng.integers(0, 256, (rows, 4, 84, 84), dtype=np.uint8),
+            (rng.random(rows) < 0.01).astype(np.float32)]
+    msg = bytes(pack.encode_append_rows(cols, np.abs(rng.standard_normal(rows)).astype(np.float32)))
+    ctx = zmq.Context(4)
+    socks = []
+    for _ in range(n_conn):
+        sk = ctx.socket(zmq.PUSH)
+        sk.set_hwm(10)
+        sk.setsockopt(zmq.LINGER, 0)
+        sk.connect(append_addr)
+        socks.append(sk)
+    gap = rows / pace_rows_per_s if pace_rows_per_s else 0.0
+    nxt, k = time.perf_counter(), 0
+    while not stop.is_set():
+        if sent.value - taken >= window or (k % 32 == 0 and sent.value - taken >= window // 2):
+            taken = (ctl.stat()["appended_rows"] - cnt0) // rows
+            if sent.value - taken >= window:
+                time.sleep(0.0005)
+                continue
+        if gap:
+            now = time.perf_counter()
+            if now < nxt:
+                time.sleep(min(nxt - now, 0.001))
+                continue
+            nxt = max(nxt + gap, now - 10 * gap)
+        try:
+            socks[k % n_conn].send(msg, zmq.NOBLOCK, copy=False)
+            with sent.get_lock():
+                sent.value += 1
+        except zmq.Again:
+            time.sleep(0.0002)
+        k += 1
+    for sk in socks:
+        sk.close(0)
+    ctx.term()
+    ctl.close()
+
+
+def apex_process(batch=512, capacity=1 << 16, seconds=1.5, n_conn=256, rows=64):
+    """BASELINE.json config 4 over the wire: the learner loop of e2e_process (TorchCudaLoader defaults +
+    Client.update_priorities) WHILE n_conn actor connections push 64-row messages in the reference's row format into
+    the same server process (test/apex-dqn: trainer.py:22-36 and worker.py:57-61 at once).  Two actor rates: paced to
+    50 k rows/s in total (256 actors x ~200 env steps/s) and unpaced (the server's ingest limit)."""
+    import multiprocessing as mp
+    from reth_b200 import service_mp
+    proc, addr = service_mp.start_per(capacity, batch, alpha=0.6, beta=0.4, sample_start=batch)
+    ctx = mp.get_context("spawn")
+    try:
+        meta = service_mp.get_meta(addr)
+        client = service_mp.Client(addr)
+        rng = np.random.default_rng(0)
+        n = 2048
+        s0 = rng.integers(0, 256, (n, 4, 84, 84), dtype=np.uint8)
+        cols = [s0, rng.integers(0, 18, n), np.zeros(n, np.float32), s0, np.zeros(n, np.float32)]
+        wts = np.abs(rng.standard_normal(n)).astype(np.float32)
+        loader = service_mp.TorchCudaLoader(addr)
+        for _ in range(0, capacity, n):
+            client.append(cols, wts)
+        loader.drain()
+        newp = np.abs(rng.standard_normal((64, batch))).astype(np.float32)
+        out = {"connections": n_conn, "rows_per_message": rows, "capacity": capacity,
+               "call": "start_per(...) in its own process; learner: TorchCudaLoader(addr) [defaults] + Client(addr).update_priorities; "
+                       "actors: PUSH connections in a second process, reference row format"}
+        for name, pace in (("paced_50k_rows_per_s", 50_000), ("unpaced", None)):
+            stop, sent = ctx.Event(), ctx.Value("q", 0)
+            snd = ctx.Process(target=_apex_sender, args=(addr, meta["append_addr"], n_conn, rows, pace, stop, sent), daemon=True)
+            snd.start()
+            t_wait = time.time() + 60
+            while sent.value < n_conn and time.time() < t_wait:      # every connection is up, slabs pinned
+                time.sleep(0.01)
+            for i in range(256):
+                data, idx, w = loader.sample()
+                client.update_priorities(idx, newp[i % 64])
+            c0 = loader.stat()
+            t0 = time.perf_counter()
+            it = 0
+            while time.perf_counter() - t0 < seconds:
+                for _ in range(64):
+                    data, idx, w = loader.sample()
+                    client.update_priorities(idx, newp[it % 64])
+                    it += 1
+            c1 = loader.stat()
+            dt = time.perf_counter() - t0
+            stop.set()
+            snd.join(20)
+            if snd.is_alive():
+                snd.kill()
+            loader.drain()
+            out[name] = {"learner_transitions_per_s": it * batch / dt,
+                         "ingest_rows_per_s": (c1["appended_rows"] - c0["appended_rows"]) / dt,
+                         "us_per_iteration": dt / max(1, it) * 1e6, "decode_backlog": c1.get("backlog"), "dropped": c1.get("dropped")}
+        loader.close()
+        client.close()
+        return out
+    finally:
+        proc.terminate()
+        proc.join()
+
+
 # ---- isolation: each leg runs in a child process (own session) under a deadline, so that a hung server or a lost
 # message can cost the bench line one key, never the line
 def _leg_main(name, kwargs, q):
@@ -97,7 +208,7 @@ def _leg_main(name, kwargs, q):
 
 
 def run_leg(name, timeout_s=180, **kwargs):
-    """-> the leg's dict, or {"error": ...}.  name: "e2e_process" | "ingest_256"."""
+    """-> the leg's dict, or {"error": ...}.  name: "e2e_process" | "ingest_256" | "apex_process"."""
     import multiprocessing as mp
     import signal
     ctx = mp.get_context("spawn")

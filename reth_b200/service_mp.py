@@ -44,6 +44,8 @@ ZMQ_DEFAULT_HWM = 10            # utils/__init__.py:12
 #   [int64 indices of all messages] [float32|float64 priorities of all messages]  (one dtype per frame)
 _UPD_MAGIC = b"RBU1"            # a reference-format message starts with a big-endian header length: first byte 0
 _UPD_FRAME = struct.Struct("<4s8sQI")
+_UPD_MAGIC2 = b"RBU2"           # ... and the number of append messages the sender had sent before this frame
+_UPD_FRAME2 = struct.Struct("<4s8sQQI")
 _UPD_HEAD = struct.Struct("<BBHI")
 
 
@@ -236,6 +238,11 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
     segments = {}                # shared-memory ingest rings of same-host clients: name -> _ShmSegment
     pending = []                 # (cuda event, segment, seq): H2D copies out of a ring still in flight
     dropped = {"append": 0, "update": 0, "late": 0}   # malformed messages dropped / requests that went ahead of late writes
+    trace_on = bool(os.environ.get("RETH_B200_TRACE"))
+
+    def trace(*what):                                  # diagnostic: the order in which the loop takes things in
+        if trace_on:
+            print("reth_b200 server trace:", *what, file=sys.stderr, flush=True)
     ready_evt.set()
 
     def append_from_ring(head, weights, key=None):
@@ -270,18 +277,24 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
             reply(owed.pop(0), {"ok": True, "op": "next", "group": int(g), "first_slot": int(g * eng.group),
                                 "n": int(eng.group)}, idx.tobytes(), w.tobytes())
 
-    def apply_updates(buf):
-        """One update frame: the reference's [indices, weights, step] message (client.py:37-39), or this
-        build's compact frame holding one or more such messages back to back."""
+    def open_update(buf):
+        """One update frame: the reference's [indices, weights, step] message (client.py:37-39), or this build's
+        compact frame holding one or more such messages back to back.
+        -> (client id | None, frame number, appends the sender had sent before it, apply())."""
         mv = memoryview(buf)
-        if mv[:4] != _UPD_MAGIC:
+        if mv[:4] not in (_UPD_MAGIC, _UPD_MAGIC2):
             (indices, weights, step), src = pack.decode_src(mv)
-            eng.update(np.asarray(indices), np.asarray(weights), bool(step))
-            if src:
-                seen.setdefault(src[0], [0, 0])[1] = int(src[1])
-            return
-        _, cid, seq, count = _UPD_FRAME.unpack_from(mv, 0)
-        at = _UPD_FRAME.size
+            def apply():
+                eng.update(np.asarray(indices), np.asarray(weights), bool(step))
+            if not src:
+                return None, 0, 0, apply
+            return src[0], int(src[1]), int(src[2]) if len(src) > 2 else 0, apply
+        if mv[:4] == _UPD_MAGIC2:
+            _, cid, seq, aseq, count = _UPD_FRAME2.unpack_from(mv, 0)
+            at = _UPD_FRAME2.size
+        else:
+            _, cid, seq, count = _UPD_FRAME.unpack_from(mv, 0)
+            aseq, at = 0, _UPD_FRAME.size
         sizes, steps, f32 = [], [], 1
         for _ in range(count):
             step, f32, _, n = _UPD_HEAD.unpack_from(mv, at)
@@ -291,8 +304,7 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
         total = sum(sizes)
         idx = np.frombuffer(mv, np.int64, total, at)
         w = np.frombuffer(mv, np.float32 if f32 else np.float64, total, at + 8 * total)
-        eng.update_block(idx, w, sizes, steps)
-        seen.setdefault(cid.hex(), [0, 0])[1] = seq
+        return cid.hex(), seq, aseq, lambda: eng.update_block(idx, w, sizes, steps)
 
     def drain_appends(wait=False):
         """Receive every pending append frame (decoded by the ingest threads), then commit what has been decoded,
@@ -317,6 +329,7 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
                 if isinstance(res, Exception):
                     raise res
                 src = take_append(*res)
+                trace("append", src, "rows", len(res[2]))
             except Exception as e:                     # one bad message from one actor must not stop the server
                 dropped["append"] += 1
                 print(f"reth_b200 server: append message dropped ({type(e).__name__}: {e})", file=sys.stderr, flush=True)
@@ -354,13 +367,37 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
                 frame = upd.recv(zmq.NOBLOCK, copy=False)
             except zmq.Again:
                 break
-            if ingest.backlog:                         # appends received earlier are applied first (one total order)
-                drain_appends(wait=True)
             try:
-                apply_updates(frame.buffer)
+                cid, seq, aseq, apply = open_update(frame.buffer)
+                # Order is per producer, as over the reference's sockets: a write-back stays behind the appends ITS sender
+                # sent before it (they travel on another socket and pass the decode threads), not behind every actor's
+                # -- with 256 actors streaming there is always a decode backlog, and a learner's write-backs (and its
+                # draws, handle_loader) waiting for all of it ran at a few thousand transitions/s (bench apex_process)
+                if cid is not None and aseq:
+                    await_appends(cid, aseq)
+                apply()
+                trace("update frame", cid, seq, "names appends", aseq, "shard", eng.shard is not None, "seen", seen.get(cid))
+                if cid is not None:
+                    seen.setdefault(cid, [0, 0])[1] = seq
             except Exception as e:
                 dropped["update"] += 1
                 print(f"reth_b200 server: update message dropped ({type(e).__name__}: {e})", file=sys.stderr, flush=True)
+
+    def await_appends(cid, aseq, timeout=2.0):
+        """Commit appends (arrival order) until message `aseq` of producer `cid` is in."""
+        t0 = time.time()                               # the clock runs only while nothing received is waiting to go in:
+        while seen.get(cid, (0, 0))[0] < aseq and time.time() - t0 < timeout:   # a decode may take seconds (the first
+            drain_appends()                                                   # one pins its staging slab: CUDA start-up)
+            if seen.get(cid, (0, 0))[0] < aseq:
+                if ingest.backlog:
+                    ingest.wait_next(0.002)
+                    t0 = time.time()
+                else:
+                    poller.poll(1)
+        if seen.get(cid, (0, 0))[0] < aseq:
+            dropped["late"] += 1
+            print(f"reth_b200 server: a write-back went ahead of append {aseq} of its sender, which never arrived",
+                  file=sys.stderr, flush=True)
 
     def await_writes(after, timeout=2.0):
         """A loader's request names the appends / write-backs its own process sent before it (they
@@ -372,9 +409,14 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
             return
         t0 = time.time()
         while behind() and time.time() - t0 < timeout:
-            poller.poll(1)
-            drain_appends(wait=True)
+            drain_appends()
             drain_updates()
+            if behind():
+                if ingest.backlog:
+                    ingest.wait_next(0.002)
+                    t0 = time.time()                   # received and being decoded: not lost
+                else:
+                    poller.poll(1)
         if behind():                                   # a write named by the request never arrived (dropped / lost)
             dropped["late"] += 1
             print(f"reth_b200 server: a loader request went ahead without writes sent before it ({timeout:.1f} s "
@@ -382,9 +424,16 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
 
     def handle_loader(ident, req):
         op = req.get("op")
-        if ingest.backlog:
-            drain_appends(wait=True)                   # drain every pending write before serving a draw (sampler_loop.py:29-36)
-        await_writes(req.get("after"))
+        if op == "stat":                               # counters as they stand: no draining, no waiting (producers' flow control)
+            rows = eng.shard.stats()["appended_rows"] if eng.shard is not None else 0
+            reply(ident, {"ok": True, "op": "stat", "cnt": eng.cnt, "appended_rows": rows, "backlog": ingest.backlog,
+                          "dropped": dropped})
+            return
+        if op == "drain" and ingest.backlog:
+            drain_appends(wait=True)                   # drain(): everything received so far
+        else:
+            drain_appends()                            # what is decoded goes in before a draw (sampler_loop.py:29-36)
+        await_writes(req.get("after"))                 # ... and everything the requesting process sent before its request
         if op == "open":
             if eng.shard is None:                      # row struct unknown until the first append
                 waiting.append((ident, req))
@@ -417,6 +466,7 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
             if not eng.ready():
                 waiting.append((ident, req))
                 return
+            trace("draw", req.get("after"), "seen", seen)
             eng.request_group()
             owed.append(ident)
             deliver()
@@ -757,7 +807,7 @@ class Client:
             with self._lock:
                 self._useq += 1
                 self.update_sock.send(pack.encode([np.asarray(indices), np.asarray(weights), step],
-                                                  extra={pack.KEY_SRC: [self._id.hex(), self._useq]}), copy=False)
+                                                  extra={pack.KEY_SRC: [self._id.hex(), self._useq, self._aseq]}), copy=False)
             return
         idx = indices if (type(indices) is np.ndarray and indices.dtype == np.int64) else np.asarray(indices, dtype=np.int64)
         w = weights if type(weights) is np.ndarray else np.asarray(weights)
@@ -783,7 +833,7 @@ class Client:
     def _flush_locked(self):
         if self._held:
             self._useq += 1
-            frame = b"".join([_UPD_FRAME.pack(_UPD_MAGIC, self._id, self._useq, self._held)] + self._heads
+            frame = b"".join([_UPD_FRAME2.pack(_UPD_MAGIC2, self._id, self._useq, self._aseq, self._held)] + self._heads
                              + self._idxs + self._ws)
             self._heads, self._idxs, self._ws, self._held = [], [], [], 0
             self.update_sock.send(frame, copy=False)
@@ -966,6 +1016,10 @@ class _RemoteLoader:
         """Parity / debug (reth_replay_ring_read): rows [first, first + n) of ring column `column` as stored."""
         head, blobs = self._call({"op": "ring", "column": int(column), "first": int(first), "n": int(n)})
         return np.frombuffer(blobs[0], np.dtype(head["dtype"])).reshape(head["shape"])
+
+    def stat(self):
+        """The server's counters as they stand (rows taken in, decode backlog, dropped messages); nothing is drained."""
+        return self._call({"op": "stat"})[0]
 
     def drain(self):
         """Block until the server has executed everything it has received so far; -> {"cnt": ...}."""
