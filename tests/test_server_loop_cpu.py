@@ -1,0 +1,205 @@
+"""The poll loop of the server process (reth_b200/service_mp.server_main) on the CPU: the real loop, sockets, decode
+threads, Client and NumpyLoader, around a stand-in engine that records the order in which the loop hands it work.
+What is pinned here is ORDER (the reference gets it from its sockets, server/sampler_loop.py:29-36,
+server/main_loop.py:44-58):
+  * a draw sees every write its own process sent before the request, however long the decode of an append takes;
+  * a write-back waits for the appends ITS sender sent before it, and for nobody else's;
+  * drain() waits for everything received."""
+import signal
+import threading
+import time
+
+import numpy as np
+import pytest
+
+
+class _Shard:
+    out_struct = [(np.dtype(np.int64), ()), (np.dtype(np.float32), ())]
+    ring_depth = 4
+    _h = None
+
+    def _ck(self, rc):
+        pass
+
+    def stats(self):
+        return {"appended_rows": 0}
+
+    def slot_read(self, slot, with_rows=False, stream=None):
+        return [np.zeros(4, np.int64), np.zeros(4, np.float32)], None, None
+
+
+class _Engine:
+    """The surface of service._Engine the loop uses; every call lands in `log`."""
+    log = []
+
+    def __init__(self, *a, **k):
+        self.topic, self.topics = "default", {"default": {"kind": "per", "sample_start": 1}}
+        self.shard = self.stream = self.pipe = None
+        self.loaders, self.max_ring, self.group, self.ahead, self.lend, self.cnt, self._owed = 0, 8, 1, 0, 1, 0, 0
+
+    def append(self, cols, w, stream_key=None):
+        self.shard = _Shard()
+        self.cnt += len(w)
+        _Engine.log.append(("append", int(cols[0][0]), len(w)))
+
+    def update(self, idx, w, step):
+        _Engine.log.append(("update", [int(i) for i in idx], self.shard is not None))
+
+    def update_block(self, idx, w, sizes, steps):
+        _Engine.log.append(("update", [int(i) for i in idx], self.shard is not None))
+
+    def ready(self):
+        return self.shard is not None
+
+    def request_group(self):
+        _Engine.log.append(("draw",))
+        self._owed += 1
+
+    def try_deliver(self):
+        if not self._owed:
+            return None
+        self._owed -= 1
+        return 0, np.zeros((1, 4), np.int64), np.zeros((1, 4))
+
+    def open_pipe(self, group, ahead, lend):
+        self.loaders += 1
+
+    def release_pipe(self):
+        self.loaders -= 1
+
+    def drain(self):
+        pass
+
+    def close(self):
+        pass
+
+
+@pytest.fixture
+def server(monkeypatch):
+    """-> (address, set_decode_delay): server_main in a thread of this process, no CUDA anywhere."""
+    import faulthandler
+    import torch
+    from reth_b200 import _cabi, service, service_mp as m
+    real = _cabi.lib()
+
+    class Lib:
+        def __getattr__(self, k):
+            return getattr(real, k)
+
+        def reth_replay_ipc_export(self, h, ex):
+            return 0
+    delay = {"first_value": None, "seconds": 0.0}
+    handlers = {}
+
+    def slab(self, nbytes, seq):                              # stands in for the pinned slab (pin_memory needs CUDA)
+        return torch.empty(max(1 << 16, nbytes), dtype=torch.uint8)
+    real_open = m.pack.open_append
+
+    def slow_open(buf, alloc=None):                           # a decode that takes long for the marked message
+        res = real_open(buf, alloc)
+        if delay["first_value"] is not None and res[0] == "columns" and int(res[1][0][0]) == delay["first_value"]:
+            time.sleep(delay["seconds"])
+        return res
+    monkeypatch.setattr(service, "_Engine", _Engine)
+    monkeypatch.setattr(m._Ingest, "_slab", slab)
+    monkeypatch.setattr(m.pack, "open_append", slow_open)
+    monkeypatch.setattr(_cabi, "lib", lambda: Lib())
+    monkeypatch.setattr(signal, "signal", lambda sig, h: handlers.__setitem__(sig, h))    # not the main thread's business
+    monkeypatch.setattr(faulthandler, "dump_traceback_later", lambda *a, **k: None)
+    _Engine.log = []
+    ports = {k: m._pick_port("127.0.0.1") for k in ("meta", "append", "update", "loader")}
+    ready = threading.Event()
+    th = threading.Thread(target=m.server_main, args=(4096, 4, "127.0.0.1", ports, None, None, 0, 8, ready), daemon=True)
+    th.start()
+    assert ready.wait(20)
+
+    def set_delay(first_value, seconds):
+        delay["first_value"], delay["seconds"] = first_value, seconds
+    yield f"tcp://127.0.0.1:{ports['meta']}", set_delay
+    handlers[signal.SIGTERM]()                                # what proc.terminate() delivers
+    th.join(10)
+    assert not th.is_alive()
+
+
+def _cols(first, n=16):
+    ids = first + np.arange(n, dtype=np.int64)
+    return [ids, ids.astype(np.float32)], np.full(n, 1e-3, np.float32)
+
+
+@pytest.mark.parametrize("wire", ["columns", "rows"])
+def test_write_back_waits_for_a_slow_decode_of_its_own_append(server, wire):
+    """The first decode of a server pins its staging slab, which starts CUDA: seconds.  The write-back sent right
+    behind the append must still land after it (it was applied to an empty buffer -- and lost -- when the wait for
+    the named append gave up after 2 s)."""
+    from reth_b200 import service_mp as m
+    addr, set_delay = server
+    set_delay(1000, 2.6)
+    client = m.Client(addr, wire=wire, coalesce=8 if wire == "columns" else 1)
+    loader = m.NumpyLoader(addr)
+    client.append(*_cols(1000))
+    client.update_priorities(np.array([5]), np.array([1e9], np.float32))
+    loader.sample()
+    assert _Engine.log[:3] == [("append", 1000, 16), ("update", [5], True), ("draw",)]
+    # steady state: write-backs held for coalescing are flushed by the request and taken in before the draw
+    for it in range(3):
+        client.update_priorities(np.array([100 + it]), np.array([1e-3], np.float32))
+        client.update_priorities(np.array([6 + it]), np.array([1e9], np.float32))
+        loader.sample()
+        assert _Engine.log[-1] == ("draw",)
+        seen = [i for e in _Engine.log[-3:-1] if e[0] == "update" for i in e[1]]
+        assert seen[-2:] == [100 + it, 6 + it], _Engine.log[-4:]
+    loader.close()
+    client.close()
+
+
+def test_a_learner_does_not_wait_for_other_producers(server):
+    """An actor's message sits in the decode threads for a while; the learner's write-back and its draw go ahead
+    (appends and write-backs of different producers are unrelated over the reference's sockets), drain() waits."""
+    import zmq
+    from reth_b200 import pack, service_mp as m
+    addr, set_delay = server
+    learner = m.Client(addr, wire="columns")
+    loader = m.NumpyLoader(addr)
+    # the actor lives in another process as far as the server can tell: its own producer id, its own sockets, and
+    # not among the clients whose writes this process's loader requests name
+    ctx = zmq.Context.instance()
+    a_app, a_upd = ctx.socket(zmq.PUSH), ctx.socket(zmq.PUSH)
+    a_app.connect(learner.meta["append_addr"])
+    a_upd.connect(learner.meta["update_addr"])
+    sent = {"a": 0, "u": 0}
+
+    def actor_append(first):
+        sent["a"] += 1
+        cols, w = _cols(first)
+        a_app.send(pack.encode_append_columns(cols, w, extra={pack.KEY_SRC: ["a" * 16, sent["a"]]}))
+
+    def actor_update(idx):
+        sent["u"] += 1                                        # the reference's message + the header field it ignores
+        a_upd.send(pack.encode([np.array([idx]), np.array([1.0], np.float32), True],
+                               extra={pack.KEY_SRC: ["a" * 16, sent["u"], sent["a"]]}))
+    learner.append(*_cols(0))
+    loader.sample()                                           # buffer exists, loader open
+    set_delay(2000, 1.5)
+    actor_append(2000)
+    time.sleep(0.2)                                           # the server has received it: it is in the decode backlog
+    n0 = len(_Engine.log)
+    t0 = time.time()
+    learner.update_priorities(np.array([7]), np.array([1.0], np.float32))
+    loader.sample()
+    assert time.time() - t0 < 1.0
+    assert _Engine.log[n0:] == [("update", [7], True), ("draw",)]
+    assert loader.stat()["backlog"] == 1
+    loader.drain()                                            # everything received so far
+    assert _Engine.log[-1] == ("append", 2000, 16)
+    # the actor's own write-back stays behind the actor's append
+    set_delay(3000, 1.0)
+    actor_append(3000)
+    actor_update(9)
+    deadline = time.time() + 5
+    while _Engine.log[-1] != ("update", [9], True) and time.time() < deadline:
+        time.sleep(0.01)
+    assert _Engine.log[-2:] == [("append", 3000, 16), ("update", [9], True)]
+    learner.close()
+    loader.close()
+    a_app.close(0)
+    a_upd.close(0)
