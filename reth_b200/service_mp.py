@@ -306,16 +306,21 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
         w = np.frombuffer(mv, np.float32 if f32 else np.float64, total, at + 8 * total)
         return cid.hex(), seq, aseq, lambda: eng.update_block(idx, w, sizes, steps)
 
-    def drain_appends(wait=False):
+    def drain_appends(wait=False, budget=4):
         """Receive every pending append frame (decoded by the ingest threads), then commit what has been decoded,
-        strictly in arrival order.  wait: block until everything received so far is committed (a loader's request
-        named these writes, or updates that must stay behind them are about to be applied)."""
+        strictly in arrival order.  wait: block until everything received so far is committed (drain()).  Otherwise
+        at most `budget` messages per call: with the actors streaming, the decode threads finish messages as fast as
+        this loop commits them, and a call that committed "everything that is ready" did not return for milliseconds
+        while a learner's request sat in its socket."""
         while True:
             try:
                 ingest.submit(app.recv(zmq.NOBLOCK, copy=False))
             except zmq.Again:
                 break
+        taken = 0
         while True:
+            if not wait and taken >= budget:
+                break
             res = ingest.pop_ready()
             if res is None:
                 if wait and ingest.backlog:
@@ -325,6 +330,7 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
                     continue
                 break
             src = None
+            taken += 1
             try:
                 if isinstance(res, Exception):
                     raise res

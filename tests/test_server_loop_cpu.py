@@ -203,3 +203,51 @@ def test_a_learner_does_not_wait_for_other_producers(server):
     loader.close()
     a_app.close(0)
     a_upd.close(0)
+
+
+def test_a_streaming_backlog_does_not_starve_the_learner(server, monkeypatch):
+    """Hundreds of actor messages decoded and waiting to be committed (each commit costs the loop a few hundred
+    microseconds of host work; 3 ms here): the learner's write-backs and draws are served between small batches of
+    commits, not after the backlog."""
+    import zmq
+    from reth_b200 import pack, service_mp as m
+    addr, _ = server
+    real_append = _Engine.append
+
+    def slow_append(self, cols, w, stream_key=None):
+        time.sleep(0.003)
+        real_append(self, cols, w, stream_key)
+    monkeypatch.setattr(_Engine, "append", slow_append)
+    learner = m.Client(addr, wire="columns")
+    loader = m.NumpyLoader(addr)
+    learner.append(*_cols(0))
+    loader.sample()
+    socks = []
+    msg = pack.encode_append_columns(*_cols(5000))
+    for _ in range(16):                                       # 16 connections x HWM 10 on either end: 300 messages fit
+        sk = zmq.Context.instance().socket(zmq.PUSH)
+        sk.connect(learner.meta["append_addr"])
+        socks.append(sk)
+    n_msgs = 0
+    for k in range(300):
+        try:
+            socks[k % 16].send(msg, zmq.NOBLOCK)
+            n_msgs += 1
+        except zmq.Again:
+            pass
+    assert n_msgs >= 200                                      # about 0.6-0.9 s of commits
+    time.sleep(0.05)
+    worst = 0.0
+    for it in range(10):
+        t0 = time.time()
+        learner.update_priorities(np.array([it]), np.array([1.0], np.float32))
+        loader.sample()
+        worst = max(worst, time.time() - t0)
+    assert loader.stat()["backlog"] > 0                       # the learner ran while the backlog was still there
+    assert worst < 0.15, worst
+    loader.drain()
+    assert sum(1 for e in _Engine.log if e[0] == "append" and e[1] == 5000) == n_msgs
+    learner.close()
+    loader.close()
+    for sk in socks:
+        sk.close(0)
