@@ -334,6 +334,9 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
             try:
                 if isinstance(res, Exception):
                     raise res
+                named = res[3]
+                if named and len(named) > 2 and seen.get(named[0], (0, 0))[1] < int(named[2]):
+                    await_updates(named[0], int(named[2]))
                 src = take_append(*res)
                 trace("append", src, "rows", len(res[2]))
             except Exception as e:                     # one bad message from one actor must not stop the server
@@ -367,12 +370,46 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
                 ingest.release(slab)
         return src
 
-    def drain_updates():
-        while True:
+    deferred = []                # update frames of OTHER producers received while an append waited for its sender's
+
+    def await_updates(cid, useq, timeout=2.0):
+        """An append names the update frames its sender had sent before it (they travel on another socket): apply
+        those first, or a write-back could land on the row that replaces the one it was meant for.  Runs inside
+        drain_appends, between two commits: frames of other producers are set aside, in order, for drain_updates
+        (applying them here could require commits of their own)."""
+        t0 = time.time()
+        while seen.get(cid, (0, 0))[1] < useq and time.time() - t0 < timeout:
             try:
                 frame = upd.recv(zmq.NOBLOCK, copy=False)
             except zmq.Again:
-                break
+                upd.poll(1)
+                continue
+            try:
+                ocid, seq, _, apply = open_update(frame.buffer)
+                if ocid != cid:
+                    deferred.append(frame)
+                    continue
+                apply()                                # the appends this frame names came before this one: they are in
+                trace("update frame", cid, seq, "ahead of append")
+                seen.setdefault(cid, [0, 0])[1] = seq
+            except Exception as e:
+                dropped["update"] += 1
+                print(f"reth_b200 server: update message dropped ({type(e).__name__}: {e})", file=sys.stderr, flush=True)
+        if seen.get(cid, (0, 0))[1] < useq:
+            dropped["late"] += 1
+            seen.setdefault(cid, [0, 0])[1] = useq     # lost: later messages do not wait for it again
+            print(f"reth_b200 server: an append went ahead of update frame {useq} of its sender, which never arrived",
+                  file=sys.stderr, flush=True)
+
+    def drain_updates():
+        while True:
+            if deferred:
+                frame = deferred.pop(0)
+            else:
+                try:
+                    frame = upd.recv(zmq.NOBLOCK, copy=False)
+                except zmq.Again:
+                    break
             try:
                 cid, seq, aseq, apply = open_update(frame.buffer)
                 # Order is per producer, as over the reference's sockets: a write-back stays behind the appends ITS sender
@@ -402,6 +439,7 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
                     poller.poll(1)
         if seen.get(cid, (0, 0))[0] < aseq:
             dropped["late"] += 1
+            seen.setdefault(cid, [0, 0])[0] = aseq     # lost (or dropped as malformed): do not wait for it again
             print(f"reth_b200 server: a write-back went ahead of append {aseq} of its sender, which never arrived",
                   file=sys.stderr, flush=True)
 
@@ -425,6 +463,9 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
                     poller.poll(1)
         if behind():                                   # a write named by the request never arrived (dropped / lost)
             dropped["late"] += 1
+            for c, (a, u) in after.items():
+                have = seen.setdefault(c, [0, 0])
+                have[0], have[1] = max(have[0], a), max(have[1], u)
             print(f"reth_b200 server: a loader request went ahead without writes sent before it ({timeout:.1f} s "
                   "wait): ordering against those writes is not guaranteed", file=sys.stderr, flush=True)
 
@@ -777,8 +818,8 @@ class Client:
         return True
 
     def _next_append(self):
-        self._aseq += 1
-        return {pack.KEY_SRC: [self._id.hex(), self._aseq]}
+        self._aseq += 1                                       # + the update frames sent before it (append() flushes first)
+        return {pack.KEY_SRC: [self._id.hex(), self._aseq, self._useq]}
 
     def append(self, data, weights, compress=False):
         assert isinstance(data, (list, tuple))                # client.py:22

@@ -251,3 +251,54 @@ def test_a_streaming_backlog_does_not_starve_the_learner(server, monkeypatch):
     loader.close()
     for sk in socks:
         sk.close(0)
+
+
+def test_an_append_waits_for_the_write_backs_its_sender_sent_before_it(server):
+    """update_priorities() then append() of one producer travel on two sockets; if the append overtakes the write-back
+    and recycles the slot, the stale priority would land on the new row.  The append names the update frames sent
+    before it and the loop applies those first; frames of other producers that arrive meanwhile keep their order."""
+    import zmq
+    from reth_b200 import pack, service_mp as m
+    addr, _ = server
+    boot = m.Client(addr, wire="columns")
+    loader = m.NumpyLoader(addr)
+    boot.append(*_cols(0))
+    loader.sample()
+    ctx = zmq.Context.instance()
+    app, upd, other = ctx.socket(zmq.PUSH), ctx.socket(zmq.PUSH), ctx.socket(zmq.PUSH)
+    app.connect(boot.meta["append_addr"])
+    upd.connect(boot.meta["update_addr"])
+    other.connect(boot.meta["update_addr"])
+    n0 = len(_Engine.log)
+    cols, w = _cols(7000)
+    app.send(pack.encode_append_columns(cols, w, extra={pack.KEY_SRC: ["b" * 16, 1, 1]}))   # names update frame 1 ...
+    time.sleep(0.3)
+    assert len(_Engine.log) == n0                             # ... and is held back for it
+    other.send(pack.encode([np.array([42]), np.array([1.0], np.float32), True], extra={pack.KEY_SRC: ["c" * 16, 1, 0]}))
+    time.sleep(0.1)
+    upd.send(pack.encode([np.array([3]), np.array([1.0], np.float32), True], extra={pack.KEY_SRC: ["b" * 16, 1, 0]}))
+    deadline = time.time() + 5
+    while len(_Engine.log) < n0 + 3 and time.time() < deadline:
+        time.sleep(0.01)
+    assert _Engine.log[n0:] == [("update", [3], True), ("append", 7000, 16), ("update", [42], True)]
+    # the real client does the naming itself
+    boot.update_priorities(np.array([8]), np.array([1.0], np.float32))
+    boot.append(*_cols(8000))
+    loader.drain()
+    assert _Engine.log[-2:] == [("update", [8], True), ("append", 8000, 16)]
+    # a frame that never arrives costs the append 2 s, not more
+    t0 = time.time()
+    app.send(pack.encode_append_columns(*_cols(9000), extra={pack.KEY_SRC: ["b" * 16, 2, 5]}))
+    while _Engine.log[-1] != ("append", 9000, 16) and time.time() - t0 < 6:
+        time.sleep(0.02)
+    assert _Engine.log[-1] == ("append", 9000, 16) and 1.5 < time.time() - t0 < 4
+    assert loader.stat()["dropped"]["late"] == 1
+    t0 = time.time()                                          # ... and it is waited for once: the next append goes straight in
+    app.send(pack.encode_append_columns(*_cols(9100), extra={pack.KEY_SRC: ["b" * 16, 3, 5]}))
+    while _Engine.log[-1] != ("append", 9100, 16) and time.time() - t0 < 3:
+        time.sleep(0.02)
+    assert _Engine.log[-1] == ("append", 9100, 16) and time.time() - t0 < 1.0
+    boot.close()
+    loader.close()
+    for sk in (app, upd, other):
+        sk.close(0)
