@@ -302,3 +302,61 @@ def test_an_append_waits_for_the_write_backs_its_sender_sent_before_it(server):
     loader.close()
     for sk in (app, upd, other):
         sk.close(0)
+
+
+def test_shared_memory_ring_appends_through_the_loop(server):
+    """Same-host fast path: the columns travel in the client's shared-memory ring, only a descriptor over ZeroMQ; the
+    server maps the segment, hands the engine views into it and reports consumption, so the ring (1 MB here) is
+    reused many times over; a message larger than the ring falls back to one ZeroMQ frame."""
+    from reth_b200 import service_mp as m
+    addr, _ = server
+    client = m.Client(addr, wire="shm", shm_mb=1)
+    loader = m.NumpyLoader(addr)
+    n0 = len(_Engine.log)
+    for k in range(40):                                       # 40 x 192 KB through a 1 MB ring
+        ids = 10_000 * (k + 1) + np.arange(16384, dtype=np.int64)
+        client.append([ids, ids.astype(np.float32)], np.ones(16384, np.float32))
+    big = 5_000_000 + np.arange(200_000, dtype=np.int64)      # 2.4 MB: does not fit the ring
+    client.append([big, big.astype(np.float32)], np.ones(len(big), np.float32))
+    loader.drain()
+    got = [e for e in _Engine.log[n0:] if e[0] == "append"]
+    assert got == [("append", 10_000 * (k + 1), 16384) for k in range(40)] + [("append", 5_000_000, 200_000)]
+    assert client._ring is not None and client._ring.seq == 40
+    client.close()
+    loader.close()
+
+
+def test_malformed_messages_are_dropped_and_counted(server):
+    """One bad message from one actor must not stop the server (the reference has no error channel either: messages
+    are fire-and-forget, client/client.py:21-39): garbage on the append and update sockets, a truncated append, an
+    unknown loader request -- counted, answered where there is someone to answer, and the loop keeps serving."""
+    import zmq
+    from reth_b200 import pack, service_mp as m
+    addr, _ = server
+    client = m.Client(addr, wire="columns")
+    loader = m.NumpyLoader(addr)
+    client.append(*_cols(0))
+    loader.sample()
+    ctx = zmq.Context.instance()
+    app, upd = ctx.socket(zmq.PUSH), ctx.socket(zmq.PUSH)
+    app.connect(client.meta["append_addr"])
+    upd.connect(client.meta["update_addr"])
+    good = bytes(pack.encode_append_rows(*_cols(100)))
+    app.send(b"\x00\x00\x00\x05garbage")
+    app.send(good[:-7])                                       # truncated body
+    upd.send(b"RBU2" + b"\x00" * 3)                           # a frame cut short
+    upd.send(b"\x00\x00\x00\x02{}")
+    app.send(good)
+    deadline = time.time() + 5
+    while ("append", 100, 16) not in _Engine.log and time.time() < deadline:
+        time.sleep(0.01)
+    assert ("append", 100, 16) in _Engine.log
+    st = loader.drain()
+    assert st["dropped"]["append"] == 2 and st["dropped"]["update"] == 2
+    with pytest.raises(RuntimeError, match="unknown op"):
+        loader._call({"op": "frobnicate"})
+    loader.sample()                                           # still serving
+    client.close()
+    loader.close()
+    app.close(0)
+    upd.close(0)
