@@ -378,12 +378,16 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
         drain_appends, between two commits: frames of other producers are set aside, in order, for drain_updates
         (applying them here could require commits of their own)."""
         t0 = time.time()
+        aside, deferred[:] = list(deferred), []        # frames set aside during an earlier wait may be this sender's
         while seen.get(cid, (0, 0))[1] < useq and time.time() - t0 < timeout:
-            try:
-                frame = upd.recv(zmq.NOBLOCK, copy=False)
-            except zmq.Again:
-                upd.poll(1)
-                continue
+            if aside:
+                frame = aside.pop(0)
+            else:
+                try:
+                    frame = upd.recv(zmq.NOBLOCK, copy=False)
+                except zmq.Again:
+                    upd.poll(1)
+                    continue
             try:
                 ocid, seq, _, apply = open_update(frame.buffer)
                 if ocid != cid:
@@ -395,6 +399,7 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
             except Exception as e:
                 dropped["update"] += 1
                 print(f"reth_b200 server: update message dropped ({type(e).__name__}: {e})", file=sys.stderr, flush=True)
+        deferred.extend(aside)                         # not looked at: they stay in order behind the ones that were
         if seen.get(cid, (0, 0))[1] < useq:
             dropped["late"] += 1
             seen.setdefault(cid, [0, 0])[1] = useq     # lost: later messages do not wait for it again

@@ -360,3 +360,40 @@ def test_malformed_messages_are_dropped_and_counted(server):
     loader.close()
     app.close(0)
     upd.close(0)
+
+
+def test_frames_set_aside_for_one_append_are_found_by_the_next(server):
+    """Two producers, each with a write-back and then an append.  While the first append waits for its sender's frame
+    the other producer's frame arrives and is set aside; the second append must find it there (not wait for the
+    socket to deliver it again)."""
+    import zmq
+    from reth_b200 import pack, service_mp as m
+    addr, _ = server
+    boot = m.Client(addr, wire="columns")
+    loader = m.NumpyLoader(addr)
+    boot.append(*_cols(0))
+    loader.sample()
+    ctx = zmq.Context.instance()
+    app, upd = ctx.socket(zmq.PUSH), ctx.socket(zmq.PUSH)
+    app.connect(boot.meta["append_addr"])
+    upd.connect(boot.meta["update_addr"])
+
+    def frame(who, idx, seq):
+        return pack.encode([np.array([idx]), np.array([1.0], np.float32), True], extra={pack.KEY_SRC: [who * 16, seq, 0]})
+    n0, t0 = len(_Engine.log), time.time()
+    app.send(pack.encode_append_columns(*_cols(1100), extra={pack.KEY_SRC: ["x" * 16, 1, 1]}))
+    upd.send(frame("y", 21, 1))
+    upd.send(frame("y", 22, 2))
+    app.send(pack.encode_append_columns(*_cols(2200), extra={pack.KEY_SRC: ["y" * 16, 1, 1]}))   # behind y's frame 1 only
+    time.sleep(0.2)
+    upd.send(frame("x", 11, 1))
+    while len(_Engine.log) < n0 + 5 and time.time() - t0 < 5:
+        time.sleep(0.01)
+    assert time.time() - t0 < 1.5                             # nobody sat out a 2 s wait
+    assert _Engine.log[n0:] == [("update", [11], True), ("append", 1100, 16), ("update", [21], True),
+                                ("append", 2200, 16), ("update", [22], True)]
+    assert loader.stat()["dropped"]["late"] == 0
+    boot.close()
+    loader.close()
+    app.close(0)
+    upd.close(0)
