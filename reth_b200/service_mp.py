@@ -433,9 +433,10 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
 
     def await_appends(cid, aseq, timeout=2.0):
         """Commit appends (arrival order) until message `aseq` of producer `cid` is in."""
-        t0 = time.time()                               # the clock runs only while nothing received is waiting to go in:
-        while seen.get(cid, (0, 0))[0] < aseq and time.time() - t0 < timeout:   # a decode may take seconds (the first
-            drain_appends()                                                   # one pins its staging slab: CUDA start-up)
+        t0 = hard = time.time()                        # the clock runs only while nothing received is waiting to go in:
+        while seen.get(cid, (0, 0))[0] < aseq and time.time() - t0 < timeout and time.time() - hard < 30:   # a decode may
+            drain_appends()                            # take seconds (the first one pins its staging slab: CUDA start-up);
+                                                       # 30 s in all, or streaming actors would keep a lost message awaited
             if seen.get(cid, (0, 0))[0] < aseq:
                 if ingest.backlog:
                     ingest.wait_next(0.002)
@@ -456,8 +457,8 @@ def server_main(capacity, batch_size, host, ports, samplers, cache_policy, devic
             return any(seen.get(c, (0, 0))[0] < a or seen.get(c, (0, 0))[1] < u for c, (a, u) in after.items())
         if not after or not behind():
             return
-        t0 = time.time()
-        while behind() and time.time() - t0 < timeout:
+        t0 = hard = time.time()
+        while behind() and time.time() - t0 < timeout and time.time() - hard < 30:
             drain_appends()
             drain_updates()
             if behind():
