@@ -397,3 +397,28 @@ def test_frames_set_aside_for_one_append_are_found_by_the_next(server):
     loader.close()
     app.close(0)
     upd.close(0)
+
+
+def test_requests_are_parked_until_the_buffer_exists(server):
+    """sampler_loop.py:25-28: nothing is emitted before the buffer holds sample_start rows; a loader that asks earlier
+    is parked (its struct is unknown until the first append, torch_cuda_loader.py:106-112) and served as soon as the
+    first rows are in -- from another producer, here."""
+    from reth_b200 import service_mp as m
+    addr, _ = server
+    loader = m.NumpyLoader(addr)
+    got = {}
+
+    def ask():
+        got["batch"] = loader.sample()
+    th = threading.Thread(target=ask, daemon=True)
+    th.start()
+    time.sleep(0.3)
+    assert th.is_alive() and not _Engine.log                  # parked: no draw on an empty buffer
+    client = m.Client(addr, wire="rows")
+    client.append(*_cols(50))
+    th.join(5)
+    assert not th.is_alive() and _Engine.log == [("append", 50, 16), ("draw",)]
+    data, idx, w = got["batch"]
+    assert idx.dtype == np.int64 and w.dtype == np.float64 and len(data) == 2
+    client.close()
+    loader.close()
