@@ -21,8 +21,10 @@ class _Shard:
     def _ck(self, rc):
         pass
 
+    rows = 0
+
     def stats(self):
-        return {"appended_rows": 0}
+        return {"appended_rows": self.rows}
 
     def slot_read(self, slot, with_rows=False, stream=None):
         return [np.zeros(4, np.int64), np.zeros(4, np.float32)], None, None
@@ -38,7 +40,8 @@ class _Engine:
         self.loaders, self.max_ring, self.group, self.ahead, self.lend, self.cnt, self._owed = 0, 8, 1, 0, 1, 0, 0
 
     def append(self, cols, w, stream_key=None):
-        self.shard = _Shard()
+        self.shard = self.shard or _Shard()
+        self.shard.rows += len(w)
         self.cnt += len(w)
         _Engine.log.append(("append", int(cols[0][0]), len(w)))
 
@@ -422,3 +425,43 @@ def test_requests_are_parked_until_the_buffer_exists(server):
     assert idx.dtype == np.int64 and w.dtype == np.float64 and len(data) == 2
     client.close()
     loader.close()
+
+
+def test_bench_actor_sender_is_paced_and_flow_controlled(server, monkeypatch):
+    """The actor side of bench.py's apex_process leg (bench_process._apex_sender): paced sends in the reference's row
+    format over many connections, never more than `window` messages outstanding (the server's row counter is read
+    through the stat request), and it stops when told to."""
+    import multiprocessing as mp
+    import os
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench_process
+    from reth_b200 import service_mp as m
+    addr, _ = server
+    real_append = _Engine.append
+    seen_max = {"outstanding": 0}
+    stop, sent = mp.Event(), mp.Value("q", 0)
+
+    def slow_append(self, cols, w, stream_key=None):
+        time.sleep(0.004)                                     # the server takes in at most 250 messages/s
+        real_append(self, cols, w, stream_key)
+        seen_max["outstanding"] = max(seen_max["outstanding"], sent.value - self.shard.rows // 8)
+    monkeypatch.setattr(_Engine, "append", slow_append)
+    meta = m.get_meta(addr)
+    th = threading.Thread(target=bench_process._apex_sender, args=(addr, meta["append_addr"], 8, 8, None, stop, sent, 32),
+                          daemon=True)
+    th.start()                                                # unpaced: only the window holds it back
+    time.sleep(1.5)
+    stop.set()
+    th.join(10)
+    assert not th.is_alive()
+    assert 100 < sent.value < 600 and seen_max["outstanding"] <= 32 + 1
+    # paced: 8-row messages at 800 rows/s = 100 messages/s
+    stop2, sent2 = mp.Event(), mp.Value("q", 0)
+    th = threading.Thread(target=bench_process._apex_sender, args=(addr, meta["append_addr"], 8, 8, 800, stop2, sent2, 32),
+                          daemon=True)
+    th.start()
+    time.sleep(1.5)
+    stop2.set()
+    th.join(10)
+    assert not th.is_alive() and 80 <= sent2.value <= 170
