@@ -385,16 +385,17 @@ def test_frames_set_aside_for_one_append_are_found_by_the_next(server):
         return pack.encode([np.array([idx]), np.array([1.0], np.float32), True], extra={pack.KEY_SRC: [who * 16, seq, 0]})
     n0, t0 = len(_Engine.log), time.time()
     app.send(pack.encode_append_columns(*_cols(1100), extra={pack.KEY_SRC: ["x" * 16, 1, 1]}))
+    time.sleep(0.1)                                           # the loop now waits for x's frame 1 and reads the update socket
     upd.send(frame("y", 21, 1))
     upd.send(frame("y", 22, 2))
-    app.send(pack.encode_append_columns(*_cols(2200), extra={pack.KEY_SRC: ["y" * 16, 1, 1]}))   # behind y's frame 1 only
+    app.send(pack.encode_append_columns(*_cols(2200), extra={pack.KEY_SRC: ["y" * 16, 1, 2]}))   # behind y's two frames
     time.sleep(0.2)
     upd.send(frame("x", 11, 1))
     while len(_Engine.log) < n0 + 5 and time.time() - t0 < 5:
         time.sleep(0.01)
     assert time.time() - t0 < 1.5                             # nobody sat out a 2 s wait
     assert _Engine.log[n0:] == [("update", [11], True), ("append", 1100, 16), ("update", [21], True),
-                                ("append", 2200, 16), ("update", [22], True)]
+                                ("update", [22], True), ("append", 2200, 16)]
     assert loader.stat()["dropped"]["late"] == 0
     boot.close()
     loader.close()
